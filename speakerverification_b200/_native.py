@@ -1,0 +1,161 @@
+"""ctypes binding of libsvb.so (the C ABI declared in include/svb.h).
+
+PyTorch is used for device memory and streams only: tensors are passed as
+``data_ptr()`` and the current CUDA stream as a raw handle.  There is no
+fallback: a missing library or a non-CUDA tensor raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsvb.so")
+
+ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
+OUT_BF16, OUT_BF16_HILO, OUT_F32 = 0, 1, 2
+STORE_ALL, STORE_MIRROR = 0, 1
+
+_c = ctypes
+_i32, _i64, _vp, _f32 = _c.c_int32, _c.c_int64, _c.c_void_p, _c.c_float
+
+
+class SvbTdnnArgs(_c.Structure):
+    _fields_ = [
+        ("rows", _i64),
+        ("x", _vp), ("x_ld", _i32), ("x_cols", _i32), ("x_plane_cols", _i32),
+        ("x2", _vp), ("x2_ld", _i32), ("x2_cols", _i32), ("x2_chunks", _i32),
+        ("w", _vp), ("cout", _i32), ("cin_pad", _i32), ("k", _i32), ("dilation", _i32), ("w_planes", _i32),
+        ("passes", _i32),
+        ("bias", _vp), ("bn_scale", _vp), ("bn_shift", _vp),
+        ("row_bias", _vp), ("row_bias_ld", _i32),
+        ("act", _i32), ("post_tanh", _i32),
+        ("row_meta", _vp), ("store_mode", _i32), ("halo", _i32),
+        ("out", _vp), ("out_ld", _i32), ("out_kind", _i32), ("out_plane_cols", _i32),
+        ("add_src", _vp), ("add_ld", _i32), ("add_planes", _i32), ("add_plane_cols", _i32),
+        ("out2", _vp), ("out2_ld", _i32), ("out2_plane_cols", _i32),
+        ("block_n", _i32),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    """Loads libsvb.so once; raises if it is missing (no CPU / eager fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libsvb.so not found at %s: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(the CUDA library is the only implementation of this path)" % LIB_PATH)
+        _lib = ctypes.CDLL(LIB_PATH)
+        _lib.svb_last_error.restype = _c.c_char_p
+        _lib.svb_launch_count.restype = _c.c_longlong
+        _declare(_lib)
+    return _lib
+
+
+def _declare(L):
+    L.svb_build_row_meta.argtypes = [_vp, _i32, _i32, _vp, _i64, _vp]
+    L.svb_split_bf16.argtypes = [_vp, _i64, _i32, _i32, _vp, _i32, _i32, _i32, _vp]
+    L.svb_pack_conv_weight.argtypes = [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]
+    L.svb_fold_bn.argtypes = [_vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _vp]
+    L.svb_tdnn_layer.argtypes = [_c.POINTER(SvbTdnnArgs), _vp]
+    for name, sig in _EXTRA_SIGS.items():
+        if hasattr(L, name):
+            getattr(L, name).argtypes = sig
+
+
+_EXTRA_SIGS = {}
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError("libsvb: %s (code %d)" % (lib().svb_last_error().decode(), rc))
+
+
+def stream_ptr():
+    return _vp(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (None -> NULL); refuses CPU tensors."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("libsvb operates on CUDA tensors only (got a %s tensor); there is no CPU path" % t.device)
+    return _vp(t.data_ptr())
+
+
+# ------------------------------------------------------------------ thin op wrappers
+def build_row_meta(frames, halo, device):
+    """int32 [rows, 4] table {utt, t, T, 0} for utterances of `frames` valid rows each."""
+    frames = [int(f) for f in frames]
+    total = sum(f + 2 * halo for f in frames)
+    meta = torch.empty((total, 4), dtype=torch.int32, device=device)
+    arr = (_i32 * len(frames))(*frames)
+    check(lib().svb_build_row_meta(arr, len(frames), halo, ptr(meta), total, stream_ptr()))
+    return meta
+
+
+def split_bf16(x, planes=1, out=None, plane_cols=None):
+    """fp32 [rows, cols] -> bf16 [rows, planes*plane_cols] (hi | lo)."""
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    rows, cols = x.shape
+    if plane_cols is None:
+        plane_cols = cols
+    if out is None:
+        out = torch.zeros((rows, planes * plane_cols), dtype=torch.bfloat16, device=x.device)
+    check(lib().svb_split_bf16(ptr(x), rows, cols, x.stride(0), ptr(out), out.stride(0), planes, plane_cols,
+                               stream_ptr()))
+    return out
+
+
+def pack_conv_weight(w, planes, cin_pad=None):
+    """nn.Conv1d weight [cout, cin, k] fp32 -> packed bf16 [cout, k*planes*cin_pad]."""
+    w = w.contiguous().float()
+    cout, cin, k = w.shape
+    if cin_pad is None:
+        cin_pad = (cin + 63) // 64 * 64
+    out = torch.empty((cout, k * planes * cin_pad), dtype=torch.bfloat16, device=w.device)
+    check(lib().svb_pack_conv_weight(ptr(w), cout, cin, k, cin_pad, planes, ptr(out), stream_ptr()))
+    return out
+
+
+def fold_bn(gamma, beta, mean, var, eps=1e-5):
+    n = gamma.numel()
+    scale = torch.empty(n, dtype=torch.float32, device=gamma.device)
+    shift = torch.empty(n, dtype=torch.float32, device=gamma.device)
+    check(lib().svb_fold_bn(ptr(gamma.contiguous()), ptr(beta.contiguous()), ptr(mean.contiguous()),
+                            ptr(var.contiguous()), n, eps, ptr(scale), ptr(shift), stream_ptr()))
+    return scale, shift
+
+
+def tdnn_layer(x, w_packed, cout, cin_pad, k, dilation, bias, bn_scale, bn_shift, out, *, act=ACT_NONE,
+               passes=1, w_planes=1, x_plane_cols=0, x_cols=None, x2=None, x2_chunks=0, row_bias=None,
+               post_tanh=False, row_meta=None, store_mode=STORE_ALL, halo=0, out_kind=OUT_BF16,
+               out_plane_cols=0, add_src=None, add_planes=1, add_plane_cols=0, out2=None,
+               out2_plane_cols=0, block_n=0, rows=None):
+    a = SvbTdnnArgs()
+    a.rows = x.shape[0] if rows is None else rows
+    a.x, a.x_ld = ptr(x), x.stride(0)
+    a.x_cols = x.shape[1] if x_cols is None else x_cols
+    a.x_plane_cols = x_plane_cols
+    if x2 is not None:
+        a.x2, a.x2_ld, a.x2_cols, a.x2_chunks = ptr(x2), x2.stride(0), x2.shape[1], x2_chunks
+    a.w, a.cout, a.cin_pad, a.k, a.dilation, a.w_planes = ptr(w_packed), cout, cin_pad, k, dilation, w_planes
+    a.passes = passes
+    a.bias, a.bn_scale, a.bn_shift = ptr(bias), ptr(bn_scale), ptr(bn_shift)
+    if row_bias is not None:
+        a.row_bias, a.row_bias_ld = ptr(row_bias), row_bias.stride(0)
+    a.act, a.post_tanh = act, int(post_tanh)
+    a.row_meta = ptr(row_meta)
+    a.store_mode, a.halo = store_mode, halo
+    a.out, a.out_ld, a.out_kind, a.out_plane_cols = ptr(out), out.stride(0), out_kind, out_plane_cols
+    if add_src is not None:
+        a.add_src, a.add_ld, a.add_planes, a.add_plane_cols = ptr(add_src), add_src.stride(0), add_planes, add_plane_cols
+        a.out2, a.out2_ld, a.out2_plane_cols = ptr(out2), out2.stride(0), out2_plane_cols
+    a.block_n = block_n
+    check(lib().svb_tdnn_layer(ctypes.byref(a), stream_ptr()))
+    return out

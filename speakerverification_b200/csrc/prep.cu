@@ -1,0 +1,98 @@
+// Operand preparation kernels: fp32 -> bf16 hi/lo planes, Conv1d weight packing, BN folding,
+// and the row bookkeeping table of the time-major-with-halos layout.
+#include <vector>
+
+#include "svb_internal.h"
+#include "svb_ptx.cuh"
+
+namespace svb {
+
+__global__ void split_bf16_kernel(const float* __restrict__ x, long long rows, int cols, int ld_in,
+                                  bf16* __restrict__ out, int ld_out, int planes, int plane_cols) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = static_cast<int>(i - r * cols);
+    const float v = x[r * ld_in + c];
+    const bf16 h = __float2bfloat16_rn(v);
+    out[r * ld_out + c] = h;
+    if (planes == 2) out[r * ld_out + plane_cols + c] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+// w [cout, cin, k] -> out [cout, k, planes, cin_pad]
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, int cout, int cin, int k, int cin_pad,
+                                        int planes, bf16* __restrict__ out) {
+  const long long total = (long long)cout * k * cin_pad;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = static_cast<int>(i % cin_pad);
+    const int j = static_cast<int>((i / cin_pad) % k);
+    const int o = static_cast<int>(i / ((long long)cin_pad * k));
+    const float v = (c < cin) ? w[((long long)o * cin + c) * k + j] : 0.f;
+    const bf16 h = __float2bfloat16_rn(v);
+    bf16* dst = out + ((long long)(o * k + j) * planes) * cin_pad + c;
+    dst[0] = h;
+    if (planes == 2) dst[cin_pad] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+__global__ void fold_bn_kernel(const float* g, const float* b, const float* m, const float* v, int n, float eps,
+                               float* scale, float* shift) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const float s = g[i] / sqrtf(v[i] + eps);
+    scale[i] = s;
+    shift[i] = b[i] - m[i] * s;
+  }
+}
+
+int build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row_meta, long long total_rows,
+                   cudaStream_t stream) {
+  std::vector<RowMeta> h(static_cast<size_t>(total_rows), RowMeta{-1, 0, 0, 0});
+  long long r = 0;
+  for (int b = 0; b < B; ++b) {
+    const int T = frames_host[b];
+    SVB_CHECK(T > 2 * halo, "utterance %d has %d frames; need more than 2*halo = %d", b, T, 2 * halo);
+    for (int t = -halo; t < T + halo; ++t, ++r) {
+      SVB_CHECK(r < total_rows, "row_meta buffer too small");
+      h[static_cast<size_t>(r)] = RowMeta{b, t, T, 0};
+    }
+  }
+  SVB_CUDA_OK(cudaMemcpyAsync(row_meta, h.data(), h.size() * sizeof(RowMeta), cudaMemcpyHostToDevice, stream));
+  SVB_CUDA_OK(cudaStreamSynchronize(stream));  // h goes out of scope
+  return 0;
+}
+
+int split_bf16(const float* x, long long rows, int cols, int ld_in, bf16* out, int ld_out, int planes,
+               int plane_cols, cudaStream_t stream) {
+  const long long total = rows * cols;
+  if (total == 0) return 0;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  split_bf16_kernel<<<grid, 256, 0, stream>>>(x, rows, cols, ld_in, out, ld_out, planes, plane_cols);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, int planes, bf16* out,
+                     cudaStream_t stream) {
+  SVB_CHECK(cin_pad % 64 == 0 && cin_pad >= cin, "cin_pad must be a multiple of 64 and >= cin");
+  const long long total = (long long)cout * k * cin_pad;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  pack_conv_weight_kernel<<<grid, 256, 0, stream>>>(w, cout, cin, k, cin_pad, planes, out);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int fold_bn(const float* g, const float* b, const float* m, const float* v, int n, float eps, float* scale,
+            float* shift, cudaStream_t stream) {
+  fold_bn_kernel<<<(n + 255) / 256, 256, 0, stream>>>(g, b, m, v, n, eps, scale, shift);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace svb

@@ -1,0 +1,80 @@
+// Internal (non-ABI) declarations shared by the .cu translation units of libsvb.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+
+namespace svb {
+
+typedef __nv_bfloat16 bf16;
+
+// ------------------------------------------------------------------ errors
+void set_error(const char* fmt, ...);
+#define SVB_CUDA_OK(expr)                                                                   \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      svb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return -2;                                                                            \
+    }                                                                                       \
+  } while (0)
+#define SVB_CHECK(cond, ...)        \
+  do {                              \
+    if (!(cond)) {                  \
+      svb::set_error(__VA_ARGS__);  \
+      return -1;                    \
+    }                               \
+  } while (0)
+
+int num_sms();
+int count_launch(int n = 1);  // running count of kernel launches (reported by bench.py)
+
+// ------------------------------------------------------------------ rows
+// Time-major activation matrices hold, per utterance, `halo` mirrored rows, T valid rows and
+// `halo` mirrored rows again.  row_meta[r] = {utterance, t (may be <0 or >=T on halo rows), T, 0};
+// utterance == -1 on rows that belong to no utterance.
+struct RowMeta { int utt, t, T, pad; };
+
+// ------------------------------------------------------------------ tensor-core GEMM
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
+enum { OUT_BF16 = 0, OUT_BF16_HILO = 1, OUT_F32 = 2 };
+enum { STORE_ALL = 0, STORE_MIRROR = 1 };
+
+struct GemmOperands {
+  // A: activations [M, lda] bf16 (K-major); optional second source for k-chunks < a2_kc.
+  const bf16* a; int lda; int a_cols;          // a_cols: columns addressable through this map
+  const bf16* a2; int lda2; int a2_cols; int a2_kc;
+  int a_plane_cols;                            // column distance hi-plane -> lo-plane in A (and A2)
+  const bf16* w; int w_rows; int w_cols;       // packed weights [N, taps*planes*kc*64]
+};
+
+struct GemmParams {
+  int M, N;
+  int kc_per_tap;        // 64-column chunks per tap per plane
+  int num_taps;
+  int tap_off[5];        // row offset of each tap
+  int num_pass;          // 1: hi*hi ; 3: hi*hi + hi*lo + lo*hi (fp32-grade split-bf16)
+  int a_plane_cols;
+  int a2_kc;
+  int w_planes;
+  const float* bias;     // [N_pad] conv bias
+  const float* scale;    // [N_pad] BN scale (applied after the activation)
+  const float* shift;    // [N_pad] BN shift
+  const float* rowbias;  // optional [utterances, rowbias_ld] added before the activation
+  int rowbias_ld;
+  int act, post_tanh;
+  const RowMeta* row_meta;
+  int store_mode, halo;
+  void* out; int out_ld; int out_kind; int out_plane_cols;
+  const bf16* add_src; int add_ld; int add_planes; int add_plane_cols;
+  void* out2; int out2_ld; int out2_plane_cols;
+};
+
+// Launches the persistent tcgen05 GEMM.  block_n in {64, 128, 256}.
+int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream);
+
+}  // namespace svb
