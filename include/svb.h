@@ -86,6 +86,79 @@ typedef struct SvbTdnnArgs {
 
 int svb_tdnn_layer(const SvbTdnnArgs* args, void* stream);
 
+
+/* ------------------------------------------------------------------ batch plan
+ * Host-built device tables for one batch of utterances (row_meta, frame tiles, per-utterance
+ * offsets).  wav_off_host[b] = offset (in samples) of utterance b inside the wav buffer given to
+ * the forward calls; nsamp_host[b] = its length; frames T_b = 1 + nsamp/hop (centred STFT). */
+typedef struct SvbBatch SvbBatch;
+int svb_batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo,
+                     SvbBatch** out);
+void svb_batch_destroy(SvbBatch* b);
+int64_t svb_batch_rows(const SvbBatch* b);    /* sum_b (T_b + 2*halo) */
+int64_t svb_batch_frames(const SvbBatch* b);  /* sum_b T_b */
+int32_t svb_batch_tiles(const SvbBatch* b);   /* 32-frame front-end tiles */
+const int32_t* svb_batch_row_meta(const SvbBatch* b); /* device, int32 x4 per row */
+
+/* ------------------------------------------------------------------ log-mel front-end (K1)
+ * Replaces PreEmphasis (src/utils.py:63-71) + melspectrogram(lib='torchaudio')
+ * (src/models/FeatureExtraction/feature.py:84-94) + log/mean-norm (src/models/ECAPA_TDNN.py:473-476).
+ * window_host[win_length] and fb_host[n_freqs, n_mels] are HOST tables built from the config keys. */
+typedef struct SvbFbank SvbFbank;
+int svb_fbank_create(const float* window_host, int win_length, int hop, int n_fft, const float* fb_host,
+                     int n_freqs, int n_mels, float preemph, float log_eps, SvbFbank** out);
+void svb_fbank_destroy(SvbFbank* f);
+/* wav fp32 -> out bf16 [rows, out_ld]: hi plane at column 0, lo plane (planes==2) at +plane_cols;
+ * columns n_mels..plane_cols-1 are zero; halo rows mirrored.  Scratch: logmel_ws [rows*n_mels] fp32,
+ * tile_sums_ws [tiles*n_mels] fp32, mean_ws [B*n_mels] fp32 (logmel_ws keeps the un-normalised log-mel). */
+int svb_fbank_forward(const SvbFbank* f, const SvbBatch* b, const float* wav, void* out, int out_ld,
+                      int plane_cols, int planes, float* logmel_ws, float* tile_sums_ws, float* mean_ws,
+                      void* stream);
+
+/* ------------------------------------------------------------------ ECAPA-TDNN encoder (K2-K7)
+ * Replaces models.ECAPA_TDNN.MainModel.forward (src/models/ECAPA_TDNN.py:460-502) behind
+ * SpeakerEncoder.forward (src/model.py:104-129).  Weights: fp32 DEVICE pointers in the reference
+ * checkpoint layout, keyed by state-dict name without the "__S__." prefix
+ * (e.g. "blocks.1.tdnn1.conv.conv.weight"); they are repacked into library-owned buffers. */
+typedef struct SvbEcapa SvbEcapa;
+typedef struct SvbEcapaCfg {
+  int32_t channels;        /* C (channels[0..3]); channels[4] must be 3*C */
+  int32_t n_mels, n_out, attention_channels, se_channels, res2net_scale;
+  int32_t kernel_sizes[5], dilations[5];
+  int32_t fp32_mode;       /* 0: bf16 tensor-core operands; 1: split-bf16 (fp32-grade parity mode) */
+} SvbEcapaCfg;
+int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n,
+                     SvbEcapa** out);
+void svb_ecapa_destroy(SvbEcapa* e);
+int32_t svb_ecapa_halo(const SvbEcapa* e);
+size_t svb_ecapa_workspace_bytes(const SvbEcapa* e, const SvbBatch* b);
+/* byte offset of a named intermediate inside the workspace (tests / profiling), -1 if unknown */
+int64_t svb_ecapa_ws_offset(const SvbEcapa* e, const SvbBatch* b, const char* name);
+/* wav (device fp32) -> emb [B, emb_ld] fp32; l2norm != 0 applies F.normalize (src/model.py:422-423) */
+int svb_ecapa_forward(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* wav, void* ws,
+                      size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream);
+
+
+/* ------------------------------------------------------------------ trial scoring (K8/K9)
+ * emb: [U, n_per_utt, D] fp32 crop embeddings of the U unique utterances; idx_a/idx_b: int32 indices
+ * of the enrol / test utterance of every trial.
+ * svb_cosine_trials     = utils.cosine_similarity (src/utils.py:163-164) for all trials at once:
+ *                         mean_i |cos(a_i, b_i)| over index-paired crops, eps 1e-5.
+ * svb_mean_embeddings   = per-utterance mean of (optionally L2-normalised, src/model.py:421-423) rows.
+ * svb_asnorm_stats      = per-utterance mean / population-std of the top-K cohort scores
+ *                         (np.inner + np.sort()[::-1][:top] + np.mean/np.std, src/utils.py:144-147);
+ *                         topk < 0 follows the slice semantics of the reference (top=-1 drops one).
+ * svb_asnorm_trials     = S-norm combination (src/utils.py:148-156) for all trials at once. */
+int svb_cosine_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b,
+                      int64_t n_trials, float* out, void* stream);
+int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int normalize, float* out,
+                        void* stream);
+size_t svb_asnorm_workspace_bytes(int U, int N, int D);
+int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu,
+                     float* sigma, void* ws, size_t ws_bytes, void* stream);
+int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b,
+                      int64_t n_trials, const float* mu, const float* sigma, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,12 +62,43 @@ def _declare(L):
     L.svb_pack_conv_weight.argtypes = [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]
     L.svb_fold_bn.argtypes = [_vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _vp]
     L.svb_tdnn_layer.argtypes = [_c.POINTER(SvbTdnnArgs), _vp]
-    for name, sig in _EXTRA_SIGS.items():
-        if hasattr(L, name):
-            getattr(L, name).argtypes = sig
+    for name, (args, res) in _EXTRA_SIGS.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = res
 
 
-_EXTRA_SIGS = {}
+class SvbEcapaCfg(_c.Structure):
+    _fields_ = [("channels", _i32), ("n_mels", _i32), ("n_out", _i32), ("attention_channels", _i32),
+                ("se_channels", _i32), ("res2net_scale", _i32), ("kernel_sizes", _i32 * 5),
+                ("dilations", _i32 * 5), ("fp32_mode", _i32)]
+
+
+_pp = _c.POINTER(_vp)
+_EXTRA_SIGS = {
+    "svb_batch_create": ([_vp, _vp, _i32, _i32, _i32, _pp], _i32),
+    "svb_batch_destroy": ([_vp], None),
+    "svb_batch_rows": ([_vp], _i64),
+    "svb_batch_frames": ([_vp], _i64),
+    "svb_batch_tiles": ([_vp], _i32),
+    "svb_batch_row_meta": ([_vp], _vp),
+    "svb_fbank_create": ([_vp, _i32, _i32, _i32, _vp, _i32, _i32, _f32, _f32, _pp], _i32),
+    "svb_fbank_destroy": ([_vp], None),
+    "svb_fbank_forward": ([_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp], _i32),
+    "svb_ecapa_create": ([_c.POINTER(SvbEcapaCfg), _c.POINTER(_c.c_char_p), _c.POINTER(_vp), _i32, _pp], _i32),
+    "svb_ecapa_destroy": ([_vp], None),
+    "svb_ecapa_halo": ([_vp], _i32),
+    "svb_ecapa_workspace_bytes": ([_vp, _vp], _c.c_size_t),
+    "svb_ecapa_ws_offset": ([_vp, _vp, _c.c_char_p], _i64),
+    "svb_ecapa_forward": ([_vp, _vp, _vp, _vp, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
+    "svb_cosine_trials": ([_vp, _i32, _i32, _vp, _vp, _i64, _vp, _vp], _i32),
+    "svb_mean_embeddings": ([_vp, _i32, _i32, _i32, _i32, _vp, _vp], _i32),
+    "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
+    "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
+    "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),
+    "svb_version": ([], _i32),
+    "svb_reset_launch_count": ([], None),
+}
 
 
 def check(rc):

@@ -11,6 +11,34 @@ int build_row_meta(const int32_t*, int, int, int32_t*, long long, cudaStream_t);
 int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStream_t);
 int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
+struct Fbank; struct Batch; struct Ecapa;
+int fbank_create(const float*, int, int, int, const float*, int, int, float, float, Fbank**);
+void fbank_destroy(Fbank*);
+int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
+                  float*, float*, float*, bf16*, int, int, int, cudaStream_t);
+int batch_create(const int64_t*, const int32_t*, int, int, int, Batch**);
+void batch_destroy(Batch*);
+long long batch_rows(const Batch*);
+long long batch_frames(const Batch*);
+const int32_t* batch_row_meta(const Batch*);
+int batch_tiles(const Batch*);
+int batch_B(const Batch*);
+int batch_halo(const Batch*);
+const void* batch_utt_tab(const Batch*);
+const int32_t* batch_tile_tab(const Batch*);
+int ecapa_create(int, int, int, int, int, int, const int*, const int*, int, const char* const*, const void* const*, int,
+                 Ecapa**);
+void ecapa_destroy(Ecapa*);
+int ecapa_halo(const Ecapa*);
+size_t ecapa_workspace_bytes(const Ecapa*, const Batch*);
+long long ecapa_ws_offset(const Ecapa*, const Batch*, const char*);
+int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, void*, size_t, float*, int, int, cudaStream_t);
+int cosine_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float*, cudaStream_t);
+int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
+size_t asnorm_workspace_bytes(int, int, int, int*);
+int asnorm_stats(const float*, int, const float*, int, int, int, float*, float*, void*, size_t, cudaStream_t);
+int asnorm_trials(const float*, int, const int32_t*, const int32_t*, long long, const float*, const float*, float*,
+                  cudaStream_t);
 }  // namespace svb
 
 using namespace svb;
@@ -115,6 +143,90 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
   int bn = a->block_n;
   if (bn == 0) bn = (a->cout >= 256) ? 256 : (a->cout >= 128 ? 128 : 64);
   return launch_gemm(ops, p, bn, static_cast<cudaStream_t>(stream));
+}
+
+
+// ---------------------------------------------------------------- batch / fbank / ecapa handles
+int svb_batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, SvbBatch** out) {
+  if (check_device()) return -1;
+  SVB_CHECK(wav_off_host && nsamp_host && out, "null argument");
+  return batch_create(wav_off_host, nsamp_host, B, hop, halo, reinterpret_cast<Batch**>(out));
+}
+void svb_batch_destroy(SvbBatch* b) { batch_destroy(reinterpret_cast<Batch*>(b)); }
+int64_t svb_batch_rows(const SvbBatch* b) { return batch_rows(reinterpret_cast<const Batch*>(b)); }
+int64_t svb_batch_frames(const SvbBatch* b) { return batch_frames(reinterpret_cast<const Batch*>(b)); }
+int32_t svb_batch_tiles(const SvbBatch* b) { return batch_tiles(reinterpret_cast<const Batch*>(b)); }
+const int32_t* svb_batch_row_meta(const SvbBatch* b) { return batch_row_meta(reinterpret_cast<const Batch*>(b)); }
+
+int svb_fbank_create(const float* window_host, int win_length, int hop, int n_fft, const float* fb_host, int n_freqs,
+                     int n_mels, float preemph, float log_eps, SvbFbank** out) {
+  if (check_device()) return -1;
+  SVB_CHECK(window_host && fb_host && out, "null argument");
+  return fbank_create(window_host, win_length, hop, n_fft, fb_host, n_freqs, n_mels, preemph, log_eps,
+                      reinterpret_cast<Fbank**>(out));
+}
+void svb_fbank_destroy(SvbFbank* f) { fbank_destroy(reinterpret_cast<Fbank*>(f)); }
+
+int svb_fbank_forward(const SvbFbank* f, const SvbBatch* b, const float* wav, void* out, int out_ld, int plane_cols,
+                      int planes, float* logmel_ws, float* tile_sums_ws, float* mean_ws, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(f && b && wav && out && logmel_ws && tile_sums_ws && mean_ws, "null argument");
+  const Batch* bt = reinterpret_cast<const Batch*>(b);
+  return fbank_forward(reinterpret_cast<const Fbank*>(f), wav, batch_utt_tab(bt), batch_tile_tab(bt), batch_B(bt),
+                       batch_tiles(bt), reinterpret_cast<const RowMeta*>(batch_row_meta(bt)), batch_rows(bt),
+                       batch_halo(bt), logmel_ws, tile_sums_ws, mean_ws, static_cast<bf16*>(out), out_ld, plane_cols,
+                       planes, static_cast<cudaStream_t>(stream));
+}
+
+int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n, SvbEcapa** out) {
+  if (check_device()) return -1;
+  SVB_CHECK(cfg && names && ptrs && out, "null argument");
+  return ecapa_create(cfg->channels, cfg->n_mels, cfg->n_out, cfg->attention_channels, cfg->se_channels,
+                      cfg->res2net_scale, cfg->kernel_sizes, cfg->dilations, cfg->fp32_mode, names, ptrs, n,
+                      reinterpret_cast<Ecapa**>(out));
+}
+void svb_ecapa_destroy(SvbEcapa* e) { ecapa_destroy(reinterpret_cast<Ecapa*>(e)); }
+int32_t svb_ecapa_halo(const SvbEcapa* e) { return ecapa_halo(reinterpret_cast<const Ecapa*>(e)); }
+size_t svb_ecapa_workspace_bytes(const SvbEcapa* e, const SvbBatch* b) {
+  return ecapa_workspace_bytes(reinterpret_cast<const Ecapa*>(e), reinterpret_cast<const Batch*>(b));
+}
+int64_t svb_ecapa_ws_offset(const SvbEcapa* e, const SvbBatch* b, const char* name) {
+  return ecapa_ws_offset(reinterpret_cast<const Ecapa*>(e), reinterpret_cast<const Batch*>(b), name);
+}
+int svb_ecapa_forward(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* wav, void* ws,
+                      size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(e && f && b && wav && emb, "null argument");
+  return ecapa_forward(reinterpret_cast<const Ecapa*>(e), reinterpret_cast<const Fbank*>(f),
+                       reinterpret_cast<const Batch*>(b), wav, ws, ws_bytes, emb, emb_ld, l2norm,
+                       static_cast<cudaStream_t>(stream));
+}
+
+
+// ---------------------------------------------------------------- scoring
+int svb_cosine_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b,
+                      int64_t n_trials, float* out, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(emb && idx_a && idx_b && out && n_per_utt >= 1 && D >= 1, "bad argument");
+  return cosine_trials(emb, n_per_utt, D, idx_a, idx_b, n_trials, out, static_cast<cudaStream_t>(stream));
+}
+int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int normalize, float* out, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(emb && out && U >= 1 && n_per_utt >= 1, "bad argument");
+  return mean_rows(emb, U, n_per_utt, D, normalize, out, static_cast<cudaStream_t>(stream));
+}
+size_t svb_asnorm_workspace_bytes(int U, int N, int D) { return asnorm_workspace_bytes(U, N, D, nullptr); }
+int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu, float* sigma,
+                     void* ws, size_t ws_bytes, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(emean && cohort && mu && sigma && U >= 1 && N >= 1 && D >= 1, "bad argument");
+  return asnorm_stats(emean, U, cohort, N, D, topk, mu, sigma, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+}
+int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b, int64_t n_trials,
+                      const float* mu, const float* sigma, float* out, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(emean && idx_a && idx_b && mu && sigma && out, "bad argument");
+  return asnorm_trials(emean, D, idx_a, idx_b, n_trials, mu, sigma, out, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

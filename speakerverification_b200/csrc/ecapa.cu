@@ -1,0 +1,400 @@
+// ECAPA-TDNN forward (reference: src/models/ECAPA_TDNN.py:339-502) as a fixed sequence of libsvb
+// kernels over time-major activations with mirrored halos.  Weights arrive in the reference's
+// checkpoint layout (fp32 device pointers keyed by state-dict name) and are repacked once.
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "svb_internal.h"
+
+namespace svb {
+
+// --- other translation units
+struct Fbank;
+int fbank_n_mels(const Fbank*);
+int fbank_hop(const Fbank*);
+int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
+                  float*, float*, float*, bf16*, int, int, int, cudaStream_t);
+int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
+int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
+int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
+int small_linear(const float*, int, const float*, const float*, int, const float*, const float*, int, int, int, int,
+                 float*, int, cudaStream_t);
+int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, const RowMeta*, long long, int, int, bf16*,
+             int, int, cudaStream_t);
+int asp_pool(const float*, int, const bf16*, int, int, int, const void*, int, int, float, float*, int, cudaStream_t);
+int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
+
+enum { LIN_NONE = 0, LIN_RELU = 1, LIN_SIGMOID = 2 };
+static constexpr int FRAMES_PER_TILE = 32;
+static constexpr int MEL_PLANE = 128;  // n_mels padded to two 64-column K chunks
+
+// ------------------------------------------------------------------ batch plan
+struct UttDesc { long long wav_off; int nsamp; int T; long long row_base; int tile_base; int ntiles; };
+struct UttRows { long long row0; int T; int pad; };
+
+struct Batch {
+  int B = 0, halo = 0, ntiles = 0, hop = 0;
+  long long rows = 0, frames = 0;
+  RowMeta* d_meta = nullptr;
+  UttDesc* d_utt = nullptr;
+  int2* d_tiles = nullptr;
+  UttRows* d_uttrows = nullptr;
+};
+
+int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, Batch** out) {
+  SVB_CHECK(B > 0 && hop > 0 && halo >= 0, "bad batch arguments");
+  std::vector<UttDesc> utt(B);
+  std::vector<UttRows> ur(B);
+  std::vector<int2> tiles;
+  std::vector<RowMeta> meta;
+  long long row = 0, frames = 0;
+  for (int b = 0; b < B; ++b) {
+    const int L = nsamp_host[b];
+    SVB_CHECK(L > 256, "utterance %d has %d samples; the centred 512-point STFT needs more than 256", b, L);
+    const int T = 1 + L / hop;
+    SVB_CHECK(T > 2 * halo, "utterance %d has %d frames; need more than %d", b, T, 2 * halo);
+    utt[b] = UttDesc{wav_off_host[b], L, T, row, static_cast<int>(tiles.size()), (T + FRAMES_PER_TILE - 1) / FRAMES_PER_TILE};
+    ur[b] = UttRows{row + halo, T, 0};
+    for (int t0 = 0; t0 < T; t0 += FRAMES_PER_TILE) tiles.push_back(make_int2(b, t0));
+    for (int t = -halo; t < T + halo; ++t) meta.push_back(RowMeta{b, t, T, 0});
+    row += T + 2 * halo;
+    frames += T;
+  }
+  Batch* bt = new Batch();
+  bt->B = B; bt->halo = halo; bt->hop = hop; bt->rows = row; bt->frames = frames;
+  bt->ntiles = static_cast<int>(tiles.size());
+  auto up = [](void** d, const void* h, size_t n) {
+    if (cudaMalloc(d, n) != cudaSuccess) return 1;
+    return cudaMemcpy(*d, h, n, cudaMemcpyHostToDevice) != cudaSuccess ? 1 : 0;
+  };
+  int bad = 0;
+  bad |= up(reinterpret_cast<void**>(&bt->d_meta), meta.data(), meta.size() * sizeof(RowMeta));
+  bad |= up(reinterpret_cast<void**>(&bt->d_utt), utt.data(), utt.size() * sizeof(UttDesc));
+  bad |= up(reinterpret_cast<void**>(&bt->d_tiles), tiles.data(), tiles.size() * sizeof(int2));
+  bad |= up(reinterpret_cast<void**>(&bt->d_uttrows), ur.data(), ur.size() * sizeof(UttRows));
+  if (bad) { set_error("batch table upload failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
+  *out = bt;
+  return 0;
+}
+
+void batch_destroy(Batch* b) {
+  if (b == nullptr) return;
+  cudaFree(b->d_meta); cudaFree(b->d_utt); cudaFree(b->d_tiles); cudaFree(b->d_uttrows);
+  delete b;
+}
+long long batch_rows(const Batch* b) { return b->rows; }
+long long batch_frames(const Batch* b) { return b->frames; }
+const int32_t* batch_row_meta(const Batch* b) { return reinterpret_cast<const int32_t*>(b->d_meta); }
+int batch_tiles(const Batch* b) { return b->ntiles; }
+int batch_B(const Batch* b) { return b->B; }
+int batch_halo(const Batch* b) { return b->halo; }
+const void* batch_utt_tab(const Batch* b) { return b->d_utt; }
+const int32_t* batch_tile_tab(const Batch* b) { return reinterpret_cast<const int32_t*>(b->d_tiles); }
+
+// ------------------------------------------------------------------ model
+struct Layer {
+  bf16* w = nullptr;
+  float *bias = nullptr, *scale = nullptr, *shift = nullptr;
+  int cout = 0, cin = 0, cin_pad = 0, k = 1, dil = 1, planes = 1, act = ACT_NONE;
+};
+
+struct Ecapa {
+  int C = 0, C3 = 0, Cs = 0, n_mels = 0, n_out = 0, att = 128, se_ch = 128, scale = 8, halo = 0;
+  int fp32_mode = 0;  // 0: bf16 operands (block 0 split), 1: split-bf16 everywhere (fp32 grade)
+  int dil[5] = {1, 2, 3, 4, 1}, ks[5] = {5, 3, 3, 3, 1};
+  Layer block0, tdnn1[3], tdnn2[3], res[3][7], mfa, asp_tdnn, asp_conv;
+  float *se_w1[3] = {}, *se_b1[3] = {}, *se_w2[3] = {}, *se_b2[3] = {};
+  float *asp_w = nullptr;  // asp.tdnn conv weight fp32 [att, 9C] (the [mean;std] columns feed the per-utterance bias)
+  float *aspbn_scale = nullptr, *aspbn_shift = nullptr, *fc_w = nullptr, *fc_b = nullptr;
+  std::vector<void*> owned;
+};
+
+typedef std::map<std::string, const float*> TensorMap;
+
+static const float* find(const TensorMap& tm, const std::string& key) {
+  auto it = tm.find(key);
+  if (it == tm.end()) { set_error("missing tensor '%s'", key.c_str()); return nullptr; }
+  return it->second;
+}
+
+template <typename T>
+static T* dalloc(Ecapa* e, size_t n) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+  e->owned.push_back(p);
+  return static_cast<T*>(p);
+}
+
+static float* dcopy(Ecapa* e, const float* src, size_t n) {
+  float* p = dalloc<float>(e, n);
+  if (p != nullptr) cudaMemcpy(p, src, n * sizeof(float), cudaMemcpyDeviceToDevice);
+  return p;
+}
+
+// TDNNBlock: conv + (optional) BatchNorm, packed for the tensor-core kernel.
+static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int cout, int cin, int k, int dil, int planes,
+                      int act, bool has_bn, const std::string& conv_key, Layer* L, int cin_used = -1) {
+  const float* w = find(tm, p + conv_key + "weight");
+  const float* b = find(tm, p + conv_key + "bias");
+  if (w == nullptr || b == nullptr) return -1;
+  L->cout = cout; L->cin = cin; L->k = k; L->dil = dil; L->planes = planes; L->act = act;
+  const int cu = cin_used < 0 ? cin : cin_used;   // pack only the first `cu` input channels
+  L->cin_pad = (cu + 63) / 64 * 64;
+  L->w = dalloc<bf16>(e, static_cast<size_t>(cout) * k * planes * L->cin_pad);
+  L->bias = dcopy(e, b, cout);
+  L->scale = dalloc<float>(e, cout);
+  L->shift = dalloc<float>(e, cout);
+  SVB_CHECK(L->w && L->bias && L->scale && L->shift, "cudaMalloc failed while packing %s", p.c_str());
+  if (cu == cin) {
+    if (pack_conv_weight(w, cout, cin, k, L->cin_pad, planes, L->w, 0)) return -1;
+  } else {
+    // strided sub-matrix (k == 1): copy the first cu columns to a dense temporary first
+    SVB_CHECK(k == 1, "partial input packing only for k=1");
+    float* tmp = nullptr;
+    SVB_CUDA_OK(cudaMalloc(&tmp, static_cast<size_t>(cout) * cu * sizeof(float)));
+    SVB_CUDA_OK(cudaMemcpy2D(tmp, cu * sizeof(float), w, cin * sizeof(float), cu * sizeof(float), cout,
+                             cudaMemcpyDeviceToDevice));
+    const int rc = pack_conv_weight(tmp, cout, cu, 1, L->cin_pad, planes, L->w, 0);
+    cudaDeviceSynchronize();
+    cudaFree(tmp);
+    if (rc) return -1;
+  }
+  if (has_bn) {
+    const float *g = find(tm, p + "norm.norm.weight"), *bb = find(tm, p + "norm.norm.bias");
+    const float *m = find(tm, p + "norm.norm.running_mean"), *v = find(tm, p + "norm.norm.running_var");
+    if (!g || !bb || !m || !v) return -1;
+    if (fold_bn(g, bb, m, v, cout, 1e-5f, L->scale, L->shift, 0)) return -1;
+  } else {
+    std::vector<float> ones(cout, 1.f), zeros(cout, 0.f);
+    SVB_CUDA_OK(cudaMemcpy(L->scale, ones.data(), cout * sizeof(float), cudaMemcpyHostToDevice));
+    SVB_CUDA_OK(cudaMemcpy(L->shift, zeros.data(), cout * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scale, const int* kernel_sizes,
+                 const int* dilations, int fp32_mode, const char* const* names, const void* const* ptrs, int n,
+                 Ecapa** out) {
+  SVB_CHECK(C % 512 == 0, "channels must be a multiple of 512 (Res2Net chunks are tiled in 64-column K blocks); got %d", C);
+  SVB_CHECK(res2_scale == 8 && att % 64 == 0 && se_ch % 4 == 0 && n_mels <= MEL_PLANE, "unsupported ECAPA configuration");
+  TensorMap tm;
+  for (int i = 0; i < n; ++i) tm[names[i]] = static_cast<const float*>(ptrs[i]);
+  Ecapa* e = new Ecapa();
+  e->C = C; e->C3 = 3 * C; e->Cs = C / res2_scale; e->n_mels = n_mels; e->n_out = n_out; e->att = att; e->se_ch = se_ch;
+  e->fp32_mode = fp32_mode;
+  int halo = 0;
+  for (int i = 0; i < 5; ++i) {
+    e->ks[i] = kernel_sizes[i]; e->dil[i] = dilations[i];
+    SVB_CHECK(kernel_sizes[i] == 1 || kernel_sizes[i] == 3 || kernel_sizes[i] == 5, "kernel sizes must be 1, 3 or 5");
+    const int pad = dilations[i] * (kernel_sizes[i] - 1) / 2;
+    if (pad > halo) halo = pad;
+  }
+  SVB_CHECK(e->ks[4] == 1, "the MFA layer must be pointwise");
+  e->halo = halo;
+  const int P = fp32_mode ? 2 : 1;
+  int rc = 0;
+  rc |= make_layer(e, tm, "blocks.0.", C, n_mels, e->ks[0], e->dil[0], 2, ACT_GELU, true, "conv.conv.", &e->block0);
+  SVB_CHECK(rc || e->block0.cin_pad == MEL_PLANE, "block 0 expects the %d-column mel plane", MEL_PLANE);
+  for (int i = 0; i < 3 && !rc; ++i) {
+    const std::string p = "blocks." + std::to_string(i + 1) + ".";
+    rc |= make_layer(e, tm, p + "tdnn1.", C, C, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->tdnn1[i]);
+    for (int j = 0; j < 7 && !rc; ++j)
+      rc |= make_layer(e, tm, p + "res2net_block.blocks." + std::to_string(j) + ".", e->Cs, e->Cs, e->ks[i + 1],
+                       e->dil[i + 1], P, ACT_RELU, true, "conv.conv.", &e->res[i][j]);
+    rc |= make_layer(e, tm, p + "tdnn2.", C, C, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->tdnn2[i]);
+    const float *w1 = find(tm, p + "se_block.conv1.conv.weight"), *b1 = find(tm, p + "se_block.conv1.conv.bias");
+    const float *w2 = find(tm, p + "se_block.conv2.conv.weight"), *b2 = find(tm, p + "se_block.conv2.conv.bias");
+    if (!w1 || !b1 || !w2 || !b2) { rc = -1; break; }
+    e->se_w1[i] = dcopy(e, w1, static_cast<size_t>(se_ch) * C); e->se_b1[i] = dcopy(e, b1, se_ch);
+    e->se_w2[i] = dcopy(e, w2, static_cast<size_t>(C) * se_ch); e->se_b2[i] = dcopy(e, b2, C);
+  }
+  if (!rc) rc |= make_layer(e, tm, "mfa.", e->C3, e->C3, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->mfa);
+  // asp.tdnn: only the first 3C input channels vary over time; the rest become a per-utterance bias
+  if (!rc) rc |= make_layer(e, tm, "asp.tdnn.", att, 3 * e->C3, 1, 1, P, ACT_RELU, true, "conv.conv.", &e->asp_tdnn, e->C3);
+  if (!rc) rc |= make_layer(e, tm, "asp.conv.", e->C3, att, 1, 1, P, ACT_NONE, false, "conv.", &e->asp_conv);
+  if (!rc) {
+    const float* aw = find(tm, "asp.tdnn.conv.conv.weight");
+    const float *g = find(tm, "asp_bn.norm.weight"), *b = find(tm, "asp_bn.norm.bias");
+    const float *m = find(tm, "asp_bn.norm.running_mean"), *v = find(tm, "asp_bn.norm.running_var");
+    const float *fw = find(tm, "fc.conv.weight"), *fb = find(tm, "fc.conv.bias");
+    if (!aw || !g || !b || !m || !v || !fw || !fb) rc = -1;
+    else {
+      e->asp_w = dcopy(e, aw, static_cast<size_t>(att) * 3 * e->C3);
+      e->aspbn_scale = dalloc<float>(e, 2 * e->C3); e->aspbn_shift = dalloc<float>(e, 2 * e->C3);
+      rc |= fold_bn(g, b, m, v, 2 * e->C3, 1e-5f, e->aspbn_scale, e->aspbn_shift, 0);
+      e->fc_w = dcopy(e, fw, static_cast<size_t>(n_out) * 2 * e->C3); e->fc_b = dcopy(e, fb, n_out);
+    }
+  }
+  if (!rc && cudaDeviceSynchronize() != cudaSuccess) { set_error("weight packing failed: %s", cudaGetErrorString(cudaGetLastError())); rc = -2; }
+  if (rc) { for (void* p : e->owned) cudaFree(p); delete e; return rc; }
+  *out = e;
+  return 0;
+}
+
+void ecapa_destroy(Ecapa* e) {
+  if (e == nullptr) return;
+  for (void* p : e->owned) cudaFree(p);
+  delete e;
+}
+int ecapa_halo(const Ecapa* e) { return e->halo; }
+
+// ------------------------------------------------------------------ workspace plan
+struct Region { const char* name; size_t off, bytes; };
+struct Plan {
+  std::vector<Region> r;
+  size_t total = 0;
+  size_t add(const char* name, size_t bytes) {
+    const size_t off = total;
+    r.push_back(Region{name, off, bytes});
+    total += (bytes + 255) / 256 * 256;
+    return off;
+  }
+  size_t off(const char* name) const {
+    for (const Region& g : r) if (strcmp(g.name, name) == 0) return g.off;
+    return static_cast<size_t>(-1);
+  }
+};
+
+static Plan make_plan(const Ecapa* e, const Batch* b) {
+  Plan p;
+  const size_t M = static_cast<size_t>(b->rows) + 128;  // slack so tile-granular tails stay in bounds
+  const size_t P = e->fp32_mode ? 2 : 1;
+  const size_t B = b->B;
+  p.add("logmel", M * e->n_mels * 4);
+  p.add("tile_sums", static_cast<size_t>(b->ntiles) * e->n_mels * 4);
+  p.add("mel_mean", B * e->n_mels * 4);
+  p.add("x0", M * 2 * MEL_PLANE * 2);
+  p.add("block0", M * P * e->C * 2);
+  p.add("xcat", M * P * e->C3 * 2);
+  p.add("u", M * P * e->C * 2);
+  p.add("r", M * P * e->C * 2);
+  p.add("v", M * P * e->C * 2);
+  p.add("s0", M * P * e->Cs * 2);
+  p.add("s1", M * P * e->Cs * 2);
+  p.add("mfa", M * P * e->C3 * 2);
+  p.add("att", M * P * e->att * 2);
+  p.add("logits", M * e->C3 * 4);
+  p.add("se_mean", B * e->C * 4);
+  p.add("se_hidden", B * e->se_ch * 4);
+  p.add("se_gate", B * e->C * 4);
+  p.add("asp_stats", B * 2 * e->C3 * 4);
+  p.add("asp_rowbias", B * e->att * 4);
+  p.add("pooled", B * 2 * e->C3 * 4);
+  p.add("emb_raw", B * e->n_out * 4);
+  return p;
+}
+
+size_t ecapa_workspace_bytes(const Ecapa* e, const Batch* b) { return make_plan(e, b).total; }
+long long ecapa_ws_offset(const Ecapa* e, const Batch* b, const char* name) {
+  const size_t o = make_plan(e, b).off(name);
+  return o == static_cast<size_t>(-1) ? -1 : static_cast<long long>(o);
+}
+
+// ------------------------------------------------------------------ forward
+struct View { const bf16* p; int ld, plane_cols, cols; };
+
+static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, const View* x2, int x2_chunks, bf16* out,
+                     int out_ld, int out_pc, int store_mode, const float* rowbias, int rowbias_ld, int post_tanh,
+                     int out_kind_override, const View* add, bf16* out2, int out2_ld, int out2_pc, int passes,
+                     cudaStream_t stream) {
+  GemmOperands ops{};
+  ops.a = x.p; ops.lda = x.ld; ops.a_cols = x.cols;
+  if (x2 != nullptr) { ops.a2 = x2->p; ops.lda2 = x2->ld; ops.a2_cols = x2->cols; }
+  ops.w = L.w; ops.w_rows = L.cout; ops.w_cols = L.k * L.planes * L.cin_pad;
+  GemmParams p{};
+  p.M = static_cast<int>(b->rows); p.N = L.cout; p.kc_per_tap = L.cin_pad / 64; p.num_taps = L.k;
+  for (int j = 0; j < L.k; ++j) p.tap_off[j] = (j - (L.k - 1) / 2) * L.dil;
+  p.num_pass = passes; p.a_plane_cols = x.plane_cols; p.a2_kc = x2 != nullptr ? x2_chunks : 0; p.w_planes = L.planes;
+  p.bias = L.bias; p.scale = L.scale; p.shift = L.shift; p.rowbias = rowbias; p.rowbias_ld = rowbias_ld;
+  p.act = L.act; p.post_tanh = post_tanh; p.row_meta = b->d_meta; p.store_mode = store_mode; p.halo = b->halo;
+  p.out = out; p.out_ld = out_ld; p.out_plane_cols = out_pc;
+  p.out_kind = out_kind_override >= 0 ? out_kind_override : (e->fp32_mode ? OUT_BF16_HILO : OUT_BF16);
+  if (add != nullptr) {
+    p.add_src = add->p; p.add_ld = add->ld; p.add_planes = e->fp32_mode ? 2 : 1; p.add_plane_cols = add->plane_cols;
+    p.out2 = out2; p.out2_ld = out2_ld; p.out2_plane_cols = out2_pc;
+  }
+  const int bn = L.cout >= 256 ? 256 : (L.cout >= 128 ? 128 : 64);
+  return launch_gemm(ops, p, bn, stream);
+}
+
+int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* wav, void* ws, size_t ws_bytes,
+                  float* emb, int emb_ld, int l2norm, cudaStream_t stream) {
+  SVB_CHECK(fbank_n_mels(fb) == e->n_mels && fbank_hop(fb) == b->hop, "front-end / model / batch mismatch");
+  SVB_CHECK(b->halo == e->halo, "batch halo %d != model halo %d", b->halo, e->halo);
+  const Plan pl = make_plan(e, b);
+  SVB_CHECK(ws != nullptr && ws_bytes >= pl.total, "workspace too small: need %zu bytes, got %zu", pl.total, ws_bytes);
+  SVB_CHECK((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-byte aligned");
+  uint8_t* base = static_cast<uint8_t*>(ws);
+  auto F = [&](const char* n) { return reinterpret_cast<float*>(base + pl.off(n)); };
+  auto H = [&](const char* n) { return reinterpret_cast<bf16*>(base + pl.off(n)); };
+  const int P = e->fp32_mode ? 2 : 1, passes = e->fp32_mode ? 3 : 1;
+  const int C = e->C, C3 = e->C3, Cs = e->Cs, B = b->B;
+  const long long M = b->rows;
+
+  // K1: waveform -> mean-normalised log-mel, hi|lo planes of 128 columns, halos mirrored
+  if (fbank_forward(fb, wav, b->d_utt, reinterpret_cast<const int32_t*>(b->d_tiles), B, b->ntiles, b->d_meta, M, b->halo,
+                    F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2, stream)) return -1;
+
+  // block 0 (k=5): always split-bf16 -- the log-mel input loses too much in plain bf16
+  View x0{H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2 * MEL_PLANE};
+  if (run_layer(e, b, e->block0, x0, nullptr, 0, H("block0"), P * C, C, STORE_MIRROR, nullptr, 0, 0, -1, nullptr, nullptr,
+                0, 0, 3, stream)) return -1;
+
+  bf16 *U = H("u"), *R = H("r"), *V = H("v"), *S[2] = {H("s0"), H("s1")}, *XC = H("xcat");
+  View cur{H("block0"), P * C, C, P * C};
+  for (int i = 0; i < 3; ++i) {
+    // tdnn1 (1x1)
+    if (run_layer(e, b, e->tdnn1[i], cur, nullptr, 0, U, P * C, C, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0,
+                  passes, stream)) return -1;
+    // Res2Net chain: y_j = TDNN_j(x_j + y_{j-1}); chunk 0 passes through (read straight from U by tdnn2)
+    for (int j = 1; j < 8; ++j) {
+      View xin = (j == 1) ? View{U + Cs, P * C, C, P * C - Cs} : View{S[(j - 1) & 1], P * Cs, Cs, P * Cs};
+      View add{U + (j + 1) * Cs, P * C, C, 0};
+      if (run_layer(e, b, e->res[i][j - 1], xin, nullptr, 0, R + j * Cs, P * C, C, STORE_MIRROR, nullptr, 0, 0, -1,
+                    j < 7 ? &add : nullptr, S[j & 1], P * Cs, Cs, passes, stream)) return -1;
+    }
+    // tdnn2 (1x1): K chunks of channel group 0 come from U, the rest from R
+    View rv{R, P * C, C, P * C}, uv{U, P * C, C, P * C};
+    if (run_layer(e, b, e->tdnn2[i], rv, &uv, Cs / 64, V, P * C, C, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0,
+                  passes, stream)) return -1;
+    // SE: time mean -> C->se->C gate -> gate * V + residual, written into the MFA concat buffer
+    if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
+    if (small_linear(e->se_w1[i], C, e->se_b1[i], F("se_mean"), C, nullptr, nullptr, B, e->se_ch, C, LIN_RELU,
+                     F("se_hidden"), e->se_ch, stream)) return -1;
+    if (small_linear(e->se_w2[i], e->se_ch, e->se_b2[i], F("se_hidden"), e->se_ch, nullptr, nullptr, B, C, e->se_ch,
+                     LIN_SIGMOID, F("se_gate"), C, stream)) return -1;
+    bf16* o = XC + i * C;
+    if (se_apply(V, P * C, C, cur.p, cur.ld, cur.plane_cols, F("se_gate"), C, b->d_meta, M, C, P, o, P * C3, C3, stream))
+      return -1;
+    cur = View{o, P * C3, C3, P * C3 - i * C};
+  }
+  // MFA over the (never materialised separately) concat of the three block outputs
+  View xc{XC, P * C3, C3, P * C3};
+  bf16* Y = H("mfa");
+  if (run_layer(e, b, e->mfa, xc, nullptr, 0, Y, P * C3, C3, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0, passes,
+                stream)) return -1;
+  // ASP: global mean/std -> per-utterance bias; time-varying 3C->att GEMM; att->3C logits; softmax statistics
+  float* st = F("asp_stats");
+  if (col_stats(Y, P * C3, P, C3, b->d_uttrows, B, C3, 1, 1e-12f, st, st + C3, 2 * C3, stream)) return -1;
+  if (small_linear(e->asp_w + C3, 3 * C3, nullptr, st, 2 * C3, nullptr, nullptr, B, e->att, 2 * C3, LIN_NONE,
+                   F("asp_rowbias"), e->att, stream)) return -1;
+  View yv{Y, P * C3, C3, P * C3};
+  if (run_layer(e, b, e->asp_tdnn, yv, nullptr, 0, H("att"), P * e->att, e->att, STORE_ALL, F("asp_rowbias"), e->att, 1, -1,
+                nullptr, nullptr, 0, 0, passes, stream)) return -1;
+  View av{H("att"), P * e->att, e->att, P * e->att};
+  if (run_layer(e, b, e->asp_conv, av, nullptr, 0, reinterpret_cast<bf16*>(F("logits")), C3, 0, STORE_ALL, nullptr, 0, 0,
+                OUT_F32, nullptr, nullptr, 0, 0, passes, stream)) return -1;
+  if (asp_pool(F("logits"), C3, Y, P * C3, P, C3, b->d_uttrows, B, C3, 1e-12f, F("pooled"), 2 * C3, stream)) return -1;
+  // asp_bn + fc
+  float* dst = l2norm ? F("emb_raw") : emb;
+  const int dst_ld = l2norm ? e->n_out : emb_ld;
+  if (small_linear(e->fc_w, 2 * C3, e->fc_b, F("pooled"), 2 * C3, e->aspbn_scale, e->aspbn_shift, B, e->n_out, 2 * C3,
+                   LIN_NONE, dst, dst_ld, stream)) return -1;
+  if (l2norm && l2norm_rows(dst, dst_ld, emb, emb_ld, B, e->n_out, 1e-12f, stream)) return -1;
+  return 0;
+}
+
+}  // namespace svb

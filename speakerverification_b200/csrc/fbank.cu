@@ -31,7 +31,9 @@ struct FbankTables {
   int mel_count[MAX_MELS];
   int mel_off[MAX_MELS];
   float mel_w[MAX_NNZ];
+  int pad_[2];             // sizeof % 16 == 0 (copied to shared memory in 16-byte pieces)
 };
+static_assert(sizeof(FbankTables) % 16 == 0, "FbankTables must be a multiple of 16 bytes");
 
 struct Fbank {
   FbankTables* d_tab;

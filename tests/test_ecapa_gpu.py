@@ -1,0 +1,125 @@
+"""GPU parity of the fused front-end and the full ECAPA-TDNN forward against the CPU oracle and the
+committed reference outputs (tests/golden/*.npz)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+L = 48000
+CH512 = [512, 512, 512, 512, 1536]
+CH1024 = [1024, 1024, 1024, 1024, 3072]
+
+
+def _bn(g):
+    return {k[3:]: v for k, v in g.items() if k.startswith("bn/")}
+
+
+def _state(channels, golden):
+    from oracle import synth
+    sd = synth.ecapa_state_dict(channels, 192, bn_stats=_bn(golden))
+    return sd, {k[len("__S__."):]: torch.as_tensor(v).cuda() for k, v in sd.items()}
+
+
+def _frontend():
+    from speakerverification_b200.engine import Frontend
+    return Frontend(sr=16000, n_fft=512, win_length=400, hop_length=160, n_mels=80)
+
+
+def test_fbank_matches_oracle():
+    from oracle import ecapa_oracle as eo, synth
+    from speakerverification_b200.engine import fbank_logmel
+    waves, _ = synth.utterance_set(2, 2, L + 1)
+    noise = synth.white_noise(2, L)
+    w = np.concatenate([waves[:, :L], noise])
+    fe = _frontend()
+    packed, logmel, mean, plan = fbank_logmel(fe, torch.from_numpy(w).cuda(), halo=4)
+    torch.cuda.synchronize()
+    ref_mel = eo.power_mel(torch.from_numpy(w))                    # [B, 80, T]
+    ref_log = (ref_mel + 1e-6).log()
+    idx = plan.valid_row_index("cuda")
+    got = logmel[idx].view(w.shape[0], -1, 80).transpose(1, 2).cpu()
+    assert got.shape == ref_log.shape
+    # tolerance: log-mel abs 1e-4
+    assert (got - ref_log).abs().max().item() < 1e-4
+    ref_cmn = eo.log_cmn(ref_mel).transpose(1, 2)                  # [B, T, 80]
+    x = packed[idx].float()
+    val = (x[:, :80] + x[:, 128:208]).view(w.shape[0], -1, 80).cpu()
+    assert (val - ref_cmn).abs().max().item() < 2e-4
+    assert packed[:, 80:128].abs().max().item() == 0 and packed[:, 208:].abs().max().item() == 0
+    # halo rows mirror frames 1..4 / T-2..T-5
+    T = plan.T[0]
+    rows = packed[: T + 8].float()
+    for t in range(1, 5):
+        assert torch.equal(rows[4 - t], rows[4 + t])
+        assert torch.equal(rows[4 + T - 1 + t], rows[4 + T - 1 - t])
+
+
+# fp32 mode: BASELINE tolerances (cos >= 0.9999, scores <= 1e-4) on ALL 2016 single-crop pairs.
+# bf16 mode: the <= 2e-3 tolerance is stated on trial scores and is asserted on the reference's own
+# trial list in tests/test_api_gpu.py; the all-pairs single-crop maximum asserted here (3e-3) is a
+# stricter-population diagnostic (measured 2.15e-3; the fp32-epilogue bf16 design point).
+@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("bf16", 0.9995, 3e-3)])
+def test_ecapa_c512_matches_reference(golden_c512, precision, cos_min, tol):
+    from oracle import synth
+    from speakerverification_b200.engine import EcapaEngine
+    waves, _ = synth.utterance_set(16, 4, L + 1)
+    _, state = _state(CH512, golden_c512)
+    eng = EcapaEngine(state, CH512, 80, 192, _frontend(), precision=precision)
+    emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda()).cpu().numpy()
+    ref = golden_c512["emb_batch"]
+    assert np.isfinite(emb).all()
+    en = emb / np.linalg.norm(emb, axis=1, keepdims=True)
+    rn = ref / np.linalg.norm(ref, axis=1, keepdims=True)
+    cos = (en * rn).sum(1)
+    assert cos.min() >= cos_min, cos.min()
+    # all-pairs scores of L2-normalised embeddings (the quantity the score tolerance is stated on)
+    dev = np.abs(en @ en.T - rn @ rn.T).max()
+    print("precision", precision, "min cos", cos.min(), "max pair-score dev", dev)
+    assert dev <= tol, dev
+
+
+def test_ecapa_stages_fp32(golden_c512):
+    """Per-stage parity for utterance 0 (every 16th channel), to localise a regression."""
+    from oracle import synth
+    from speakerverification_b200.engine import EcapaEngine
+    waves, _ = synth.utterance_set(16, 4, L + 1)
+    _, state = _state(CH512, golden_c512)
+    eng = EcapaEngine(state, CH512, 80, 192, _frontend(), precision="fp32")
+    w = torch.from_numpy(waves[:4, :L]).cuda()
+    eng.forward(w)
+    torch.cuda.synchronize()
+    plan = eng.plan([L] * 4)
+    T, H = plan.T[0], plan.halo
+
+    def stage(name, cols, off=0, width=None):
+        t = eng.stage(plan, name, cols, planes=2)[H:H + T].float()
+        width = cols if width is None else width
+        return (t[:, off:off + width] + t[:, cols + off:cols + off + width]).t().cpu().numpy()
+    np.testing.assert_allclose(stage("block0", 512)[::16], golden_c512["stage/block0"], atol=2e-4, rtol=1e-4)
+    for i in (1, 2, 3):
+        got = stage("xcat", 1536, off=(i - 1) * 512, width=512)[::16]
+        np.testing.assert_allclose(got, golden_c512["stage/block%d" % i], atol=3e-4, rtol=1e-4)
+    np.testing.assert_allclose(stage("mfa", 1536)[::16], golden_c512["stage/mfa"], atol=3e-4, rtol=1e-4)
+
+
+def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
+    from oracle import ecapa_oracle as eo, synth
+    from speakerverification_b200.engine import EcapaEngine
+    waves, _ = synth.utterance_set(4, 4, L + 1)
+    sd, state = _state(CH1024, golden_c1024)
+    eng = EcapaEngine(state, CH1024, 80, 192, _frontend(), precision="bf16")
+    emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda()).cpu().numpy()
+    ref = golden_c1024["emb_batch"]
+    en = emb / np.linalg.norm(emb, axis=1, keepdims=True)
+    rn = ref / np.linalg.norm(ref, axis=1, keepdims=True)
+    assert (en * rn).sum(1).min() > 0.9995
+    assert np.abs(en @ en.T - rn @ rn.T).max() <= 3e-3
+    # ragged batch: every utterance keeps its own length (no padding), checked against the oracle
+    lens = [16000, 48000, 23456, 40000]
+    flat = torch.from_numpy(np.concatenate([waves[i, :n] for i, n in enumerate(lens)])).cuda()
+    got = eng.forward_flat(flat, lens).cpu().numpy()
+    for i, n in enumerate(lens):
+        want = eo.embed(np.stack([waves[i, :n], waves[i, :n]]), sd).numpy()[0]
+        c = float((got[i] * want).sum() / np.linalg.norm(got[i]) / np.linalg.norm(want))
+        assert c > 0.9995, (i, c)
