@@ -115,6 +115,11 @@ int svb_fbank_forward(const SvbFbank* f, const SvbBatch* b, const float* wav, vo
                       int plane_cols, int planes, float* logmel_ws, float* tile_sums_ws, float* mean_ws,
                       void* stream);
 
+/* Feature-plugin entry: power-mel only (what compute_features(x) returns at src/model.py:112-113),
+ * written time-major into mel_rows [rows*n_mels] fp32 (valid rows; halo rows untouched). */
+int svb_fbank_power(const SvbFbank* f, const SvbBatch* b, const float* wav, float* mel_rows,
+                    float* tile_sums_ws, void* stream);
+
 /* ------------------------------------------------------------------ ECAPA-TDNN encoder (K2-K7)
  * Replaces models.ECAPA_TDNN.MainModel.forward (src/models/ECAPA_TDNN.py:460-502) behind
  * SpeakerEncoder.forward (src/model.py:104-129).  Weights: fp32 DEVICE pointers in the reference
@@ -138,6 +143,10 @@ int64_t svb_ecapa_ws_offset(const SvbEcapa* e, const SvbBatch* b, const char* na
 int svb_ecapa_forward(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* wav, void* ws,
                       size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream);
 
+/* Encoder-plugin entry (MainModel.forward(x) with x = power-mel, src/models/ECAPA_TDNN.py:460-502):
+ * mel_rows [rows, n_mels] fp32 power-mel in the time-major layout (valid rows filled). */
+int svb_ecapa_forward_mel(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* mel_rows,
+                          void* ws, size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream);
 
 /* ------------------------------------------------------------------ trial scoring (K8/K9)
  * emb: [U, n_per_utt, D] fp32 crop embeddings of the U unique utterances; idx_a/idx_b: int32 indices

@@ -125,4 +125,4 @@ if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count())
     make([512, 512, 512, 512, 1536], 192, "cfg1_c512")
-    make([1024, 1024, 1024, 1024, 3072], 192, "cfg2_c1024", n_spk=4, per_spk=4, full=False)
+    make([1024, 1024, 1024, 1024, 3072], 192, "cfg2_c1024")

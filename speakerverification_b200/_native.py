@@ -91,6 +91,8 @@ _EXTRA_SIGS = {
     "svb_ecapa_workspace_bytes": ([_vp, _vp], _c.c_size_t),
     "svb_ecapa_ws_offset": ([_vp, _vp, _c.c_char_p], _i64),
     "svb_ecapa_forward": ([_vp, _vp, _vp, _vp, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
+    "svb_fbank_power": ([_vp, _vp, _vp, _vp, _vp, _vp], _i32),
+    "svb_ecapa_forward_mel": ([_vp, _vp, _vp, _vp, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
     "svb_cosine_trials": ([_vp, _i32, _i32, _vp, _vp, _i64, _vp, _vp], _i32),
     "svb_mean_embeddings": ([_vp, _i32, _i32, _i32, _i32, _vp, _vp], _i32),
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),

@@ -1,0 +1,54 @@
+"""Host-side mirror of the reference's evaluation-mode waveform loader
+(``loadWAV``, src/processing/audio_loader.py:53-152; ``normalize_audio_amp``,
+src/processing/wav_conversion.py:35-41).  Training augmentation branches are out of scope."""
+from pathlib import Path
+
+import numpy as np
+
+
+def _read_wav(path):
+    try:
+        import soundfile as sf
+        audio, sr = sf.read(path, dtype="float32", always_2d=False)
+        return audio, sr
+    except ImportError:
+        from scipy.io import wavfile
+        sr, data = wavfile.read(path)
+        if np.issubdtype(data.dtype, np.integer):
+            data = data.astype(np.float32) / float(-np.iinfo(data.dtype).min)   # soundfile's float32 scaling
+        return data.astype(np.float32), sr
+
+
+def normalize_audio_amp(signal):
+    try:
+        info = np.iinfo(signal.dtype)
+        return signal / max(info.max, -info.min)
+    except ValueError:
+        return signal / max(signal.max(), -signal.min())
+
+
+def loadWAV(audio_source, audio_spec=None, evalmode=True, num_eval=10, augment=False, augment_options=None,
+            target_db=None, read_mode="sf", random_chunk=True, load_all=False, dtype=np.float32, **kwargs):
+    """path or ndarray -> [num_eval, sentence_len*sr] evenly spaced crops (whole signal if num_eval == 0)."""
+    if not audio_spec:
+        audio_spec = {"sample_rate": 8000, "channels": 1, "sentence_len": 2.0, "win_len": 0.025, "hop_len": 0.01}
+    if augment or not evalmode:
+        raise NotImplementedError("training-mode loading / augmentation is outside the inference hot path")
+    if isinstance(audio_source, (str, Path)):
+        audio, _ = _read_wav(str(Path(audio_source)))
+    elif isinstance(audio_source, np.ndarray):
+        audio = normalize_audio_amp(audio_source)
+    else:
+        raise TypeError("Invalid format of audio source, available: str, ndarray")
+    if load_all:
+        return np.expand_dims(audio, 0)
+    sr = audio_spec["sample_rate"]
+    max_audio = int(audio_spec["sentence_len"] * sr)
+    n = audio.shape[0]
+    if n <= max_audio:
+        audio = np.pad(audio, (0, max_audio - n + 1), "wrap")
+        n = audio.shape[0]
+    if num_eval == 0:
+        return np.stack([audio], axis=0).astype(dtype)
+    starts = np.linspace(0, n - max_audio, num=num_eval)
+    return np.stack([audio[int(s):int(s) + max_audio] for s in starts], axis=0).astype(dtype)

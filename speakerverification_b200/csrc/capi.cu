@@ -15,7 +15,7 @@ struct Fbank; struct Batch; struct Ecapa;
 int fbank_create(const float*, int, int, int, const float*, int, int, float, float, Fbank**);
 void fbank_destroy(Fbank*);
 int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
-                  float*, float*, float*, bf16*, int, int, int, cudaStream_t);
+                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
 int batch_create(const int64_t*, const int32_t*, int, int, int, Batch**);
 void batch_destroy(Batch*);
 long long batch_rows(const Batch*);
@@ -32,7 +32,8 @@ void ecapa_destroy(Ecapa*);
 int ecapa_halo(const Ecapa*);
 size_t ecapa_workspace_bytes(const Ecapa*, const Batch*);
 long long ecapa_ws_offset(const Ecapa*, const Batch*, const char*);
-int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, void*, size_t, float*, int, int, cudaStream_t);
+int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, int, void*, size_t, float*, int, int,
+                  cudaStream_t);
 int cosine_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float*, cudaStream_t);
 int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
 size_t asnorm_workspace_bytes(int, int, int, int*);
@@ -175,7 +176,18 @@ int svb_fbank_forward(const SvbFbank* f, const SvbBatch* b, const float* wav, vo
   return fbank_forward(reinterpret_cast<const Fbank*>(f), wav, batch_utt_tab(bt), batch_tile_tab(bt), batch_B(bt),
                        batch_tiles(bt), reinterpret_cast<const RowMeta*>(batch_row_meta(bt)), batch_rows(bt),
                        batch_halo(bt), logmel_ws, tile_sums_ws, mean_ws, static_cast<bf16*>(out), out_ld, plane_cols,
-                       planes, static_cast<cudaStream_t>(stream));
+                       planes, 0, static_cast<cudaStream_t>(stream));
+}
+
+int svb_fbank_power(const SvbFbank* f, const SvbBatch* b, const float* wav, float* mel_rows, float* tile_sums_ws,
+                    void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(f && b && wav && mel_rows && tile_sums_ws, "null argument");
+  const Batch* bt = reinterpret_cast<const Batch*>(b);
+  return fbank_forward(reinterpret_cast<const Fbank*>(f), wav, batch_utt_tab(bt), batch_tile_tab(bt), batch_B(bt),
+                       batch_tiles(bt), reinterpret_cast<const RowMeta*>(batch_row_meta(bt)), batch_rows(bt),
+                       batch_halo(bt), mel_rows, tile_sums_ws, nullptr, nullptr, 0, 0, 0, 1,
+                       static_cast<cudaStream_t>(stream));
 }
 
 int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n, SvbEcapa** out) {
@@ -198,7 +210,15 @@ int svb_ecapa_forward(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, c
   if (check_device()) return -1;
   SVB_CHECK(e && f && b && wav && emb, "null argument");
   return ecapa_forward(reinterpret_cast<const Ecapa*>(e), reinterpret_cast<const Fbank*>(f),
-                       reinterpret_cast<const Batch*>(b), wav, ws, ws_bytes, emb, emb_ld, l2norm,
+                       reinterpret_cast<const Batch*>(b), wav, 0, ws, ws_bytes, emb, emb_ld, l2norm,
+                       static_cast<cudaStream_t>(stream));
+}
+int svb_ecapa_forward_mel(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* mel_rows, void* ws,
+                          size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(e && f && b && mel_rows && emb, "null argument");
+  return ecapa_forward(reinterpret_cast<const Ecapa*>(e), reinterpret_cast<const Fbank*>(f),
+                       reinterpret_cast<const Batch*>(b), mel_rows, 1, ws, ws_bytes, emb, emb_ld, l2norm,
                        static_cast<cudaStream_t>(stream));
 }
 

@@ -16,7 +16,9 @@ struct Fbank;
 int fbank_n_mels(const Fbank*);
 int fbank_hop(const Fbank*);
 int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
-                  float*, float*, float*, bf16*, int, int, int, cudaStream_t);
+                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
+int fbank_from_power(const Fbank*, const float*, const void*, int, const RowMeta*, long long, int, float*, float*, bf16*,
+                     int, int, int, cudaStream_t);
 int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
@@ -320,8 +322,10 @@ static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, con
   return launch_gemm(ops, p, bn, stream);
 }
 
-int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* wav, void* ws, size_t ws_bytes,
-                  float* emb, int emb_ld, int l2norm, cudaStream_t stream) {
+// input_kind 0: `input` is the waveform buffer (fused front-end); 1: `input` holds power-mel rows
+// [rows, n_mels] fp32 in the time-major layout (encoder-plugin entry, features computed by the caller).
+int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* wav, int input_kind, void* ws,
+                  size_t ws_bytes, float* emb, int emb_ld, int l2norm, cudaStream_t stream) {
   SVB_CHECK(fbank_n_mels(fb) == e->n_mels && fbank_hop(fb) == b->hop, "front-end / model / batch mismatch");
   SVB_CHECK(b->halo == e->halo, "batch halo %d != model halo %d", b->halo, e->halo);
   const Plan pl = make_plan(e, b);
@@ -335,8 +339,14 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   const long long M = b->rows;
 
   // K1: waveform -> mean-normalised log-mel, hi|lo planes of 128 columns, halos mirrored
-  if (fbank_forward(fb, wav, b->d_utt, reinterpret_cast<const int32_t*>(b->d_tiles), B, b->ntiles, b->d_meta, M, b->halo,
-                    F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2, stream)) return -1;
+  if (input_kind == 0) {
+    if (fbank_forward(fb, wav, b->d_utt, reinterpret_cast<const int32_t*>(b->d_tiles), B, b->ntiles, b->d_meta, M,
+                      b->halo, F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2, 0,
+                      stream)) return -1;
+  } else {
+    if (fbank_from_power(fb, wav, b->d_utt, B, b->d_meta, M, b->halo, F("logmel"), F("mel_mean"), H("x0"),
+                         2 * MEL_PLANE, MEL_PLANE, 2, stream)) return -1;
+  }
 
   // block 0 (k=5): always split-bf16 -- the log-mel input loses too much in plain bf16
   View x0{H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2 * MEL_PLANE};

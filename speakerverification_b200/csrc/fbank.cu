@@ -9,6 +9,7 @@
 // The power spectrum [B,257,T] the reference materialises in HBM never leaves shared memory.
 #include <math.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "svb_internal.h"
@@ -51,7 +52,7 @@ __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
 __global__ void __launch_bounds__(FB_WARPS * 32)
 fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ utts,
                     const int2* __restrict__ tiles, const FbankTables* __restrict__ tab, int hop, int n_mels,
-                    float preemph, float log_eps, int halo, float* __restrict__ logmel,
+                    float preemph, float log_eps, int halo, int raw_power, float* __restrict__ logmel,
                     float* __restrict__ tile_sums) {
   extern __shared__ __align__(16) uint8_t fb_smem[];
   FbankTables* st = reinterpret_cast<FbankTables*>(fb_smem);
@@ -152,7 +153,7 @@ fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ u
         const float* wv = st->mel_w + st->mel_off[m];
         float sacc = 0.f;
         for (int i = 0; i < cnt; ++i) sacc = fmaf(pw[b0 + i], wv[i], sacc);
-        const float lm = logf(sacc + log_eps);
+        const float lm = raw_power ? sacc : logf(sacc + log_eps);
         logmel[row * n_mels + m] = lm;
         acc[q] += lm;
       }
@@ -204,6 +205,23 @@ __global__ void fbank_cmn_pack_kernel(const float* __restrict__ logmel, const fl
   }
 }
 
+// Encoder-plugin entry (features computed elsewhere): power-mel rows -> log(x + eps) rows.
+__global__ void log_rows_kernel(const float* __restrict__ power, long long n, float log_eps, float* __restrict__ out) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = logf(power[i] + log_eps);
+}
+// per-utterance column mean over the valid rows of an fp32 [rows, n_mels] matrix
+__global__ void utt_mean_f32_kernel(const float* __restrict__ x, const UttDesc* __restrict__ utts, int halo, int n_mels,
+                                    float* __restrict__ mean) {
+  const UttDesc u = utts[blockIdx.x];
+  for (int m = threadIdx.x; m < n_mels; m += blockDim.x) {
+    float s = 0.f;
+    for (int t = 0; t < u.T; ++t) s += x[(u.row_base + halo + t) * n_mels + m];
+    mean[blockIdx.x * n_mels + m] = s / static_cast<float>(u.T);
+  }
+}
+
 // ------------------------------------------------------------------ host
 int fbank_create(const float* window_host, int win_length, int hop, int n_fft, const float* fb_host, int n_freqs,
                  int n_mels, float preemph, float log_eps, Fbank** out) {
@@ -251,10 +269,35 @@ size_t fbank_smem_bytes(const Fbank* f) {
          (static_cast<size_t>(f->hop) * (FRAMES_PER_TILE - 1) + NFFT) * sizeof(float);
 }
 
+static int pack_rows(const Fbank* f, const RowMeta* meta, long long rows, const float* logmel_ws, const float* mean_ws,
+                     bf16* out, int out_ld, int plane_cols, int planes, cudaStream_t stream) {
+  const int rows_per_block = 8;
+  fbank_cmn_pack_kernel<<<static_cast<int>((rows + rows_per_block - 1) / rows_per_block), rows_per_block * 32, 0,
+                          stream>>>(logmel_ws, mean_ws, meta, rows, f->n_mels, out, out_ld, plane_cols, planes);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// power-mel rows [rows, n_mels] (time-major, valid rows filled) -> packed mean-normalised log-mel
+int fbank_from_power(const Fbank* f, const float* power_rows, const void* utt_tab, int B, const RowMeta* meta,
+                     long long rows, int halo, float* logmel_ws, float* mean_ws, bf16* out, int out_ld, int plane_cols,
+                     int planes, cudaStream_t stream) {
+  SVB_CHECK(plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
+  const long long n = rows * f->n_mels;
+  log_rows_kernel<<<static_cast<int>(std::min<long long>((n + 255) / 256, 148 * 16)), 256, 0, stream>>>(
+      power_rows, n, f->log_eps, logmel_ws);
+  utt_mean_f32_kernel<<<B, 128, 0, stream>>>(logmel_ws, static_cast<const UttDesc*>(utt_tab), halo, f->n_mels, mean_ws);
+  count_launch(2);
+  SVB_CUDA_OK(cudaGetLastError());
+  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream);
+}
+
+// mode 0: full front-end (log, mean normalisation, bf16 pack); mode 1: power-mel rows only (logmel_ws receives them)
 int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const int32_t* tile_tab, int B, int ntiles,
                   const RowMeta* meta, long long rows, int halo, float* logmel_ws, float* tile_sums_ws,
-                  float* mean_ws, bf16* out, int out_ld, int plane_cols, int planes, cudaStream_t stream) {
-  SVB_CHECK(plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
+                  float* mean_ws, bf16* out, int out_ld, int plane_cols, int planes, int mode, cudaStream_t stream) {
+  SVB_CHECK(mode == 1 || plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
   const size_t smem = fbank_smem_bytes(f);
   static bool attr_set = false;
   if (!attr_set) {
@@ -264,14 +307,14 @@ int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const i
   }
   fbank_logmel_kernel<<<ntiles, FB_WARPS * 32, smem, stream>>>(
       wav, static_cast<const UttDesc*>(utt_tab), reinterpret_cast<const int2*>(tile_tab), f->d_tab, f->hop,
-      f->n_mels, f->preemph, f->log_eps, halo, logmel_ws, tile_sums_ws);
-  fbank_mean_kernel<<<B, 128, 0, stream>>>(static_cast<const UttDesc*>(utt_tab), tile_sums_ws, f->n_mels, mean_ws);
-  const int rows_per_block = 8;
-  fbank_cmn_pack_kernel<<<static_cast<int>((rows + rows_per_block - 1) / rows_per_block), rows_per_block * 32, 0,
-                          stream>>>(logmel_ws, mean_ws, meta, rows, f->n_mels, out, out_ld, plane_cols, planes);
-  count_launch(3);
+      f->n_mels, f->preemph, f->log_eps, halo, mode, logmel_ws, tile_sums_ws);
+  count_launch();
   SVB_CUDA_OK(cudaGetLastError());
-  return 0;
+  if (mode == 1) return 0;
+  fbank_mean_kernel<<<B, 128, 0, stream>>>(static_cast<const UttDesc*>(utt_tab), tile_sums_ws, f->n_mels, mean_ws);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream);
 }
 
 }  // namespace svb

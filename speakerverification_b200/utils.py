@@ -1,0 +1,145 @@
+"""Host-side mirror of the scoring and metric functions of the reference's ``src/utils.py``:
+``similarity_measure`` / ``cosine_similarity`` / ``ZT_norm_similarity`` (:126-169) run on libsvb
+kernels; the EER / minDCF metrics (:74-121, :221-275) are host fp64 like the reference.
+Batched entry points (``score_trials``) replace the per-trial Python loop of src/model.py:415-448."""
+import numpy as np
+import torch
+
+from . import _native as nv
+
+
+def _dev(t, device=None):
+    if isinstance(t, np.ndarray):
+        t = torch.from_numpy(np.ascontiguousarray(t))
+    t = t.to(dtype=torch.float32)
+    if not t.is_cuda:
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        t = t.to(device)
+    return t.contiguous()
+
+
+# ------------------------------------------------------------------ batched device scoring
+def cosine_trials(emb, idx_a, idx_b):
+    """emb [U, n, D] CUDA fp32; int32 index tensors -> [trials] fp32 (mean_i |cos(a_i, b_i)|)."""
+    U, n, D = emb.shape
+    out = torch.empty(idx_a.numel(), dtype=torch.float32, device=emb.device)
+    nv.check(nv.lib().svb_cosine_trials(nv.ptr(emb), n, D, nv.ptr(idx_a), nv.ptr(idx_b), idx_a.numel(), nv.ptr(out),
+                                        nv.stream_ptr()))
+    return out
+
+
+def mean_embeddings(emb, normalize):
+    U, n, D = emb.shape
+    out = torch.empty((U, D), dtype=torch.float32, device=emb.device)
+    nv.check(nv.lib().svb_mean_embeddings(nv.ptr(emb), U, n, D, int(normalize), nv.ptr(out), nv.stream_ptr()))
+    return out
+
+
+def asnorm_stats(emean, cohorts, top):
+    """Per-utterance (mu, sigma) of the `top` largest cohort scores; emean [U, D], cohorts [N, D]."""
+    U, D = emean.shape
+    N = cohorts.shape[0]
+    need = nv.lib().svb_asnorm_workspace_bytes(U, N, D)
+    ws = torch.empty(need, dtype=torch.uint8, device=emean.device)
+    mu = torch.empty(U, dtype=torch.float32, device=emean.device)
+    sg = torch.empty(U, dtype=torch.float32, device=emean.device)
+    nv.check(nv.lib().svb_asnorm_stats(nv.ptr(emean), U, nv.ptr(cohorts), N, D, int(top), nv.ptr(mu), nv.ptr(sg),
+                                       nv.ptr(ws), need, nv.stream_ptr()))
+    return mu, sg
+
+
+def asnorm_trials(emean, idx_a, idx_b, mu, sigma):
+    out = torch.empty(idx_a.numel(), dtype=torch.float32, device=emean.device)
+    nv.check(nv.lib().svb_asnorm_trials(nv.ptr(emean), emean.shape[1], nv.ptr(idx_a), nv.ptr(idx_b), idx_a.numel(),
+                                        nv.ptr(mu), nv.ptr(sigma), nv.ptr(out), nv.stream_ptr()))
+    return out
+
+
+def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200, normalize=True):
+    """All trials at once.  emb [U, n, D] (raw crop embeddings); returns a CUDA fp32 vector.
+    'cosine' = utils.cosine_similarity per trial; 'norm' = utils.ZT_norm_similarity(top)."""
+    if scoring_mode == "cosine":
+        return cosine_trials(emb, idx_a, idx_b)      # cosine is scale invariant: normalisation is a no-op
+    if scoring_mode == "norm":
+        if cohorts is None:
+            raise ValueError("scoring_mode='norm' needs a cohort bank")
+        em = mean_embeddings(emb, normalize)
+        mu, sg = asnorm_stats(em, _dev(cohorts, emb.device), top)
+        return asnorm_trials(em, idx_a, idx_b, mu, sg)
+    raise NotImplementedError("scoring_mode %r (only 'cosine' and 'norm' are on the hot path)" % (scoring_mode,))
+
+
+# ------------------------------------------------------------------ per-trial reference signatures
+def cosine_similarity(ref, com, **kwargs):
+    ref, com = _dev(ref), _dev(com, None)
+    emb = torch.stack([ref.view(-1, ref.shape[-1]), com.view(-1, com.shape[-1])])
+    i0 = torch.zeros(1, dtype=torch.int32, device=emb.device)
+    return float(cosine_trials(emb, i0, i0 + 1).item())
+
+
+def ZT_norm_similarity(ref, com, cohorts, top=-1):
+    ref, com = _dev(ref), _dev(com)
+    emb = torch.stack([ref.view(-1, ref.shape[-1]), com.view(-1, com.shape[-1])])
+    i0 = torch.zeros(1, dtype=torch.int32, device=emb.device)
+    em = mean_embeddings(emb, False)
+    mu, sg = asnorm_stats(em, _dev(cohorts, emb.device), top)
+    return float(asnorm_trials(em, i0, i0 + 1, mu, sg).item())
+
+
+def similarity_measure(method="cosine", ref=None, com=None, *args, **kwargs):
+    """Same dispatch as src/utils.py:126-132.  Unlike the reference, extra positionals are accepted,
+    so the call site src/model.py:434-438 (zt_norm with the cohort passed positionally) works."""
+    if method == "cosine":
+        return cosine_similarity(ref, com, **kwargs)
+    if method == "zt_norm":
+        return ZT_norm_similarity(ref, com, *args, **kwargs)
+    raise NotImplementedError("similarity method %r is not on the accelerated path" % (method,))
+
+
+# ------------------------------------------------------------------ metrics (host, fp64)
+def tuneThresholdfromScore(scores, labels, target_fa, target_fr=None):
+    """src/utils.py:74-121 (sklearn roc_curve / precision_recall_curve); same result dict."""
+    from sklearn import metrics
+    labels = np.nan_to_num(labels)
+    scores = np.nan_to_num(scores)
+    fpr, tpr, thresholds = metrics.roc_curve(labels, scores, pos_label=1)
+    gmean = np.sqrt(tpr * (1 - fpr))
+    idxG = int(np.argmax(gmean))
+    fnr = (1 - tpr) * 100
+    fpr = fpr * 100
+    tuned = []
+    if target_fr:
+        for tfr in target_fr:
+            idx = np.nanargmin(np.absolute(tfr - fnr))
+            tuned.append([thresholds[idx], fpr[idx], fnr[idx]])
+    for tfa in target_fa:
+        idx = np.nanargmin(np.absolute(tfa - fpr))
+        tuned.append([thresholds[idx], fpr[idx], fnr[idx]])
+    idxE = np.nanargmin(np.absolute(fnr - fpr))
+    eer = np.mean([fpr[idxE], fnr[idxE]])
+    precision, recall, thr_pr = metrics.precision_recall_curve(labels, scores, pos_label=1)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        fscore = (2 * precision * recall) / (precision + recall)
+    ix = int(np.nanargmax(fscore))
+    return {"gmean": [idxG, gmean[idxG], thresholds[idxG]],
+            "roc": [tuned, eer, metrics.auc(fpr, tpr), thresholds[idxE]],
+            "prec_recall": [precision, recall, fscore[ix], thr_pr[min(ix, len(thr_pr) - 1)]]}
+
+
+def ComputeErrorRates(scores, labels):
+    """src/utils.py:221-256 vectorised: (fnrs, fprs, thresholds) over ascending scores."""
+    scores = np.asarray(scores, dtype=np.float64)
+    labels = np.asarray(labels, dtype=np.float64)
+    order = np.argsort(scores, kind="stable")
+    lab = labels[order]
+    fnrs = np.cumsum(lab) / lab.sum()
+    fprs = 1 - np.cumsum(1 - lab) / (len(lab) - lab.sum())
+    return list(fnrs), list(fprs), list(scores[order])
+
+
+def ComputeMinDcf(fnrs, fprs, thresholds, p_target, c_miss, c_fa):
+    """src/utils.py:262-275."""
+    c_det = c_miss * np.asarray(fnrs) * p_target + c_fa * np.asarray(fprs) * (1 - p_target)
+    i = int(np.argmin(c_det))
+    return float(c_det[i] / min(c_miss * p_target, c_fa * (1 - p_target))), thresholds[i]

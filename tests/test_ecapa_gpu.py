@@ -106,7 +106,7 @@ def test_ecapa_stages_fp32(golden_c512):
 def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
     from oracle import ecapa_oracle as eo, synth
     from speakerverification_b200.engine import EcapaEngine
-    waves, _ = synth.utterance_set(4, 4, L + 1)
+    waves, _ = synth.utterance_set(16, 4, L + 1)
     sd, state = _state(CH1024, golden_c1024)
     eng = EcapaEngine(state, CH1024, 80, 192, _frontend(), precision="bf16")
     emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda()).cpu().numpy()
@@ -114,7 +114,9 @@ def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
     en = emb / np.linalg.norm(emb, axis=1, keepdims=True)
     rn = ref / np.linalg.norm(ref, axis=1, keepdims=True)
     assert (en * rn).sum(1).min() > 0.9995
-    assert np.abs(en @ en.T - rn @ rn.T).max() <= 3e-3
+    dev = np.abs(en @ en.T - rn @ rn.T).max()
+    print("C=1024 bf16: min cos", (en * rn).sum(1).min(), "max all-pairs score dev", dev)
+    assert dev <= 3e-3
     # ragged batch: every utterance keeps its own length (no padding), checked against the oracle
     lens = [16000, 48000, 23456, 40000]
     flat = torch.from_numpy(np.concatenate([waves[i, :n] for i, n in enumerate(lens)])).cuda()

@@ -1,0 +1,96 @@
+"""GPU parity of the scoring kernels (C ABI svb_cosine_trials / svb_asnorm_*) against the reference's
+own scores (tests/golden) and the numpy oracle."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _trials():
+    from oracle import synth
+    spk = np.repeat(np.arange(16), 4)
+    return synth.trial_list(spk, 1000)
+
+
+def test_cosine_trials_match_reference(golden_c512):
+    from speakerverification_b200 import utils as U
+    lab, ti, tj = _trials()
+    emb = torch.from_numpy(golden_c512["emb_list"]).cuda()
+    ia = torch.from_numpy(ti.astype(np.int32)).cuda()
+    ib = torch.from_numpy(tj.astype(np.int32)).cuda()
+    got = U.cosine_trials(emb, ia, ib).cpu().numpy()
+    assert np.abs(got - golden_c512["scores_cos"]).max() <= 1e-5
+    # per-trial signature of the reference (utils.similarity_measure)
+    s = U.similarity_measure("cosine", emb[ti[0]], emb[tj[0]])
+    assert abs(s - golden_c512["scores_cos"][0]) <= 1e-5
+
+
+@pytest.mark.parametrize("K", [200, 300])
+def test_asnorm_matches_reference(golden_c512, K):
+    from speakerverification_b200 import utils as U
+    lab, ti, tj = _trials()
+    emb = torch.from_numpy(golden_c512["emb_list"]).cuda()
+    ia = torch.from_numpy(ti.astype(np.int32)).cuda()
+    ib = torch.from_numpy(tj.astype(np.int32)).cuda()
+    got = U.score_trials(emb, ia, ib, "norm", golden_c512["cohort"], top=K, normalize=True).cpu().numpy()
+    ref = golden_c512["scores_asnorm%d" % K]
+    assert np.abs(got - ref).max() <= 1e-4, np.abs(got - ref).max()
+    # reference per-trial call with the cohort passed positionally (src/model.py:434-438)
+    en = torch.nn.functional.normalize(emb, dim=2)
+    s = U.similarity_measure("zt_norm", en[ti[3]], en[tj[3]], golden_c512["cohort"], top=K)
+    assert abs(s - ref[3]) <= 1e-4
+
+
+def test_asnorm_metrics_identical(golden_c512):
+    from oracle import scoring_oracle as so
+    from speakerverification_b200 import utils as U
+    lab, ti, tj = _trials()
+    emb = torch.from_numpy(golden_c512["emb_list"]).cuda()
+    ia = torch.from_numpy(ti.astype(np.int32)).cuda()
+    ib = torch.from_numpy(tj.astype(np.int32)).cuda()
+    for mode, name in (("cosine", "scores_cos"), ("norm", "scores_asnorm300")):
+        got = U.score_trials(emb, ia, ib, mode, golden_c512["cohort"], top=300).cpu().numpy()
+        res = U.tuneThresholdfromScore(got, lab, [1, 0.1])
+        fn, fp, th = U.ComputeErrorRates(got, lab)
+        dcf, _ = U.ComputeMinDcf(fn, fp, th, 0.05, 1, 1)
+        assert round(float(res["roc"][1]), 4) == round(float(golden_c512["eer/" + name]), 4)
+        assert round(dcf, 4) == round(float(golden_c512["mindcf/" + name]), 4)
+        assert round(so.eer_percent(got, lab)[0], 4) == round(float(golden_c512["eer/" + name]), 4)
+
+
+@pytest.mark.parametrize("U_,N,D,K", [(37, 300, 192, 300), (64, 1000, 192, -1), (130, 20000, 192, 300),
+                                      (5, 6000, 192, 300), (9, 257, 64, 1)])
+def test_topk_stats_vs_numpy(U_, N, D, K):
+    from speakerverification_b200 import utils as U
+    rng = np.random.default_rng(N + D)
+    e = rng.standard_normal((U_, D)).astype(np.float32)
+    e /= np.linalg.norm(e, axis=1, keepdims=True)
+    c = rng.standard_normal((N, D)).astype(np.float32)
+    c /= np.linalg.norm(c, axis=1, keepdims=True)
+    c[N // 2:N // 2 + 7] = c[0]                       # exact ties inside the cohort
+    mu, sg = U.asnorm_stats(torch.from_numpy(e).cuda(), torch.from_numpy(c).cuda(), K)
+    S = np.sort(np.inner(e.astype(np.float64), c.astype(np.float64)), axis=1)[:, ::-1]
+    S = S[:, :K] if K != -1 else S[:, :-1]
+    np.testing.assert_allclose(mu.cpu().numpy(), S.mean(1), atol=2e-6)
+    np.testing.assert_allclose(sg.cpu().numpy(), S.std(1), atol=2e-6)
+
+
+def test_scoring_sweep_properties():
+    """cfg5-style synthetic sweep at reduced size: symmetry and invariance properties that hold at any size."""
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    e, spk = synth.scoring_embeddings(4096, 100)
+    c, _ = synth.scoring_embeddings(2048, 64, seed=9)
+    emb = torch.from_numpy(e).cuda().unsqueeze(1)
+    rng = np.random.default_rng(0)
+    ia = torch.from_numpy(rng.integers(0, 4096, 20000).astype(np.int32)).cuda()
+    ib = torch.from_numpy(rng.integers(0, 4096, 20000).astype(np.int32)).cuda()
+    s_ab = U.score_trials(emb, ia, ib, "norm", c, top=300)
+    s_ba = U.score_trials(emb, ib, ia, "norm", c, top=300)
+    assert torch.equal(s_ab, s_ba)                                   # S-norm is symmetric
+    perm = torch.randperm(2048)
+    s_perm = U.score_trials(emb, ia, ib, "norm", c[perm.numpy()], top=300)
+    assert (s_ab - s_perm).abs().max().item() < 1e-4                 # cohort order is irrelevant
+    same = U.score_trials(emb, ia, ia, "cosine")
+    assert (same - 1).abs().max().item() < 1e-6
