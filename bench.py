@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Throughput bench for the B200 speaker-embedding hot path (contract: task statement / DESIGN.md).
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): ECAPA-TDNN C=1024, 80-mel fbank, 10 000 synthetic 3 s 16 kHz
+utterances per GPU, bf16 tensor-core operands.  One step = one pass of the hot path (waveform ->
+embedding) over all utterances.  `value` is device-timed with the waveforms resident in HBM; `e2e`
+goes through the public API (ModelHandling.embed_batches) from pinned HOST buffers with the H2D
+copies and the D2H read of the embeddings inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CH = [1024, 1024, 1024, 1024, 3072]
+N_OUT = 192
+L = 48000
+FLOP_PER_UTT = 11.29e9          # 37.50 MFLOP/frame x 301 frames (C=1024, 3 s crop)
+MFA_MAC_PER_FRAME = 9437184     # SURVEY.md 8a GEMM table, mfa row (3C x 3C)
+
+
+def model_args(device, precision):
+    return dict(device=device, gpu=int(os.environ.get("LOCAL_RANK", 0)), seed=0, save_folder="/tmp/svb_bench",
+                model={"name": "ECAPA_TDNN", "nOut": N_OUT}, channels=CH,
+                criterion={"name": "AAmSoftmaxAP", "margin": 0.2, "scale": 30}, nClasses=10,
+                classifier={"input_size": N_OUT, "out_neurons": 10},
+                optimizer={"name": "adam", "weight_decay": 2e-5, "lr_decay": 0.95}, lr=1e-3,
+                callbacks={"name": "steplr"}, step_size=10, features="melspectrogram", lib="torchaudio", n_mels=80,
+                n_mfcc=80, sr=16000, n_fft=512, win_length=400, hop_length=160,
+                audio_spec={"sample_rate": 16000, "channels": 1, "sentence_len": 3.0, "win_len": 0.025, "hop_len": 0.01},
+                dataloader_options={"nPerSpeaker": 2, "num_workers": 0, "batch_size": 4, "shuffle": False},
+                augment=False, augment_options={"augment_chain": []}, mixedprec=False, svb_precision=precision)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], d.get("bf16_tflops_sustained", d["bf16_tflops"]), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def synth_waves(n, device, seed):
+    """n distinct 3 s utterances: speaker-like harmonic signals (oracle/synth.py) mixed, shifted and scaled on the GPU."""
+    from oracle import synth
+    pool, _ = synth.utterance_set(8, 4, L)
+    pool = torch.from_numpy(pool).to(device)
+    g = torch.Generator(device=device).manual_seed(seed)
+    out = torch.empty((n, L), dtype=torch.float32, device=device)
+    for i0 in range(0, n, 1000):
+        m = min(1000, n - i0)
+        a = torch.randint(0, pool.shape[0], (m,), generator=g, device=device)
+        b = torch.randint(0, pool.shape[0], (m,), generator=g, device=device)
+        w = torch.rand((m, 1), generator=g, device=device)
+        gain = 0.2 + 0.8 * torch.rand((m, 1), generator=g, device=device)
+        x = w * pool[a] + (1 - w) * torch.roll(pool[b], 7919, dims=1)
+        out[i0:i0 + m] = gain * x + 0.01 * torch.randn((m, L), generator=g, device=device)
+    return out
+
+
+def cpu_reference_rate(n_utts, batch=16):
+    """Reference CPU path (oracle port of SpeakerEncoder.forward, fp32, all host threads): embeddings/s."""
+    from oracle import ecapa_oracle as eo, synth
+    torch.set_num_threads(os.cpu_count())
+    sd = synth.ecapa_state_dict(CH, N_OUT)
+    sd = {k: torch.as_tensor(v) for k, v in sd.items()}
+    rng = np.random.default_rng(0)
+    waves = (0.1 * rng.standard_normal((batch, L))).astype(np.float32)
+    eo.embed(waves, sd)                                  # warm-up
+    t0 = time.perf_counter()
+    done = 0
+    while done < n_utts:
+        eo.embed(waves, sd)
+        done += batch
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the Python reference tree
+    itself cannot travel to the GPU box), timed on the host cores."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    per_step = 32
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_rate(16)
+    t0 = time.perf_counter()
+    n = 0
+    for _ in range(args.steps):
+        _, done, _ = cpu_reference_rate(per_step)
+        n += done
+    dt = time.perf_counter() - t0
+    val = n / dt
+    print(json.dumps({
+        "impl": "reference", "metric": "ECAPA embeddings/sec (3 s utt)", "value": val, "unit": "embeddings/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ECAPA-TDNN C=1024, 80-mel fbank, 3 s 16 kHz utterances (configs[1])",
+                   "sample": "%d utterances per step, batch 16" % per_step},
+        "cpu_baseline": {"value": val, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
+                         "sample": "%d x 3 s utterances per step, batch 16, torch fp32 oracle port" % per_step},
+        "e2e": {"value": val, "unit": "embeddings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def gemm_roofline(device, batch_rows, halo=4):
+    """Times the dominant kernel (gemm_tc_kernel<256>) alone on the MFA shape of one encoder launch."""
+    from speakerverification_b200 import _native as nv
+    C3 = CH[4]
+    T = 1 + L // 160
+    M = batch_rows * (T + 2 * halo)
+    a = torch.randn((M, C3), device=device).to(torch.bfloat16)
+    w = torch.randn((C3, C3, 1), device=device) / C3 ** 0.5
+    wp = nv.pack_conv_weight(w, planes=1)
+    z = torch.zeros(C3, device=device)
+    o = torch.ones(C3, device=device)
+    out = torch.empty((M, C3), dtype=torch.bfloat16, device=device)
+    run = lambda: nv.tdnn_layer(a, wp, C3, C3, 1, 1, z, o, z, out, act=nv.ACT_GELU)
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    reps = 10
+    ev[0].record()
+    for _ in range(reps):
+        run()
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1]) / reps
+    flops = 2.0 * MFA_MAC_PER_FRAME * batch_rows * T       # algorithmic: valid frames only
+    return flops / (ms * 1e-3) / 1e12, ms
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="svb", choices=["svb", "reference"])
+    ap.add_argument("--utts", type=int, default=10000)
+    ap.add_argument("--batch-rows", type=int, default=256)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    from speakerverification_b200 import _native as nv
+    from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
+    from oracle import synth
+    margs = model_args("cuda", args.precision)
+    net = WrappedModel(SpeakerEncoder(**margs))
+    handle = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=args.batch_rows))
+    sd = net.module.state_dict()
+    for k, v in synth.ecapa_state_dict(CH, N_OUT).items():      # random-init weights of the named architecture
+        sd[k].copy_(torch.as_tensor(v))
+    net.eval()
+    eng = net.module.engine()
+
+    U = args.utts
+    waves = synth_waves(U, device, seed=100 + rank)
+    emb = torch.empty((U, N_OUT), dtype=torch.float32, device=device)
+    gathered = torch.empty((world * U, N_OUT), dtype=torch.float32, device=device) if world > 1 else None
+
+    def step():
+        for r0 in range(0, U, args.batch_rows):
+            eng.forward(waves[r0:r0 + args.batch_rows], out=emb[r0:r0 + args.batch_rows])
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, emb)          # the path's one exchange step
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    nv.lib().svb_reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(nv.lib().svb_launch_count())
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * U * args.steps / (ms * 1e-3)
+
+    # end to end through the public API from pinned host buffers
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((U, L), dtype=torch.float32).pin_memory()
+        host.copy_(waves)
+        torch.cuda.synchronize()
+        handle.embed_batches(host[:4 * args.batch_rows]).cpu()  # warm-up
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            out = handle.embed_batches(host).cpu()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * U * args.steps / dt, "unit": "embeddings/s", "h2d_bytes_per_step": U * L * 4,
+               "d2h_bytes_per_step": U * N_OUT * 4, "api": "ModelHandling.embed_batches(pinned host [U, L]) -> .cpu()"}
+        assert out.shape == (U, N_OUT) and bool(torch.isfinite(out).all())
+
+    if rank == 0:
+        hbm, tf_burst, tf_sust, src = peaks()
+        ach, gemm_ms = gemm_roofline(device, args.batch_rows)
+        line = {
+            "metric": "ECAPA embeddings/sec (3 s utt)", "value": value, "unit": "embeddings/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)", "data": "synthetic",
+            "config": {"workload": "ECAPA-TDNN C=1024 nOut=192, 80-mel fbank (16 kHz, n_fft 512, win 400, hop 160), "
+                                   "%d synthetic 3 s utterances per GPU (configs[1])" % U,
+                       "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
+                       "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * L * 4 / 1e9)},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"kernel": "gemm_tc_kernel<256> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
+                         "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
+                         "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
+            "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
+                            "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
+                            "note": "whole step, algorithmic 11.29 GFLOP per utterance vs sustained bf16 peak"},
+        }
+        if world == 1:
+            rate, n, dt = cpu_reference_rate(64)
+            line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
