@@ -318,6 +318,10 @@ static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, con
     p.add_src = add->p; p.add_ld = add->ld; p.add_planes = e->fp32_mode ? 2 : 1; p.add_plane_cols = add->plane_cols;
     p.out2 = out2; p.out2_ld = out2_ld; p.out2_plane_cols = out2_pc;
   }
+  const bool pointwise = L.k == 1 && store_mode == STORE_ALL && p.out_kind != OUT_F32 && add == nullptr && L.cout % 64 == 0 &&
+                         ((L.act == ACT_GELU && rowbias == nullptr && !post_tanh) ||
+                          (L.act == ACT_RELU && rowbias != nullptr && post_tanh));
+  if (pointwise) return launch_gemm_pw(ops, p, stream);
   const int bn = L.cout >= 256 ? 256 : (L.cout >= 128 ? 128 : 64);
   return launch_gemm(ops, p, bn, stream);
 }

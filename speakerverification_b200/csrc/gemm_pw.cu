@@ -1,0 +1,326 @@
+// Pointwise (k = 1) TDNN layers of ECAPA-TDNN -- tdnn1 / tdnn2 / mfa / asp.tdnn -- as a persistent
+// warp-specialised tcgen05 GEMM with a lean epilogue (reference: TDNNBlock = norm(activation(conv(x))),
+// src/models/ECAPA_TDNN.py:27-69; 92 % of the encoder's FLOPs are these layers).
+//
+//   out[r, n] = BN( act( sum_c A[r, c] * W[n, c] + bias[n] (+ rowbias[utt(r), n]) ) )  (+ tanh)
+//
+// Same mainloop as gemm_tc.cu (TMA -> 128B-swizzled smem ring -> tcgen05.mma, fp32 accumulators double
+// buffered in TMEM).  What differs is the epilogue, which was the bottleneck of the K=1024 layers
+// (profiles/r01_ncu_tdnn_v0.md: 41 instructions per output element, IPC 1.6, tensor pipe 32 % busy):
+//   * activation / output kind / row-bias are template parameters (no per-element runtime branches);
+//   * GELU(erf) is gelu_fast (11 FP32 + 2 MUFU, abs err 3.3e-7) instead of erff (~25 instructions);
+//   * results are packed to bf16 in registers, staged per warp in a 4 KB 128B-swizzled smem box and
+//     written with ONE TMA store per 32 x 64 block (coalesced, asynchronous) instead of 32 uncoalesced
+//     16-byte row stores per warp instruction.
+// Pointwise layers compute halo rows in place (the input halo rows mirror valid rows and the op is
+// per-row), so every row of a tile is stored and no mirror logic is needed.
+#include "svb_internal.h"
+#include "svb_ptx.cuh"
+
+namespace svb {
+
+static constexpr int BLOCK_M = 128;
+static constexpr int BLOCK_K = 64;
+static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
+static constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
+static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // one warp's 32 rows x 64 bf16 columns
+
+template <int BN>
+struct PwCfg {
+  static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int OUT_BYTES = 8 * OUT_BOX_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024;
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+struct PwParams {
+  int M, N;
+  int kc;                // 64-column K chunks per plane
+  int num_pass;          // 1: hi*hi ; 3: hi*hi + hi*lo + lo*hi
+  int a_plane_cols, a2_kc, w_planes;
+  const float* bias;
+  const float* scale;
+  const float* shift;
+  const float* rowbias;  // [utterances, rowbias_ld] (RBT instances only)
+  int rowbias_ld;
+  const RowMeta* row_meta;
+  int out_plane_cols;    // column offset of the lo plane in the output (HILO instances only)
+};
+
+__device__ __forceinline__ float tanh_exact(float x) {
+  // tanh(x) = 1 - 2 / (exp(2x) + 1); ex2/rcp approximations are ~1e-7 relative, far inside the fp32-mode budget
+  const float e = fast_ex2(x * 2.88539008178f);
+  return 1.0f - 2.0f * fast_rcp(e + 1.0f);
+}
+
+template <int BN, int ACT, bool RBT, bool HILO>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmOut,
+               const PwParams p) {
+  using Cfg = PwCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[STAGES];
+  __shared__ __align__(8) uint64_t tfull_bar[2];
+  __shared__ __align__(8) uint64_t tempty_bar[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t out_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+
+  const int num_m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  const int num_n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = num_m_tiles * num_n_tiles;
+  const int kc = p.kc;
+  const int num_kb = p.num_pass * kc;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmA2);
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmOut);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tfull_bar[a]), 1);
+      mbar_init(smem_u32(&tempty_bar[a]), 8);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(&tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / num_n_tiles) * BLOCK_M;
+        const int n0 = (tile % num_n_tiles) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int pass = kb / kc;
+          const int kcx = kb - pass * kc;
+          const int aplane = (pass == 2) ? 1 : 0;
+          const int wplane = (pass == 1) ? 1 : 0;
+          const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
+          const int w_col = (wplane * kc + kcx) * BLOCK_K;
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          tma_load_2d(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, fb, a_col, m0);
+          tma_load_2d(sa + A_STAGE_BYTES, &tmW, fb, w_col, n0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(smem_u32(&full_bar[stage]), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          umma_commit(smem_u32(&empty_bar[stage]));
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(smem_u32(&tfull_bar[acc]));
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================== epilogue: TMEM -> regs -> swizzled smem -> TMA store
+    const int ew = warp - 4;
+    const int quad = ew & 3;   // == warp % 4: the TMEM lane quadrant this warp may read
+    const int half = ew >> 2;  // column half of the tile
+    const uint32_t my_box = out_base + ew * OUT_BOX_BYTES;
+    const uint32_t my_row = my_box + lane * 128;
+    const int sw = lane & 7;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m0 = (tile / num_n_tiles) * BLOCK_M;
+      const int n0 = (tile % num_n_tiles) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      const float* rb = nullptr;
+      if (RBT) {
+        const long long row = m0 + quad * 32 + lane;
+        const int utt = (row < p.M) ? p.row_meta[row].utt : -1;
+        rb = p.rowbias + static_cast<long long>(utt < 0 ? 0 : utt) * p.rowbias_ld;
+      }
+      mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < BN / 128; ++c) {
+        const int col0 = half * (BN / 2) + c * 64;
+        const int n = n0 + col0;
+        if (n >= p.N) break;
+        uint32_t hi[32];
+        uint32_t lo[32];   // dead (eliminated) unless HILO
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + acc * BN + col0 + hh * 32 + (static_cast<uint32_t>(quad * 32) << 16), r);
+          tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n + hh * 32);
+          const float4* s4 = reinterpret_cast<const float4*>(p.scale + n + hh * 32);
+          const float4* h4 = reinterpret_cast<const float4*>(p.shift + n + hh * 32);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 b = __ldg(b4 + i), s = __ldg(s4 + i), h = __ldg(h4 + i);
+            float x0 = __uint_as_float(r[4 * i]) + b.x, x1 = __uint_as_float(r[4 * i + 1]) + b.y;
+            float x2 = __uint_as_float(r[4 * i + 2]) + b.z, x3 = __uint_as_float(r[4 * i + 3]) + b.w;
+            if (RBT) {
+              const float4 q = __ldg(reinterpret_cast<const float4*>(rb + n + hh * 32) + i);
+              x0 += q.x; x1 += q.y; x2 += q.z; x3 += q.w;
+            }
+            if (ACT == ACT_GELU) {
+              x0 = gelu_fast(x0); x1 = gelu_fast(x1); x2 = gelu_fast(x2); x3 = gelu_fast(x3);
+            } else if (ACT == ACT_RELU) {
+              x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f);
+            }
+            x0 = fmaf(x0, s.x, h.x); x1 = fmaf(x1, s.y, h.y);
+            x2 = fmaf(x2, s.z, h.z); x3 = fmaf(x3, s.w, h.w);
+            if (RBT) { x0 = tanh_exact(x0); x1 = tanh_exact(x1); x2 = tanh_exact(x2); x3 = tanh_exact(x3); }
+            const uint32_t p0 = pack_bf16x2(x0, x1), p1 = pack_bf16x2(x2, x3);
+            hi[hh * 16 + 2 * i] = p0;
+            hi[hh * 16 + 2 * i + 1] = p1;
+            if (HILO) {
+              lo[hh * 16 + 2 * i] = pack_bf16x2(x0 - bf16_lo_f(p0), x1 - bf16_hi_f(p0));
+              lo[hh * 16 + 2 * i + 1] = pack_bf16x2(x2 - bf16_lo_f(p1), x3 - bf16_hi_f(p1));
+            }
+          }
+        }
+        // stage the 32 x 64 block (row = lane, 128 bytes, 16-byte chunks XOR-swizzled by row & 7) and store it
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(hi[4 * j]),
+                       "r"(hi[4 * j + 1]), "r"(hi[4 * j + 2]), "r"(hi[4 * j + 3])
+                       : "memory");
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmOut, my_box, n, m0 + quad * 32);
+          bulk_commit();
+        }
+        if (HILO) {
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)),
+                         "r"(lo[4 * j]), "r"(lo[4 * j + 1]), "r"(lo[4 * j + 2]), "r"(lo[4 * j + 3])
+                         : "memory");
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmOut, my_box, p.out_plane_cols + n, m0 + quad * 32);
+            bulk_commit();
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+    }
+    if (lane == 0) bulk_wait<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ------------------------------------------------------------------ host side
+template <int BN, int ACT, bool RBT, bool HILO>
+static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& o,
+                       const PwParams& p, cudaStream_t stream) {
+  using Cfg = PwCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_pw_kernel<BN, ACT, RBT, HILO><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// Pointwise TDNN layer.  `g` carries the operand description shared with launch_gemm (taps must be 1,
+// store_mode STORE_ALL, bf16 output).  Supported: GELU layers with N % 256-tileable outputs (tdnn1/tdnn2/mfa)
+// and the ReLU + row-bias + tanh attention layer (asp.tdnn).
+int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t stream) {
+  SVB_CHECK(g.num_taps == 1 && g.tap_off[0] == 0 && g.store_mode == STORE_ALL, "launch_gemm_pw handles pointwise layers only");
+  SVB_CHECK(g.out_kind == OUT_BF16 || g.out_kind == OUT_BF16_HILO, "launch_gemm_pw writes bf16");
+  SVB_CHECK(g.N % 64 == 0 && g.out2 == nullptr, "launch_gemm_pw: N must be a multiple of 64 and there is no second output");
+  SVB_CHECK(g.num_pass == 1 || g.num_pass == 3, "num_pass must be 1 or 3");
+  const bool rbt = g.rowbias != nullptr;
+  SVB_CHECK(rbt == (g.post_tanh != 0), "row-bias and tanh come together (asp.tdnn)");
+  SVB_CHECK(!rbt || g.row_meta != nullptr, "row-bias needs row_meta");
+  const bool hilo = g.out_kind == OUT_BF16_HILO;
+  const int bn = (g.N >= 256 && !rbt) ? 256 : 128;
+  CUtensorMap ma, ma2, mw, mo;
+  if (make_map(&ma, ops.a, g.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
+  if (ops.a2 != nullptr) {
+    if (make_map(&ma2, ops.a2, g.M, ops.a2_cols, ops.lda2, BLOCK_M)) return -1;
+  } else {
+    ma2 = ma;
+  }
+  if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;
+  const long long out_cols = hilo ? static_cast<long long>(g.out_plane_cols) + g.N : g.N;
+  if (make_map(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;
+  PwParams p{};
+  p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
+  p.a2_kc = g.a2_kc; p.w_planes = g.w_planes; p.bias = g.bias; p.scale = g.scale; p.shift = g.shift;
+  p.rowbias = g.rowbias; p.rowbias_ld = g.rowbias_ld; p.row_meta = g.row_meta; p.out_plane_cols = g.out_plane_cols;
+  if (rbt) {
+    SVB_CHECK(g.act == ACT_RELU, "the row-bias instance is ReLU + BN + tanh");
+    return hilo ? launch_pw_t<128, ACT_RELU, true, true>(ma, ma2, mw, mo, p, stream)
+                : launch_pw_t<128, ACT_RELU, true, false>(ma, ma2, mw, mo, p, stream);
+  }
+  SVB_CHECK(g.act == ACT_GELU, "the plain pointwise instance is GELU + BN");
+  if (bn == 256)
+    return hilo ? launch_pw_t<256, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
+                : launch_pw_t<256, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
+  return hilo ? launch_pw_t<128, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
+              : launch_pw_t<128, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
+}
+
+}  // namespace svb

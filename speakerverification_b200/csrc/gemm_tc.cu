@@ -315,7 +315,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2D bf16 row-major matrix [rows, ld] exposing `cols` columns; box = [64 cols, box_rows], 128B swizzle.
-static int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   SVB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   SVB_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0,

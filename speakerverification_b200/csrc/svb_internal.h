@@ -74,7 +74,13 @@ struct GemmParams {
   void* out2; int out2_ld; int out2_plane_cols;
 };
 
+// 2D bf16 row-major matrix [rows, ld] exposing `cols` columns as a TMA map; box = [64 cols, box_rows], 128B swizzle.
+int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
+
 // Launches the persistent tcgen05 GEMM.  block_n in {64, 128, 256}.
 int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream);
+
+// Pointwise (k = 1, STORE_ALL, bf16 out) layers through the lean-epilogue kernel of gemm_pw.cu.
+int launch_gemm_pw(const GemmOperands& ops, const GemmParams& p, cudaStream_t stream);
 
 }  // namespace svb
