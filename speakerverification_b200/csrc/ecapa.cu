@@ -26,7 +26,8 @@ int small_linear(const float*, int, const float*, const float*, int, const float
                  float*, int, cudaStream_t);
 int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, const RowMeta*, long long, int, int, bf16*,
              int, int, cudaStream_t);
-int asp_pool(const float*, int, const bf16*, int, int, int, const void*, int, int, float, float*, int, cudaStream_t);
+int asp_fused(const bf16*, const bf16*, int, int, const bf16*, int, long long, const void*, int, int, const float*, int, float,
+              float*, int, cudaStream_t);
 int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
 
 enum { LIN_NONE = 0, LIN_RELU = 1, LIN_SIGMOID = 2 };
@@ -181,7 +182,8 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
                  const int* dilations, int fp32_mode, const char* const* names, const void* const* ptrs, int n,
                  Ecapa** out) {
   SVB_CHECK(C % 512 == 0, "channels must be a multiple of 512 (Res2Net chunks are tiled in 64-column K blocks); got %d", C);
-  SVB_CHECK(res2_scale == 8 && att % 64 == 0 && se_ch % 4 == 0 && n_mels <= MEL_PLANE, "unsupported ECAPA configuration");
+  SVB_CHECK(res2_scale == 8 && att == 128 && se_ch % 4 == 0 && n_mels <= MEL_PLANE,
+            "unsupported ECAPA configuration (attention_channels must be 128, res2net_scale 8)");
   TensorMap tm;
   for (int i = 0; i < n; ++i) tm[names[i]] = static_cast<const float*>(ptrs[i]);
   Ecapa* e = new Ecapa();
@@ -278,7 +280,6 @@ static Plan make_plan(const Ecapa* e, const Batch* b) {
   p.add("s1", M * P * e->Cs * 2);
   p.add("mfa", M * P * e->C3 * 2);
   p.add("att", M * P * e->att * 2);
-  p.add("logits", M * e->C3 * 4);
   p.add("se_mean", B * e->C * 4);
   p.add("se_hidden", B * e->se_ch * 4);
   p.add("se_gate", B * e->C * 4);
@@ -398,10 +399,9 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   View yv{Y, P * C3, C3, P * C3};
   if (run_layer(e, b, e->asp_tdnn, yv, nullptr, 0, H("att"), P * e->att, e->att, STORE_ALL, F("asp_rowbias"), e->att, 1, -1,
                 nullptr, nullptr, 0, 0, passes, stream)) return -1;
-  View av{H("att"), P * e->att, e->att, P * e->att};
-  if (run_layer(e, b, e->asp_conv, av, nullptr, 0, reinterpret_cast<bf16*>(F("logits")), C3, 0, STORE_ALL, nullptr, 0, 0,
-                OUT_F32, nullptr, nullptr, 0, 0, passes, stream)) return -1;
-  if (asp_pool(F("logits"), C3, Y, P * C3, P, C3, b->d_uttrows, B, C3, 1e-12f, F("pooled"), 2 * C3, stream)) return -1;
+  // asp.conv + softmax over time + weighted mean / std in one kernel (logits never reach HBM)
+  if (asp_fused(H("att"), Y, P * C3, C3, e->asp_conv.w, P, M, b->d_uttrows, B, C3, st, 2 * C3, 1e-12f, F("pooled"), 2 * C3,
+                stream)) return -1;
   // asp_bn + fc
   float* dst = l2norm ? F("emb_raw") : emb;
   const int dst_ld = l2norm ? e->n_out : emb_ld;
