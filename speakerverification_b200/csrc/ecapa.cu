@@ -3,6 +3,7 @@
 // checkpoint layout (fp32 device pointers keyed by state-dict name) and are repacked once.
 #include <string.h>
 
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
@@ -23,7 +24,8 @@ int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t)
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
 int small_linear(const float*, int, const float*, const float*, int, const float*, const float*, int, int, int, int,
-                 float*, int, cudaStream_t);
+                 float*, int, float*, cudaStream_t);
+size_t small_linear_ws_floats(int, int, int);
 int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, const RowMeta*, long long, int, int, bf16*,
              int, int, cudaStream_t);
 int asp_fused(const bf16*, const bf16*, int, int, const bf16*, int, long long, const void*, int, int, const float*, int, float,
@@ -287,6 +289,11 @@ static Plan make_plan(const Ecapa* e, const Batch* b) {
   p.add("asp_rowbias", B * e->att * 4);
   p.add("pooled", B * 2 * e->C3 * 4);
   p.add("emb_raw", B * e->n_out * 4);
+  size_t lp = small_linear_ws_floats(b->B, e->se_ch, e->C);
+  lp = std::max(lp, small_linear_ws_floats(b->B, e->C, e->se_ch));
+  lp = std::max(lp, small_linear_ws_floats(b->B, e->att, 2 * e->C3));
+  lp = std::max(lp, small_linear_ws_floats(b->B, e->n_out, 2 * e->C3));
+  p.add("lin_part", (lp + 4) * 4);
   return p;
 }
 
@@ -378,9 +385,9 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     // SE: time mean -> C->se->C gate -> gate * V + residual, written into the MFA concat buffer
     if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
     if (small_linear(e->se_w1[i], C, e->se_b1[i], F("se_mean"), C, nullptr, nullptr, B, e->se_ch, C, LIN_RELU,
-                     F("se_hidden"), e->se_ch, stream)) return -1;
+                     F("se_hidden"), e->se_ch, F("lin_part"), stream)) return -1;
     if (small_linear(e->se_w2[i], e->se_ch, e->se_b2[i], F("se_hidden"), e->se_ch, nullptr, nullptr, B, C, e->se_ch,
-                     LIN_SIGMOID, F("se_gate"), C, stream)) return -1;
+                     LIN_SIGMOID, F("se_gate"), C, F("lin_part"), stream)) return -1;
     bf16* o = XC + i * C;
     if (se_apply(V, P * C, C, cur.p, cur.ld, cur.plane_cols, F("se_gate"), C, b->d_meta, M, C, P, o, P * C3, C3, stream))
       return -1;
@@ -395,7 +402,7 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   float* st = F("asp_stats");
   if (col_stats(Y, P * C3, P, C3, b->d_uttrows, B, C3, 1, 1e-12f, st, st + C3, 2 * C3, stream)) return -1;
   if (small_linear(e->asp_w + C3, 3 * C3, nullptr, st, 2 * C3, nullptr, nullptr, B, e->att, 2 * C3, LIN_NONE,
-                   F("asp_rowbias"), e->att, stream)) return -1;
+                   F("asp_rowbias"), e->att, F("lin_part"), stream)) return -1;
   View yv{Y, P * C3, C3, P * C3};
   if (run_layer(e, b, e->asp_tdnn, yv, nullptr, 0, H("att"), P * e->att, e->att, STORE_ALL, F("asp_rowbias"), e->att, 1, -1,
                 nullptr, nullptr, 0, 0, passes, stream)) return -1;
@@ -406,7 +413,7 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   float* dst = l2norm ? F("emb_raw") : emb;
   const int dst_ld = l2norm ? e->n_out : emb_ld;
   if (small_linear(e->fc_w, 2 * C3, e->fc_b, F("pooled"), 2 * C3, e->aspbn_scale, e->aspbn_shift, B, e->n_out, 2 * C3,
-                   LIN_NONE, dst, dst_ld, stream)) return -1;
+                   LIN_NONE, dst, dst_ld, F("lin_part"), stream)) return -1;
   if (l2norm && l2norm_rows(dst, dst_ld, emb, emb_ld, B, e->n_out, 1e-12f, stream)) return -1;
   return 0;
 }

@@ -78,52 +78,89 @@ col_stats_kernel(const bf16* __restrict__ x, int ld, int planes, int plane_cols,
   }
 }
 
-// out[b, j] = act( sum_c W[j, c] * (in[b, c] * in_scale[c] + in_shift[c]) + bias[j] ), fp32.
-// grid (ceil(J/8), ceil(B/8)), block 256: warp -> output j, 8 utterances share each weight read.
+// out[b, j] = act( sum_c W[j, c] * (in[b, c] * in_scale[c] + in_shift[c]) + bias[j] ), fp32 SIMT.
+// The per-utterance dense layers (SE squeeze/excite, ASP context bias, asp_bn + fc head) are skinny:
+// B utterances x J outputs x K up to 6C.  64 x 64 output tiles, 4 x 4 per thread, K split across
+// gridDim.z so that ~148 CTAs are busy; partial sums are reduced in a FIXED order by a second tiny
+// kernel (no atomics: results are bit-reproducible run to run).
 enum { LIN_NONE = 0, LIN_RELU = 1, LIN_SIGMOID = 2 };
+static constexpr int SL_TILE = 64, SL_KSTEP = 32, SL_PAD = 68;
+
+__device__ __forceinline__ float lin_act(float v, int act) {
+  if (act == LIN_RELU) return fmaxf(v, 0.f);
+  if (act == LIN_SIGMOID) return 1.f / (1.f + expf(-v));
+  return v;
+}
+
 __global__ void __launch_bounds__(256)
-small_linear_kernel(const float* __restrict__ W, int w_ld, const float* __restrict__ bias, const float* __restrict__ in,
-                    int in_ld, const float* __restrict__ in_scale, const float* __restrict__ in_shift, int B, int J,
-                    int K, int act, float* __restrict__ out, int out_ld) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x * 8 + warp;
-  const int b0 = blockIdx.y * 8;
-  if (j >= J) return;
-  float acc[8];
+skinny_linear_kernel(const float* __restrict__ W, int w_ld, const float* __restrict__ bias, const float* __restrict__ in,
+                     int in_ld, const float* __restrict__ in_scale, const float* __restrict__ in_shift, int B, int J,
+                     int K, int slice, int act, float* __restrict__ out, int out_ld, float* __restrict__ part) {
+  __shared__ __align__(16) float As[SL_KSTEP][SL_PAD];
+  __shared__ __align__(16) float Ws[SL_KSTEP][SL_PAD];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int j0 = blockIdx.x * SL_TILE, b0 = blockIdx.y * SL_TILE;
+  const int k_begin = blockIdx.z * slice, k_end = min(K, k_begin + slice);
+  float acc[4][4];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  const float* wr = W + static_cast<long long>(j) * w_ld;
-  for (int c = lane * 4; c < K; c += 128) {
-    const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + c));
-    float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (in_scale != nullptr) {
-      sc = __ldg(reinterpret_cast<const float4*>(in_scale + c));
-      sh = __ldg(reinterpret_cast<const float4*>(in_shift + c));
-    }
+  for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (b0 + i < B) {
-        const float4 x4 = *reinterpret_cast<const float4*>(in + static_cast<long long>(b0 + i) * in_ld + c);
-        acc[i] = fmaf(w4.x, fmaf(x4.x, sc.x, sh.x), acc[i]);
-        acc[i] = fmaf(w4.y, fmaf(x4.y, sc.y, sh.y), acc[i]);
-        acc[i] = fmaf(w4.z, fmaf(x4.z, sc.z, sh.z), acc[i]);
-        acc[i] = fmaf(w4.w, fmaf(x4.w, sc.w, sh.w), acc[i]);
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int kk = k_begin; kk < k_end; kk += SL_KSTEP) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int idx = tid + i * 256;
+      const int row = idx >> 3, kq = (idx & 7) * 4, k = kk + kq;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), w = a;
+      if (k < k_end) {
+        if (b0 + row < B) {
+          a = *reinterpret_cast<const float4*>(in + static_cast<long long>(b0 + row) * in_ld + k);
+          if (in_scale != nullptr) {
+            const float4 sc = __ldg(reinterpret_cast<const float4*>(in_scale + k));
+            const float4 sh = __ldg(reinterpret_cast<const float4*>(in_shift + k));
+            a.x = fmaf(a.x, sc.x, sh.x); a.y = fmaf(a.y, sc.y, sh.y); a.z = fmaf(a.z, sc.z, sh.z); a.w = fmaf(a.w, sc.w, sh.w);
+          }
+        }
+        if (j0 + row < J) w = __ldg(reinterpret_cast<const float4*>(W + static_cast<long long>(j0 + row) * w_ld + k));
       }
+      As[kq][row] = a.x; As[kq + 1][row] = a.y; As[kq + 2][row] = a.z; As[kq + 3][row] = a.w;
+      Ws[kq][row] = w.x; Ws[kq + 1][row] = w.y; Ws[kq + 2][row] = w.z; Ws[kq + 3][row] = w.w;
     }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < SL_KSTEP; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 w = *reinterpret_cast<const float4*>(&Ws[k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+    }
+    __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = warp_sum(acc[i]);
-  if (lane == 0) {
-    const float bj = bias != nullptr ? bias[j] : 0.f;
+  for (int i = 0; i < 4; ++i) {
+    const int b = b0 + ty * 4 + i;
+    if (b >= B) continue;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
-      if (b0 + i < B) {
-        float v = acc[i] + bj;
-        if (act == LIN_RELU) v = fmaxf(v, 0.f);
-        else if (act == LIN_SIGMOID) v = 1.f / (1.f + expf(-v));
-        out[static_cast<long long>(b0 + i) * out_ld + j] = v;
-      }
+    for (int j = 0; j < 4; ++j) {
+      const int jj = j0 + tx * 4 + j;
+      if (jj >= J) continue;
+      if (part != nullptr) part[(static_cast<long long>(blockIdx.z) * B + b) * J + jj] = acc[i][j];
+      else out[static_cast<long long>(b) * out_ld + jj] = lin_act(acc[i][j] + (bias != nullptr ? bias[jj] : 0.f), act);
+    }
   }
+}
+
+__global__ void skinny_reduce_kernel(const float* __restrict__ part, int S, int B, int J, const float* __restrict__ bias,
+                                     int act, float* __restrict__ out, int out_ld) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * J) return;
+  const int b = i / J, j = i - b * J;
+  float v = 0.f;
+  for (int s = 0; s < S; ++s) v += part[static_cast<long long>(s) * B * J + i];
+  out[static_cast<long long>(b) * out_ld + j] = lin_act(v + (bias != nullptr ? bias[j] : 0.f), act);
 }
 
 // out[row, c] = gate[utt, c] * x[row, c] + resid[row, c] over every row of an utterance (halo rows too).
@@ -240,12 +277,33 @@ int col_stats(const bf16* x, int ld, int planes, int plane_cols, const void* utt
   return 0;
 }
 
+// part_ws: scratch for the split-K partial sums, at least small_linear_ws_floats(B, J, K) floats
+static int sl_splits(int K, int* slice_out) {
+  int slice = (K / 16 + SL_KSTEP - 1) / SL_KSTEP * SL_KSTEP;
+  if (slice < 128) slice = 128;
+  if (slice_out) *slice_out = slice;
+  return (K + slice - 1) / slice;
+}
+size_t small_linear_ws_floats(int B, int J, int K) {
+  const int S = sl_splits(K, nullptr);
+  return S > 1 ? static_cast<size_t>(S) * B * J : 0;
+}
+
 int small_linear(const float* W, int w_ld, const float* bias, const float* in, int in_ld, const float* in_scale,
-                 const float* in_shift, int B, int J, int K, int act, float* out, int out_ld, cudaStream_t stream) {
+                 const float* in_shift, int B, int J, int K, int act, float* out, int out_ld, float* part_ws,
+                 cudaStream_t stream) {
   SVB_CHECK(K % 4 == 0 && in_ld % 4 == 0 && w_ld % 4 == 0, "small_linear needs 16-byte aligned rows");
-  dim3 grid((J + 7) / 8, (B + 7) / 8);
-  small_linear_kernel<<<grid, 256, 0, stream>>>(W, w_ld, bias, in, in_ld, in_scale, in_shift, B, J, K, act, out, out_ld);
+  int slice = 0;
+  const int S = sl_splits(K, &slice);
+  SVB_CHECK(S == 1 || part_ws != nullptr, "small_linear: split-K scratch missing");
+  dim3 grid((J + SL_TILE - 1) / SL_TILE, (B + SL_TILE - 1) / SL_TILE, S);
+  skinny_linear_kernel<<<grid, 256, 0, stream>>>(W, w_ld, bias, in, in_ld, in_scale, in_shift, B, J, K, slice, act, out,
+                                                 out_ld, S > 1 ? part_ws : nullptr);
   count_launch();
+  if (S > 1) {
+    skinny_reduce_kernel<<<(B * J + 255) / 256, 256, 0, stream>>>(part_ws, S, B, J, bias, act, out, out_ld);
+    count_launch();
+  }
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -3,7 +3,7 @@ import csv, sys, re, collections
 rows = [r for r in csv.DictReader(l for l in open(sys.argv[1]) if l.startswith('"'))]
 names = [r["Kernel Name"] for r in rows]
 last = max(i for i, n in enumerate(names) if "fbank_logmel_kernel" in n)
-end = max(i for i, n in enumerate(names) if "small_linear_kernel" in n or "l2norm" in n) + 1
+end = max(i for i, n in enumerate(names) if "skinny" in n or "small_linear_kernel" in n or "l2norm" in n) + 1
 agg = collections.OrderedDict()
 seq = []
 for r in rows[last:end]:
