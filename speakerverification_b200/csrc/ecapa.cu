@@ -31,6 +31,10 @@ int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, co
 int asp_fused(const bf16*, const bf16*, int, int, const bf16*, int, long long, const void*, int, int, const float*, int, float,
               float*, int, cudaStream_t);
 int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
+size_t res2net_scratch_bytes(int, int);
+int res2net_seg_frames();
+int res2net_chain(const bf16*, bf16*, int, int, long long, const bf16* const*, const float* const*, const float* const*,
+                  const float* const*, int, int, const void*, int, const void*, void*, cudaStream_t);
 
 enum { LIN_NONE = 0, LIN_RELU = 1, LIN_SIGMOID = 2 };
 static constexpr int FRAMES_PER_TILE = 32;
@@ -39,9 +43,11 @@ static constexpr int MEL_PLANE = 128;  // n_mels padded to two 64-column K chunk
 // ------------------------------------------------------------------ batch plan
 struct UttDesc { long long wav_off; int nsamp; int T; long long row_base; int tile_base; int ntiles; };
 struct UttRows { long long row0; int T; int pad; };
+struct SegItem { int utt, seg; };
 
 struct Batch {
-  int B = 0, halo = 0, ntiles = 0, hop = 0;
+  int B = 0, halo = 0, ntiles = 0, hop = 0, nsegs = 0;
+  SegItem* d_segs = nullptr;
   long long rows = 0, frames = 0;
   RowMeta* d_meta = nullptr;
   UttDesc* d_utt = nullptr;
@@ -55,6 +61,8 @@ int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, 
   std::vector<UttRows> ur(B);
   std::vector<int2> tiles;
   std::vector<RowMeta> meta;
+  std::vector<SegItem> segs;
+  const int seg_frames = res2net_seg_frames();
   long long row = 0, frames = 0;
   for (int b = 0; b < B; ++b) {
     const int L = nsamp_host[b];
@@ -64,6 +72,7 @@ int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, 
     utt[b] = UttDesc{wav_off_host[b], L, T, row, static_cast<int>(tiles.size()), (T + FRAMES_PER_TILE - 1) / FRAMES_PER_TILE};
     ur[b] = UttRows{row + halo, T, 0};
     for (int t0 = 0; t0 < T; t0 += FRAMES_PER_TILE) tiles.push_back(make_int2(b, t0));
+    for (int sg = 0; sg * seg_frames < T; ++sg) segs.push_back(SegItem{b, sg});
     for (int t = -halo; t < T + halo; ++t) meta.push_back(RowMeta{b, t, T, 0});
     row += T + 2 * halo;
     frames += T;
@@ -80,6 +89,8 @@ int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, 
   bad |= up(reinterpret_cast<void**>(&bt->d_utt), utt.data(), utt.size() * sizeof(UttDesc));
   bad |= up(reinterpret_cast<void**>(&bt->d_tiles), tiles.data(), tiles.size() * sizeof(int2));
   bad |= up(reinterpret_cast<void**>(&bt->d_uttrows), ur.data(), ur.size() * sizeof(UttRows));
+  bad |= up(reinterpret_cast<void**>(&bt->d_segs), segs.data(), segs.size() * sizeof(SegItem));
+  bt->nsegs = static_cast<int>(segs.size());
   if (bad) { set_error("batch table upload failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
   *out = bt;
   return 0;
@@ -87,7 +98,7 @@ int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, 
 
 void batch_destroy(Batch* b) {
   if (b == nullptr) return;
-  cudaFree(b->d_meta); cudaFree(b->d_utt); cudaFree(b->d_tiles); cudaFree(b->d_uttrows);
+  cudaFree(b->d_meta); cudaFree(b->d_utt); cudaFree(b->d_tiles); cudaFree(b->d_uttrows); cudaFree(b->d_segs);
   delete b;
 }
 long long batch_rows(const Batch* b) { return b->rows; }
@@ -280,6 +291,7 @@ static Plan make_plan(const Ecapa* e, const Batch* b) {
   p.add("v", M * P * e->C * 2);
   p.add("s0", M * P * e->Cs * 2);
   p.add("s1", M * P * e->Cs * 2);
+  p.add("chain_scratch", res2net_scratch_bytes(e->Cs, static_cast<int>(P)));
   p.add("mfa", M * P * e->C3 * 2);
   p.add("att", M * P * e->att * 2);
   p.add("se_mean", B * e->C * 4);
@@ -372,7 +384,14 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     if (run_layer(e, b, e->tdnn1[i], cur, nullptr, 0, U, P * C, C, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0,
                   passes, stream)) return -1;
     // Res2Net chain: y_j = TDNN_j(x_j + y_{j-1}); chunk 0 passes through (read straight from U by tdnn2)
-    for (int j = 1; j < 8; ++j) {
+    const bool fused_chain = e->ks[i + 1] == 3 && e->dil[i + 1] <= 4 && (Cs == 64 || Cs == 128);
+    if (fused_chain) {
+      const bf16* w[7]; const float *bs[7], *sc[7], *sh[7];
+      for (int j = 0; j < 7; ++j) { w[j] = e->res[i][j].w; bs[j] = e->res[i][j].bias; sc[j] = e->res[i][j].scale; sh[j] = e->res[i][j].shift; }
+      if (res2net_chain(U, R, C, P, M, w, bs, sc, sh, e->dil[i + 1], b->halo, b->d_segs, b->nsegs, b->d_uttrows,
+                        base + pl.off("chain_scratch"), stream)) return -1;
+    }
+    for (int j = 1; j < 8 && !fused_chain; ++j) {
       View xin = (j == 1) ? View{U + Cs, P * C, C, P * C - Cs} : View{S[(j - 1) & 1], P * Cs, Cs, P * Cs};
       View add{U + (j + 1) * Cs, P * C, C, 0};
       if (run_layer(e, b, e->res[i][j - 1], xin, nullptr, 0, R + j * Cs, P * C, C, STORE_MIRROR, nullptr, 0, 0, -1,

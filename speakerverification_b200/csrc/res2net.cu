@@ -1,0 +1,352 @@
+// Res2NetBlock (reference: src/models/ECAPA_TDNN.py:72-129) as ONE persistent kernel per SE-Res2Net
+// block instead of 7 dependent GEMM launches:
+//
+//   y_1 = f_1(x_1),  y_j = f_j(x_j + y_{j-1})  (j = 2..7),   f_j = BN(ReLU(conv1d_k3_dilated_reflect(.)))
+//
+// where x_j is channel chunk j (Cs = C/8 channels) of the tdnn1 output U and y_j goes to chunk j of R.
+// The 7 steps are strictly sequential and each needs +-d frames of its input, so a launch per step is
+// latency bound (49 us each, 159 TFLOP/s; profiles/r01_launches_forward_b256_bf16_v0.txt).  Here one CTA
+// owns a window of 384 consecutive rows (a whole 3 s utterance with its reflect halos, or a 320-frame
+// segment of a long utterance plus 7*d recomputed context frames per side) and walks the whole chain:
+//
+//   * step input (x_j + y_{j-1}) lives in a CTA-private scratch strip (2 x 392 rows, L2 resident);
+//     the three dilated taps are row-shifted TMA loads of that strip (im2col-free, as in gemm_tc.cu);
+//   * per K block the producer loads ONE weight tile and the three 128-row A tiles, the MMA thread
+//     issues tcgen05.mma into three TMEM accumulators (3 x Cs columns), so weights cross L2 once per step;
+//   * the epilogue applies bias/ReLU/BN in fp32, writes y_j to R (valid frames + mirrored reflect halo
+//     rows) and x_{j+1} + y_j to the other scratch strip, fences the generic-proxy stores towards the
+//     async proxy (fence.proxy.async.global) and releases the producer for the next step.
+// Rows of the window that belong to no valid context (beyond 7*d of a segment edge, or neighbouring
+// utterances) carry garbage that never reaches a stored output: a conv output row depends only on its
+// own three input rows.
+#include "svb_internal.h"
+#include "svb_ptx.cuh"
+
+namespace svb {
+
+struct UttRows { long long row0; int T; int pad; };
+
+static constexpr int RC_THREADS = 384;     // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
+static constexpr int RC_MT = 3;            // 128-row M tiles per window
+static constexpr int RC_WIN = RC_MT * 128; // rows per window
+static constexpr int RC_GUARD = 4;         // scratch guard rows before / after the window (>= max dilation)
+static constexpr int RC_STRIP = RC_WIN + 2 * RC_GUARD;
+static constexpr int RC_SEG = 320;         // output frames per segment (RC_SEG + 14 * d <= RC_WIN for d <= 4)
+static constexpr int RC_STEPS = 7;
+static constexpr int RC_STAGES = 3;
+static constexpr int RC_A_BYTES = 128 * 64 * 2;
+
+struct alignas(64) ChainMaps {
+  CUtensorMap u;            // tdnn1 output U [rows, P*C], box [64, 128]
+  CUtensorMap s;            // scratch strips [grid*2*RC_STRIP, P*Cs], box [64, 128]
+  CUtensorMap w[RC_STEPS];  // packed weights [Cs, 3*P*Cs], box [64, Cs]
+};
+
+struct SegItem { int utt, seg; };
+
+struct ChainParams {
+  long long M;
+  int n_items;
+  const SegItem* items;
+  const UttRows* utts;
+  int C, P, dil, halo;
+  const bf16* U; int u_ld;
+  bf16* R; int r_ld;
+  bf16* S; int s_ld;        // scratch base, row stride
+  const float* bias[RC_STEPS];
+  const float* scale[RC_STEPS];
+  const float* shift[RC_STEPS];
+};
+
+// 32 fp32 values -> bf16 hi (and lo) planes of one row
+template <bool SPLIT>
+__device__ __forceinline__ void store_row32(bf16* dst, int plane_cols, const float (&v)[32]) {
+  uint32_t hi[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) hi[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+  uint4* d = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) d[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
+  if (SPLIT) {
+    uint32_t lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) lo[i] = pack_bf16x2(v[2 * i] - bf16_lo_f(hi[i]), v[2 * i + 1] - bf16_hi_f(hi[i]));
+    uint4* dl = reinterpret_cast<uint4*>(dst + plane_cols);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dl[i] = make_uint4(lo[4 * i], lo[4 * i + 1], lo[4 * i + 2], lo[4 * i + 3]);
+  }
+}
+
+template <bool SPLIT>
+__device__ __forceinline__ void add_row32(const bf16* src, int plane_cols, float (&v)[32]) {
+#pragma unroll
+  for (int pl = 0; pl < (SPLIT ? 2 : 1); ++pl) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src + pl * plane_cols);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 u = __ldg(s4 + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        v[8 * i + 2 * q] += bf16_lo_f(w[q]);
+        v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
+      }
+    }
+  }
+}
+
+template <int CS, bool SPLIT>
+__global__ void __launch_bounds__(RC_THREADS, 1)
+res2net_chain_kernel(const __grid_constant__ ChainMaps tm, const ChainParams p) {
+  constexpr int P = SPLIT ? 2 : 1;
+  constexpr int KC = CS / 64;
+  constexpr int W_BYTES = CS * 128;
+  constexpr int STAGE_STRIDE = 3 * RC_A_BYTES + 16384;
+  constexpr int STAGE_BYTES = 3 * RC_A_BYTES + W_BYTES;
+  constexpr int NPASS = SPLIT ? 3 : 1;
+  constexpr int NKB = 3 * NPASS * KC;
+  constexpr int TMEM_COLS = (3 * CS > 256) ? 512 : 256;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[RC_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[RC_STAGES];
+  __shared__ __align__(8) uint64_t tfull_bar, tempty_bar, sready_bar;
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int d = p.dil, H = p.halo;
+  const int strip0 = blockIdx.x * 2 * RC_STRIP;   // first scratch row of this CTA (strip b at + b * RC_STRIP)
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm.u);
+    tma_prefetch_desc(&tm.s);
+    for (int j = 0; j < RC_STEPS; ++j) tma_prefetch_desc(&tm.w[j]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < RC_STAGES; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    mbar_init(smem_u32(&tfull_bar), 1);
+    mbar_init(smem_u32(&tempty_bar), 8);
+    mbar_init(smem_u32(&sready_bar), 8);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, nwait = 0;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        const SegItem it = p.items[item];
+        const UttRows u = p.utts[it.utt];
+        const int s0 = it.seg * RC_SEG;
+        const int tw0 = max(s0 - RC_STEPS * d, -H);
+        const int g0 = static_cast<int>(u.row0) + tw0;
+        for (int j = 1; j <= RC_STEPS; ++j) {
+          if (j >= 2) { mbar_wait(smem_u32(&sready_bar), nwait & 1u); ++nwait; }
+          const int arow = (j == 1) ? g0 : strip0 + (j & 1) * RC_STRIP + RC_GUARD;
+          const int acol0 = (j == 1) ? CS : 0;
+          const int aplane_cols = (j == 1) ? p.C : CS;
+          const CUtensorMap* am = (j == 1) ? &tm.u : &tm.s;
+          for (int kb = 0; kb < NKB; ++kb) {
+            const int tap = kb / (NPASS * KC);
+            const int rem = kb - tap * (NPASS * KC);
+            const int pass = rem / KC;
+            const int kcx = rem - pass * KC;
+            const int aplane = (pass == 2) ? 1 : 0;
+            const int wplane = (pass == 1) ? 1 : 0;
+            const int off = (tap - 1) * d;
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+            mbar_arrive_expect_tx(fb, STAGE_BYTES);
+            const uint32_t sa = smem_base + stage * STAGE_STRIDE;
+            tma_load_2d(sa + 3 * RC_A_BYTES, &tm.w[j - 1], fb, ((tap * P + wplane) * KC + kcx) * 64, 0);
+#pragma unroll
+            for (int mt = 0; mt < RC_MT; ++mt)
+              tma_load_2d(sa + mt * RC_A_BYTES, am, fb, aplane * aplane_cols + acol0 + kcx * 64, arow + mt * 128 + off);
+            if (++stage == RC_STAGES) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, CS);
+      int stage = 0;
+      uint32_t phase = 0, nstep = 0;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
+          mbar_wait(smem_u32(&tempty_bar), (nstep & 1u) ^ 1u);
+          tc_fence_after();
+          for (int kb = 0; kb < NKB; ++kb) {
+            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            tc_fence_after();
+            const uint32_t sa = smem_base + stage * STAGE_STRIDE;
+            const uint64_t bdesc = umma_desc_sw128(sa + 3 * RC_A_BYTES);
+#pragma unroll
+            for (int mt = 0; mt < RC_MT; ++mt) {
+              const uint64_t adesc = umma_desc_sw128(sa + mt * RC_A_BYTES);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(tmem_base + mt * CS, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            }
+            umma_commit(smem_u32(&empty_bar[stage]));
+            if (++stage == RC_STAGES) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit(smem_u32(&tfull_bar));
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================== epilogue
+    constexpr int NCOLH = CS / 2;          // columns per warp (two column halves)
+    const int ew = warp - 4;
+    const int quad = ew & 3;               // == warp % 4: TMEM lane quadrant
+    const int half = ew >> 2;
+    const uint32_t lane_sel = static_cast<uint32_t>(quad * 32) << 16;
+    uint32_t nstep = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const SegItem it = p.items[item];
+      const UttRows u = p.utts[it.utt];
+      const int T = u.T;
+      const int s0 = it.seg * RC_SEG;
+      const int e0 = min(T, s0 + RC_SEG);
+      const int tw0 = max(s0 - RC_STEPS * d, -H);
+      const long long g0 = u.row0 + tw0;
+      // per M tile: local row, targets in the scratch strip (own row unless it is a reflect-halo row, plus the
+      // halo rows this frame mirrors into) and whether this frame is an output frame of the segment
+      int lrow[RC_MT], mir_lo[RC_MT], mir_hi[RC_MT];
+      bool own_s[RC_MT], out_r[RC_MT], xok[RC_MT];
+#pragma unroll
+      for (int mt = 0; mt < RC_MT; ++mt) {
+        const int l = mt * 128 + quad * 32 + lane;
+        const int t = tw0 + l;
+        const bool in_utt = t >= 0 && t < T;
+        const bool halo_row = (t >= -H && t < 0) || (t >= T && t < T + H);
+        lrow[mt] = l;
+        own_s[mt] = !halo_row;
+        out_r[mt] = in_utt && t >= s0 && t < e0;
+        mir_lo[mt] = (in_utt && t >= 1 && t <= H && l - 2 * t >= 0) ? l - 2 * t : -1;
+        const int ee = T - 1 - t;
+        mir_hi[mt] = (in_utt && ee >= 1 && ee <= H && l + 2 * ee < RC_WIN) ? l + 2 * ee : -1;
+        xok[mt] = (g0 + l >= 0) && (g0 + l < p.M);
+      }
+      for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
+        const float* bias = p.bias[j - 1];
+        const float* scale = p.scale[j - 1];
+        const float* shift = p.shift[j - 1];
+        bf16* sdst = p.S + static_cast<long long>(strip0 + ((j + 1) & 1) * RC_STRIP + RC_GUARD) * p.s_ld;
+        mbar_wait(smem_u32(&tfull_bar), nstep & 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int mt = 0; mt < RC_MT; ++mt) {
+#pragma unroll 1
+          for (int g = 0; g < NCOLH / 32; ++g) {
+            const int col = half * NCOLH + g * 32;
+            uint32_t r[32];
+            tmem_ld32(tmem_base + mt * CS + col + lane_sel, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+              const float4 s = __ldg(reinterpret_cast<const float4*>(scale + col) + i);
+              const float4 h = __ldg(reinterpret_cast<const float4*>(shift + col) + i);
+              v[4 * i] = fmaf(fmaxf(__uint_as_float(r[4 * i]) + b.x, 0.f), s.x, h.x);
+              v[4 * i + 1] = fmaf(fmaxf(__uint_as_float(r[4 * i + 1]) + b.y, 0.f), s.y, h.y);
+              v[4 * i + 2] = fmaf(fmaxf(__uint_as_float(r[4 * i + 2]) + b.z, 0.f), s.z, h.z);
+              v[4 * i + 3] = fmaf(fmaxf(__uint_as_float(r[4 * i + 3]) + b.w, 0.f), s.w, h.w);
+            }
+            const long long grow = g0 + lrow[mt];
+            if (out_r[mt]) {
+              bf16* rd = p.R + grow * p.r_ld + j * CS + col;
+              store_row32<SPLIT>(rd, p.C, v);
+              if (mir_lo[mt] >= 0) store_row32<SPLIT>(rd + static_cast<long long>(mir_lo[mt] - lrow[mt]) * p.r_ld, p.C, v);
+              if (mir_hi[mt] >= 0) store_row32<SPLIT>(rd + static_cast<long long>(mir_hi[mt] - lrow[mt]) * p.r_ld, p.C, v);
+            }
+            if (j < RC_STEPS) {
+              if (xok[mt]) add_row32<SPLIT>(p.U + grow * p.u_ld + (j + 1) * CS + col, p.C, v);
+              if (own_s[mt]) store_row32<SPLIT>(sdst + static_cast<long long>(lrow[mt]) * p.s_ld + col, CS, v);
+              if (mir_lo[mt] >= 0) store_row32<SPLIT>(sdst + static_cast<long long>(mir_lo[mt]) * p.s_ld + col, CS, v);
+              if (mir_hi[mt] >= 0) store_row32<SPLIT>(sdst + static_cast<long long>(mir_hi[mt]) * p.s_ld + col, CS, v);
+            }
+          }
+        }
+        tc_fence_before();
+        if (j < RC_STEPS) {
+          __threadfence();                                              // strip stores performed at GPU scope (L2) ...
+          asm volatile("fence.proxy.async.global;" ::: "memory");       // ... and ordered before the async-proxy (TMA) reads
+        }
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&tempty_bar));
+          if (j < RC_STEPS) mbar_arrive(smem_u32(&sready_bar));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------ host side
+size_t res2net_scratch_bytes(int Cs, int planes) {
+  return static_cast<size_t>(num_sms()) * 2 * RC_STRIP * planes * Cs * sizeof(bf16);
+}
+int res2net_seg_frames() { return RC_SEG; }
+
+template <int CS, bool SPLIT>
+static int launch_chain(const ChainMaps& tm, const ChainParams& p, cudaStream_t stream) {
+  constexpr int SMEM = RC_STAGES * (3 * RC_A_BYTES + 16384) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SVB_CUDA_OK(cudaFuncSetAttribute(res2net_chain_kernel<CS, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_set = true;
+  }
+  const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
+  res2net_chain_kernel<CS, SPLIT><<<grid, RC_THREADS, SMEM, stream>>>(tm, p);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// U, R: [rows, planes*C] bf16 (hi | lo at +C).  w[j] packed [Cs, 3*planes*Cs]; items: device table of (utt, segment)
+// with segments of res2net_seg_frames() frames; scratch: res2net_scratch_bytes(Cs, planes) bytes.
+int res2net_chain(const bf16* U, bf16* R, int C, int planes, long long rows, const bf16* const* w, const float* const* bias,
+                  const float* const* scale, const float* const* shift, int dil, int halo, const void* items, int n_items,
+                  const void* utts, void* scratch, cudaStream_t stream) {
+  const int Cs = C / 8;
+  SVB_CHECK(Cs == 64 || Cs == 128, "the fused Res2Net chain supports C = 512 or 1024 (Res2Net chunks of 64 / 128 channels)");
+  SVB_CHECK(dil >= 1 && dil <= RC_GUARD && halo >= dil && RC_SEG + 2 * RC_STEPS * dil <= RC_WIN, "unsupported dilation %d", dil);
+  ChainMaps tm;
+  if (make_map(&tm.u, U, rows, static_cast<long long>(planes) * C, static_cast<long long>(planes) * C, 128)) return -1;
+  const long long srows = static_cast<long long>(num_sms()) * 2 * RC_STRIP;
+  if (make_map(&tm.s, scratch, srows, planes * Cs, planes * Cs, 128)) return -1;
+  for (int j = 0; j < RC_STEPS; ++j)
+    if (make_map(&tm.w[j], w[j], Cs, 3 * planes * Cs, 3 * planes * Cs, Cs)) return -1;
+  ChainParams p{};
+  p.M = rows; p.n_items = n_items; p.items = static_cast<const SegItem*>(items);
+  p.utts = static_cast<const UttRows*>(utts);
+  p.C = C; p.P = planes; p.dil = dil; p.halo = halo;
+  p.U = U; p.u_ld = planes * C; p.R = R; p.r_ld = planes * C;
+  p.S = static_cast<bf16*>(scratch); p.s_ld = planes * Cs;
+  for (int j = 0; j < RC_STEPS; ++j) { p.bias[j] = bias[j]; p.scale[j] = scale[j]; p.shift[j] = shift[j]; }
+  if (Cs == 128) return planes == 2 ? launch_chain<128, true>(tm, p, stream) : launch_chain<128, false>(tm, p, stream);
+  return planes == 2 ? launch_chain<64, true>(tm, p, stream) : launch_chain<64, false>(tm, p, stream);
+}
+
+}  // namespace svb
