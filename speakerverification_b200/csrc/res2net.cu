@@ -303,6 +303,265 @@ res2net_chain_kernel(const __grid_constant__ ChainMaps tm, const ChainParams p) 
   if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
+// ------------------------------------------------------------------ shared-memory resident variant (1 plane)
+// bf16 mode: the step input never leaves the SM.  The activation strip (400 rows x Cs channels, K-major,
+// 128B swizzle, one plane per 64-channel K chunk) stays in shared memory for the whole chain; the epilogue
+// writes x_{j+1} + y_j straight into it in the UMMA operand layout and the three dilated taps are the SAME
+// strip read through descriptors whose start address is shifted by +-d rows (d * 128 bytes).  A hardware
+// probe (tools/desc_shift_test.cu, profiles/r01_desc_shift_probe.txt) shows that tcgen05 applies the 128B
+// swizzle to absolute shared-memory address bits, so any 128-byte-aligned start row is legal with the
+// descriptor's base_offset field left 0.  Per step only the weights (3 taps) cross L2; they are loaded
+// while the previous step's epilogue runs.
+static constexpr int RS_ROWS = 400;                 // strip rows in smem: 4 guard + 384 window + 4 guard + 8 pad
+static constexpr int RS_PLANE = RS_ROWS * 128;      // bytes per 64-channel K chunk plane
+static constexpr int RS_BOX = 200;                  // TMA box rows for the step-1 strip load (2 boxes per plane)
+
+struct alignas(64) ChainMapsS {
+  CUtensorMap u;            // U [rows, C], box [64, RS_BOX]
+  CUtensorMap w[RC_STEPS];  // packed weights [Cs, 3*Cs], box [64, Cs]
+};
+
+template <int CS>
+__global__ void __launch_bounds__(RC_THREADS, 1)
+res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainParams p) {
+  constexpr int KC = CS / 64;
+  constexpr int W_TILE = CS * 128;
+  constexpr int W_BYTES = 3 * KC * W_TILE;
+  constexpr int A_BYTES = KC * RS_PLANE;
+  constexpr int TMEM_COLS = (3 * CS > 256) ? 512 : 256;
+  constexpr int NCOLH = CS / 2;
+  constexpr int NG = NCOLH / 32;        // 32-column groups per warp per M tile
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t afull_bar, aempty_bar, wfull_bar, wempty_bar, tfull_bar, tempty_bar, sready_bar;
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t w_smem = smem_base + A_BYTES;
+  const int d = p.dil, H = p.halo;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm.u);
+    for (int j = 0; j < RC_STEPS; ++j) tma_prefetch_desc(&tm.w[j]);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(smem_u32(&afull_bar), 1);
+    mbar_init(smem_u32(&aempty_bar), 1);
+    mbar_init(smem_u32(&wfull_bar), 1);
+    mbar_init(smem_u32(&wempty_bar), 1);
+    mbar_init(smem_u32(&tfull_bar), 1);
+    mbar_init(smem_u32(&tempty_bar), 8);
+    mbar_init(smem_u32(&sready_bar), 8);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer: strip of step 1, weights of every step
+    if (elect_one()) {
+      uint32_t nitem = 0, nw = 0;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++nitem) {
+        const SegItem it = p.items[item];
+        const UttRows u = p.utts[it.utt];
+        const int tw0 = max(it.seg * RC_SEG - RC_STEPS * d, -H);
+        const int g0 = static_cast<int>(u.row0) + tw0;
+        mbar_wait(smem_u32(&aempty_bar), (nitem & 1u) ^ 1u);      // previous item's last MMAs have read the strip
+        const uint32_t ab = smem_u32(&afull_bar);
+        mbar_arrive_expect_tx(ab, KC * 2 * RS_BOX * 128);
+        for (int kcx = 0; kcx < KC; ++kcx)
+          for (int h = 0; h < 2; ++h)
+            tma_load_2d(a_smem + kcx * RS_PLANE + h * RS_BOX * 128, &tm.u, ab, CS + kcx * 64, g0 - RC_GUARD + h * RS_BOX);
+        for (int j = 1; j <= RC_STEPS; ++j, ++nw) {
+          mbar_wait(smem_u32(&wempty_bar), (nw & 1u) ^ 1u);       // previous step's MMAs have read the weights
+          const uint32_t wb = smem_u32(&wfull_bar);
+          mbar_arrive_expect_tx(wb, W_BYTES);
+          for (int tap = 0; tap < 3; ++tap)
+            for (int kcx = 0; kcx < KC; ++kcx)
+              tma_load_2d(w_smem + (tap * KC + kcx) * W_TILE, &tm.w[j - 1], wb, (tap * KC + kcx) * 64, 0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, CS);
+      uint32_t nitem = 0, nstep = 0, nsr = 0;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++nitem) {
+        for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
+          mbar_wait(smem_u32(&wfull_bar), nstep & 1u);
+          if (j == 1) mbar_wait(smem_u32(&afull_bar), nitem & 1u);
+          else { mbar_wait(smem_u32(&sready_bar), nsr & 1u); ++nsr; }
+          mbar_wait(smem_u32(&tempty_bar), (nstep & 1u) ^ 1u);
+          tc_fence_after();
+#pragma unroll
+          for (int mt = 0; mt < RC_MT; ++mt) {
+            uint32_t accf = 0;
+#pragma unroll
+            for (int tap = 0; tap < 3; ++tap) {
+#pragma unroll
+              for (int kcx = 0; kcx < KC; ++kcx) {
+                const uint64_t adesc = umma_desc_sw128(a_smem + kcx * RS_PLANE + (RC_GUARD + mt * 128 + (tap - 1) * d) * 128);
+                const uint64_t bdesc = umma_desc_sw128(w_smem + (tap * KC + kcx) * W_TILE);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { umma_bf16(tmem_base + mt * CS, adesc + 2 * k, bdesc + 2 * k, idesc, accf); accf = 1; }
+              }
+            }
+          }
+          umma_commit(smem_u32(&wempty_bar));
+          umma_commit(smem_u32(&tfull_bar));
+          if (j == RC_STEPS) umma_commit(smem_u32(&aempty_bar));
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================== epilogue
+    const int ew = warp - 4;
+    const int quad = ew & 3;               // == warp % 4: TMEM lane quadrant
+    const int half = ew >> 2;
+    const uint32_t lane_sel = static_cast<uint32_t>(quad * 32) << 16;
+    uint32_t nstep = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const SegItem it = p.items[item];
+      const UttRows u = p.utts[it.utt];
+      const int T = u.T;
+      const int s0 = it.seg * RC_SEG;
+      const int e0 = min(T, s0 + RC_SEG);
+      const int tw0 = max(s0 - RC_STEPS * d, -H);
+      const long long g0 = u.row0 + tw0;
+      int lrow[RC_MT], mir_lo[RC_MT], mir_hi[RC_MT];
+      bool own_s[RC_MT], out_r[RC_MT], xok[RC_MT];
+#pragma unroll
+      for (int mt = 0; mt < RC_MT; ++mt) {
+        const int l = mt * 128 + quad * 32 + lane;
+        const int t = tw0 + l;
+        const bool in_utt = t >= 0 && t < T;
+        const bool halo_row = (t >= -H && t < 0) || (t >= T && t < T + H);
+        lrow[mt] = l;
+        own_s[mt] = !halo_row;
+        out_r[mt] = in_utt && t >= s0 && t < e0;
+        mir_lo[mt] = (in_utt && t >= 1 && t <= H && l - 2 * t >= 0) ? l - 2 * t : -1;
+        const int ee = T - 1 - t;
+        mir_hi[mt] = (in_utt && ee >= 1 && ee <= H && l + 2 * ee < RC_WIN) ? l + 2 * ee : -1;
+        xok[mt] = (g0 + l >= 0) && (g0 + l < p.M);
+      }
+      for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
+        const float* bias = p.bias[j - 1];
+        const float* scale = p.scale[j - 1];
+        const float* shift = p.shift[j - 1];
+        if (j < RC_STEPS) {
+          // x_{j+1} does not depend on this step's MMAs: pull it towards L2 while they run
+#pragma unroll
+          for (int mt = 0; mt < RC_MT; ++mt)
+            if (xok[mt])
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(p.U + (g0 + lrow[mt]) * p.u_ld + (j + 1) * CS + half * NCOLH));
+        }
+        mbar_wait(smem_u32(&tfull_bar), nstep & 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int mt = 0; mt < RC_MT; ++mt) {
+#pragma unroll 1
+         for (int g = 0; g < NG; ++g) {
+          const int col = half * NCOLH + g * 32;
+          const long long grow = g0 + lrow[mt];
+          uint4 xr[4];
+          const bool addx = (j < RC_STEPS) && xok[mt];
+          if (addx) {
+            const uint4* xs = reinterpret_cast<const uint4*>(p.U + grow * p.u_ld + (j + 1) * CS + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) xr[i] = __ldg(xs + i);
+          }
+          uint32_t r[32];
+          tmem_ld32(tmem_base + mt * CS + col + lane_sel, r);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+            const float4 sc = __ldg(reinterpret_cast<const float4*>(scale + col) + i);
+            const float4 h = __ldg(reinterpret_cast<const float4*>(shift + col) + i);
+            v[4 * i] = fmaf(fmaxf(__uint_as_float(r[4 * i]) + b.x, 0.f), sc.x, h.x);
+            v[4 * i + 1] = fmaf(fmaxf(__uint_as_float(r[4 * i + 1]) + b.y, 0.f), sc.y, h.y);
+            v[4 * i + 2] = fmaf(fmaxf(__uint_as_float(r[4 * i + 2]) + b.z, 0.f), sc.z, h.z);
+            v[4 * i + 3] = fmaf(fmaxf(__uint_as_float(r[4 * i + 3]) + b.w, 0.f), sc.w, h.w);
+          }
+          if (out_r[mt]) {
+            bf16* rd = p.R + grow * p.r_ld + j * CS + col;
+            store_row32<false>(rd, p.C, v);
+            if (mir_lo[mt] >= 0) store_row32<false>(rd + static_cast<long long>(mir_lo[mt] - lrow[mt]) * p.r_ld, p.C, v);
+            if (mir_hi[mt] >= 0) store_row32<false>(rd + static_cast<long long>(mir_hi[mt] - lrow[mt]) * p.r_ld, p.C, v);
+          }
+          if (j < RC_STEPS) {
+            if (addx) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint32_t w[4] = {xr[i].x, xr[i].y, xr[i].z, xr[i].w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  v[8 * i + 2 * q] += bf16_lo_f(w[q]);
+                  v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
+                }
+              }
+            }
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+            const uint32_t plane = a_smem + (col >> 6) * RS_PLANE;
+            const int ci0 = (col & 63) >> 3;
+            const int tg[3] = {own_s[mt] ? lrow[mt] : -1, mir_lo[mt], mir_hi[mt]};
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              if (tg[q] < 0) continue;
+              const int rho = RC_GUARD + tg[q];
+              const uint32_t rowaddr = plane + rho * 128;
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((ci0 + i) ^ (rho & 7)) << 4)),
+                             "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3])
+                             : "memory");
+            }
+          }
+         }
+        }
+        tc_fence_before();
+        if (j < RC_STEPS) fence_proxy_async();     // strip stores (generic proxy) -> visible to the tensor core (async proxy)
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&tempty_bar));
+          if (j < RC_STEPS) mbar_arrive(smem_u32(&sready_bar));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+template <int CS>
+static int launch_chain_smem(const ChainMapsS& tm, const ChainParams& p, cudaStream_t stream) {
+  constexpr int SMEM = (CS / 64) * RS_PLANE + 3 * (CS / 64) * CS * 128 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SVB_CUDA_OK(cudaFuncSetAttribute(res2net_chain_smem_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_set = true;
+  }
+  const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
+  res2net_chain_smem_kernel<CS><<<grid, RC_THREADS, SMEM, stream>>>(tm, p);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 // ------------------------------------------------------------------ host side
 size_t res2net_scratch_bytes(int Cs, int planes) {
   return static_cast<size_t>(num_sms()) * 2 * RC_STRIP * planes * Cs * sizeof(bf16);
@@ -332,6 +591,19 @@ int res2net_chain(const bf16* U, bf16* R, int C, int planes, long long rows, con
   const int Cs = C / 8;
   SVB_CHECK(Cs == 64 || Cs == 128, "the fused Res2Net chain supports C = 512 or 1024 (Res2Net chunks of 64 / 128 channels)");
   SVB_CHECK(dil >= 1 && dil <= RC_GUARD && halo >= dil && RC_SEG + 2 * RC_STEPS * dil <= RC_WIN, "unsupported dilation %d", dil);
+  if (planes == 1) {
+    ChainMapsS ts;
+    if (make_map(&ts.u, U, rows, C, C, RS_BOX)) return -1;
+    for (int j = 0; j < RC_STEPS; ++j)
+      if (make_map(&ts.w[j], w[j], Cs, 3 * Cs, 3 * Cs, Cs)) return -1;
+    ChainParams q{};
+    q.M = rows; q.n_items = n_items; q.items = static_cast<const SegItem*>(items);
+    q.utts = static_cast<const UttRows*>(utts);
+    q.C = C; q.P = 1; q.dil = dil; q.halo = halo;
+    q.U = U; q.u_ld = C; q.R = R; q.r_ld = C;
+    for (int j = 0; j < RC_STEPS; ++j) { q.bias[j] = bias[j]; q.scale[j] = scale[j]; q.shift[j] = shift[j]; }
+    return Cs == 128 ? launch_chain_smem<128>(ts, q, stream) : launch_chain_smem<64>(ts, q, stream);
+  }
   ChainMaps tm;
   if (make_map(&tm.u, U, rows, static_cast<long long>(planes) * C, static_cast<long long>(planes) * C, 128)) return -1;
   const long long srows = static_cast<long long>(num_sms()) * 2 * RC_STRIP;
