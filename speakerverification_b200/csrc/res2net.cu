@@ -19,6 +19,8 @@
 // Rows of the window that belong to no valid context (beyond 7*d of a segment edge, or neighbouring
 // utterances) carry garbage that never reaches a stored output: a conv output row depends only on its
 // own three input rows.
+#include <stdlib.h>
+
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -56,6 +58,7 @@ struct ChainParams {
   const float* bias[RC_STEPS];
   const float* scale[RC_STEPS];
   const float* shift[RC_STEPS];
+  long long* dbg;           // optional phase timestamps of CTA 0 (SVB_CHAIN_DBG=1): [step][4] clock64 values
 };
 
 // 32 fp32 values -> bf16 hi (and lo) planes of one row
@@ -314,6 +317,7 @@ res2net_chain_kernel(const __grid_constant__ ChainMaps tm, const ChainParams p) 
 // while the previous step's epilogue runs.
 static constexpr int RS_ROWS = 400;                 // strip rows in smem: 4 guard + 384 window + 4 guard + 8 pad
 static constexpr int RS_PLANE = RS_ROWS * 128;      // bytes per 64-channel K chunk plane
+static constexpr int RS_PITCH = 80;                 // staging tile row pitch (64 data bytes + 16: conflict-free row writes)
 static constexpr int RS_BOX = 200;                  // TMA box rows for the step-1 strip load (2 boxes per plane)
 
 struct alignas(64) ChainMapsS {
@@ -340,6 +344,8 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t a_smem = smem_base;
   const uint32_t w_smem = smem_base + A_BYTES;
+  const uint32_t stg = w_smem + W_BYTES + (warp >= 4 ? warp - 4 : 0) * 32 * RS_PITCH;   // per-epilogue-warp staging tile
+  float* prm_gen = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + A_BYTES + W_BYTES + 8 * 32 * RS_PITCH);
   const int d = p.dil, H = p.halo;
 
   if (warp == 0 && lane == 0) {
@@ -402,6 +408,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
           else { mbar_wait(smem_u32(&sready_bar), nsr & 1u); ++nsr; }
           mbar_wait(smem_u32(&tempty_bar), (nstep & 1u) ^ 1u);
           tc_fence_after();
+          if (p.dbg != nullptr && blockIdx.x == 0 && nstep < 64) p.dbg[nstep * 4 + 0] = clock64();
 #pragma unroll
           for (int mt = 0; mt < RC_MT; ++mt) {
             uint32_t accf = 0;
@@ -419,6 +426,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
           umma_commit(smem_u32(&wempty_bar));
           umma_commit(smem_u32(&tfull_bar));
           if (j == RC_STEPS) umma_commit(smem_u32(&aempty_bar));
+          if (p.dbg != nullptr && blockIdx.x == 0 && nstep < 64) p.dbg[nstep * 4 + 1] = clock64();
         }
       }
     }
@@ -453,85 +461,143 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
         mir_hi[mt] = (in_utt && ee >= 1 && ee <= H && l + 2 * ee < RC_WIN) ? l + 2 * ee : -1;
         xok[mt] = (g0 + l >= 0) && (g0 + l < p.M);
       }
+      // L1 handles one 128-byte line per cycle: a warp instruction in which every lane touches its own row costs
+      // 32 tag cycles, and an epilogue built from such accesses (thread = TMEM lane = row) ran 21 k cycles per step.
+      // All global traffic below is therefore issued in a "coalesced" mapping (instruction i covers rows 8i + lane/4,
+      // 16-byte chunk lane%4 of a 64-byte row segment: 8 lines per instruction) and transposed to / from the
+      // thread-per-row mapping through a small per-warp staging tile in shared memory.
+      uint32_t m_out[RC_MT];
+#pragma unroll
+      for (int mt = 0; mt < RC_MT; ++mt) m_out[mt] = __ballot_sync(0xffffffffu, out_r[mt]);
+      const int crow = lane >> 2, cchk = lane & 3;
+      const long long gq = g0 + quad * 32;     // global row of this warp's first row in M tile 0
+      auto load_x = [&](int mt, int g, int j, uint4 (&xc)[4]) {
+        const int colx = (j + 1) * CS + half * NCOLH + g * 32 + cchk * 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const long long row = gq + mt * 128 + 8 * i + crow;
+          xc[i] = (row >= 0 && row < p.M) ? __ldg(reinterpret_cast<const uint4*>(p.U + row * p.u_ld + colx)) : make_uint4(0, 0, 0, 0);
+        }
+      };
       for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
-        const float* bias = p.bias[j - 1];
-        const float* scale = p.scale[j - 1];
-        const float* shift = p.shift[j - 1];
+        // this step's bias / BN scale / BN shift -> shared memory (double buffered by step parity)
+        float* prm = prm_gen + (nstep & 1u) * 3 * CS;
+        for (int i = ew * 32 + lane; i < 3 * CS; i += 256) {
+          const int arr = i / CS, c = i - arr * CS;
+          const float* src = arr == 0 ? p.bias[j - 1] : (arr == 1 ? p.scale[j - 1] : p.shift[j - 1]);
+          prm[i] = __ldg(src + c);
+        }
+        uint4 xc[4];
         if (j < RC_STEPS) {
-          // x_{j+1} does not depend on this step's MMAs: pull it towards L2 while they run
+          // x_{j+1} does not depend on this step's MMAs: pull it towards L2 and fetch the first group while they run
 #pragma unroll
           for (int mt = 0; mt < RC_MT; ++mt)
             if (xok[mt])
               asm volatile("prefetch.global.L2 [%0];" ::"l"(p.U + (g0 + lrow[mt]) * p.u_ld + (j + 1) * CS + half * NCOLH));
+          load_x(0, 0, j, xc);
         }
+        named_bar_sync(1, 256);
         mbar_wait(smem_u32(&tfull_bar), nstep & 1u);
         tc_fence_after();
+        if (p.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0 && nstep < 64) p.dbg[nstep * 4 + 2] = clock64();
 #pragma unroll
         for (int mt = 0; mt < RC_MT; ++mt) {
 #pragma unroll 1
-         for (int g = 0; g < NG; ++g) {
-          const int col = half * NCOLH + g * 32;
-          const long long grow = g0 + lrow[mt];
-          uint4 xr[4];
-          const bool addx = (j < RC_STEPS) && xok[mt];
-          if (addx) {
-            const uint4* xs = reinterpret_cast<const uint4*>(p.U + grow * p.u_ld + (j + 1) * CS + col);
+          for (int g = 0; g < NG; ++g) {
+            const int col = half * NCOLH + g * 32;
+            uint4 xrow[4];
+            if (j < RC_STEPS) {
+              // transpose the x tile: coalesced registers -> staging -> own row
 #pragma unroll
-            for (int i = 0; i < 4; ++i) xr[i] = __ldg(xs + i);
-          }
-          uint32_t r[32];
-          tmem_ld32(tmem_base + mt * CS + col + lane_sel, r);
-          tmem_ld_wait();
-          float v[32];
+              for (int i = 0; i < 4; ++i)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + (8 * i + crow) * RS_PITCH + cchk * 16),
+                             "r"(xc[i].x), "r"(xc[i].y), "r"(xc[i].z), "r"(xc[i].w) : "memory");
+              __syncwarp();
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
-            const float4 sc = __ldg(reinterpret_cast<const float4*>(scale + col) + i);
-            const float4 h = __ldg(reinterpret_cast<const float4*>(shift + col) + i);
-            v[4 * i] = fmaf(fmaxf(__uint_as_float(r[4 * i]) + b.x, 0.f), sc.x, h.x);
-            v[4 * i + 1] = fmaf(fmaxf(__uint_as_float(r[4 * i + 1]) + b.y, 0.f), sc.y, h.y);
-            v[4 * i + 2] = fmaf(fmaxf(__uint_as_float(r[4 * i + 2]) + b.z, 0.f), sc.z, h.z);
-            v[4 * i + 3] = fmaf(fmaxf(__uint_as_float(r[4 * i + 3]) + b.w, 0.f), sc.w, h.w);
-          }
-          if (out_r[mt]) {
-            bf16* rd = p.R + grow * p.r_ld + j * CS + col;
-            store_row32<false>(rd, p.C, v);
-            if (mir_lo[mt] >= 0) store_row32<false>(rd + static_cast<long long>(mir_lo[mt] - lrow[mt]) * p.r_ld, p.C, v);
-            if (mir_hi[mt] >= 0) store_row32<false>(rd + static_cast<long long>(mir_hi[mt] - lrow[mt]) * p.r_ld, p.C, v);
-          }
-          if (j < RC_STEPS) {
-            if (addx) {
+              for (int i = 0; i < 4; ++i)
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(xrow[i].x), "=r"(xrow[i].y), "=r"(xrow[i].z),
+                             "=r"(xrow[i].w) : "r"(stg + lane * RS_PITCH + i * 16) : "memory");
+              __syncwarp();
+              const int gn = (g + 1 < NG) ? g + 1 : 0, mn = (g + 1 < NG) ? mt : mt + 1;
+              if (mn < RC_MT) load_x(mn, gn, j, xc);
+            }
+            uint32_t r[32];
+            tmem_ld32(tmem_base + mt * CS + col + lane_sel, r);
+            tmem_ld_wait();
+            float v[32];
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint32_t w[4] = {xr[i].x, xr[i].y, xr[i].z, xr[i].w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  v[8 * i + 2 * q] += bf16_lo_f(w[q]);
-                  v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
-                }
-              }
+            for (int i = 0; i < 8; ++i) {
+              const float4 b = *reinterpret_cast<const float4*>(prm + col + 4 * i);
+              const float4 sc = *reinterpret_cast<const float4*>(prm + CS + col + 4 * i);
+              const float4 h = *reinterpret_cast<const float4*>(prm + 2 * CS + col + 4 * i);
+              v[4 * i] = fmaf(fmaxf(__uint_as_float(r[4 * i]) + b.x, 0.f), sc.x, h.x);
+              v[4 * i + 1] = fmaf(fmaxf(__uint_as_float(r[4 * i + 1]) + b.y, 0.f), sc.y, h.y);
+              v[4 * i + 2] = fmaf(fmaxf(__uint_as_float(r[4 * i + 2]) + b.z, 0.f), sc.z, h.z);
+              v[4 * i + 3] = fmaf(fmaxf(__uint_as_float(r[4 * i + 3]) + b.w, 0.f), sc.w, h.w);
             }
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-            const uint32_t plane = a_smem + (col >> 6) * RS_PLANE;
-            const int ci0 = (col & 63) >> 3;
-            const int tg[3] = {own_s[mt] ? lrow[mt] : -1, mir_lo[mt], mir_hi[mt]};
+            // y_j -> R: own row into staging, then coalesced stores of the segment's output rows
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              if (tg[q] < 0) continue;
-              const int rho = RC_GUARD + tg[q];
-              const uint32_t rowaddr = plane + rho * 128;
+            for (int i = 0; i < 4; ++i)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + lane * RS_PITCH + i * 16), "r"(pk[4 * i]),
+                           "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
+            __syncwarp();
+            bf16* rbase = p.R + (gq + mt * 128) * p.r_ld + j * CS + col + cchk * 8;
 #pragma unroll
-              for (int i = 0; i < 4; ++i)
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((ci0 + i) ^ (rho & 7)) << 4)),
-                             "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3])
-                             : "memory");
+            for (int i = 0; i < 4; ++i) {
+              const int rr = 8 * i + crow;
+              if ((m_out[mt] >> rr) & 1u) {
+                uint4 o;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
+                             : "r"(stg + rr * RS_PITCH + cchk * 16) : "memory");
+                *reinterpret_cast<uint4*>(rbase + static_cast<long long>(rr) * p.r_ld) = o;
+              }
+            }
+            if (out_r[mt] && (mir_lo[mt] >= 0 || mir_hi[mt] >= 0)) {
+              // reflect-halo copies of the first / last H frames (a handful of rows per utterance): direct row stores
+              bf16* rd = p.R + (g0 + lrow[mt]) * p.r_ld + j * CS + col;
+              if (mir_lo[mt] >= 0) {
+                uint4* dd = reinterpret_cast<uint4*>(rd + static_cast<long long>(mir_lo[mt] - lrow[mt]) * p.r_ld);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) dd[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              }
+              if (mir_hi[mt] >= 0) {
+                uint4* dd = reinterpret_cast<uint4*>(rd + static_cast<long long>(mir_hi[mt] - lrow[mt]) * p.r_ld);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) dd[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              }
+            }
+            __syncwarp();
+            if (j < RC_STEPS) {
+              // next step's input x_{j+1} + y_j (single rounding from fp32) straight into the operand strip
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint32_t w[4] = {xrow[i].x, xrow[i].y, xrow[i].z, xrow[i].w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  pk[4 * i + q] = pack_bf16x2(v[8 * i + 2 * q] + bf16_lo_f(w[q]), v[8 * i + 2 * q + 1] + bf16_hi_f(w[q]));
+              }
+              const uint32_t plane = a_smem + (col >> 6) * RS_PLANE;
+              const int ci0 = (col & 63) >> 3;
+              const int tg[3] = {own_s[mt] ? lrow[mt] : -1, mir_lo[mt], mir_hi[mt]};
+#pragma unroll
+              for (int q = 0; q < 3; ++q) {
+                if (tg[q] < 0) continue;
+                const int rho = RC_GUARD + tg[q];
+                const uint32_t rowaddr = plane + rho * 128;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((ci0 + i) ^ (rho & 7)) << 4)),
+                               "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3])
+                               : "memory");
+              }
             }
           }
-         }
         }
         tc_fence_before();
+        if (p.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0 && nstep < 64) p.dbg[nstep * 4 + 3] = clock64();
         if (j < RC_STEPS) fence_proxy_async();     // strip stores (generic proxy) -> visible to the tensor core (async proxy)
         __syncwarp();
         if (lane == 0) {
@@ -549,7 +615,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
 
 template <int CS>
 static int launch_chain_smem(const ChainMapsS& tm, const ChainParams& p, cudaStream_t stream) {
-  constexpr int SMEM = (CS / 64) * RS_PLANE + 3 * (CS / 64) * CS * 128 + 1024;
+  constexpr int SMEM = (CS / 64) * RS_PLANE + 3 * (CS / 64) * CS * 128 + 8 * 32 * RS_PITCH + 2 * 3 * CS * 4 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     SVB_CUDA_OK(cudaFuncSetAttribute(res2net_chain_smem_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
@@ -602,6 +668,22 @@ int res2net_chain(const bf16* U, bf16* R, int C, int planes, long long rows, con
     q.C = C; q.P = 1; q.dil = dil; q.halo = halo;
     q.U = U; q.u_ld = C; q.R = R; q.r_ld = C;
     for (int j = 0; j < RC_STEPS; ++j) { q.bias[j] = bias[j]; q.scale[j] = scale[j]; q.shift[j] = shift[j]; }
+    if (getenv("SVB_CHAIN_DBG") != nullptr) {
+      // diagnostics: per-step phase timestamps of CTA 0 (MMA start / MMA issued / epilogue start / epilogue end)
+      long long* d_dbg = nullptr;
+      SVB_CUDA_OK(cudaMalloc(&d_dbg, 64 * 4 * sizeof(long long)));
+      SVB_CUDA_OK(cudaMemsetAsync(d_dbg, 0, 64 * 4 * sizeof(long long), stream));
+      q.dbg = d_dbg;
+      const int rc = Cs == 128 ? launch_chain_smem<128>(ts, q, stream) : launch_chain_smem<64>(ts, q, stream);
+      long long h[64 * 4];
+      SVB_CUDA_OK(cudaStreamSynchronize(stream));
+      SVB_CUDA_OK(cudaMemcpy(h, d_dbg, sizeof(h), cudaMemcpyDeviceToHost));
+      cudaFree(d_dbg);
+      for (int i = 0; i < 14 && h[i * 4] != 0; ++i)
+        fprintf(stderr, "chain step %2d: mma_wait_end +%6lld | issue %5lld | mma->epi_start %6lld | epilogue %6lld clk\n", i,
+                i ? h[i * 4] - h[(i - 1) * 4 + 3] : 0LL, h[i * 4 + 1] - h[i * 4], h[i * 4 + 2] - h[i * 4], h[i * 4 + 3] - h[i * 4 + 2]);
+      return rc;
+    }
     return Cs == 128 ? launch_chain_smem<128>(ts, q, stream) : launch_chain_smem<64>(ts, q, stream);
   }
   ChainMaps tm;
