@@ -153,7 +153,7 @@ def run_reference(args):
 
 
 def gemm_roofline(device, batch_rows, halo=4):
-    """Times the dominant kernel (gemm_tc_kernel<256>) alone on the MFA shape of one encoder launch."""
+    """Times the dominant kernel (gemm_pw_kernel<256, GELU>) alone on the MFA shape of one encoder launch."""
     from speakerverification_b200 import _native as nv
     C3 = CH[4]
     T = 1 + L // 160
@@ -290,7 +290,7 @@ def main():
                        "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
                        "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * L * 4 / 1e9)},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "roofline": {"kernel": "gemm_tc_kernel<256> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
+            "roofline": {"kernel": "gemm_pw_kernel<256,GELU> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
                          "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
                          "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
             "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,

@@ -142,6 +142,12 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
   p.out2_ld = a->out2_ld;
   p.out2_plane_cols = a->out2_plane_cols;
   int bn = a->block_n;
+  // pointwise GELU / (ReLU + row-bias + tanh) layers with bf16 output take the lean-epilogue kernel (gemm_pw.cu)
+  const bool pointwise = bn == 0 && a->k == 1 && a->store_mode == SVB_STORE_ALL && a->out_kind != SVB_OUT_F32 &&
+                         p.out2 == nullptr && a->cout % 64 == 0 && p.num_pass != 2 &&
+                         ((a->act == SVB_ACT_GELU && a->row_bias == nullptr && !a->post_tanh) ||
+                          (a->act == SVB_ACT_RELU && a->row_bias != nullptr && a->post_tanh && a->row_meta != nullptr));
+  if (pointwise) return launch_gemm_pw(ops, p, static_cast<cudaStream_t>(stream));
   if (bn == 0) bn = (a->cout >= 256) ? 256 : (a->cout >= 128 ? 128 : 64);
   return launch_gemm(ops, p, bn, static_cast<cudaStream_t>(stream));
 }

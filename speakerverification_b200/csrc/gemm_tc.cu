@@ -11,7 +11,8 @@
 //   realised on the STORE side: every utterance owns `halo` mirrored rows before and after its
 //   valid rows, written by the producing layer (STORE_MIRROR) or computed in place by pointwise
 //   layers (STORE_ALL), so loads never need boundary handling.
-// * fp32-grade mode: operands are split hi+lo bf16 and the K loop runs hi*hi + hi*lo + lo*hi.
+// * fp32-grade mode: operands are split hi+lo bf16 and the K loop runs hi*hi + hi*lo + lo*hi
+//   (num_pass 3); num_pass 2 splits only the activations (hi*hi + lo*hi: bf16 weights, fp32-grade input).
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -127,8 +128,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / kb_per_tap;
           const int rem = kb - tap * kb_per_tap;
-          const int pass = rem / kc;
-          const int kcx = rem - pass * kc;
+          const int pass_i = rem / kc;
+          const int kcx = rem - pass_i * kc;
+          const int pass = (p.num_pass == 2 && pass_i == 1) ? 2 : pass_i;   // 2 passes: hi*hi + lo(A)*hi(W)
           const int aplane = (pass == 2) ? 1 : 0;
           const int wplane = (pass == 1) ? 1 : 0;
           const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
@@ -351,7 +353,7 @@ static int launch_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorM
 
 int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream) {
   SVB_CHECK(p.M > 0 && p.N > 0 && p.kc_per_tap > 0 && p.num_taps >= 1 && p.num_taps <= 5, "bad GEMM shape");
-  SVB_CHECK(p.num_pass == 1 || p.num_pass == 3, "num_pass must be 1 or 3");
+  SVB_CHECK(p.num_pass >= 1 && p.num_pass <= 3, "num_pass must be 1, 2 or 3");
   SVB_CHECK(p.N % 32 == 0, "N must be a multiple of 32 (got %d)", p.N);
   CUtensorMap ma, ma2, mw;
   if (make_map(&ma, ops.a, p.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;

@@ -25,57 +25,47 @@ __device__ __forceinline__ void load8(const bf16* p, int planes, int plane_cols,
 }
 
 // grid (C/256, B), block 256: warp w sweeps rows w, w+8, ...; lane owns 8 consecutive channels.
-// mode 0: mean only (SE squeeze).  mode 1: mean and std = sqrt(clamp(mean((x-mean)^2), eps)) (ASP global context).
+// mode 0: mean only (SE squeeze).  mode 1: mean and std = sqrt(clamp(mean((x-mean)^2), eps)) (ASP global context),
+// in ONE pass over x: sums are taken around the first frame s = x[0] (sum (x-s), sum (x-s)^2), so
+// var = E[(x-s)^2] - (E[x-s])^2 has no large-offset cancellation, and x (486 MB for the MFA output of a
+// 256-utterance launch, far beyond L2) is read from HBM once instead of twice.
 __global__ void __launch_bounds__(256)
 col_stats_kernel(const bf16* __restrict__ x, int ld, int planes, int plane_cols, const UttRows* __restrict__ utts,
                  int C, int mode, float eps, float* __restrict__ mean_out, float* __restrict__ std_out, int out_ld) {
   __shared__ float red[8][256];
-  __shared__ float mean_s[256];
+  __shared__ float red2[8][256];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c0 = blockIdx.x * 256 + lane * 8;
   const UttRows u = utts[blockIdx.y];
   const bool active = c0 < C;
-  float acc[8];
+  float acc[8], acc2[8], sh[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  if (active)
+  for (int i = 0; i < 8; ++i) { acc[i] = 0.f; acc2[i] = 0.f; sh[i] = 0.f; }
+  if (active) {
+    if (mode == 1) load8(x + u.row0 * ld + c0, planes, plane_cols, sh);
     for (int t = warp; t < u.T; t += 8) {
       float v[8];
       load8(x + (u.row0 + t) * ld + c0, planes, plane_cols, v);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) acc[i] += v[i];
+      for (int i = 0; i < 8; ++i) { const float d = v[i] - sh[i]; acc[i] += d; acc2[i] = fmaf(d, d, acc2[i]); }
     }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) red[warp][lane * 8 + i] = acc[i];
-  __syncthreads();
-  {
-    float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
-    const float m = s / static_cast<float>(u.T);
-    mean_s[threadIdx.x] = m;
-    const int c = blockIdx.x * 256 + threadIdx.x;
-    if (c < C) mean_out[static_cast<long long>(blockIdx.y) * out_ld + c] = m;
   }
-  if (mode == 0) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { red[warp][lane * 8 + i] = acc[i]; red2[warp][lane * 8 + i] = acc2[i]; }
   __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  if (active)
-    for (int t = warp; t < u.T; t += 8) {
-      float v[8];
-      load8(x + (u.row0 + t) * ld + c0, planes, plane_cols, v);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) { const float d = v[i] - mean_s[lane * 8 + i]; acc[i] = fmaf(d, d, acc[i]); }
-    }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) red[warp][lane * 8 + i] = acc[i];
-  __syncthreads();
-  {
-    float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
-    const int c = blockIdx.x * 256 + threadIdx.x;
-    if (c < C) std_out[static_cast<long long>(blockIdx.y) * out_ld + c] = sqrtf(fmaxf(s / static_cast<float>(u.T), eps));
+  float s = 0.f, q = 0.f;
+  for (int w = 0; w < 8; ++w) { s += red[w][threadIdx.x]; q += red2[w][threadIdx.x]; }
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  const float inv = 1.f / static_cast<float>(u.T);
+  const float d = s * inv;
+  float shift = 0.f;
+  if (mode == 1) {
+    shift = __bfloat162float(x[u.row0 * ld + c]);
+    if (planes == 2) shift += __bfloat162float(x[u.row0 * ld + plane_cols + c]);
   }
+  mean_out[static_cast<long long>(blockIdx.y) * out_ld + c] = shift + d;
+  if (mode == 1) std_out[static_cast<long long>(blockIdx.y) * out_ld + c] = sqrtf(fmaxf(q * inv - d * d, eps));
 }
 
 // out[b, j] = act( sum_c W[j, c] * (in[b, c] * in_scale[c] + in_shift[c]) + bias[j] ), fp32 SIMT.
