@@ -48,19 +48,66 @@ struct UttDesc { long long wav_off; int nsamp; int T; long long row_base; int ti
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
   return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 mul_mi(float2 a) { return make_float2(a.y, -a.x); }   // a * (-i)
+
+// forward 4-point DFT (W4 = -i), in place
+__device__ __forceinline__ void dft4(float2& a0, float2& a1, float2& a2, float2& a3) {
+  const float2 s02 = cadd(a0, a2), d02 = csub(a0, a2), s13 = cadd(a1, a3), d13 = mul_mi(csub(a1, a3));
+  a0 = cadd(s02, s13); a1 = cadd(d02, d13); a2 = csub(s02, s13); a3 = csub(d02, d13);
+}
+
+// forward 16-point DFT in registers, natural order in and out: A[k] = sum_n a[n] W16^{nk}.
+// n = na + 4 nb, k = kb + 4 ka: 4-point DFTs over nb, twiddle W16^{na kb}, 4-point DFTs over na.
+__device__ __forceinline__ void fft16(float2 (&a)[16]) {
+  constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R2 = 0.70710678118654752f;
+#pragma unroll
+  for (int na = 0; na < 4; ++na) dft4(a[na], a[na + 4], a[na + 8], a[na + 12]);   // a[na + 4 kb] = B[na][kb]
+  // twiddles W16^{na * kb}
+  a[5] = cmul(a[5], make_float2(C1, -S1));      // na 1 kb 1: W^1
+  a[9] = cmul(a[9], make_float2(R2, -R2));      // na 1 kb 2: W^2
+  a[13] = cmul(a[13], make_float2(S1, -C1));    // na 1 kb 3: W^3
+  a[6] = cmul(a[6], make_float2(R2, -R2));      // na 2 kb 1: W^2
+  a[10] = mul_mi(a[10]);                        // na 2 kb 2: W^4 = -i
+  a[14] = cmul(a[14], make_float2(-R2, -R2));   // na 2 kb 3: W^6
+  a[7] = cmul(a[7], make_float2(S1, -C1));      // na 3 kb 1: W^3
+  a[11] = cmul(a[11], make_float2(-R2, -R2));   // na 3 kb 2: W^6
+  a[15] = cmul(a[15], make_float2(-C1, S1));    // na 3 kb 3: W^9
+#pragma unroll
+  for (int kb = 0; kb < 4; ++kb) dft4(a[4 * kb], a[4 * kb + 1], a[4 * kb + 2], a[4 * kb + 3]);  // over na -> ka
+  // now a[4 kb + ka] = A[kb + 4 ka]: transpose the 4 x 4 index grid to natural order
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = i + 1; j < 4; ++j) { const float2 t = a[4 * i + j]; a[4 * i + j] = a[4 * j + i]; a[4 * j + i] = t; }
+}
+
+// One CTA per 32-frame tile, 4 warps.  A frame is transformed by a HALF warp (16 threads): the 512-point real
+// FFT is a 256-point complex FFT of the even/odd packed, windowed frame, factored 16 x 16: each thread runs a
+// 16-point FFT in registers, the 16 x 16 transpose goes once through shared memory, a second 16-point FFT in
+// registers, and the real-FFT split pairs bins k and 256-k with two warp shuffles per bin.  Window and twiddle
+// factors live in registers (fixed per thread), so per frame shared memory is touched for the samples, one
+// transpose and the 257-bin power spectrum feeding the sparse mel sums.
+static constexpr int EX_PITCH = 18;   // float2 per transpose row (144 B: 16-byte aligned, conflict-free 128-bit reads)
+static constexpr int EX_FRAME = 16 * EX_PITCH;   // float2 per frame buffer
 
 __global__ void __launch_bounds__(FB_WARPS * 32)
 fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ utts,
-                    const int2* __restrict__ tiles, const FbankTables* __restrict__ tab, int hop, int n_mels,
+                    const int2* __restrict__ tiles, const FbankTables* __restrict__ tab, int hop, int n_mels, int nnz,
                     float preemph, float log_eps, int halo, int raw_power, float* __restrict__ logmel,
                     float* __restrict__ tile_sums) {
   extern __shared__ __align__(16) uint8_t fb_smem[];
-  FbankTables* st = reinterpret_cast<FbankTables*>(fb_smem);
-  float2* fftbuf = reinterpret_cast<float2*>(fb_smem + sizeof(FbankTables));      // [warps][2][256]
-  float* sums = reinterpret_cast<float*>(fftbuf + FB_WARPS * 512);                // [warps][MAX_MELS]
-  float* samp = sums + FB_WARPS * MAX_MELS;                                       // staged samples
+  float2* exch = reinterpret_cast<float2*>(fb_smem);                                   // [warps][2][EX_FRAME]
+  float* sums = reinterpret_cast<float*>(exch + FB_WARPS * 2 * EX_FRAME);              // [warps*2][MAX_MELS]
+  int* mstart = reinterpret_cast<int*>(sums + FB_WARPS * 2 * MAX_MELS);                // [MAX_MELS]
+  int* mcount = mstart + MAX_MELS;
+  int* moff = mcount + MAX_MELS;
+  float* melw = reinterpret_cast<float*>(moff + MAX_MELS);                             // [nnz]
+  float* samp = melw + ((nnz + 3) & ~3);                                               // staged samples
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n1 = lane & 15, fi = lane >> 4;
   const int2 tile = tiles[blockIdx.x];
   const UttDesc u = utts[tile.x];
   const int t0 = tile.y;
@@ -68,12 +115,8 @@ fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ u
   const int L = u.nsamp;
   const float* x = wav + u.wav_off;
 
-  // tables -> smem (coalesced 16B copies)
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(tab);
-    uint4* dst = reinterpret_cast<uint4*>(st);
-    for (int i = threadIdx.x; i < static_cast<int>(sizeof(FbankTables) / 16); i += blockDim.x) dst[i] = __ldg(src + i);
-  }
+  for (int i = threadIdx.x; i < MAX_MELS; i += blockDim.x) { mstart[i] = tab->mel_start[i]; mcount[i] = tab->mel_count[i]; moff[i] = tab->mel_off[i]; }
+  for (int i = threadIdx.x; i < nnz; i += blockDim.x) melw[i] = tab->mel_w[i];
   // pre-emphasised, reflect-padded samples of this tile: padded index i <-> sample j = i - 256
   const int nsmp = hop * (nf - 1) + NFFT;
   const long long i0 = static_cast<long long>(hop) * t0;
@@ -85,88 +128,91 @@ fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ u
     const float prev = __ldg(x + (j > 0 ? j - 1 : 1));   // reflect pad of one sample on the left
     samp[i] = cur - preemph * prev;
   }
+  // per-thread constants: window taps of its 16 packed points, W256^{n1 k2}, W512^{k2' + 16 k1} (k2' = n1 as well)
+  float2 win[16], tw2[16], tw5[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const int n = n1 + 16 * q;
+    win[q] = make_float2(tab->window[2 * n], tab->window[2 * n + 1]);
+    tw2[q] = tab->tw256[n1 * q];
+    tw5[q] = tab->tw512[n1 + 16 * q];
+  }
   __syncthreads();
 
-  float2* A = fftbuf + warp * 512;
-  float2* Bf = A + 256;
-  float acc[MAX_MELS / 32];
+  float2* ex = exch + (warp * 2 + fi) * EX_FRAME;
+  float* pw = reinterpret_cast<float*>(ex);
+  float acc[MAX_MELS / 16];
 #pragma unroll
-  for (int q = 0; q < MAX_MELS / 32; ++q) acc[q] = 0.f;
+  for (int q = 0; q < MAX_MELS / 16; ++q) acc[q] = 0.f;
+  const int src_lane = (lane & 16) | ((16 - n1) & 15);
 
-  for (int f = warp; f < nf; f += FB_WARPS) {
-    const float* s = samp + hop * f;
-    // pack even/odd samples into a 256-point complex sequence
+  for (int fb = 0; fb < nf; fb += FB_WARPS * 2) {
+    const int fr = fb + warp * 2 + fi;
+    const bool live = fr < nf;
+    const int f = live ? fr : nf - 1;
+    const float2* s2 = reinterpret_cast<const float2*>(samp + hop * f);   // hop is even: 8-byte aligned
+    float2 a[16];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int n = lane + 32 * j;
-      A[n] = make_float2(st->window[2 * n] * s[2 * n], st->window[2 * n + 1] * s[2 * n + 1]);
+    for (int q = 0; q < 16; ++q) {
+      const float2 v = s2[n1 + 16 * q];
+      a[q] = make_float2(v.x * win[q].x, v.y * win[q].y);
     }
+    fft16(a);                                               // over n2 -> a[k2] = Y[n1, k2]
+#pragma unroll
+    for (int k2 = 1; k2 < 16; ++k2) a[k2] = cmul(a[k2], tw2[k2]);
+#pragma unroll
+    for (int k2 = 0; k2 < 16; ++k2) ex[k2 * EX_PITCH + n1] = a[k2];
     __syncwarp();
-    // Stockham radix-4, 4 passes (Ns = 1, 4, 16, 64)
-    float2* src = A;
-    float2* dst = Bf;
+    {
+      const float4* row = reinterpret_cast<const float4*>(ex + n1 * EX_PITCH);   // thread k2 = n1 reads Y[:, k2]
 #pragma unroll
-    for (int pass = 0; pass < 4; ++pass) {
-      const int Ns = 1 << (2 * pass);
-      const int tstep = 64 >> (2 * pass);   // 256 / (4 * Ns)
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int j = lane + 32 * h;
-        const int jm = j & (Ns - 1);
-        float2 v0 = src[j], v1 = src[j + 64], v2 = src[j + 128], v3 = src[j + 192];
-        if (pass > 0) {
-          v1 = cmul(v1, st->tw256[jm * tstep]);
-          v2 = cmul(v2, st->tw256[2 * jm * tstep]);
-          v3 = cmul(v3, st->tw256[3 * jm * tstep]);
-        }
-        const float2 a0 = make_float2(v0.x + v2.x, v0.y + v2.y);
-        const float2 a1 = make_float2(v0.x - v2.x, v0.y - v2.y);
-        const float2 a2 = make_float2(v1.x + v3.x, v1.y + v3.y);
-        const float2 a3 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i * (v1 - v3)
-        const int j0 = ((j - jm) << 2) + jm;
-        dst[j0] = make_float2(a0.x + a2.x, a0.y + a2.y);
-        dst[j0 + Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
-        dst[j0 + 2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
-        dst[j0 + 3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+      for (int q = 0; q < 8; ++q) {
+        const float4 v = row[q];
+        a[2 * q] = make_float2(v.x, v.y);
+        a[2 * q + 1] = make_float2(v.z, v.w);
       }
-      __syncwarp();
-      float2* tmp = src; src = dst; dst = tmp;
     }
-    // src == A holds Z = FFT256(z).  Real-FFT split and power spectrum -> pw (aliases Bf).
-    float* pw = reinterpret_cast<float*>(Bf);
-    for (int k = lane; k < NBIN; k += 32) {
-      const float2 a = A[k & 255];
-      const float2 bq = A[(256 - k) & 255];
-      const float2 e = make_float2(0.5f * (a.x + bq.x), 0.5f * (a.y - bq.y));
-      const float2 o = make_float2(0.5f * (a.y + bq.y), -0.5f * (a.x - bq.x));
-      const float2 wo = cmul(st->tw512[k], o);
+    fft16(a);                                               // over n1 -> a[k1] = Z[k2 + 16 k1]
+    __syncwarp();
+    // real-FFT split: X[k] = E + W512^k O with E, O from Z[k] and Z[256 - k]; power spectrum to shared memory
+#pragma unroll
+    for (int k1 = 0; k1 < 16; ++k1) {
+      float pr = __shfl_sync(0xffffffffu, a[15 - k1].x, src_lane);
+      float pi = __shfl_sync(0xffffffffu, a[15 - k1].y, src_lane);
+      if (n1 == 0) { pr = a[(16 - k1) & 15].x; pi = a[(16 - k1) & 15].y; }
+      const float2 e = make_float2(0.5f * (a[k1].x + pr), 0.5f * (a[k1].y - pi));
+      const float2 o = make_float2(0.5f * (a[k1].y + pi), -0.5f * (a[k1].x - pr));
+      const float2 wo = cmul(tw5[k1], o);
       const float re = e.x + wo.x, im = e.y + wo.y;
-      pw[k] = re * re + im * im;
+      pw[n1 + 16 * k1] = re * re + im * im;
     }
+    if (n1 == 0) { const float dd = a[0].x - a[0].y; pw[256] = dd * dd; }
     __syncwarp();
     const long long row = u.row_base + halo + t0 + f;
 #pragma unroll
-    for (int q = 0; q < MAX_MELS / 32; ++q) {
-      const int m = lane + 32 * q;
+    for (int q = 0; q < MAX_MELS / 16; ++q) {
+      const int m = n1 + 16 * q;
       if (m < n_mels) {
-        const int b0 = st->mel_start[m], cnt = st->mel_count[m];
-        const float* wv = st->mel_w + st->mel_off[m];
+        const int b0 = mstart[m], cnt = mcount[m];
+        const float* wv = melw + moff[m];
         float sacc = 0.f;
         for (int i = 0; i < cnt; ++i) sacc = fmaf(pw[b0 + i], wv[i], sacc);
         const float lm = raw_power ? sacc : logf(sacc + log_eps);
-        logmel[row * n_mels + m] = lm;
-        acc[q] += lm;
+        if (live) {
+          logmel[row * n_mels + m] = lm;
+          acc[q] += lm;
+        }
       }
     }
     __syncwarp();
   }
-  // deterministic per-tile column sums (fixed warp order)
+  // deterministic per-tile column sums (fixed slot order)
 #pragma unroll
-  for (int q = 0; q < MAX_MELS / 32; ++q) sums[warp * MAX_MELS + lane + 32 * q] = acc[q];
+  for (int q = 0; q < MAX_MELS / 16; ++q) sums[(warp * 2 + fi) * MAX_MELS + n1 + 16 * q] = acc[q];
   __syncthreads();
   for (int m = threadIdx.x; m < n_mels; m += blockDim.x) {
     float s = 0.f;
-    for (int w = 0; w < FB_WARPS; ++w) s += sums[w * MAX_MELS + m];
+    for (int w = 0; w < FB_WARPS * 2; ++w) s += sums[w * MAX_MELS + m];
     tile_sums[static_cast<long long>(blockIdx.x) * n_mels + m] = s;
   }
 }
@@ -265,7 +311,8 @@ int fbank_n_mels(const Fbank* f) { return f->n_mels; }
 int fbank_hop(const Fbank* f) { return f->hop; }
 
 size_t fbank_smem_bytes(const Fbank* f) {
-  return sizeof(FbankTables) + FB_WARPS * 512 * sizeof(float2) + FB_WARPS * MAX_MELS * sizeof(float) +
+  return FB_WARPS * 2 * EX_FRAME * sizeof(float2) + FB_WARPS * 2 * MAX_MELS * sizeof(float) + 3 * MAX_MELS * sizeof(int) +
+         static_cast<size_t>((f->nnz + 3) & ~3) * sizeof(float) +
          (static_cast<size_t>(f->hop) * (FRAMES_PER_TILE - 1) + NFFT) * sizeof(float);
 }
 
@@ -307,7 +354,7 @@ int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const i
   }
   fbank_logmel_kernel<<<ntiles, FB_WARPS * 32, smem, stream>>>(
       wav, static_cast<const UttDesc*>(utt_tab), reinterpret_cast<const int2*>(tile_tab), f->d_tab, f->hop,
-      f->n_mels, f->preemph, f->log_eps, halo, mode, logmel_ws, tile_sums_ws);
+      f->n_mels, f->nnz, f->preemph, f->log_eps, halo, mode, logmel_ws, tile_sums_ws);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   if (mode == 1) return 0;
