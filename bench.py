@@ -107,8 +107,9 @@ def synth_waves(n, device, seed):
     return out
 
 
-def cpu_reference_rate(n_utts, batch=16):
-    """Reference CPU path (oracle port of SpeakerEncoder.forward, fp32, all host threads): embeddings/s."""
+def cpu_reference_rate(n_utts, batch=16, min_seconds=0.0):
+    """Reference CPU path (oracle port of SpeakerEncoder.forward, fp32, all host threads): embeddings/s.
+    Runs at least n_utts utterances and at least min_seconds of CPU work."""
     from oracle import ecapa_oracle as eo, synth
     torch.set_num_threads(os.cpu_count())
     sd = synth.ecapa_state_dict(CH, N_OUT)
@@ -118,7 +119,7 @@ def cpu_reference_rate(n_utts, batch=16):
     eo.embed(waves, sd)                                  # warm-up
     t0 = time.perf_counter()
     done = 0
-    while done < n_utts:
+    while done < n_utts or time.perf_counter() - t0 < min_seconds:
         eo.embed(waves, sd)
         done += batch
     dt = time.perf_counter() - t0
@@ -131,7 +132,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    per_step = 32
+    per_step = 128
     for _ in range(min(args.warmup, 1)):
         cpu_reference_rate(16)
     t0 = time.perf_counter()
@@ -298,7 +299,7 @@ def main():
                             "note": "whole step, algorithmic 11.29 GFLOP per utterance vs sustained bf16 peak"},
         }
         if world == 1:
-            rate, n, dt = cpu_reference_rate(64)
+            rate, n, dt = cpu_reference_rate(64, min_seconds=12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}
         print(json.dumps(line))

@@ -219,6 +219,38 @@ class ModelHandling(object):
             full[idx] = parts[r][:len(idx)]
         return full
 
+    @staticmethod
+    def shard_balanced(lengths, world):
+        """Greedy length-balanced assignment for ragged utterances: longest first onto
+        the least-loaded rank.  Returns `world` index arrays, each in ascending item order; identical on
+        every rank (pure function of the lengths)."""
+        lengths = np.asarray(lengths, dtype=np.int64)
+        order = np.argsort(-lengths, kind="stable")
+        loads = [0] * world
+        parts = [[] for _ in range(world)]
+        for i in order:
+            r = min(range(world), key=lambda k: (loads[k], k))
+            parts[r].append(int(i))
+            loads[r] += int(lengths[i])
+        return [np.asarray(sorted(p), dtype=np.int64) for p in parts]
+
+    @staticmethod
+    def gather_assigned(local, parts, rank, world):
+        """All-gather for an explicit assignment `parts` (from shard_balanced): [len(parts[rank]), ...] per rank
+        -> [n_items, ...] in item order on every rank."""
+        import torch.distributed as dist
+        n_items = int(sum(len(p) for p in parts))
+        per = max(1, max(len(p) for p in parts))
+        pad = torch.zeros((per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        pad[:local.shape[0]] = local
+        allp = torch.empty((world * per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(allp, pad)
+        full = torch.empty((n_items,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        for r in range(world):
+            if len(parts[r]):
+                full[torch.as_tensor(parts[r], device=local.device)] = allp[r * per:r * per + len(parts[r])]
+        return full
+
     # ------------------------------------------------------------------ evaluation from a trial list
     def evaluateFromList(self, listfilename, distributed, dataloader_options, cohorts_path="checkpoint/dump_cohorts.npy",
                          num_eval=10, scoring_mode="cosine", **kwargs):
