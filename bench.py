@@ -132,6 +132,27 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
+    if args.workload == "scoring":
+        U, N, NT = min(args.score_utts, 20000), args.score_cohort, 4096
+        e, c, ia, ib = scoring_inputs(U, N, NT)
+        cpu_scoring_rate(e, c, ia, ib, 300, 0.5)
+        t0 = time.perf_counter()
+        n = 0
+        for _ in range(args.steps):
+            _, done, _ = cpu_scoring_rate(e, c, ia, ib, 300, 3.0)
+            n += done
+        dt = time.perf_counter() - t0
+        val = n / dt
+        print(json.dumps({
+            "impl": "reference", "metric": "AS-norm trials/sec", "value": val, "unit": "trials/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "scoring sweep (configs[4]): per-trial AS-norm vs %d-cohort, top-300, D=%d" % (N, N_OUT),
+                       "sample": "3 s of trials per step"},
+            "cpu_baseline": {"value": val, "unit": "trials/s", "cores": os.cpu_count(), "kind": "port",
+                             "sample": "%d trials, per-trial ZT_norm_similarity loop (numpy)" % n},
+            "e2e": {"value": val, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     per_step = 128
     for _ in range(min(args.warmup, 1)):
         cpu_reference_rate(16)
@@ -151,6 +172,118 @@ def run_reference(args):
         "cpu_baseline": {"value": val, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                          "sample": "%d x 3 s utterances per step, batch 16, torch fp32 oracle port" % per_step},
         "e2e": {"value": val, "unit": "embeddings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------ scoring sweep (BASELINE.json configs[4])
+def scoring_inputs(U, N, n_trials, seed=3):
+    """cfg5: unit embeddings around 2 000 speaker centroids, disjoint cohort, seeded trial pairs (10 % target)."""
+    from oracle import synth
+    e, spk = synth.scoring_embeddings(U, 2000, seed=seed)
+    c, _ = synth.scoring_embeddings(N, 2000, seed=seed + 100)
+    rng = np.random.default_rng(seed + 1)
+    ia = rng.integers(0, U, n_trials)
+    ib = rng.integers(0, U, n_trials)
+    order = np.argsort(spk, kind="stable")
+    pos = rng.integers(0, U - 1, n_trials // 10)
+    nxt = np.where(spk[order[pos]] == spk[order[pos + 1]], pos + 1, np.maximum(pos - 1, 0))
+    ia[:len(pos)], ib[:len(pos)] = order[pos], order[nxt]
+    return e, c, ia.astype(np.int32), ib.astype(np.int32)
+
+
+def cpu_scoring_rate(e, c, ia, ib, top, min_seconds):
+    """The reference's own per-trial formulation (utils.ZT_norm_similarity in the loop of model.py:415-448;
+    oracle port, numpy on all host threads): two [N, D] x [D, n] products and two full sorts per trial."""
+    from oracle import scoring_oracle as so
+    t0 = time.perf_counter()
+    n = 0
+    while time.perf_counter() - t0 < min_seconds or n < 8:
+        so.asnorm_score(e[ia[n]][None], e[ib[n]][None], c, top)
+        n += 1
+    dt = time.perf_counter() - t0
+    return n / dt, n, dt
+
+
+def run_scoring(args, device, rank, world, dist, steps, full_line=True):
+    """AS-norm trials/sec: per step, cohort statistics (top-K mean/std against N cohort vectors) of this rank's
+    U unique utterances and the S-norm scores of its n_trials trials (trial- and utterance-sharded, weak)."""
+    from speakerverification_b200 import _native as nv
+    from speakerverification_b200 import utils as SU
+    U, N, K, NT, D = args.score_utts, args.score_cohort, 300, args.score_trials, N_OUT
+    e, c, ia, ib = scoring_inputs(U, N, NT, seed=3 + rank)
+    emb = torch.from_numpy(e).to(device)
+    coh = torch.from_numpy(c).to(device)
+    tia, tib = torch.from_numpy(ia).to(device), torch.from_numpy(ib).to(device)
+
+    def step():
+        mu, sg = SU.asnorm_stats(emb, coh, K)
+        return SU.asnorm_trials(emb, tia, tib, mu, sg)
+
+    for _ in range(3):
+        out = step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    nv.lib().svb_reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = int(nv.lib().svb_launch_count())
+    if world > 1:
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * NT * steps / (ms * 1e-3)
+    # end to end: host embeddings / cohort / trial indices in, host scores out, through utils.score_trials
+    he = torch.from_numpy(e).unsqueeze(1).pin_memory()
+    hia, hib = torch.from_numpy(ia).pin_memory(), torch.from_numpy(ib).pin_memory()
+    hc = torch.from_numpy(c).pin_memory()
+
+    def e2e_step():
+        d = he.to(device, non_blocking=True)
+        return SU.score_trials(d, hia.to(device, non_blocking=True), hib.to(device, non_blocking=True), "norm",
+                               hc.to(device, non_blocking=True), top=K, normalize=False).cpu()
+    e2e_step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        hs = e2e_step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    assert bool(torch.isfinite(hs).all()) and torch.allclose(hs, out.cpu(), atol=1e-5)
+    res = {"metric": "AS-norm trials/sec", "value": value, "unit": "trials/s", "n_gpus": world, "steps": steps,
+           "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "bf16x3 (split, fp32 grade) GEMM, fp64 top-K statistics", "data": "synthetic",
+           "config": {"workload": "scoring sweep (configs[4]): %d trials over %d unique embeddings vs %d-cohort, "
+                                  "top-%d AS-norm, D=%d, per GPU" % (NT, U, N, K, D),
+                      "l2": "score matrix produced in L2-resident row chunks; embeddings+cohort %.0f MB per step"
+                            % ((U + N) * D * 4 / 1e6)},
+           "e2e": {"value": world * NT * steps / dt, "unit": "trials/s",
+                   "h2d_bytes_per_step": (U + N) * D * 4 + 2 * NT * 4, "d2h_bytes_per_step": NT * 4,
+                   "api": "utils.score_trials(emb, idx_a, idx_b, 'norm', cohorts, top) from pinned host buffers"},
+           "gpu_launches": launches}
+    if rank == 0:
+        hbm, tf_burst, tf_sust, src = peaks()
+        flops = 2.0 * U * N * D
+        res["roofline"] = {"kernel": "cohort-score GEMM + top-K select (svb_asnorm_stats), whole phase",
+                           "bound": "tensor", "achieved": flops * steps / (ms * 1e-3) / 1e12, "peak": tf_sust / 3.0,
+                           "unit": "TFLOP/s", "frac": flops * steps / (ms * 1e-3) / 1e12 / (tf_sust / 3.0),
+                           "traffic": None,
+                           "note": "algorithmic 2*U*N*D FLOP per step over the step time; fp32-grade scores cost 3 "
+                                   "bf16 passes, so the bound is the sustained bf16 peak / 3 (" + src + ")"}
+        if world == 1 and full_line:
+            rate, n, dtc = cpu_scoring_rate(e, c, ia, ib, K, 10.0)
+            res["cpu_baseline"] = {"value": rate, "unit": "trials/s", "cores": os.cpu_count(), "kind": "port",
+                                   "sample": "%d trials of the same sweep, per-trial ZT_norm_similarity loop "
+                                             "(numpy, %.1f s)" % (n, dtc)}
+    return res
 
 
 def gemm_roofline(device, batch_rows, halo=4):
@@ -191,6 +324,10 @@ def main():
     ap.add_argument("--batch-rows", type=int, default=256)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="embed", choices=["embed", "scoring"])
+    ap.add_argument("--score-utts", type=int, default=200000)
+    ap.add_argument("--score-cohort", type=int, default=20000)
+    ap.add_argument("--score-trials", type=int, default=1000000)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -204,6 +341,19 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
+
+    if args.workload == "scoring":
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        res = run_scoring(args, device, rank, world, dist, args.steps)
+        if rank == 0:
+            res["warmup"] = 3
+            res["clocks"] = sampler.stop()
+            print(json.dumps(res))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     from speakerverification_b200 import _native as nv
     from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
@@ -299,6 +449,10 @@ def main():
                             "note": "whole step, algorithmic 11.29 GFLOP per utterance vs sustained bf16 peak"},
         }
         if world == 1:
+            del waves, emb
+            torch.cuda.empty_cache()
+            sc = run_scoring(args, device, rank, world, dist, max(args.steps, 3), full_line=False)
+            line["scoring"] = {k: sc[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "roofline")}
             rate, n, dt = cpu_reference_rate(64, min_seconds=12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}

@@ -24,6 +24,7 @@ static constexpr int BLOCK_K = 64;
 static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 static constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
 static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // one warp's 32 rows x 64 bf16 columns
+static constexpr int ACT_RAW_F32 = 3;               // epilogue variant: no bias/act/BN, fp32 accumulators stored as is
 
 template <int BN>
 struct PwCfg {
@@ -186,6 +187,29 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int col0 = half * (BN / 2) + c * 64;
         const int n = n0 + col0;
         if (n >= p.N) break;
+        if (ACT == ACT_RAW_F32) {
+          // raw fp32 accumulators (cohort scores): two 32 x 32 fp32 boxes per 64 columns, same swizzled staging
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + acc * BN + col0 + hh * 32 + (static_cast<uint32_t>(quad * 32) << 16), r);
+            tmem_ld_wait();
+            if (lane == 0) bulk_wait_read<0>();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(r[4 * j]),
+                           "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                           : "memory");
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmOut, my_box, n + hh * 32, m0 + quad * 32);
+              bulk_commit();
+            }
+          }
+          continue;
+        }
         uint32_t hi[32];
         uint32_t lo[32];   // dead (eliminated) unless HILO
 #pragma unroll
@@ -321,6 +345,23 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
                 : launch_pw_t<256, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
   return hilo ? launch_pw_t<128, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
               : launch_pw_t<128, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
+}
+
+// Plain fp32-output GEMM  out[M, N] = A * W^T  (no bias / activation / BN): the cohort-score matrix of AS-norm.
+// out_ld in floats; N a multiple of 64.
+int launch_gemm_f32(const GemmOperands& ops, const GemmParams& g, cudaStream_t stream) {
+  SVB_CHECK(g.num_taps == 1 && g.tap_off[0] == 0 && g.N % 64 == 0, "launch_gemm_f32: pointwise, N % 64 == 0");
+  SVB_CHECK((reinterpret_cast<uintptr_t>(g.out) & 15) == 0 && (g.out_ld * 4) % 16 == 0, "fp32 output must be 16-byte aligned");
+  const int bn = g.N >= 256 ? 256 : 128;
+  CUtensorMap ma, mw, mo;
+  if (make_map(&ma, ops.a, g.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
+  if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;
+  if (make_map_f32(&mo, g.out, g.M, g.N, g.out_ld, 32)) return -1;
+  PwParams p{};
+  p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
+  p.a2_kc = 0; p.w_planes = g.w_planes;
+  return bn == 256 ? launch_pw_t<256, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream)
+                   : launch_pw_t<128, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream);
 }
 
 }  // namespace svb

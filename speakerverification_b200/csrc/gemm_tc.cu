@@ -333,6 +333,21 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
+// 2D fp32 row-major matrix [rows, ld] exposing `cols` columns; box = [32 cols (128 B), box_rows], 128B swizzle.
+int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  SVB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {32, static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SVB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (fp32) failed with code %d", static_cast<int>(r));
+  return 0;
+}
+
 template <int BN>
 static int launch_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const GemmParams& p,
                     cudaStream_t stream) {

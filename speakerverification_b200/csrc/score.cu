@@ -153,6 +153,315 @@ topk_stats_kernel(const float* __restrict__ S, int ld, int N, int K, float* __re
   }
 }
 
+// Row cached in shared memory, value-linear first level.  S is read ONCE (float4; from L2 when the GEMM chunk
+// that produced it is still resident).  Cohort scores of one utterance cluster in a handful of float exponents,
+// so a radix pass on the key's top bits would serialise thousands of shared-memory atomics on a few bins;
+// instead level 0 histograms the values LINEARLY over the row's [min, max] (2048 bins, conflicts rare), which
+// leaves only the few candidates of the threshold bin for the exact key-radix select.
+//   1. load row -> smem, block min/max            2. linear histogram, find the bin holding the K-th largest
+//   3. sweep: bins above -> fp64 sum / sum-sq, threshold bin -> candidate list (cap TOPK_CAND)
+//   4. exact 3-pass key radix among the candidates (or, on overflow of the list, over the whole row with the
+//      bin as a filter) -> K-th key and the number of copies of it that belong to the top-K set.
+// Dynamic smem: N floats.
+#define TOPK_CAND 2048
+__device__ __forceinline__ int lin_bin(float v, float lo, float scale) {
+  return min(2047, __float2int_rz((v - lo) * scale));   // saturating; -inf maps below bin 0
+}
+
+// All NT threads: walks `nb` (multiple of NT) histogram bins from the top and finds the bin in which the
+// cumulative count reaches `remaining`.  Writes sel[0] = prefix | bin << shift, sel[1] = how many elements
+// of that bin are still needed.  Ends with a barrier.
+template <int NT>
+__device__ __forceinline__ void find_bin(const uint32_t* hist, int nb, uint32_t remaining, uint32_t prefix, int shift,
+                                         uint32_t* sel, uint32_t* wtot) {
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  constexpr int NW = NT / 32;
+  // nb is NT or 2 * NT or 4 * NT (1024 / 2048 bins); unused slots count zero
+  const int per = nb / NT;
+  const int b0 = nb - 1 - tid * per;
+  const uint32_t c0 = hist[b0];
+  const uint32_t c1 = per > 1 ? hist[b0 - 1] : 0u;
+  const uint32_t c2 = per > 2 ? hist[b0 - 2] : 0u;
+  const uint32_t c3 = per > 2 ? hist[b0 - 3] : 0u;
+  const uint32_t mine = c0 + c1 + c2 + c3;
+  uint32_t incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) wtot[wid] = incl;
+  __syncthreads();
+  if (wid == 0) {      // exclusive scan of the warp totals by one warp
+    const uint32_t t = lane < NW ? wtot[lane] : 0u;
+    uint32_t x = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += v;
+    }
+    if (lane < NW) wtot[lane] = x - t;
+  }
+  __syncthreads();
+  incl += wtot[wid];
+  const uint32_t excl = incl - mine;
+  if (excl < remaining && incl >= remaining) {
+    uint32_t run = excl;
+    int j = 0;
+    if (run + c0 < remaining) { run += c0; j = 1;
+      if (run + c1 < remaining) { run += c1; j = 2;
+        if (run + c2 < remaining) { run += c2; j = 3; } } }
+    sel[0] = prefix | (static_cast<uint32_t>(b0 - j) << shift);
+    sel[1] = remaining - run;
+  }
+  __syncthreads();
+}
+
+template <bool FILTER, int NT>
+__device__ __forceinline__ void radix_kth(const float* __restrict__ src, int n, float lo, float scale, int bin_sel,
+                                          uint32_t need, uint32_t* hist, uint32_t* sel, uint32_t* wtot,
+                                          uint32_t& kth_out, uint32_t& copies_out) {
+  const int tid = threadIdx.x;
+  uint32_t prefix = 0, prefix_mask = 0, remaining = need;
+  const int shifts[3] = {21, 10, 0};
+  const int bits[3] = {11, 11, 10};
+  for (int pass = 0; pass < 3; ++pass) {
+    const int nb = 1 << bits[pass];
+    for (int i = tid; i < nb; i += NT) hist[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += NT) {
+      const float v = src[i];
+      if (FILTER && lin_bin(v, lo, scale) != bin_sel) continue;
+      const uint32_t k = f2key(v);
+      if ((k & prefix_mask) == prefix) atomicAdd(&hist[(k >> shifts[pass]) & (nb - 1)], 1u);
+    }
+    __syncthreads();
+    find_bin<NT>(hist, nb, remaining, prefix, shifts[pass], sel, wtot);
+    prefix = sel[0];
+    remaining = sel[1];
+    prefix_mask |= static_cast<uint32_t>(nb - 1) << shifts[pass];
+    __syncthreads();
+  }
+  kth_out = prefix;
+  copies_out = remaining;
+}
+
+__global__ void __launch_bounds__(512)
+topk_stats_smem_kernel(const float* __restrict__ S, int ld, int N, int K, float* __restrict__ mu,
+                       float* __restrict__ sigma) {
+  extern __shared__ float vals[];
+  __shared__ uint32_t hist[2048];
+  __shared__ float cand[TOPK_CAND];
+  __shared__ uint32_t sel[2], ncand_s, wtot[16];
+  __shared__ float red_lo[16], red_hi[16];
+  __shared__ double red_s[16], red_q[16];
+  const float* row = S + static_cast<long long>(blockIdx.x) * ld;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < 2048; i += 512) hist[i] = 0;
+  if (tid == 0) ncand_s = 0;
+  // 1. load + min/max
+  float lo = INFINITY, hi = -INFINITY;
+  const int n4 = N >> 2;
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  for (int i = tid; i < n4; i += 512) {
+    const float4 v = row4[i];
+    reinterpret_cast<float4*>(vals)[i] = v;
+    lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
+    hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+  }
+  for (int i = (n4 << 2) + tid; i < N; i += 512) {
+    const float v = row[i];
+    vals[i] = v;
+    lo = fminf(lo, v); hi = fmaxf(hi, v);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if (lane == 0) { red_lo[wid] = lo; red_hi[wid] = hi; }
+  __syncthreads();
+  lo = red_lo[0]; hi = red_hi[0];
+  for (int w = 1; w < 16; ++w) { lo = fminf(lo, red_lo[w]); hi = fmaxf(hi, red_hi[w]); }
+  const float range = hi - lo;
+  // a constant (or non-finite-range) row goes through the key radix alone: every element lands in bin 0
+  const float scale = (range > 0.f && range < INFINITY) ? 2047.f / range : 0.f;
+  // 2. linear histogram, threshold bin
+  for (int i = tid; i < N; i += 512) atomicAdd(&hist[lin_bin(vals[i], lo, scale)], 1u);
+  __syncthreads();
+  find_bin<512>(hist, 2048, static_cast<uint32_t>(K), 0u, 0, sel, wtot);
+  const int bin_sel = static_cast<int>(sel[0]);
+  const uint32_t need = sel[1];          // how many of the threshold bin's elements belong to the top-K set
+  __syncthreads();
+  // 3. sweep
+  double s = 0.0, q = 0.0;
+  for (int i = tid; i < N; i += 512) {
+    const float v = vals[i];
+    const int b = lin_bin(v, lo, scale);
+    if (b > bin_sel) { s += v; q += static_cast<double>(v) * v; }
+    else if (b == bin_sel) {
+      const uint32_t slot = atomicAdd(&ncand_s, 1u);
+      if (slot < TOPK_CAND) cand[slot] = v;
+    }
+  }
+  __syncthreads();
+  const uint32_t ncand = ncand_s;
+  // 4. exact select inside the threshold bin
+  uint32_t kth, copies;
+  if (ncand <= TOPK_CAND) {
+    radix_kth<false, 512>(cand, static_cast<int>(ncand), lo, scale, bin_sel, need, hist, sel, wtot, kth, copies);
+    for (int i = tid; i < static_cast<int>(ncand); i += 512) {
+      const float v = cand[i];
+      if (f2key(v) > kth) { s += v; q += static_cast<double>(v) * v; }
+    }
+  } else {
+    radix_kth<true, 512>(vals, N, lo, scale, bin_sel, need, hist, sel, wtot, kth, copies);
+    for (int i = tid; i < N; i += 512) {
+      const float v = vals[i];
+      if (lin_bin(v, lo, scale) == bin_sel && f2key(v) > kth) { s += v; q += static_cast<double>(v) * v; }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) { red_s[wid] = s; red_q[wid] = q; }
+  __syncthreads();
+  if (tid == 0) {
+    double ts = 0.0, tq = 0.0;
+    for (int w = 0; w < 16; ++w) { ts += red_s[w]; tq += red_q[w]; }
+    if (copies > 0) {
+      const double kv = key2f(kth);
+      ts += copies * kv;
+      tq += copies * kv * kv;
+    }
+    const double m = ts / K;
+    const double var = fmax(tq / K - m * m, 0.0);
+    mu[blockIdx.x] = static_cast<float>(m);
+    sigma[blockIdx.x] = static_cast<float>(sqrt(var));
+  }
+}
+
+// Register-resident variant for N <= NT * 4 * PER4: each thread keeps PER4 float4 of the row in registers (all
+// loads in flight at once, one L2 round trip), so the kernel needs no dynamic shared memory and four CTAs share
+// an SM.  Same algorithm as topk_stats_smem_kernel.
+template <int PER4, int NT>
+__global__ void __launch_bounds__(NT, 2048 / NT / 2 > 0 ? 2048 / NT / 2 : 1)
+topk_stats_reg_kernel(const float* __restrict__ S, int ld, int N, int K, float* __restrict__ mu,
+                      float* __restrict__ sigma) {
+  __shared__ uint32_t hist[2048];
+  __shared__ float cand[TOPK_CAND];
+  __shared__ uint32_t sel[2], ncand_s, wtot[NT / 32];
+  __shared__ float red_lo[NT / 32], red_hi[NT / 32];
+  __shared__ double red_s[NT / 32], red_q[NT / 32];
+  const float* row = S + static_cast<long long>(blockIdx.x) * ld;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < 2048; i += NT) hist[i] = 0;
+  if (tid == 0) ncand_s = 0;
+  // 1. load (rows are padded to a multiple of 64 floats, so whole float4 reads stay inside the row); slots past
+  //    N hold -inf: never counted, never above the threshold bin
+  float v[PER4 * 4];
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  const int n4 = (N + 3) >> 2;
+  const float NINF = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < PER4; ++j) {
+    const int i4 = tid + NT * j;
+    float4 q = make_float4(NINF, NINF, NINF, NINF);
+    if (i4 < n4) {
+      q = row4[i4];
+      if (4 * i4 + 1 >= N) q.y = NINF;
+      if (4 * i4 + 2 >= N) q.z = NINF;
+      if (4 * i4 + 3 >= N) q.w = NINF;
+    }
+    v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+  }
+  float lo = INFINITY, hi = NINF;
+#pragma unroll
+  for (int j = 0; j < PER4 * 4; ++j) {
+    hi = fmaxf(hi, v[j]);
+    lo = fminf(lo, v[j] == NINF ? INFINITY : v[j]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if (lane == 0) { red_lo[wid] = lo; red_hi[wid] = hi; }
+  __syncthreads();
+  lo = red_lo[0]; hi = red_hi[0];
+  for (int w = 1; w < NT / 32; ++w) { lo = fminf(lo, red_lo[w]); hi = fmaxf(hi, red_hi[w]); }
+  const float range = hi - lo;
+  const float scale = (range > 0.f && range < INFINITY) ? 2047.f / range : 0.f;
+  // 2. linear histogram (predicated shared-memory atomics, no branches)
+#pragma unroll
+  for (int j = 0; j < PER4 * 4; ++j)
+    if (v[j] != NINF) atomicAdd(&hist[lin_bin(v[j], lo, scale)], 1u);
+  __syncthreads();
+  find_bin<NT>(hist, 2048, static_cast<uint32_t>(K), 0u, 0, sel, wtot);
+  const int bin_sel = static_cast<int>(sel[0]);
+  const uint32_t need = sel[1];
+  __syncthreads();
+  // 3. sweep: one rarely-taken branch per element
+  double s = 0.0, q = 0.0;
+#pragma unroll
+  for (int j = 0; j < PER4 * 4; ++j) {
+    const int b = lin_bin(v[j], lo, scale);          // -inf -> negative bin
+    if (b >= bin_sel) {
+      if (b > bin_sel) { s += v[j]; q += static_cast<double>(v[j]) * v[j]; }
+      else {
+        const uint32_t slot = atomicAdd(&ncand_s, 1u);
+        if (slot < TOPK_CAND) cand[slot] = v[j];
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t ncand = ncand_s;
+  uint32_t kth = 0, copies = 0;
+  if (ncand <= NT) {
+    // few candidates (the usual case): thread t ranks candidate t by counting; the `need` best are summed
+    // directly (ties broken by slot, which cannot change a sum of equal values)
+    if (tid < static_cast<int>(ncand)) {
+      const float mine = cand[tid];
+      uint32_t rank = 0;
+      for (int i = 0; i < static_cast<int>(ncand); ++i) {
+        const float c = cand[i];
+        rank += (c > mine || (c == mine && i < tid)) ? 1u : 0u;
+      }
+      if (rank < need) { s += mine; q += static_cast<double>(mine) * mine; }
+    }
+  } else if (ncand <= TOPK_CAND) {
+    radix_kth<false, NT>(cand, static_cast<int>(ncand), lo, scale, bin_sel, need, hist, sel, wtot, kth, copies);
+    for (int i = tid; i < static_cast<int>(ncand); i += NT) {
+      const float c = cand[i];
+      if (f2key(c) > kth) { s += c; q += static_cast<double>(c) * c; }
+    }
+  } else {
+    radix_kth<true, NT>(row, N, lo, scale, bin_sel, need, hist, sel, wtot, kth, copies);   // degenerate rows: re-read
+#pragma unroll
+    for (int j = 0; j < PER4 * 4; ++j) {
+      if (lin_bin(v[j], lo, scale) == bin_sel && f2key(v[j]) > kth) { s += v[j]; q += static_cast<double>(v[j]) * v[j]; }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) { red_s[wid] = s; red_q[wid] = q; }
+  __syncthreads();
+  if (tid == 0) {
+    double ts = 0.0, tq = 0.0;
+    for (int w = 0; w < NT / 32; ++w) { ts += red_s[w]; tq += red_q[w]; }
+    if (copies > 0) {
+      const double kv = key2f(kth);
+      ts += copies * kv;
+      tq += copies * kv * kv;
+    }
+    const double m = ts / K;
+    const double var = fmax(tq / K - m * m, 0.0);
+    mu[blockIdx.x] = static_cast<float>(m);
+    sigma[blockIdx.x] = static_cast<float>(sqrt(var));
+  }
+}
+
 // ---------------------------------------------------------------- AS-norm trial scores
 // emean [U, D]; out = 0.5 * ((s - mu_a)/sigma_a + (s - mu_b)/sigma_b), s = <emean_a, emean_b>.
 __global__ void asnorm_trials_kernel(const float* __restrict__ emean, int D, const int32_t* __restrict__ ia,
@@ -192,13 +501,49 @@ int mean_rows(const float* emb, int U, int n, int D, int normalize, float* out, 
 
 static size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 
+// Workspace plan.  The U x N score matrix is never materialised as a whole: it is produced in row chunks of at
+// most S_CHUNK_BYTES (about one L2's worth, so most of a chunk is still cache resident when the selection
+// kernel reads it back, once).  Measured (profiles/r01_scoring.md): 40 MB chunks keep S fully in L2 but cost
+// more in per-launch fill/drain of the 9-k-block GEMM tiles than the DRAM round trip of 133 MB chunks.
+static const size_t S_CHUNK_BYTES = 144u << 20;
+static const int TOPK_SMEM_MAX_N = 50000;   // row cached in smem (<= 200 KB)
+
+struct AsnormPlan { int Dp, Np, chunk; size_t o_w, o_zeros, o_ones, o_a, o_s, total; };
+
+static AsnormPlan asnorm_plan(int U, int N, int D) {
+  AsnormPlan p{};
+  p.Dp = (D + 63) / 64 * 64;
+  p.Np = (N + 63) / 64 * 64;
+  // rows per chunk: a multiple of 128 that keeps S within S_CHUNK_BYTES and fills whole waves of the
+  // persistent GEMM (tiles / (ceil(tiles / SMs) * SMs) maximal)
+  const long long cap = std::max<long long>(1, static_cast<long long>(S_CHUNK_BYTES / (static_cast<size_t>(p.Np) * 4)) / 128);
+  const long long all = (static_cast<long long>(U) + 127) / 128;
+  const int n_tiles = (p.Np + 255) / 256, sms = std::max(1, num_sms());
+  long long best = std::min(cap, all);
+  if (all > cap) {
+    double best_eff = 0.0;
+    for (long long mt = std::max<long long>(1, cap / 2); mt <= cap; ++mt) {
+      const long long tiles = mt * n_tiles;
+      const double eff = static_cast<double>(tiles) / (static_cast<double>((tiles + sms - 1) / sms) * sms);
+      if (eff >= best_eff) { best_eff = eff; best = mt; }
+    }
+  }
+  p.chunk = static_cast<int>(best * 128);
+  const size_t Upad = (static_cast<size_t>(U) + 127) / 128 * 128;
+  size_t o = 0;
+  p.o_w = o; o += align256(static_cast<size_t>(N) * 2 * p.Dp * 2);
+  p.o_zeros = o; o += align256(static_cast<size_t>(p.Np) * 4);
+  p.o_ones = o; o += align256(static_cast<size_t>(p.Np) * 4);
+  p.o_a = o; o += align256(Upad * 2 * p.Dp * 2);
+  p.o_s = o; o += align256(static_cast<size_t>(p.chunk) * p.Np * 4);
+  p.total = o;
+  return p;
+}
+
 size_t asnorm_workspace_bytes(int U, int N, int D, int* chunk_out) {
-  const int Dp = (D + 63) / 64 * 64, Np = (N + 31) / 32 * 32;
-  const size_t fixed = align256(static_cast<size_t>(N) * 2 * Dp * 2) + 3 * align256(static_cast<size_t>(Np) * 4);
-  long long chunk = std::min<long long>(U, std::max<long long>(128, (1LL << 30) / (static_cast<long long>(Np) * 4)));
-  chunk = (chunk + 127) / 128 * 128;
-  if (chunk_out) *chunk_out = static_cast<int>(chunk);
-  return fixed + align256(static_cast<size_t>(chunk) * 2 * Dp * 2) + align256(static_cast<size_t>(chunk) * Np * 4);
+  const AsnormPlan p = asnorm_plan(U, N, D);
+  if (chunk_out) *chunk_out = p.chunk;
+  return p.total;
 }
 
 // mu/sigma of the top-K cohort scores of every row of emean [U, D].
@@ -208,35 +553,51 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
   if (K < 0) K = N + K;            // numpy slice semantics of S[::-1][:top] (top=-1 drops the smallest)
   if (K > N) K = N;
   SVB_CHECK(K >= 1, "top-K must select at least one cohort score (N=%d, top=%d)", N, topk);
-  int chunk = 0;
-  const size_t need = asnorm_workspace_bytes(U, N, D, &chunk);
-  SVB_CHECK(ws != nullptr && ws_bytes >= need, "AS-norm workspace too small: need %zu bytes, got %zu", need, ws_bytes);
-  const int Dp = (D + 63) / 64 * 64, Np = (N + 31) / 32 * 32;
-  uint8_t* p = static_cast<uint8_t*>(ws);
-  bf16* wpk = reinterpret_cast<bf16*>(p); p += align256(static_cast<size_t>(N) * 2 * Dp * 2);
-  float* zeros = reinterpret_cast<float*>(p); p += align256(static_cast<size_t>(Np) * 4);
-  float* ones = reinterpret_cast<float*>(p); p += align256(static_cast<size_t>(Np) * 4);
-  p += align256(static_cast<size_t>(Np) * 4);
-  bf16* a16 = reinterpret_cast<bf16*>(p); p += align256(static_cast<size_t>(chunk) * 2 * Dp * 2);
-  float* S = reinterpret_cast<float*>(p);
-  // cohort [N, D] is a k=1 "conv weight" [cout=N, cin=D, 1]
+  const AsnormPlan pl = asnorm_plan(U, N, D);
+  SVB_CHECK(ws != nullptr && ws_bytes >= pl.total, "AS-norm workspace too small: need %zu bytes, got %zu", pl.total,
+            ws_bytes);
+  const int Dp = pl.Dp, Np = pl.Np, chunk = pl.chunk;
+  uint8_t* base = static_cast<uint8_t*>(ws);
+  bf16* wpk = reinterpret_cast<bf16*>(base + pl.o_w);
+  float* zeros = reinterpret_cast<float*>(base + pl.o_zeros);
+  float* ones = reinterpret_cast<float*>(base + pl.o_ones);
+  bf16* a16 = reinterpret_cast<bf16*>(base + pl.o_a);
+  float* S = reinterpret_cast<float*>(base + pl.o_s);
+  // cohort [N, D] is a k=1 "conv weight" [cout=N, cin=D, 1]; embeddings are split into hi|lo planes once
   if (pack_conv_weight(cohort, N, D, 1, Dp, 2, wpk, stream)) return -1;
   fill_kernel<<<(Np + 255) / 256, 256, 0, stream>>>(zeros, Np, 0.f);
   fill_kernel<<<(Np + 255) / 256, 256, 0, stream>>>(ones, Np, 1.f);
   count_launch(2);
+  const size_t Upad = (static_cast<size_t>(U) + 127) / 128 * 128;
+  SVB_CUDA_OK(cudaMemsetAsync(a16, 0, Upad * 2 * Dp * 2, stream));
+  if (split_bf16(emean, U, D, D, a16, 2 * Dp, 2, Dp, stream)) return -1;
+  const bool smem_rows = N <= TOPK_SMEM_MAX_N;
+  if (smem_rows) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      SVB_CUDA_OK(cudaFuncSetAttribute(topk_stats_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       TOPK_SMEM_MAX_N * 4));
+      attr_set = true;
+    }
+  }
   for (int u0 = 0; u0 < U; u0 += chunk) {
     const int rows = std::min(chunk, U - u0);
-    SVB_CUDA_OK(cudaMemsetAsync(a16, 0, static_cast<size_t>(rows) * 2 * Dp * 2, stream));
-    if (split_bf16(emean + static_cast<long long>(u0) * D, rows, D, D, a16, 2 * Dp, 2, Dp, stream)) return -1;
     GemmOperands ops{};
-    ops.a = a16; ops.lda = 2 * Dp; ops.a_cols = 2 * Dp;
+    ops.a = a16 + static_cast<size_t>(u0) * 2 * Dp; ops.lda = 2 * Dp; ops.a_cols = 2 * Dp;
     ops.w = wpk; ops.w_rows = N; ops.w_cols = 2 * Dp;
     GemmParams g{};
     g.M = rows; g.N = Np; g.kc_per_tap = Dp / 64; g.num_taps = 1; g.tap_off[0] = 0; g.num_pass = 3;
     g.a_plane_cols = Dp; g.w_planes = 2; g.bias = zeros; g.scale = ones; g.shift = zeros;
     g.act = ACT_NONE; g.store_mode = STORE_ALL; g.out = S; g.out_ld = Np; g.out_kind = OUT_F32;
-    if (launch_gemm(ops, g, Np >= 256 ? 256 : (Np >= 128 ? 128 : 64), stream)) return -1;
-    topk_stats_kernel<<<rows, 256, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+    if (launch_gemm_f32(ops, g, stream)) return -1;
+    if (N <= 512 * 16)
+      topk_stats_reg_kernel<4, 512><<<rows, 512, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+    else if (N <= 1024 * 24)
+      topk_stats_reg_kernel<6, 1024><<<rows, 1024, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+    else if (smem_rows)
+      topk_stats_smem_kernel<<<rows, 512, static_cast<size_t>(Np) * 4, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+    else
+      topk_stats_kernel<<<rows, 256, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
     count_launch();
     SVB_CUDA_OK(cudaGetLastError());
   }

@@ -77,6 +77,10 @@ struct GemmParams {
 // 2D bf16 row-major matrix [rows, ld] exposing `cols` columns as a TMA map; box = [64 cols, box_rows], 128B swizzle.
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 
+int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
+// Plain fp32-output GEMM out[M, N] = A * W^T through the TMA-store epilogue of gemm_pw.cu (N % 64 == 0).
+int launch_gemm_f32(const GemmOperands& ops, const GemmParams& p, cudaStream_t stream);
+
 // Launches the persistent tcgen05 GEMM.  block_n in {64, 128, 256}.
 int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream);
 
