@@ -121,8 +121,51 @@ def make(channels, n_out, tag, n_spk=16, per_spk=4, n_trials=1000, n_cohort=300,
     print("wrote", path, os.path.getsize(path) // 1024, "KiB")
 
 
+def make_rawnet(tag="cfg4_rawnet2", n_spk=4, per_spk=4, n_out=512, L4=64000):
+    """RawNet2_custom (sinc + GRU, 4 s crops): embeddings through the reference's
+    SpeakerEncoder(features='raw') and strided per-stage dumps for utterance 0."""
+    ref_loader.load()
+    net, handle, args = ref_loader.build([512] * 4 + [1536], n_out, sentence_len=4.0, features="raw",
+                                         model_name="RawNet2_custom")
+    sd = synth.rawnet2_state_dict(n_out, L4)
+    _load_weights(net, sd)
+    waves, spk = synth.utterance_set(n_spk, per_spk, L4)
+    bn = _calibrate_bn(net, waves, batch=8)
+    out = {"bn/" + k: v for k, v in bn.items()}
+    S = net.module.__S__
+    store = {}
+    hs = [S.first_bn.register_forward_hook(lambda m, i, o: store.__setitem__("front", torch.nn.functional.leaky_relu(o.detach(), 0.3)))]
+    for li in range(6):
+        hs.append(getattr(S, "layer%d" % (li + 1)).register_forward_hook(
+            lambda m, i, o, li=li: store.__setitem__("layer%d" % (li + 1), o.detach())))
+    hs.append(S.gru.register_forward_hook(lambda m, i, o: store.__setitem__("gru", o[0][:, -1, :].detach())))
+    with torch.no_grad():
+        emb = net(torch.from_numpy(waves))
+    for h in hs:
+        h.remove()
+    out["emb_batch"] = emb.numpy()
+    out["stage/front"] = store["front"][0, ::8, ::25].numpy()
+    for li in range(6):
+        k = "layer%d" % (li + 1)
+        step = max(1, store[k].shape[2] // 400)
+        out["stage/" + k] = store[k][0, ::8, ::step].numpy()
+    out["stage/gru"] = store["gru"].numpy()
+    # cosine trial scores over all pairs (src/utils.py:163-164, n = 1 crop per utterance)
+    _, ref_utils = ref_loader.load()
+    lab, ti, tj = synth.trial_list(spk, 120)
+    out["scores_cos"] = np.asarray([float(ref_utils.cosine_similarity(emb[i:i + 1], emb[j:j + 1])) for i, j in zip(ti, tj)])
+    path = os.path.join(GOLD, "%s.npz" % tag)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count())
-    make([512, 512, 512, 512, 1536], 192, "cfg1_c512")
-    make([1024, 1024, 1024, 1024, 3072], 192, "cfg2_c1024")
+    which = sys.argv[1:] or ["cfg1", "cfg2", "cfg4"]
+    if "cfg1" in which:
+        make([512, 512, 512, 512, 1536], 192, "cfg1_c512")
+    if "cfg2" in which:
+        make([1024, 1024, 1024, 1024, 3072], 192, "cfg2_c1024")
+    if "cfg4" in which:
+        make_rawnet()

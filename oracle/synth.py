@@ -156,3 +156,94 @@ def scoring_embeddings(n_utts, n_speakers, dim=192, noise=0.7, seed=3):
     e = cent[spk] + noise * rng.standard_normal((n_utts, dim)) / np.sqrt(dim)
     e /= np.linalg.norm(e, axis=1, keepdims=True)
     return e.astype(np.float32), spk
+
+
+# --------------------------------------------------------------------------------------
+# RawNet2 state dict in the reference's checkpoint layout
+# --------------------------------------------------------------------------------------
+RAWNET_LAYERS = [1, 1, 1, 2, 1, 2]
+RAWNET_FILTERS = [128, 128, 256, 256, 512, 512]
+
+
+def rawnet2_param_shapes(n_out=512, n_samples=64000, gru_node=1024, prefix="__S__."):
+    """Ordered (key, shape, kind) list matching RawNet2_custom.MainModel's state-dict (144 entries)."""
+    out = []
+
+    def bn(p, c):
+        out.append((p + "weight", (c,), "g"))
+        out.append((p + "bias", (c,), "beta"))
+        out.append((p + "running_mean", (c,), "rm"))
+        out.append((p + "running_var", (c,), "rv"))
+        out.append((p + "num_batches_tracked", (), "nbt"))
+
+    P = prefix
+    out.append((P + "ln.gamma", (n_samples,), "g"))
+    out.append((P + "ln.beta", (n_samples,), "beta"))
+    out.append((P + "first_conv.low_hz_", (RAWNET_FILTERS[0], 1), "sinc_low"))
+    out.append((P + "first_conv.band_hz_", (RAWNET_FILTERS[0], 1), "sinc_band"))
+    bn(P + "first_bn.", RAWNET_FILTERS[0])
+    inpl = RAWNET_FILTERS[0]
+    for li, (nb, planes) in enumerate(zip(RAWNET_LAYERS, RAWNET_FILTERS)):
+        for bi in range(nb):
+            p = P + "layer%d.%d." % (li + 1, bi)
+            bn(p + "bn1.", inpl)
+            out.append((p + "conv1.weight", (planes, inpl, 3), "w"))
+            bn(p + "bn2.", planes)
+            out.append((p + "conv2.weight", (planes, planes, 3), "w"))
+            out.append((p + "afms.alpha", (planes, 1), "g"))
+            out.append((p + "afms.fc.weight", (planes, planes), "lin"))
+            out.append((p + "afms.fc.bias", (planes,), "b"))
+            if inpl != planes:
+                out.append((p + "shortcut.0.weight", (planes, inpl, 1), "w"))
+            inpl = planes
+    bn(P + "bn_before_gru.", RAWNET_FILTERS[5])
+    out.append((P + "gru.weight_ih_l0", (3 * gru_node, RAWNET_FILTERS[5]), "gru"))
+    out.append((P + "gru.weight_hh_l0", (3 * gru_node, gru_node), "gru"))
+    out.append((P + "gru.bias_ih_l0", (3 * gru_node,), "gru"))
+    out.append((P + "gru.bias_hh_l0", (3 * gru_node,), "gru"))
+    out.append((P + "fc_after_gru.weight", (n_out, gru_node), "lin"))
+    out.append((P + "fc_after_gru.bias", (n_out,), "b"))
+    out.append((P + "fc.weight", (n_out, 2 * RAWNET_FILTERS[5]), "lin"))
+    out.append((P + "fc.bias", (n_out,), "b"))
+    return out
+
+
+def rawnet2_state_dict(n_out=512, n_samples=64000, gru_node=1024, seed=4321, bn_stats=None, sample_rate=16000):
+    """Random RawNet2 weights (numpy float32) under the reference's key names; sinc bands start from the
+    reference's mel-spaced initialisation (RawNet_baseline.py:296-309) with a seeded perturbation."""
+    rng = np.random.default_rng(seed)
+    sd = {}
+    to_mel = lambda hz: 2595 * np.log10(1 + hz / 700)
+    to_hz = lambda mel: 700 * (10 ** (mel / 2595) - 1)
+    hz = to_hz(np.linspace(to_mel(10), to_mel(sample_rate / 2 - 100), RAWNET_FILTERS[0] + 1))
+    for key, shape, kind in rawnet2_param_shapes(n_out, n_samples, gru_node):
+        if kind == "w":
+            fan_in = shape[1] * shape[2]
+            v = rng.uniform(-1.0, 1.0, size=shape) * np.sqrt(4.5 / fan_in)
+        elif kind == "lin":
+            v = rng.uniform(-1.0, 1.0, size=shape) * np.sqrt(3.0 / shape[1])
+        elif kind == "gru":
+            v = rng.uniform(-1.0, 1.0, size=shape) / np.sqrt(gru_node)
+        elif kind == "b":
+            v = rng.uniform(-0.1, 0.1, size=shape)
+        elif kind == "g":
+            v = rng.uniform(0.5, 1.5, size=shape)
+        elif kind == "beta":
+            v = 0.1 * rng.standard_normal(shape)
+        elif kind == "rm":
+            v = 0.1 * rng.standard_normal(shape)
+        elif kind == "rv":
+            v = rng.uniform(0.5, 1.5, size=shape)
+        elif kind == "sinc_low":
+            v = (hz[:-1] * rng.uniform(0.9, 1.1, size=hz[:-1].shape)).reshape(shape)
+        elif kind == "sinc_band":
+            v = (np.diff(hz) * rng.uniform(0.8, 1.2, size=hz[:-1].shape)).reshape(shape)
+        else:
+            sd[key] = np.asarray(1, dtype=np.int64)
+            continue
+        sd[key] = v.astype(np.float32)
+    if bn_stats:
+        for k, v in bn_stats.items():
+            assert k in sd and sd[k].shape == v.shape, k
+            sd[k] = np.asarray(v, dtype=np.float32)
+    return sd
