@@ -148,6 +148,35 @@ int svb_ecapa_forward(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, c
 int svb_ecapa_forward_mel(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* b, const float* mel_rows,
                           void* ws, size_t ws_bytes, float* emb, int emb_ld, int l2norm, void* stream);
 
+/* ------------------------------------------------------------------ RawNet2 raw-waveform encoder
+ * Replaces models.RawNet2_custom.MainModel.forward (src/models/RawNet2_custom.py:161-227, defaults
+ * front_proc='sinc', aggregate='gru', layers [1,1,1,2,1,2], filters [128,128,256,256,512,512], :230-243) behind
+ * SpeakerEncoder.forward with features == 'raw' (src/model.py:104-129): LayerNorm over samples, SincConv_fast +
+ * |.| + max_pool1d(3) + first_bn + LeakyReLU(0.3), eight RawNetBasicBlocks with AFMS
+ * (src/models/RawNet_baseline.py:13-24, 48-68, 181-361), bn_before_gru, GRU(512 -> gru_node) last state,
+ * fc_after_gru.  Weights: fp32 DEVICE pointers in the reference checkpoint layout keyed by state-dict name
+ * without the "__S__." prefix ("ln.gamma", "first_conv.low_hz_", "layer3.0.shortcut.0.weight", ...).
+ * Every utterance has exactly n_samples samples (ln.gamma / ln.beta have that length in the reference). */
+typedef struct SvbRawnet2 SvbRawnet2;
+typedef struct SvbRawnet2Cfg {
+  int32_t n_samples;       /* audio_spec.sentence_len * sample_rate (64 000 for 4 s at 16 kHz) */
+  int32_t n_out;           /* code_dim / nOut */
+  int32_t gru_node;        /* 1024 */
+  int32_t sample_rate;
+  int32_t fp32_mode;       /* 0: bf16 tensor-core operands; 1: split-bf16 (fp32-grade parity mode) */
+} SvbRawnet2Cfg;
+int svb_rawnet2_create(const SvbRawnet2Cfg* cfg, const char* const* names, const void* const* ptrs, int n,
+                       SvbRawnet2** out);
+void svb_rawnet2_destroy(SvbRawnet2* e);
+size_t svb_rawnet2_workspace_bytes(const SvbRawnet2* e, int B);
+/* byte offset of a named intermediate inside the workspace (tests / profiling), -1 if unknown */
+int64_t svb_rawnet2_ws_offset(const SvbRawnet2* e, int B, const char* name);
+/* frames entering residual block `level` (0..7); level 8 = frames entering the GRU */
+int32_t svb_rawnet2_frames(const SvbRawnet2* e, int level);
+/* wav [B, wav_ld] fp32 (device) -> emb [B, emb_ld] fp32; l2norm != 0 applies F.normalize (src/model.py:422-423) */
+int svb_rawnet2_forward(const SvbRawnet2* e, const float* wav, int64_t wav_ld, int B, void* ws, size_t ws_bytes,
+                        float* emb, int emb_ld, int l2norm, void* stream);
+
 /* ------------------------------------------------------------------ trial scoring (K8/K9)
  * emb: [U, n_per_utt, D] fp32 crop embeddings of the U unique utterances; idx_a/idx_b: int32 indices
  * of the enrol / test utterance of every trial.

@@ -107,3 +107,42 @@ def rawnet2_forward(wave, sd, prefix="__S__.", stages=None, sample_rate=16000):
         stages["gru"] = h
     out = F.linear(h, sd[P + "fc_after_gru.weight"], sd[P + "fc_after_gru.bias"])         # :198
     return out.squeeze()
+
+
+# ------------------------------------------------------------------ bf16-operand emulation
+def _r(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def rawnet2_forward_bf16emu(wave, sd, prefix="__S__.", sample_rate=16000):
+    """The same network with every stored activation and every tensor-core weight rounded to bfloat16 exactly
+    where libsvb's bf16 mode rounds (fp32 accumulation, fp32 BN / AFMS / GRU-gate arithmetic, hi+lo split of the
+    normalised waveform, fp32-grade GRU recurrence).  It separates two things the fp32 comparison mixes: whether
+    the kernels compute what bf16 operands imply (this function, tight tolerance) and how far bf16 operands drift
+    from fp32 on a given checkpoint (a property of the checkpoint, loose tolerance)."""
+    sd = {k: torch.as_tensor(v) for k, v in sd.items()}
+    P = prefix
+    x = torch.as_tensor(wave, dtype=torch.float32)
+    x = layer_norm_samples(x, sd[P + "ln.gamma"], sd[P + "ln.beta"])
+    xh = _r(x)
+    x = xh + _r(x - xh)
+    filt = _r(sinc_filters(sd[P + "first_conv.low_hz_"], sd[P + "first_conv.band_hz_"], sample_rate=sample_rate))
+    v = F.max_pool1d(torch.abs(F.conv1d(x.unsqueeze(1), filt.unsqueeze(1))), 3)
+    v = F.leaky_relu(_bn(v, sd, P + "first_bn."), 0.3)
+    names = [(li + 1, bi, bi == nb - 1) for li, nb in enumerate(LAYERS) for bi in range(nb)]
+    pre = [P + "layer%d.%d.bn1." % (l, b) for l, b, _ in names] + [P + "bn_before_gru."]
+    x_r, a_r = _r(v), _r(F.leaky_relu(_bn(v, sd, pre[0]), 0.3))
+    for i, (l, b, down) in enumerate(names):
+        p = P + "layer%d.%d." % (l, b)
+        h = _r(F.leaky_relu(_bn(F.conv1d(a_r, _r(sd[p + "conv1.weight"]), padding=1), sd, p + "bn2."), 0.3))
+        sc = _r(F.conv1d(a_r, _r(sd[p + "shortcut.0.weight"]))) if (p + "shortcut.0.weight") in sd else x_r
+        z = _r(F.conv1d(h, _r(sd[p + "conv2.weight"]), padding=1) + sc)
+        if down:
+            z = F.max_pool1d(z, 3)
+        y = torch.sigmoid(F.linear(z.mean(dim=2), sd[p + "afms.fc.weight"], sd[p + "afms.fc.bias"])).unsqueeze(-1)
+        v = (z + sd[p + "afms.alpha"]) * y
+        x_r, a_r = _r(v), _r(F.leaky_relu(_bn(v, sd, pre[i + 1]), 0.3))
+    gsd = dict(sd)
+    gsd[P + "gru.weight_ih_l0"] = _r(sd[P + "gru.weight_ih_l0"])
+    h = gru_last(a_r.permute(0, 2, 1), gsd, P + "gru.")
+    return F.linear(h, sd[P + "fc_after_gru.weight"], sd[P + "fc_after_gru.bias"]).squeeze()

@@ -74,6 +74,10 @@ class SvbEcapaCfg(_c.Structure):
                 ("dilations", _i32 * 5), ("fp32_mode", _i32)]
 
 
+class SvbRawnet2Cfg(_c.Structure):
+    _fields_ = [("n_samples", _i32), ("n_out", _i32), ("gru_node", _i32), ("sample_rate", _i32), ("fp32_mode", _i32)]
+
+
 _pp = _c.POINTER(_vp)
 _EXTRA_SIGS = {
     "svb_batch_create": ([_vp, _vp, _i32, _i32, _i32, _pp], _i32),
@@ -98,6 +102,12 @@ _EXTRA_SIGS = {
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
     "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
     "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),
+    "svb_rawnet2_create": ([_c.POINTER(SvbRawnet2Cfg), _c.POINTER(_c.c_char_p), _c.POINTER(_vp), _i32, _pp], _i32),
+    "svb_rawnet2_destroy": ([_vp], None),
+    "svb_rawnet2_workspace_bytes": ([_vp, _i32], _c.c_size_t),
+    "svb_rawnet2_ws_offset": ([_vp, _i32, _c.c_char_p], _i64),
+    "svb_rawnet2_frames": ([_vp, _i32], _i32),
+    "svb_rawnet2_forward": ([_vp, _vp, _i64, _i32, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
     "svb_version": ([], _i32),
     "svb_reset_launch_count": ([], None),
 }

@@ -40,6 +40,13 @@ size_t asnorm_workspace_bytes(int, int, int, int*);
 int asnorm_stats(const float*, int, const float*, int, int, int, float*, float*, void*, size_t, cudaStream_t);
 int asnorm_trials(const float*, int, const int32_t*, const int32_t*, long long, const float*, const float*, float*,
                   cudaStream_t);
+struct Rawnet2;
+int rawnet2_create(int, int, int, int, int, const char* const*, const void* const*, int, Rawnet2**);
+void rawnet2_destroy(Rawnet2*);
+size_t rawnet2_workspace_bytes(const Rawnet2*, int);
+long long rawnet2_ws_offset(const Rawnet2*, int, const char*);
+int rawnet2_frames(const Rawnet2*, int);
+int rawnet2_forward(const Rawnet2*, const float*, long long, int, void*, size_t, float*, int, int, cudaStream_t);
 }  // namespace svb
 
 using namespace svb;
@@ -253,6 +260,32 @@ int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int
   if (check_device()) return -1;
   SVB_CHECK(emean && idx_a && idx_b && mu && sigma && out, "bad argument");
   return asnorm_trials(emean, D, idx_a, idx_b, n_trials, mu, sigma, out, static_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------- RawNet2
+int svb_rawnet2_create(const SvbRawnet2Cfg* cfg, const char* const* names, const void* const* ptrs, int n,
+                       SvbRawnet2** out) {
+  if (check_device()) return -1;
+  SVB_CHECK(cfg && names && ptrs && out && n > 0, "bad argument");
+  return rawnet2_create(cfg->n_samples, cfg->n_out, cfg->gru_node, cfg->sample_rate, cfg->fp32_mode, names, ptrs, n,
+                        reinterpret_cast<Rawnet2**>(out));
+}
+void svb_rawnet2_destroy(SvbRawnet2* e) { rawnet2_destroy(reinterpret_cast<Rawnet2*>(e)); }
+size_t svb_rawnet2_workspace_bytes(const SvbRawnet2* e, int B) {
+  return (e && B > 0) ? rawnet2_workspace_bytes(reinterpret_cast<const Rawnet2*>(e), B) : 0;
+}
+int64_t svb_rawnet2_ws_offset(const SvbRawnet2* e, int B, const char* name) {
+  return (e && name) ? rawnet2_ws_offset(reinterpret_cast<const Rawnet2*>(e), B, name) : -1;
+}
+int32_t svb_rawnet2_frames(const SvbRawnet2* e, int level) {
+  return e ? rawnet2_frames(reinterpret_cast<const Rawnet2*>(e), level) : -1;
+}
+int svb_rawnet2_forward(const SvbRawnet2* e, const float* wav, int64_t wav_ld, int B, void* ws, size_t ws_bytes,
+                        float* emb, int emb_ld, int l2norm, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(e && wav && ws && emb && B > 0, "bad argument");
+  return rawnet2_forward(reinterpret_cast<const Rawnet2*>(e), wav, wav_ld, B, ws, ws_bytes, emb, emb_ld, l2norm,
+                         static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

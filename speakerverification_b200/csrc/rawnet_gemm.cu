@@ -1,0 +1,350 @@
+// tcgen05 implicit-GEMM kernels for the RawNet2 raw-waveform encoder (reference:
+// src/models/RawNet2_custom.py:161-227, src/models/RawNet_baseline.py:181-361).
+//
+// Same persistent warp-specialised skeleton as gemm_tc.cu (warp 0 TMA producer, warp 1 tcgen05.mma issuer,
+// fp32 accumulators double buffered in TMEM, 8 epilogue warps); what is specific to RawNet2 is the operand view
+// of the first layer and the epilogues:
+//
+//  EPI_SINC   SincConv_fast (128 band-pass FIRs x 251 taps, stride 1, RawNet_baseline.py:339-361) + abs +
+//             max_pool1d(3) + first_bn + LeakyReLU(0.3) (RawNet2_custom.py:171-176) and layer1's bn1 + LeakyReLU
+//             (RawNet_baseline.py:221).  The conv is a GEMM over a SLIDING-WINDOW view of the normalised
+//             waveform: A row m = samples [48 m, 48 m + 320) -- a TMA map whose row stride (96 B) is smaller
+//             than its row extent (profiles/r01_tma_overlap_probe.txt) -- against 48 shifted copies of every
+//             filter (W'[(jg, f, ph), k'] = h[f, k' - (3 jg + ph)]), so one accumulator row holds outputs
+//             t = 48 m .. 48 m + 47 of all filters, ordered so that the three phases of a pooling window are
+//             adjacent columns: the max-pool is a 3-column max inside one thread.  No im2col, no [B,128,63750]
+//             intermediate in HBM (the reference writes 32.6 MB per utterance there).
+//  EPI_AFF_LRELU   conv1 of a RawNetBasicBlock: lrelu(bn2(conv1(a)))  (RawNet_baseline.py:223-224)
+//  EPI_ADD         conv2 + shortcut                                    (RawNet_baseline.py:224-225)
+//  EPI_PLAIN       1x1 shortcut conv                                    (RawNet_baseline.py:213-217,222)
+//
+// Activations are time-major rows [utt][1 zero row | T rows | 1 zero row][C] bf16: the zero rows ARE the conv's
+// zero padding, so the k=3 taps are row-shifted TMA loads.  Every tensor is one bf16 plane in bf16 mode and
+// hi|lo planes in fp32-grade mode (operand and residual-carrier plane counts are separate parameters).  T is the same for
+// every utterance (the model's LayerNorm weights fix the input length, RawNet_baseline.py:13-24), so
+// utterance / frame of a row are computed arithmetically.
+#include "svb_internal.h"
+#include "svb_ptx.cuh"
+
+namespace svb {
+
+static constexpr int BLOCK_M = 128;
+static constexpr int BLOCK_K = 64;
+static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
+static constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
+
+enum { EPI_SINC = 0, EPI_AFF_LRELU = 1, EPI_ADD = 2, EPI_PLAIN = 3 };
+
+template <int BN>
+struct RnCfg {
+  static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = (BN >= 192) ? 4 : 6;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
+  static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;   // power of two
+};
+
+__device__ __forceinline__ float lrelu03(float x) { return x > 0.f ? x : 0.3f * x; }
+
+// 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// n consecutive fp32 values -> bf16 hi (and lo = v - hi) planes at dst / dst + plane_cols (N multiple of 8)
+template <int N>
+__device__ __forceinline__ void store_planes(bf16* dst, int planes, int plane_cols, const float (&v)[N]) {
+  uint32_t hi[N / 2];
+#pragma unroll
+  for (int i = 0; i < N / 2; ++i) hi[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+  uint4* d = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+  for (int i = 0; i < N / 8; ++i) d[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
+  if (planes == 2) {
+    uint32_t lo[N / 2];
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i)
+      lo[i] = pack_bf16x2(v[2 * i] - bf16_lo_f(hi[i]), v[2 * i + 1] - bf16_hi_f(hi[i]));
+    uint4* dl = reinterpret_cast<uint4*>(dst + plane_cols);
+#pragma unroll
+    for (int i = 0; i < N / 8; ++i) dl[i] = make_uint4(lo[4 * i], lo[4 * i + 1], lo[4 * i + 2], lo[4 * i + 3]);
+  }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const RnGemmParams p) {
+  using Cfg = RnCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[STAGES];
+  __shared__ __align__(8) uint64_t tfull_bar[2];
+  __shared__ __align__(8) uint64_t tempty_bar[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+
+  const int num_m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  const int num_n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = num_m_tiles * num_n_tiles;
+  const int kc = p.kc_per_tap;
+  const int kb_per_tap = p.num_pass * kc;
+  const int num_kb = p.num_taps * kb_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tfull_bar[a]), 1);
+      mbar_init(smem_u32(&tempty_bar[a]), 8);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(&tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        // n fastest: consecutive CTAs share the A tile (L2), W is small and stays cache resident
+        const int m0 = (tile / num_n_tiles) * BLOCK_M;
+        const int n0 = (tile % num_n_tiles) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int tap = kb / kb_per_tap;
+          const int rem = kb - tap * kb_per_tap;
+          const int pass_i = rem / kc;
+          const int kcx = rem - pass_i * kc;
+          // 0: hi*hi   1: hi(A)*lo(W)   2: lo(A)*hi(W); two passes = split activations, bf16 weights (0 and 2)
+          const int pass = (p.num_pass == 2 && pass_i == 1) ? 2 : pass_i;
+          const int aplane = (pass == 2) ? 1 : 0;
+          const int wplane = (pass == 1) ? 1 : 0;
+          const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
+          const int a_row = m0 + p.tap_off[tap];
+          const int w_col = ((tap * p.w_planes + wplane) * kc + kcx) * BLOCK_K;
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          tma_load_2d(sa, &tmA, fb, a_col, a_row);
+          tma_load_2d(sa + A_STAGE_BYTES, &tmW, fb, w_col, n0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(smem_u32(&full_bar[stage]), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          umma_commit(smem_u32(&empty_bar[stage]));
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(smem_u32(&tfull_bar[acc]));
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================== epilogue
+    const int ew = warp - 4;
+    const int quad = ew & 3;   // TMEM lane quadrant of this warp
+    const int half = ew >> 2;  // column half of the tile
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m0 = (tile / num_n_tiles) * BLOCK_M;
+      const int nt = tile % num_n_tiles;
+      const int n0 = nt * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      const long long row = m0 + quad * 32 + lane;
+      const uint32_t tbase = tmem_base + acc * BN + (static_cast<uint32_t>(quad * 32) << 16);
+
+      if (EPI == EPI_SINC) {
+        // row = window index; this tile = pooled output jg of 64 filters; this warp half = 32 of them
+        const int utt = static_cast<int>(row / p.Mu);
+        const int ml = static_cast<int>(row - static_cast<long long>(utt) * p.Mu);
+        const int jg = nt >> 1;
+        const int f0 = (nt & 1) * 64 + half * 32;
+        const int t_out = 16 * ml + jg;
+        const bool valid = row < p.M && utt < p.B && t_out < p.T;
+        const long long orow = static_cast<long long>(utt) * p.Tp + 1 + t_out;
+        mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+        tc_fence_after();
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+          // 48 accumulator columns = 16 filters x 3 pooling phases
+          uint32_t ra[32];
+          uint32_t rb[16];
+          const uint32_t col = half * 96 + h2 * 48;
+          tmem_ld32(tbase + col, ra);
+          tmem_ld16(tbase + col + 32, rb);
+          tmem_ld_wait();
+          if (valid) {
+            float x0[16], a0[16];
+            const int f = f0 + h2 * 16;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              float c[3];
+#pragma unroll
+              for (int q = 0; q < 3; ++q) {
+                const int j = 3 * i + q;
+                c[q] = fabsf(__uint_as_float(j < 32 ? ra[j < 32 ? j : 0] : rb[j >= 32 ? j - 32 : 0]));
+              }
+              const float mx = fmaxf(c[0], fmaxf(c[1], c[2]));
+              const float x = lrelu03(fmaf(mx, __ldg(p.s1 + f + i), __ldg(p.h1 + f + i)));
+              x0[i] = x;
+              a0[i] = lrelu03(fmaf(x, __ldg(p.s2 + f + i), __ldg(p.h2 + f + i)));
+            }
+            store_planes<16>(p.out + orow * p.out_ld + f, p.out_planes, p.out_plane_cols, x0);
+            store_planes<16>(p.out2 + orow * p.out2_ld + f, p.out2_planes, p.out2_plane_cols, a0);
+          }
+        }
+      } else {
+        const int utt = static_cast<int>(row / p.Tp);
+        const int t = static_cast<int>(row - static_cast<long long>(utt) * p.Tp) - 1;
+        const bool in_m = row < p.M;
+        const bool valid = in_m && t >= 0 && t < p.T;
+        mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int col0 = half * (BN / 2) + c * 32;
+          uint32_t r[32];
+          tmem_ld32(tbase + col0, r);
+          tmem_ld_wait();
+          const int n = n0 + col0;
+          if (n >= p.N || !in_m) continue;
+          float v[32];
+          if (EPI == EPI_AFF_LRELU) {
+            // zero rows stay zero: they are the next conv's padding
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              v[i] = valid ? lrelu03(fmaf(__uint_as_float(r[i]), __ldg(p.s1 + n + i), __ldg(p.h1 + n + i))) : 0.f;
+            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          } else if (EPI == EPI_ADD) {
+            if (!valid) continue;
+            const bf16* ap = p.add + row * p.add_ld + n;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap) + i);
+              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                v[8 * i + 2 * q] = __uint_as_float(r[8 * i + 2 * q]) + bf16_lo_f(w[q]);
+                v[8 * i + 2 * q + 1] = __uint_as_float(r[8 * i + 2 * q + 1]) + bf16_hi_f(w[q]);
+              }
+            }
+            if (p.add_planes == 2) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + p.add_plane_cols) + i);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  v[8 * i + 2 * q] += bf16_lo_f(w[q]);
+                  v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
+                }
+              }
+            }
+            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          } else {
+            if (!valid) continue;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ------------------------------------------------------------------ host side
+template <int BN, int EPI>
+static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const RnGemmParams& p, cudaStream_t stream) {
+  using Cfg = RnCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  rn_gemm_kernel<BN, EPI><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, w, p);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// a: activation matrix (or the sliding-window waveform view when epi == EPI_SINC: a_ld = 48, a_cols = extent)
+int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, long long a_ld, const bf16* w,
+                   int w_rows, int w_cols, const RnGemmParams& p, cudaStream_t stream) {
+  SVB_CHECK(p.num_pass >= 1 && p.num_pass <= 3, "num_pass must be 1, 2 or 3");
+  CUtensorMap ma, mw;
+  if (make_map(&ma, a, a_rows, a_cols, a_ld, BLOCK_M)) return -1;
+  if (epi == EPI_SINC) {
+    SVB_CHECK(p.N % 192 == 0, "sinc GEMM: N must be a multiple of 192");
+    if (make_map(&mw, w, w_rows, w_cols, w_cols, 192)) return -1;
+    return launch_rn_t<192, EPI_SINC>(ma, mw, p, stream);
+  }
+  SVB_CHECK(p.N % 128 == 0, "RawNet conv GEMM: N must be a multiple of 128");
+  const int bn = (p.N % 256 == 0) ? 256 : 128;
+  if (make_map(&mw, w, w_rows, w_cols, w_cols, bn)) return -1;
+  if (bn == 256) {
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, p, stream);
+    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, p, stream);
+    return launch_rn_t<256, EPI_PLAIN>(ma, mw, p, stream);
+  }
+  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, p, stream);
+  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, p, stream);
+  return launch_rn_t<128, EPI_PLAIN>(ma, mw, p, stream);
+}
+
+}  // namespace svb

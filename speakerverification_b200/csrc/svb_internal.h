@@ -74,6 +74,19 @@ struct GemmParams {
   void* out2; int out2_ld; int out2_plane_cols;
 };
 
+// RawNet2 GEMMs (rawnet_gemm.cu): fixed-length utterances, rows [utt][1 zero | T | 1 zero]
+struct RnGemmParams {
+  int M, N;
+  int kc_per_tap, num_taps, tap_off[3], num_pass, a_plane_cols, w_planes;
+  int T, Tp;               // valid rows per utterance / rows per utterance of the OUTPUT layout
+  int Mu, B;               // sinc: GEMM rows (48-sample windows) per utterance, utterances
+  const float *s1, *h1;    // affine applied to the accumulator (first_bn / bn2)
+  const float *s2, *h2;    // sinc: second affine (layer1 bn1) for the pre-activated copy
+  const bf16* add; int add_ld, add_planes, add_plane_cols;
+  bf16* out; int out_ld, out_planes, out_plane_cols;
+  bf16* out2; int out2_ld, out2_planes, out2_plane_cols;
+};
+
 // 2D bf16 row-major matrix [rows, ld] exposing `cols` columns as a TMA map; box = [64 cols, box_rows], 128B swizzle.
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 

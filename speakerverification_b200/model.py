@@ -19,11 +19,11 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from . import ecapa_tdnn, feature
+from . import ecapa_tdnn, feature, rawnet2_custom
 from . import utils as svb_utils
 from .audio_loader import loadWAV
 
-_ENCODERS = {"ECAPA_TDNN": ecapa_tdnn.MainModel}
+_ENCODERS = {"ECAPA_TDNN": ecapa_tdnn.MainModel, "RawNet2_custom": rawnet2_custom.MainModel}
 # losses of the reference whose constructor sets test_normalize = False (src/losses/Prototypical.py:21)
 # or leaves it unset (AttributeError -> False at src/model.py:90-94); every other loss sets True.
 _NO_TEST_NORMALIZE = {"Prototypical", "AngularPenaltySMLoss", "CircleLoss", "CircleLossV2", "GE2ELoss",
@@ -67,9 +67,12 @@ class SpeakerEncoder(nn.Module):
         self.device = torch.device(f"{device}:{self.gpu}")
         self.n_mels = kwargs["n_mels"]
         self.features = features.lower()
-        if self.features != "melspectrogram":
-            raise NotImplementedError("features=%r: only the mel-spectrogram front-end is on the accelerated path" % features)
-        self.compute_features = feature.melspectrogram(**kwargs).to(self.device)
+        if self.features == "melspectrogram":
+            self.compute_features = feature.melspectrogram(**kwargs).to(self.device)
+        elif self.features == "raw":
+            self.compute_features = None                     # src/model.py:64-65: raw-waveform encoders
+        else:
+            raise NotImplementedError("features=%r: only 'melspectrogram' and 'raw' are on the accelerated path" % features)
         name = self.model["name"]
         if not isinstance(name, str) or name not in _ENCODERS:
             raise NotImplementedError("model %r is outside the accelerated hot path (available: %s)" % (name, sorted(_ENCODERS)))
@@ -83,7 +86,7 @@ class SpeakerEncoder(nn.Module):
             raise NotImplementedError("include_top (classifier head) belongs to the training path")
 
     def engine(self):
-        return self.__S__.engine(self.compute_features.frontend())
+        return self.__S__.engine(self.compute_features.frontend() if self.compute_features is not None else None)
 
     def forward(self, data, label=None):
         """[*, L] waveform crops (host or device) -> [B, nOut]; same reshape and ``squeeze`` as src/model.py:104-129."""
