@@ -43,6 +43,32 @@ def model_args(device, precision):
                 augment=False, augment_options={"augment_chain": []}, mixedprec=False, svb_precision=precision)
 
 
+def rawnet_args(device, precision):
+    a = model_args(device, precision)
+    a.update(model={"name": "RawNet2_custom", "nOut": 512}, features="raw",
+             audio_spec={"sample_rate": 16000, "channels": 1, "sentence_len": 4.0, "win_len": 0.025, "hop_len": 0.01},
+             classifier={"input_size": 512, "out_neurons": 10})
+    return a
+
+
+def cpu_rawnet_rate(min_seconds, batch=8):
+    """Reference CPU path of RawNet2_custom (oracle port, fp32, all host threads): embeddings/s."""
+    from oracle import rawnet_oracle as ro, synth
+    torch.set_num_threads(os.cpu_count())
+    sd = synth.rawnet2_state_dict()
+    rng = np.random.default_rng(0)
+    waves = (0.1 * rng.standard_normal((batch, 64000))).astype(np.float32)
+    with torch.no_grad():
+        ro.rawnet2_forward(waves[:2], sd)
+        t0 = time.perf_counter()
+        done = 0
+        while time.perf_counter() - t0 < min_seconds or done == 0:
+            ro.rawnet2_forward(waves, sd)
+            done += batch
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -152,6 +178,24 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": "trials/s", "cores": os.cpu_count(), "kind": "port",
                              "sample": "%d trials, per-trial ZT_norm_similarity loop (numpy)" % n},
             "e2e": {"value": val, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    if args.workload == "rawnet2":
+        t0 = time.perf_counter()
+        n = 0
+        for _ in range(args.steps):
+            _, done, _ = cpu_rawnet_rate(3.0)
+            n += done
+        dt = time.perf_counter() - t0
+        val = n / dt
+        print(json.dumps({
+            "impl": "reference", "metric": "RawNet2 embeddings/sec (4 s utt)", "value": val, "unit": "embeddings/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "RawNet2_custom (sinc + GRU) nOut=512, 4 s 16 kHz utterances (configs[3])",
+                       "sample": "3 s of batches of 8 per step"},
+            "cpu_baseline": {"value": val, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
+                             "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port" % n},
+            "e2e": {"value": val, "unit": "embeddings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
     per_step = 128
     for _ in range(min(args.warmup, 1)):
@@ -324,7 +368,7 @@ def main():
     ap.add_argument("--batch-rows", type=int, default=256)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="embed", choices=["embed", "scoring"])
+    ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2"])
     ap.add_argument("--score-utts", type=int, default=200000)
     ap.add_argument("--score-cohort", type=int, default=20000)
     ap.add_argument("--score-trials", type=int, default=1000000)
@@ -358,11 +402,16 @@ def main():
     from speakerverification_b200 import _native as nv
     from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
     from oracle import synth
-    margs = model_args("cuda", args.precision)
+    rawnet = args.workload == "rawnet2"
+    global L, N_OUT, FLOP_PER_UTT
+    if rawnet:
+        L, N_OUT, FLOP_PER_UTT = 64000, 512, 13.96e9        # 13.96 GFLOP per 4 s crop
+    margs = rawnet_args("cuda", args.precision) if rawnet else model_args("cuda", args.precision)
     net = WrappedModel(SpeakerEncoder(**margs))
     handle = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=args.batch_rows))
     sd = net.module.state_dict()
-    for k, v in synth.ecapa_state_dict(CH, N_OUT).items():      # random-init weights of the named architecture
+    weights = synth.rawnet2_state_dict() if rawnet else synth.ecapa_state_dict(CH, N_OUT)
+    for k, v in weights.items():                                # random-init weights of the named architecture
         sd[k].copy_(torch.as_tensor(v))
     net.eval()
     eng = net.module.engine()
@@ -428,7 +477,47 @@ def main():
                "d2h_bytes_per_step": U * N_OUT * 4, "api": "ModelHandling.embed_batches(pinned host [U, L]) -> .cpu()"}
         assert out.shape == (U, N_OUT) and bool(torch.isfinite(out).all())
 
-    if rank == 0:
+    if rank == 0 and rawnet:
+        hbm, tf_burst, tf_sust, src = peaks()
+        # dominant kernel: the sliding-window sinc GEMM (front end = LayerNorm + sinc GEMM, timed alone)
+        os.environ["SVB_RAWNET_STOP"] = "-1"
+        wv = waves[:args.batch_rows]
+        for _ in range(3):
+            eng.forward(wv)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        for _ in range(10):
+            eng.forward(wv)
+        ev[1].record()
+        torch.cuda.synchronize()
+        del os.environ["SVB_RAWNET_STOP"]
+        front_ms = ev[0].elapsed_time(ev[1]) / 10
+        ach = 4.10e9 * wv.shape[0] / (front_ms * 1e-3) / 1e12
+        line = {
+            "metric": "RawNet2 embeddings/sec (4 s utt)", "value": value, "unit": "embeddings/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)", "data": "synthetic",
+            "config": {"workload": "RawNet2_custom (sinc front-end + 8 residual blocks + GRU) nOut=512, %d synthetic 4 s "
+                                   "16 kHz utterances per GPU (configs[3])" % U,
+                       "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
+                       "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * L * 4 / 1e9)},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"kernel": "rn_gemm_kernel<192,EPI_SINC> (+ LayerNorm kernel) of one %d-utterance launch" % wv.shape[0],
+                         "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
+                         "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": front_ms,
+                         "note": "algorithmic 4.10 GFLOP per utterance (SURVEY 8a a23); the GEMM executes 1.27x that "
+                                 "(K padded 251 -> 320)"},
+            "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
+                            "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
+                            "note": "whole step, algorithmic 13.96 GFLOP per utterance vs sustained bf16 peak"},
+        }
+        if world == 1:
+            rate, n, dt = cpu_rawnet_rate(12.0)
+            line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port (%.1f s)" % (n, dt)}
+        print(json.dumps(line))
+    elif rank == 0:
         hbm, tf_burst, tf_sust, src = peaks()
         ach, gemm_ms = gemm_roofline(device, args.batch_rows)
         line = {

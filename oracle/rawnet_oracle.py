@@ -116,16 +116,15 @@ def _r(t):
 
 def rawnet2_forward_bf16emu(wave, sd, prefix="__S__.", sample_rate=16000):
     """The same network with every stored activation and every tensor-core weight rounded to bfloat16 exactly
-    where libsvb's bf16 mode rounds (fp32 accumulation, fp32 BN / AFMS / GRU-gate arithmetic, hi+lo split of the
-    normalised waveform, fp32-grade GRU recurrence).  It separates two things the fp32 comparison mixes: whether
+    where libsvb's bf16 mode rounds (fp32 accumulation, fp32 BN / AFMS / GRU-gate arithmetic, fp32-grade GRU
+    recurrence).  It separates two things the fp32 comparison mixes: whether
     the kernels compute what bf16 operands imply (this function, tight tolerance) and how far bf16 operands drift
     from fp32 on a given checkpoint (a property of the checkpoint, loose tolerance)."""
     sd = {k: torch.as_tensor(v) for k, v in sd.items()}
     P = prefix
     x = torch.as_tensor(wave, dtype=torch.float32)
     x = layer_norm_samples(x, sd[P + "ln.gamma"], sd[P + "ln.beta"])
-    xh = _r(x)
-    x = xh + _r(x - xh)
+    x = _r(x)
     filt = _r(sinc_filters(sd[P + "first_conv.low_hz_"], sd[P + "first_conv.band_hz_"], sample_rate=sample_rate))
     v = F.max_pool1d(torch.abs(F.conv1d(x.unsqueeze(1), filt.unsqueeze(1))), 3)
     v = F.leaky_relu(_bn(v, sd, P + "first_bn."), 0.3)

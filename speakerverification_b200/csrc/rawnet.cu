@@ -186,31 +186,43 @@ rn_fc_kernel(const float* __restrict__ in, int nchunk, float in_scale, int Cin, 
 // K_apply: AFMS scaling (RawNet_baseline.py:64-66) and the NEXT pre-activation (bn1 / bn_before_gru + LeakyReLU 0.3).
 //   x = (zp + alpha[c]) * gate[u, c]  -> xo (valid rows; only when the next block's shortcut is the identity)
 //   a = lrelu(s[c] * x + h[c])        -> ao (zero on the padding rows)
+// grid (row chunks, utterances); a thread owns 8 channels (per-channel constants in registers) and walks rows.
 __global__ void __launch_bounds__(256)
 rn_apply_kernel(const bf16* __restrict__ zp, int zp_ld, int planes, int zp_plane_cols, int T, int C,
                 const float* __restrict__ alpha, const float* __restrict__ gate, const float* __restrict__ s,
                 const float* __restrict__ h, bf16* __restrict__ xo, int xo_ld, int xo_plane_cols, bf16* __restrict__ ao,
-                int ao_ld, int ao_planes, int ao_plane_cols, long long rows) {
-  const int cg = C / 8;
-  const long long idx = blockIdx.x * 256LL + threadIdx.x;
-  if (idx >= rows * cg) return;
-  const long long row = idx / cg;
-  const int c = static_cast<int>(idx - row * cg) * 8;
-  const int utt = static_cast<int>(row / (T + 2));
-  const int t = static_cast<int>(row - static_cast<long long>(utt) * (T + 2)) - 1;
-  float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (t >= 0 && t < T) {
-    float v[8];
-    load8(zp + row * zp_ld + c, planes, zp_plane_cols, v);
+                int ao_ld, int ao_planes, int ao_plane_cols, int rows_per_cta) {
+  const int cg = C >> 3;
+  const int utt = blockIdx.y;
+  const int g = threadIdx.x % cg, tl = threadIdx.x / cg, tstep = 256 / cg;
+  const int c = g * 8;
+  float al[8], gt[8], sc[8], sh[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float x = (v[i] + __ldg(alpha + c + i)) * __ldg(gate + static_cast<long long>(utt) * C + c + i);
-      v[i] = x;
-      a[i] = lrelu03(fmaf(x, __ldg(s + c + i), __ldg(h + c + i)));
-    }
-    if (xo != nullptr) store8(xo + row * xo_ld + c, planes, xo_plane_cols, v);
+  for (int i = 0; i < 8; ++i) {
+    al[i] = __ldg(alpha + c + i);
+    gt[i] = __ldg(gate + static_cast<long long>(utt) * C + c + i);
+    sc[i] = __ldg(s + c + i);
+    sh[i] = __ldg(h + c + i);
   }
-  store8(ao + row * ao_ld + c, ao_planes, ao_plane_cols, a);
+  const int r0 = blockIdx.x * rows_per_cta;                 // row inside the utterance: 0 .. T + 1 (t = r - 1)
+  const int r1 = min(T + 2, r0 + rows_per_cta);
+  const long long base = static_cast<long long>(utt) * (T + 2);
+  for (int r = r0 + tl; r < r1; r += tstep) {
+    const long long row = base + r;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (r >= 1 && r <= T) {
+      float v[8];
+      load8(zp + row * zp_ld + c, planes, zp_plane_cols, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float x = (v[i] + al[i]) * gt[i];
+        v[i] = x;
+        a[i] = lrelu03(fmaf(x, sc[i], sh[i]));
+      }
+      if (xo != nullptr) store8(xo + row * xo_ld + c, planes, xo_plane_cols, v);
+    }
+    store8(ao + row * ao_ld + c, ao_planes, ao_plane_cols, a);
+  }
 }
 
 // GRU gates (torch.nn.GRU cell): r = sig(gi_r + gh_r), z = sig(gi_z + gh_z), n = tanh(gi_n + r * gh_n),
@@ -238,6 +250,14 @@ rn_gru_gate_kernel(const float* __restrict__ gi, long long gi_row_stride, long l
   const bf16 hi = __float2bfloat16_rn(hnew);
   h16[static_cast<long long>(u) * h16_ld + j] = hi;
   h16[static_cast<long long>(u) * h16_ld + H + j] = __float2bfloat16_rn(hnew - __bfloat162float(hi));
+}
+
+// zero padding rows (first and last row of every utterance) of a [B * (T + 2), ld] matrix
+__global__ void rn_zero_halo_kernel(bf16* __restrict__ a, int ld, int T, int B) {
+  const int u = blockIdx.x >> 1, which = blockIdx.x & 1;
+  if (u >= B) return;
+  uint4* row = reinterpret_cast<uint4*>(a + (static_cast<long long>(u) * (T + 2) + (which ? T + 1 : 0)) * ld);
+  for (int i = threadIdx.x; i < ld / 8; i += blockDim.x) row[i] = make_uint4(0, 0, 0, 0);
 }
 
 __global__ void rn_fill_kernel(float* p, long long n, float v) {
@@ -537,18 +557,20 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
 
   // ---- front: LayerNorm -> sinc GEMM (+abs, maxpool3, first_bn, lrelu, layer1.bn1, lrelu)
   const long long plane_dist = (static_cast<long long>(B) * e->Lp + 63) / 64 * 64;
-  // The normalised signal is ALWAYS kept as hi|lo planes: a narrow band-pass output can sit far below the
-  // signal's total energy, so bf16 rounding noise on the samples (white, -54 dB) would swamp it.  bf16 mode
-  // runs two passes (hi*W + lo*W, bf16 filters), fp32-grade mode three.
+  // The normalised signal is written as hi|lo planes.  fp32-grade mode runs the three split passes; bf16 mode
+  // uses the hi plane only (one pass).  Measured on the synthetic speech set (tools/rawnet_bf16_err.py): adding the
+  // lo(A) pass lowers the front-end error from 3.3e-3 to 2.6e-3 rms (the rest is the bf16 rounding of the stored
+  // output) and does not change the embedding error, for +0.9 ms per 256 utterances; SVB_SINC_PASSES=2 enables it.
   SVB_CUDA_OK(cudaMemsetAsync(xn, 0, (static_cast<size_t>(B) * e->Lp * 2 + 4096) * 2, st));
   rn_ln_kernel<<<B, 1024, 0, st>>>(wav, wav_ld, e->L, e->Lp, e->ln_g, e->ln_b, 1e-6f, xn, plane_dist, 2);
   count_launch();
   // the first block's padding rows must be zero: the sinc epilogue writes valid rows only
-  SVB_CUDA_OK(cudaMemsetAsync(ab[0], 0, rows_bytes(P, B, e->T[0], 128), st));
+  rn_zero_halo_kernel<<<2 * B, 64, 0, st>>>(ab[0], P * 128, e->T[0], B);
+  count_launch();
   {
     RnGemmParams g{};
     g.M = B * e->Mu; g.N = 16 * 128 * 3; g.kc_per_tap = SINC_K / 64; g.num_taps = 1; g.tap_off[0] = 0;
-    g.num_pass = P == 2 ? 3 : 2; g.a_plane_cols = static_cast<int>(plane_dist); g.w_planes = P;
+    g.num_pass = P == 2 ? 3 : (getenv("SVB_SINC_PASSES") ? atoi(getenv("SVB_SINC_PASSES")) : 1); g.a_plane_cols = static_cast<int>(plane_dist); g.w_planes = P;
     g.T = e->T[0]; g.Tp = e->T[0] + 2; g.Mu = e->Mu; g.B = B;
     g.s1 = e->fbn_s; g.h1 = e->fbn_h; g.s2 = e->blk[0].s1; g.h2 = e->blk[0].h1;
     g.out = xb[0]; g.out_ld = PX * 128; g.out_planes = PX; g.out_plane_cols = 128;
@@ -592,11 +614,11 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     const float* ns = last ? e->gbn_s : e->blk[i + 1].s1;
     const float* nh = last ? e->gbn_h : e->blk[i + 1].h1;
     const bool need_x = !last && e->blk[i + 1].wsc == nullptr;
-    const long long rows = static_cast<long long>(B) * (Tout + 2);
     const bf16* src = k.down ? zpb : zb;
-    rn_apply_kernel<<<static_cast<unsigned>((rows * (k.cout / 8) + 255) / 256), 256, 0, st>>>(
+    const int rows_per_cta = 128;
+    rn_apply_kernel<<<dim3((Tout + 2 + rows_per_cta - 1) / rows_per_cta, B), 256, 0, st>>>(
         src, PX * k.cout, PX, k.cout, Tout, k.cout, k.alpha, gate, ns, nh, need_x ? xb[nxt] : nullptr, PX * k.cout, k.cout,
-        ab[nxt], P * k.cout, P, k.cout, rows);
+        ab[nxt], P * k.cout, P, k.cout, rows_per_cta);
     count_launch();
     SVB_CUDA_OK(cudaGetLastError());
     cur = nxt;
