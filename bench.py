@@ -117,7 +117,7 @@ class ClockSampler:
 
 def synth_waves(n, device, seed):
     """n distinct 3 s utterances: speaker-like harmonic signals (oracle/synth.py) mixed, shifted and scaled on the GPU."""
-    from oracle import synth
+    from speakerverification_b200 import synth
     pool, _ = synth.utterance_set(8, 4, L)
     pool = torch.from_numpy(pool).to(device)
     g = torch.Generator(device=device).manual_seed(seed)
@@ -179,6 +179,32 @@ def run_reference(args):
                              "sample": "%d trials, per-trial ZT_norm_similarity loop (numpy)" % n},
             "e2e": {"value": val, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
+    if args.workload == "eval":
+        from speakerverification_b200 import synth
+        U, NT = args.eval_utts, args.eval_trials
+        lengths = synth.ragged_lengths(U, seed=2)
+        signals = eval_signals(lengths[:64], seed=50)
+        cohort, _ = synth.scoring_embeddings(6000, 2000, seed=103)
+        t0 = time.perf_counter()
+        acc = []
+        for _ in range(args.steps):
+            acc.append(cpu_eval_rate(signals, cohort, 300, 6.0))
+        dt = time.perf_counter() - t0
+        t_emb = float(np.mean([a[0] / (a[4] / a[2]) for a in acc])) * float(lengths.sum()) / 16000.0 / U
+        t_trial = float(np.mean([a[1] for a in acc]))
+        val = 1.0 / (t_emb + t_trial * NT / U)
+        print(json.dumps({
+            "impl": "reference", "metric": "full-length eval utterances/sec (2-20 s utt, fbank + ECAPA + AS-norm)",
+            "value": val, "unit": "utterances/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "full-length eval (configs[2]): ragged U(2,20) s utterances, ECAPA-TDNN C=1024, AS-norm "
+                                   "vs 6000-cohort top-300, %d trials per %d utterances" % (NT, U),
+                       "sample": "about 8 s of CPU work per step, composed per utterance"},
+            "cpu_baseline": {"value": val, "unit": "utterances/s", "cores": os.cpu_count(), "kind": "port",
+                             "sample": "%d whole utterances + %d trials per step, oracle port" % (acc[0][2], acc[0][3])},
+            "e2e": {"value": val, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     if args.workload == "rawnet2":
         t0 = time.perf_counter()
         n = 0
@@ -221,7 +247,7 @@ def run_reference(args):
 # ------------------------------------------------------------------ scoring sweep (BASELINE.json configs[4])
 def scoring_inputs(U, N, n_trials, seed=3):
     """cfg5: unit embeddings around 2 000 speaker centroids, disjoint cohort, seeded trial pairs (10 % target)."""
-    from oracle import synth
+    from speakerverification_b200 import synth
     e, spk = synth.scoring_embeddings(U, 2000, seed=seed)
     c, _ = synth.scoring_embeddings(N, 2000, seed=seed + 100)
     rng = np.random.default_rng(seed + 1)
@@ -330,6 +356,183 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
     return res
 
 
+# ------------------------------------------------------------------ full-length eval (BASELINE.json configs[2])
+def eval_signals(lengths, seed):
+    """int16 PCM utterances of the given lengths (speaker-like pool, per-utterance shift and gain)."""
+    from speakerverification_b200 import synth
+    pool, _ = synth.utterance_set(8, 2, 320000)
+    rng = np.random.default_rng(seed)
+    out = []
+    for n in lengths:
+        a, sh, g = rng.integers(0, len(pool)), rng.integers(0, 320000), rng.uniform(0.3, 1.0)
+        x = np.roll(pool[a], int(sh))[:int(n)]
+        out.append(np.round(g * x / 0.3 * 20000).astype(np.int16))
+    return out
+
+
+def cpu_eval_rate(signals, cohort, top, min_seconds):
+    """Reference CPU path of the full-length eval (oracle port, all host threads): one forward per whole utterance
+    (src/model.py:380-396) + per-trial AS-norm loop (src/model.py:415-448), on a bounded sample."""
+    from oracle import ecapa_oracle as eo, scoring_oracle as so
+    from speakerverification_b200 import synth
+    torch.set_num_threads(os.cpu_count())
+    sd = {k: torch.as_tensor(v) for k, v in synth.ecapa_state_dict(CH, N_OUT).items()}
+    t0 = time.perf_counter()
+    embs, secs = [], 0.0
+    for x in signals:
+        embs.append(eo.embed((x.astype(np.float32) / 32768.0)[None], sd).numpy())
+        secs += len(x) / 16000.0
+        if time.perf_counter() - t0 > min_seconds and len(embs) >= 2:
+            break
+    t_emb = (time.perf_counter() - t0) / len(embs)
+    t1 = time.perf_counter()
+    nt = 0
+    while time.perf_counter() - t1 < 2.0:
+        so.asnorm_score(embs[nt % len(embs)], embs[(nt + 1) % len(embs)], cohort, top)
+        nt += 1
+    t_trial = (time.perf_counter() - t1) / nt
+    return t_emb, t_trial, len(embs), nt, secs
+
+
+def run_eval(args, device, rank, world, dist):
+    """cfg3: ragged 2-20 s utterances -> whole-utterance embeddings (num_eval = 0) -> AS-norm (6 000 cohort, top-300)
+    -> trial scores.  Utterances are sharded length-balanced (ModelHandling.shard_balanced); the exchange steps are the
+    all-gathers of the embedding shards, of the (mu, sigma) shards and of the score slices."""
+    from speakerverification_b200 import _native as nv
+    from speakerverification_b200 import synth
+    from speakerverification_b200 import utils as SU
+    from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
+    U, N, K, NT = args.eval_utts, 6000, 300, args.eval_trials
+    margs = model_args("cuda", args.precision)
+    net = WrappedModel(SpeakerEncoder(**margs))
+    handle = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=4096,
+                                       svb_batch_samples=args.batch_rows * L))
+    sd = net.module.state_dict()
+    for k, v in synth.ecapa_state_dict(CH, N_OUT).items():
+        sd[k].copy_(torch.as_tensor(v))
+    net.eval()
+    eng = net.module.engine()
+    lengths = synth.ragged_lengths(world * U, seed=2)
+    parts = ModelHandling.shard_balanced(lengths, world)
+    mine = parts[rank]
+    signals = eval_signals(lengths[mine], seed=50 + rank)
+    cohort, _ = synth.scoring_embeddings(N, 2000, seed=103)
+    coh = torch.from_numpy(cohort).to(device)
+    rng = np.random.default_rng(9)
+    ia_all = torch.from_numpy(rng.integers(0, world * U, world * NT).astype(np.int32)).to(device)
+    ib_all = torch.from_numpy(rng.integers(0, world * U, world * NT).astype(np.int32)).to(device)
+    ia, ib = ia_all[rank * NT:(rank + 1) * NT], ib_all[rank * NT:(rank + 1) * NT]
+    # device-resident staging for `value`: fp32 samples back to back, launches of <= batch_samples
+    # (signals of <= 3 s are wrap-padded to L + 1 samples as loadWAV does, src/processing/audio_loader.py:126-129)
+    staged = [np.pad(x, (0, L + 1 - len(x)), "wrap") if len(x) <= L else x for x in signals]
+    flat = torch.from_numpy(np.concatenate(staged).astype(np.float32) / 32768.0).to(device)
+    groups, i, off = [], 0, 0
+    while i < len(staged):
+        j, tot = i, 0
+        while j < len(staged) and (j == i or tot + len(staged[j]) <= handle.batch_samples):
+            tot += len(staged[j])
+            j += 1
+        groups.append((i, j, off, tot))
+        off += tot
+        i = j
+    emb = torch.empty((len(signals), N_OUT), dtype=torch.float32, device=device)
+
+    def score(e_local):
+        e_local = torch.nn.functional.normalize(e_local, dim=1)
+        full = ModelHandling.gather_assigned(e_local, parts, rank, world) if world > 1 else e_local
+        mu, sg = SU.asnorm_stats(e_local, coh, K)
+        if world > 1:
+            st = ModelHandling.gather_assigned(torch.stack([mu, sg], 1), parts, rank, world)
+            mu, sg = st[:, 0].contiguous(), st[:, 1].contiguous()
+        sc = SU.asnorm_trials(full, ia, ib, mu, sg)
+        if world > 1:
+            allsc = torch.empty(world * NT, dtype=torch.float32, device=device)
+            dist.all_gather_into_tensor(allsc, sc)
+            return allsc
+        return sc
+
+    def step():
+        for (a, b, o, tot) in groups:
+            eng.forward_flat(flat[o:o + tot], [len(x) for x in staged[a:b]], out=emb[a:b])
+        return score(emb)
+
+    for _ in range(max(args.warmup, 3)):
+        out = step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", 0)))
+    if rank == 0:
+        sampler.start()
+    nv.lib().svb_reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(nv.lib().svb_launch_count())
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # end to end: int16 PCM on the host -> GPU crop/stack stage -> encoder -> gathers -> scores on the host
+    handle.embed_signals(signals[:64], 0)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_emb = handle.embed_signals(signals, 0).view(len(signals), N_OUT)
+        hs = score(e2e_emb).cpu()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    cos = torch.nn.functional.cosine_similarity(e2e_emb, emb, dim=1)
+    assert bool(torch.isfinite(hs).all()) and float(cos.min()) > 0.9999, (float(cos.min()), float((hs - out.cpu()).abs().max()))
+    if rank != 0:
+        return
+    audio_s = float(lengths.sum()) / 16000.0
+    frames = float((1 + lengths // 160).sum())
+    hbm, tf_burst, tf_sust, src = peaks()
+    tfl = frames * 37.50e6 * args.steps / (ms * 1e-3) / 1e12 / world
+    line = {"metric": "full-length eval utterances/sec (2-20 s utt, fbank + ECAPA + AS-norm)",
+            "value": world * U * args.steps / (ms * 1e-3), "unit": "utterances/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)",
+            "data": "synthetic",
+            "config": {"workload": "full-length eval (configs[2]): %d ragged U(2,20) s utterances per GPU, whole-utterance "
+                                   "ECAPA-TDNN C=1024 embeddings, AS-norm vs 6000-cohort top-300, %d trials per GPU"
+                                   % (U, NT),
+                       "parallelism": "utterances length-balanced over %d GPU(s); all-gather of embeddings, (mu, sigma) "
+                                      "and score slices" % world,
+                       "audio_seconds_per_s": audio_s * args.steps / (ms * 1e-3),
+                       "equiv_3s_embeddings_per_s": frames / 301.0 * args.steps / (ms * 1e-3),
+                       "l2": "inputs larger than L2 (%.2f GB of samples per GPU per step)" % (flat.numel() * 4 / 1e9)},
+            "e2e": {"value": world * U * args.steps / dt, "unit": "utterances/s",
+                    "h2d_bytes_per_step": int(sum(len(x) for x in signals)) * 2, "d2h_bytes_per_step": world * NT * 4,
+                    "api": "ModelHandling.embed_signals(int16 PCM list, num_eval=0) -> gathers -> utils.asnorm_* -> .cpu()"},
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"kernel": "whole step (tensor-bound encoder), algorithmic 37.50 MFLOP per frame", "bound": "tensor",
+                         "achieved": tfl, "peak": tf_sust, "unit": "TFLOP/s", "frac": tfl / tf_sust, "traffic": None,
+                         "peak_source": src + " (sustained)"}}
+    if world == 1:
+        t_emb, t_trial, ne, nt, secs = cpu_eval_rate(signals, cohort, K, 12.0)
+        per_utt = t_emb * (audio_s / U) / (secs / ne) + t_trial * NT / U
+        line["cpu_baseline"] = {"value": 1.0 / per_utt, "unit": "utterances/s", "cores": os.cpu_count(), "kind": "port",
+                                "sample": "%d whole utterances (%.0f s of audio) + %d AS-norm trials, torch/numpy oracle "
+                                          "port; composed per utterance at the workload's mean length and trials per "
+                                          "utterance" % (ne, secs, nt)}
+    print(json.dumps(line))
+
+
 def gemm_roofline(device, batch_rows, halo=4):
     """Times the dominant kernel (gemm_pw_kernel<256, GELU>) alone on the MFA shape of one encoder launch."""
     from speakerverification_b200 import _native as nv
@@ -368,7 +571,9 @@ def main():
     ap.add_argument("--batch-rows", type=int, default=256)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2"])
+    ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2", "eval"])
+    ap.add_argument("--eval-utts", type=int, default=2000)
+    ap.add_argument("--eval-trials", type=int, default=100000)
     ap.add_argument("--score-utts", type=int, default=200000)
     ap.add_argument("--score-cohort", type=int, default=20000)
     ap.add_argument("--score-trials", type=int, default=1000000)
@@ -399,9 +604,15 @@ def main():
             dist.destroy_process_group()
         return
 
+    if args.workload == "eval":
+        run_eval(args, device, rank, world, dist)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
     from speakerverification_b200 import _native as nv
     from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
-    from oracle import synth
+    from speakerverification_b200 import synth
     rawnet = args.workload == "rawnet2"
     global L, N_OUT, FLOP_PER_UTT
     if rawnet:

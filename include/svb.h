@@ -100,6 +100,21 @@ int64_t svb_batch_frames(const SvbBatch* b);  /* sum_b T_b */
 int32_t svb_batch_tiles(const SvbBatch* b);   /* 32-frame front-end tiles */
 const int32_t* svb_batch_row_meta(const SvbBatch* b); /* device, int32 x4 per row */
 
+/* ------------------------------------------------------------------ crop / stack stage
+ * Replaces the evaluation branch of loadWAV (src/processing/audio_loader.py:110-150: wrap-pad of short
+ * signals :126-129, num_eval evenly spaced crops :134,147-148) and the stacking done by test_data_loader
+ * (src/dataloader.py:275-292).  Each utterance is uploaded ONCE as PCM (int16 as stored in the wav file, or
+ * fp32) and staged on the device: out[dst_off + i] = float(pcm[src_off + i mod src_len]) (* 1/32768 for int16,
+ * soundfile's float32 scaling) for i < dst_len, i.e. np.pad(audio, (0, dst_len - src_len), 'wrap').
+ * Crops are not materialised: crop j of utterance u is the row (wav_off = dst_off[u] + int(linspace(0,
+ * dst_len - L, n)[j]), nsamp = L) handed to svb_batch_create.  segs is a DEVICE array of U records. */
+typedef struct SvbPcmSeg {
+  int64_t src_off, dst_off;   /* in samples */
+  int32_t src_len, dst_len;
+} SvbPcmSeg;
+int svb_pcm_stage(const void* pcm, int sample_kind /* 0 = fp32, 1 = int16 */, const SvbPcmSeg* segs, int U,
+                  int max_dst_len, float* out, void* stream);
+
 /* ------------------------------------------------------------------ log-mel front-end (K1)
  * Replaces PreEmphasis (src/utils.py:63-71) + melspectrogram(lib='torchaudio')
  * (src/models/FeatureExtraction/feature.py:84-94) + log/mean-norm (src/models/ECAPA_TDNN.py:473-476).

@@ -86,6 +86,7 @@ _EXTRA_SIGS = {
     "svb_batch_frames": ([_vp], _i64),
     "svb_batch_tiles": ([_vp], _i32),
     "svb_batch_row_meta": ([_vp], _vp),
+    "svb_pcm_stage": ([_vp, _i32, _vp, _i32, _i32, _vp, _vp], _i32),
     "svb_fbank_create": ([_vp, _i32, _i32, _i32, _vp, _i32, _i32, _f32, _f32, _pp], _i32),
     "svb_fbank_destroy": ([_vp], None),
     "svb_fbank_forward": ([_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp], _i32),

@@ -19,6 +19,38 @@ def _read_wav(path):
         return data.astype(np.float32), sr
 
 
+def read_pcm(path):
+    """Samples of a wav file as stored: int16 for PCM-16 files (uploaded as is, scaled by 1/32768 on the
+    device = soundfile's float32 convention), float32 otherwise.  Feeds the GPU crop/stack stage."""
+    try:
+        import soundfile as sf
+        if sf.info(path).subtype == "PCM_16":
+            return sf.read(path, dtype="int16", always_2d=False)[0]
+        return sf.read(path, dtype="float32", always_2d=False)[0]
+    except ImportError:
+        from scipy.io import wavfile
+        _, data = wavfile.read(path)
+        if data.dtype == np.int16:
+            return data
+        if np.issubdtype(data.dtype, np.integer):
+            return data.astype(np.float32) / float(-np.iinfo(data.dtype).min)
+        return data.astype(np.float32)
+
+
+def crop_plan(src_len, audio_spec, num_eval):
+    """Index arithmetic of loadWAV's evaluation branch (src/processing/audio_loader.py:110-150) without touching
+    samples.  Returns (dst_len [U] int64: length after the wrap-pad of :126-129, starts: list of U int64 arrays with the
+    crop start offsets int(linspace(0, dst_len - L, num_eval)) of :134,147-148 ([0] and whole signal when
+    num_eval == 0), L)."""
+    L = int(audio_spec["sentence_len"] * audio_spec["sample_rate"])
+    src_len = np.asarray(src_len, dtype=np.int64)
+    dst_len = np.where(src_len <= L, L + 1, src_len)
+    if num_eval == 0:
+        return dst_len, [np.zeros(1, dtype=np.int64) for _ in src_len], L
+    starts = [np.array([int(s) for s in np.linspace(0, n - L, num=num_eval)], dtype=np.int64) for n in dst_len]
+    return dst_len, starts, L
+
+
 def normalize_audio_amp(signal):
     try:
         info = np.iinfo(signal.dtype)

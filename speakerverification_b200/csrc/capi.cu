@@ -11,6 +11,7 @@ int build_row_meta(const int32_t*, int, int, int32_t*, long long, cudaStream_t);
 int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStream_t);
 int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
+int pcm_stage(const void*, int, const PcmSeg*, int, int, float*, cudaStream_t);
 struct Fbank; struct Batch; struct Ecapa;
 int fbank_create(const float*, int, int, int, const float*, int, int, float, float, Fbank**);
 void fbank_destroy(Fbank*);
@@ -75,6 +76,14 @@ int svb_build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row
                        void* stream) {
   if (check_device()) return -1;
   return build_row_meta(frames_host, B, halo, row_meta, total_rows, static_cast<cudaStream_t>(stream));
+}
+
+int svb_pcm_stage(const void* pcm, int sample_kind, const SvbPcmSeg* segs, int U, int max_dst_len, float* out,
+                  void* stream) {
+  if (check_device()) return -1;
+  static_assert(sizeof(SvbPcmSeg) == sizeof(PcmSeg), "SvbPcmSeg layout");
+  return pcm_stage(pcm, sample_kind, reinterpret_cast<const PcmSeg*>(segs), U, max_dst_len, out,
+                   static_cast<cudaStream_t>(stream));
 }
 
 int svb_split_bf16(const float* x, int64_t rows, int cols, int ld_in, void* out, int ld_out, int planes,

@@ -48,6 +48,39 @@ __global__ void fold_bn_kernel(const float* g, const float* b, const float* m, c
   }
 }
 
+// Crop/stack stage of the evaluation loader (loadWAV eval mode, src/processing/audio_loader.py:110-150):
+// utterance u's PCM (int16 or fp32, src_off/src_len) is converted to fp32 (int16 / 32768 = soundfile's
+// float32 scaling) and laid down at dst_off with np.pad(..., 'wrap') semantics for dst_len > src_len.
+// The crops themselves are never materialised: a crop is a row offset into this staged buffer (svb_batch_create).
+template <typename T>
+__global__ void pcm_stage_kernel(const T* __restrict__ pcm, const PcmSeg* __restrict__ segs, float* __restrict__ out) {
+  const PcmSeg s = segs[blockIdx.y];
+  const T* src = pcm + s.src_off;
+  float* dst = out + s.dst_off;
+  const float scale = (sizeof(T) == 2) ? (1.0f / 32768.0f) : 1.0f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < s.dst_len; i += gridDim.x * blockDim.x) {
+    const int j = (i < s.src_len) ? i : (i % s.src_len);
+    dst[i] = static_cast<float>(src[j]) * scale;
+  }
+}
+
+int pcm_stage(const void* pcm, int sample_kind, const PcmSeg* segs, int U, int max_len, float* out,
+              cudaStream_t stream) {
+  SVB_CHECK(sample_kind == 0 || sample_kind == 1, "sample_kind must be 0 (fp32) or 1 (int16)");
+  if (U == 0) return 0;
+  SVB_CHECK(U <= 65535, "at most 65535 utterances per staging call");
+  int gx = (max_len + 256 * 8 - 1) / (256 * 8);
+  gx = gx < 1 ? 1 : (gx > 64 ? 64 : gx);
+  const dim3 grid(gx, U);
+  if (sample_kind == 1)
+    pcm_stage_kernel<int16_t><<<grid, 256, 0, stream>>>(static_cast<const int16_t*>(pcm), segs, out);
+  else
+    pcm_stage_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(pcm), segs, out);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row_meta, long long total_rows,
                    cudaStream_t stream) {
   std::vector<RowMeta> h(static_cast<size_t>(total_rows), RowMeta{-1, 0, 0, 0});

@@ -38,6 +38,8 @@ int count_launch(int n = 1);  // running count of kernel launches (reported by b
 // `halo` mirrored rows again.  row_meta[r] = {utterance, t (may be <0 or >=T on halo rows), T, 0};
 // utterance == -1 on rows that belong to no utterance.
 struct RowMeta { int utt, t, T, pad; };
+// one utterance of the crop/stack stage (svb_pcm_stage): same layout as SvbPcmSeg in include/svb.h
+struct PcmSeg { long long src_off, dst_off; int src_len, dst_len; };
 
 // ------------------------------------------------------------------ tensor-core GEMM
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };

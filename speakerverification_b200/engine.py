@@ -126,6 +126,7 @@ class EcapaEngine:
         self.handle = h
         self.halo = nv.lib().svb_ecapa_halo(h)
         self._plans = {}
+        self._row_plans = []
         self._ws = None
 
     def plan(self, nsamp):
@@ -150,6 +151,26 @@ class EcapaEngine:
             raise RuntimeError("wave input must be an fp32 CUDA tensor")
         plan = self.plan(nsamp)
         assert wav_flat.numel() >= sum(plan.nsamp)
+        ws = self.workspace(plan)
+        if out is None:
+            out = torch.empty((plan.B, self.n_out), dtype=torch.float32, device=self.device)
+        nv.check(nv.lib().svb_ecapa_forward(self.handle, self.frontend.handle, plan.handle, nv.ptr(wav_flat),
+                                            nv.ptr(ws), ws.numel(), nv.ptr(out), out.stride(0), int(l2norm),
+                                            nv.stream_ptr()))
+        return out
+
+    def forward_rows(self, wav_flat, wav_off, nsamp, l2norm=False, out=None):
+        """Rows given as (offset, length) views into one staged fp32 CUDA buffer (crops of the same utterance may
+        overlap; nothing is copied).  The plan is specific to the offsets and is not cached."""
+        if not wav_flat.is_cuda or wav_flat.dtype != torch.float32:
+            raise RuntimeError("wave input must be an fp32 CUDA tensor")
+        plan = BatchPlan(nsamp, self.frontend.hop, self.halo, wav_off=wav_off)
+        # freeing a plan is a device-wide sync (cudaFree): retire plans a few launches late so that the copy
+        # stream keeps running ahead of the encoder
+        self._row_plans.append(plan)
+        if len(self._row_plans) > 4:
+            self._row_plans.pop(0)
+        assert max(int(o) + int(n) for o, n in zip(wav_off, nsamp)) <= wav_flat.numel()
         ws = self.workspace(plan)
         if out is None:
             out = torch.empty((plan.B, self.n_out), dtype=torch.float32, device=self.device)

@@ -21,7 +21,8 @@ import torch.nn.functional as F
 
 from . import ecapa_tdnn, feature, rawnet2_custom
 from . import utils as svb_utils
-from .audio_loader import loadWAV
+from . import _native as nv
+from .audio_loader import crop_plan, loadWAV, read_pcm
 
 _ENCODERS = {"ECAPA_TDNN": ecapa_tdnn.MainModel, "RawNet2_custom": rawnet2_custom.MainModel}
 # losses of the reference whose constructor sets test_normalize = False (src/losses/Prototypical.py:21)
@@ -163,6 +164,84 @@ class ModelHandling(object):
             freed[k].record(main)
         return out
 
+    def embed_signals(self, signals, num_eval):
+        """GPU crop/stack pipeline (replaces loadWAV eval mode + test_data_loader stacking,
+        src/processing/audio_loader.py:110-150, src/dataloader.py:275-292): `signals` is a list of 1-D int16 / float32
+        HOST arrays.  Every utterance crosses PCIe once (int16 stays int16), is converted / wrap-padded on the device
+        by svb_pcm_stage, and its num_eval crops are row offsets into that staged buffer -- no crop is copied.
+        Launches are double-buffered: the H2D copy of group i+1 overlaps the encoder on group i.
+        Returns CUDA [U, n, D] (n = num_eval, or 1 whole-utterance row when num_eval == 0)."""
+        eng = self._engine()
+        U = len(signals)
+        n = num_eval if num_eval > 0 else 1
+        out = torch.empty((U * n, eng.n_out), dtype=torch.float32, device=self.device)
+        if U == 0:
+            return out.view(0, n, eng.n_out)
+        i16 = all(s.dtype == np.int16 for s in signals)
+        if not i16:
+            signals = [s.astype(np.float32) / 32768.0 if s.dtype == np.int16 else np.asarray(s, dtype=np.float32)
+                       for s in signals]
+        src_len = np.array([len(s) for s in signals], dtype=np.int64)
+        dst_len, starts, L = crop_plan(src_len, self.audio_spec, num_eval)
+        # groups of utterances per encoder launch
+        groups, i = [], 0
+        while i < U:
+            j, rows, samples = i, 0, 0
+            while j < U and (j == i or (rows + n <= self.batch_rows and
+                                        (num_eval > 0 or samples + dst_len[j] <= self.batch_samples))):
+                rows += n
+                samples += int(dst_len[j])
+                j += 1
+            groups.append((i, j))
+            i = j
+        max_src = max(int(src_len[a:b].sum()) for a, b in groups)
+        max_dst = max(int(dst_len[a:b].sum()) for a, b in groups)
+        max_u = max(b - a for a, b in groups)
+        np_dt, t_dt = (np.int16, torch.int16) if i16 else (np.float32, torch.float32)
+        seg_dt = np.dtype([("src_off", "<i8"), ("dst_off", "<i8"), ("src_len", "<i4"), ("dst_len", "<i4")])
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        main = torch.cuda.current_stream(self.device)
+        h_pcm = [torch.empty(max_src, dtype=t_dt).pin_memory() for _ in range(2)]
+        h_seg = [torch.empty(max_u * seg_dt.itemsize, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        d_pcm = [torch.empty(max_src, dtype=t_dt, device=self.device) for _ in range(2)]
+        d_seg = [torch.empty(max_u * seg_dt.itemsize, dtype=torch.uint8, device=self.device) for _ in range(2)]
+        d_wav = [torch.empty(max_dst, dtype=torch.float32, device=self.device) for _ in range(2)]
+        ready = [torch.cuda.Event() for _ in range(2)]
+        freed = [torch.cuda.Event() for _ in range(2)]
+        for g, (a, b) in enumerate(groups):
+            k = g & 1
+            if g >= 2:
+                ready[k].synchronize()                       # the pinned buffers of group g-2 have been consumed
+            segs = np.zeros(b - a, dtype=seg_dt)
+            segs["src_len"], segs["dst_len"] = src_len[a:b], dst_len[a:b]
+            segs["src_off"] = np.concatenate([[0], np.cumsum(src_len[a:b])[:-1]])
+            segs["dst_off"] = np.concatenate([[0], np.cumsum(dst_len[a:b])[:-1]])
+            hp = h_pcm[k].numpy()
+            for u in range(a, b):
+                o = int(segs["src_off"][u - a])
+                hp[o:o + len(signals[u])] = signals[u]
+            nsrc = int(src_len[a:b].sum())
+            h_seg[k].numpy()[:segs.nbytes] = segs.view(np.uint8)
+            with torch.cuda.stream(self._copy_stream):
+                if g >= 2:
+                    self._copy_stream.wait_event(freed[k])
+                d_pcm[k][:nsrc].copy_(h_pcm[k][:nsrc], non_blocking=True)
+                d_seg[k][:segs.nbytes].copy_(h_seg[k][:segs.nbytes], non_blocking=True)
+                ready[k].record(self._copy_stream)
+            main.wait_event(ready[k])
+            nv.check(nv.lib().svb_pcm_stage(nv.ptr(d_pcm[k]), 1 if i16 else 0, nv.ptr(d_seg[k]), b - a,
+                                            int(dst_len[a:b].max()), nv.ptr(d_wav[k]), nv.stream_ptr()))
+            offs, lens = [], []
+            for u in range(a, b):
+                base = int(segs["dst_off"][u - a])
+                for st in starts[u]:
+                    offs.append(base + int(st))
+                    lens.append(L if num_eval > 0 else int(dst_len[u]))
+            eng.forward_rows(d_wav[k], offs, lens, out=out[a * n:b * n])
+            freed[k].record(main)
+        return out.view(U, n, eng.n_out)
+
     def _embed_ragged(self, signals):
         """Whole-utterance embeddings (num_eval == 0): every signal keeps its own length."""
         eng = self._engine()
@@ -189,7 +268,14 @@ class ModelHandling(object):
 
     def _embed_files(self, files, num_eval, num_workers=0):
         """list of paths -> CUDA [U, n, D] crop embeddings (n = num_eval, or 1 when num_eval == 0)."""
-        crops = self._load_crops(files, num_eval, num_workers)
+        if hasattr(self._engine(), "forward_rows"):
+            if num_workers and num_workers > 1:
+                with ThreadPoolExecutor(num_workers) as ex:
+                    signals = list(ex.map(read_pcm, [str(Path(f)) for f in files]))
+            else:
+                signals = [read_pcm(str(Path(f))) for f in files]
+            return self.embed_signals(signals, num_eval)
+        crops = self._load_crops(files, num_eval, num_workers)      # fixed-length raw-waveform encoders (RawNet2)
         if num_eval == 0:
             return self._embed_ragged([c[0] for c in crops]).unsqueeze(1)
         allc = torch.from_numpy(np.concatenate(crops, axis=0))

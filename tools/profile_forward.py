@@ -2,7 +2,7 @@
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from oracle import synth
+from speakerverification_b200 import synth
 from speakerverification_b200.engine import EcapaEngine, Frontend
 
 CH = [1024, 1024, 1024, 1024, 3072]

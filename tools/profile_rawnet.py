@@ -2,7 +2,7 @@
 import os, sys, time
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from oracle import synth
+from speakerverification_b200 import synth
 from speakerverification_b200.rawnet2_custom import RawNet2Engine
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
