@@ -69,6 +69,24 @@ def cpu_rawnet_rate(min_seconds, batch=8):
     return done / dt, done, dt
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Everything the libraries print (model banner, NCCL version line) goes to stderr; stdout carries the ONE JSON line."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -169,7 +187,7 @@ def run_reference(args):
             n += done
         dt = time.perf_counter() - t0
         val = n / dt
-        print(json.dumps({
+        emit(json.dumps({
             "impl": "reference", "metric": "AS-norm trials/sec", "value": val, "unit": "trials/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -193,7 +211,7 @@ def run_reference(args):
         t_emb = float(np.mean([a[0] / (a[4] / a[2]) for a in acc])) * float(lengths.sum()) / 16000.0 / U
         t_trial = float(np.mean([a[1] for a in acc]))
         val = 1.0 / (t_emb + t_trial * NT / U)
-        print(json.dumps({
+        emit(json.dumps({
             "impl": "reference", "metric": "full-length eval utterances/sec (2-20 s utt, fbank + ECAPA + AS-norm)",
             "value": val, "unit": "utterances/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -213,7 +231,7 @@ def run_reference(args):
             n += done
         dt = time.perf_counter() - t0
         val = n / dt
-        print(json.dumps({
+        emit(json.dumps({
             "impl": "reference", "metric": "RawNet2 embeddings/sec (4 s utt)", "value": val, "unit": "embeddings/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -233,7 +251,7 @@ def run_reference(args):
         n += done
     dt = time.perf_counter() - t0
     val = n / dt
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "ECAPA embeddings/sec (3 s utt)", "value": val, "unit": "embeddings/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -530,7 +548,7 @@ def run_eval(args, device, rank, world, dist):
                                 "sample": "%d whole utterances (%.0f s of audio) + %d AS-norm trials, torch/numpy oracle "
                                           "port; composed per utterance at the workload's mean length and trials per "
                                           "utterance" % (ne, secs, nt)}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 
 def gemm_roofline(device, batch_rows, halo=4):
@@ -578,6 +596,7 @@ def main():
     ap.add_argument("--score-cohort", type=int, default=20000)
     ap.add_argument("--score-trials", type=int, default=1000000)
     args = ap.parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
 
@@ -599,7 +618,7 @@ def main():
         if rank == 0:
             res["warmup"] = 3
             res["clocks"] = sampler.stop()
-            print(json.dumps(res))
+            emit(json.dumps(res))
         if world > 1:
             dist.destroy_process_group()
         return
@@ -727,7 +746,7 @@ def main():
             rate, n, dt = cpu_rawnet_rate(12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port (%.1f s)" % (n, dt)}
-        print(json.dumps(line))
+        emit(json.dumps(line))
     elif rank == 0:
         hbm, tf_burst, tf_sust, src = peaks()
         ach, gemm_ms = gemm_roofline(device, args.batch_rows)
@@ -756,7 +775,7 @@ def main():
             rate, n, dt = cpu_reference_rate(64, min_seconds=12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 

@@ -94,6 +94,13 @@ int svb_tdnn_layer(const SvbTdnnArgs* args, void* stream);
 typedef struct SvbBatch SvbBatch;
 int svb_batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo,
                      SvbBatch** out);
+/* Same plan with CALLER-OWNED tables: built in blob_pinned_host (page-locked host memory) and uploaded with one
+ * stream-ordered copy into blob_dev (256-byte aligned device memory), both of svb_batch_blob_bytes() bytes.  No
+ * allocation and no synchronisation: used for the per-launch plans of the crop/stack pipeline.  The blobs must outlive
+ * the plan and the host blob must not be rewritten before the copy has executed. */
+size_t svb_batch_blob_bytes(const int32_t* nsamp_host, int B, int hop, int halo);
+int svb_batch_create_into(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo,
+                          void* blob_pinned_host, void* blob_dev, size_t blob_bytes, void* stream, SvbBatch** out);
 void svb_batch_destroy(SvbBatch* b);
 int64_t svb_batch_rows(const SvbBatch* b);    /* sum_b (T_b + 2*halo) */
 int64_t svb_batch_frames(const SvbBatch* b);  /* sum_b T_b */

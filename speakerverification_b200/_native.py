@@ -81,6 +81,8 @@ class SvbRawnet2Cfg(_c.Structure):
 _pp = _c.POINTER(_vp)
 _EXTRA_SIGS = {
     "svb_batch_create": ([_vp, _vp, _i32, _i32, _i32, _pp], _i32),
+    "svb_batch_blob_bytes": ([_vp, _i32, _i32, _i32], _c.c_size_t),
+    "svb_batch_create_into": ([_vp, _vp, _i32, _i32, _i32, _vp, _vp, _c.c_size_t, _vp, _pp], _i32),
     "svb_batch_destroy": ([_vp], None),
     "svb_batch_rows": ([_vp], _i64),
     "svb_batch_frames": ([_vp], _i64),

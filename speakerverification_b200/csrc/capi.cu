@@ -18,6 +18,8 @@ void fbank_destroy(Fbank*);
 int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
                   float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
 int batch_create(const int64_t*, const int32_t*, int, int, int, Batch**);
+int batch_create_into(const int64_t*, const int32_t*, int, int, int, void*, void*, size_t, cudaStream_t, Batch**);
+size_t batch_blob_bytes(const int32_t*, int, int, int);
 void batch_destroy(Batch*);
 long long batch_rows(const Batch*);
 long long batch_frames(const Batch*);
@@ -174,6 +176,17 @@ int svb_batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int
   if (check_device()) return -1;
   SVB_CHECK(wav_off_host && nsamp_host && out, "null argument");
   return batch_create(wav_off_host, nsamp_host, B, hop, halo, reinterpret_cast<Batch**>(out));
+}
+size_t svb_batch_blob_bytes(const int32_t* nsamp_host, int B, int hop, int halo) {
+  if (!nsamp_host) return 0;
+  return batch_blob_bytes(nsamp_host, B, hop, halo);
+}
+int svb_batch_create_into(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo,
+                          void* blob_pinned_host, void* blob_dev, size_t blob_bytes, void* stream, SvbBatch** out) {
+  if (check_device()) return -1;
+  SVB_CHECK(wav_off_host && nsamp_host && out, "null argument");
+  return batch_create_into(wav_off_host, nsamp_host, B, hop, halo, blob_pinned_host, blob_dev, blob_bytes,
+                           static_cast<cudaStream_t>(stream), reinterpret_cast<Batch**>(out));
 }
 void svb_batch_destroy(SvbBatch* b) { batch_destroy(reinterpret_cast<Batch*>(b)); }
 int64_t svb_batch_rows(const SvbBatch* b) { return batch_rows(reinterpret_cast<const Batch*>(b)); }

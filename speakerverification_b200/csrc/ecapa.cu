@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <map>
 #include <string>
+#include <cstring>
 #include <vector>
 
 #include "svb_internal.h"
@@ -53,52 +54,131 @@ struct Batch {
   UttDesc* d_utt = nullptr;
   int2* d_tiles = nullptr;
   UttRows* d_uttrows = nullptr;
+  uint8_t* d_blob = nullptr;   // the one allocation the five tables live in
 };
 
-int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, Batch** out) {
+// Host tables of a plan, laid out in one blob (sub-tables 256-byte aligned).
+struct BatchTables {
+  size_t o_meta, o_utt, o_tiles, o_ur, o_segs;
+  long long rows, frames;
+  int ntiles, nsegs;
+};
+
+static int batch_tables(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, BatchTables* t) {
   SVB_CHECK(B > 0 && hop > 0 && halo >= 0, "bad batch arguments");
-  std::vector<UttDesc> utt(B);
-  std::vector<UttRows> ur(B);
-  std::vector<int2> tiles;
-  std::vector<RowMeta> meta;
-  std::vector<SegItem> segs;
   const int seg_frames = res2net_seg_frames();
   long long row = 0, frames = 0;
+  size_t ntiles = 0, nsegs = 0;
   for (int b = 0; b < B; ++b) {
     const int L = nsamp_host[b];
     SVB_CHECK(L > 256, "utterance %d has %d samples; the centred 512-point STFT needs more than 256", b, L);
     const int T = 1 + L / hop;
     SVB_CHECK(T > 2 * halo, "utterance %d has %d frames; need more than %d", b, T, 2 * halo);
-    utt[b] = UttDesc{wav_off_host[b], L, T, row, static_cast<int>(tiles.size()), (T + FRAMES_PER_TILE - 1) / FRAMES_PER_TILE};
-    ur[b] = UttRows{row + halo, T, 0};
-    for (int t0 = 0; t0 < T; t0 += FRAMES_PER_TILE) tiles.push_back(make_int2(b, t0));
-    for (int sg = 0; sg * seg_frames < T; ++sg) segs.push_back(SegItem{b, sg});
-    for (int t = -halo; t < T + halo; ++t) meta.push_back(RowMeta{b, t, T, 0});
+    ntiles += (T + FRAMES_PER_TILE - 1) / FRAMES_PER_TILE;
+    nsegs += (T + seg_frames - 1) / seg_frames;
     row += T + 2 * halo;
     frames += T;
   }
+  auto al = [](size_t n) { return (n + 255) & ~static_cast<size_t>(255); };
+  t->rows = row; t->frames = frames; t->ntiles = static_cast<int>(ntiles); t->nsegs = static_cast<int>(nsegs);
+  t->o_meta = 0;
+  t->o_utt = t->o_meta + al(static_cast<size_t>(row) * sizeof(RowMeta));
+  t->o_tiles = t->o_utt + al(static_cast<size_t>(B) * sizeof(UttDesc));
+  t->o_ur = t->o_tiles + al(ntiles * sizeof(int2));
+  t->o_segs = t->o_ur + al(static_cast<size_t>(B) * sizeof(UttRows));
+  const size_t total = t->o_segs + al(nsegs * sizeof(SegItem));
+  (void)total;
+  return 0;
+}
+
+static size_t batch_blob_total(const BatchTables& t) {
+  auto al = [](size_t n) { return (n + 255) & ~static_cast<size_t>(255); };
+  return t.o_segs + al(static_cast<size_t>(t.nsegs) * sizeof(SegItem));
+}
+
+static void batch_fill(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, const BatchTables& t,
+                       uint8_t* blob) {
+  const int seg_frames = res2net_seg_frames();
+  RowMeta* meta = reinterpret_cast<RowMeta*>(blob + t.o_meta);
+  UttDesc* utt = reinterpret_cast<UttDesc*>(blob + t.o_utt);
+  int2* tiles = reinterpret_cast<int2*>(blob + t.o_tiles);
+  UttRows* ur = reinterpret_cast<UttRows*>(blob + t.o_ur);
+  SegItem* segs = reinterpret_cast<SegItem*>(blob + t.o_segs);
+  long long row = 0;
+  int nt = 0, ns = 0;
+  for (int b = 0; b < B; ++b) {
+    const int L = nsamp_host[b];
+    const int T = 1 + L / hop;
+    utt[b] = UttDesc{wav_off_host[b], L, T, row, nt, (T + FRAMES_PER_TILE - 1) / FRAMES_PER_TILE};
+    ur[b] = UttRows{row + halo, T, 0};
+    for (int t0 = 0; t0 < T; t0 += FRAMES_PER_TILE) tiles[nt++] = make_int2(b, t0);
+    for (int sg = 0; sg * seg_frames < T; ++sg) segs[ns++] = SegItem{b, sg};
+    for (int tt = -halo; tt < T + halo; ++tt) *meta++ = RowMeta{b, tt, T, 0};
+    row += T + 2 * halo;
+  }
+}
+
+static void batch_bind(Batch* bt, const BatchTables& t, uint8_t* d, int B, int hop, int halo) {
+  bt->B = B; bt->halo = halo; bt->hop = hop; bt->rows = t.rows; bt->frames = t.frames;
+  bt->ntiles = t.ntiles; bt->nsegs = t.nsegs;
+  bt->d_meta = reinterpret_cast<RowMeta*>(d + t.o_meta);
+  bt->d_utt = reinterpret_cast<UttDesc*>(d + t.o_utt);
+  bt->d_tiles = reinterpret_cast<int2*>(d + t.o_tiles);
+  bt->d_uttrows = reinterpret_cast<UttRows*>(d + t.o_ur);
+  bt->d_segs = reinterpret_cast<SegItem*>(d + t.o_segs);
+}
+
+size_t batch_blob_bytes(const int32_t* nsamp_host, int B, int hop, int halo) {
+  BatchTables t;
+  std::vector<int64_t> zero(static_cast<size_t>(B > 0 ? B : 0), 0);
+  if (batch_tables(zero.data(), nsamp_host, B, hop, halo, &t)) return 0;
+  return batch_blob_total(t);
+}
+
+// Library-owned tables: one device allocation filled by one (synchronous) copy.
+int batch_create(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, Batch** out) {
+  BatchTables t;
+  if (batch_tables(wav_off_host, nsamp_host, B, hop, halo, &t)) return -1;
+  const size_t total = batch_blob_total(t);
+  std::vector<uint8_t> blob(total, 0);
+  batch_fill(wav_off_host, nsamp_host, B, hop, halo, t, blob.data());
+  uint8_t* d = nullptr;
+  if (cudaMalloc(reinterpret_cast<void**>(&d), total) != cudaSuccess ||
+      cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
+    set_error("batch table upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (d) cudaFree(d);
+    return -2;
+  }
   Batch* bt = new Batch();
-  bt->B = B; bt->halo = halo; bt->hop = hop; bt->rows = row; bt->frames = frames;
-  bt->ntiles = static_cast<int>(tiles.size());
-  auto up = [](void** d, const void* h, size_t n) {
-    if (cudaMalloc(d, n) != cudaSuccess) return 1;
-    return cudaMemcpy(*d, h, n, cudaMemcpyHostToDevice) != cudaSuccess ? 1 : 0;
-  };
-  int bad = 0;
-  bad |= up(reinterpret_cast<void**>(&bt->d_meta), meta.data(), meta.size() * sizeof(RowMeta));
-  bad |= up(reinterpret_cast<void**>(&bt->d_utt), utt.data(), utt.size() * sizeof(UttDesc));
-  bad |= up(reinterpret_cast<void**>(&bt->d_tiles), tiles.data(), tiles.size() * sizeof(int2));
-  bad |= up(reinterpret_cast<void**>(&bt->d_uttrows), ur.data(), ur.size() * sizeof(UttRows));
-  bad |= up(reinterpret_cast<void**>(&bt->d_segs), segs.data(), segs.size() * sizeof(SegItem));
-  bt->nsegs = static_cast<int>(segs.size());
-  if (bad) { set_error("batch table upload failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
+  batch_bind(bt, t, d, B, hop, halo);
+  bt->d_blob = d;
+  *out = bt;
+  return 0;
+}
+
+// Caller-owned tables (the per-launch plans of the crop/stack pipeline): the tables are built in the caller's PINNED
+// host blob and uploaded with one stream-ordered copy into the caller's device blob -- no allocation, no
+// synchronisation, so plan construction never stalls the encoder stream.  Both blobs must stay valid (and the host
+// blob unmodified until the copy has executed) for the life of the plan.
+int batch_create_into(const int64_t* wav_off_host, const int32_t* nsamp_host, int B, int hop, int halo, void* host_blob,
+                      void* dev_blob, size_t blob_bytes, cudaStream_t stream, Batch** out) {
+  BatchTables t;
+  if (batch_tables(wav_off_host, nsamp_host, B, hop, halo, &t)) return -1;
+  const size_t total = batch_blob_total(t);
+  SVB_CHECK(host_blob && dev_blob && blob_bytes >= total, "plan blobs too small: need %zu bytes, have %zu", total, blob_bytes);
+  SVB_CHECK((reinterpret_cast<uintptr_t>(dev_blob) & 255) == 0, "device blob must be 256-byte aligned");
+  batch_fill(wav_off_host, nsamp_host, B, hop, halo, t, static_cast<uint8_t*>(host_blob));
+  SVB_CUDA_OK(cudaMemcpyAsync(dev_blob, host_blob, total, cudaMemcpyHostToDevice, stream));
+  Batch* bt = new Batch();
+  batch_bind(bt, t, static_cast<uint8_t*>(dev_blob), B, hop, halo);
+  bt->d_blob = nullptr;       // not ours
   *out = bt;
   return 0;
 }
 
 void batch_destroy(Batch* b) {
   if (b == nullptr) return;
-  cudaFree(b->d_meta); cudaFree(b->d_utt); cudaFree(b->d_tiles); cudaFree(b->d_uttrows); cudaFree(b->d_segs);
+  cudaFree(b->d_blob);
   delete b;
 }
 long long batch_rows(const Batch* b) { return b->rows; }

@@ -60,16 +60,28 @@ class Frontend:
 class BatchPlan:
     """Device tables for a batch of utterances laid out back to back in one wav buffer."""
 
-    def __init__(self, nsamp, hop, halo, wav_off=None):
-        nsamp = [int(n) for n in nsamp]
+    def __init__(self, nsamp, hop, halo, wav_off=None, blobs=None):
+        """`blobs` = (pinned host uint8 tensor, device uint8 tensor): caller-owned tables uploaded on the current
+        stream without any synchronisation (svb_batch_create_into); otherwise the library allocates them."""
+        ns_np = np.ascontiguousarray(nsamp, dtype=np.int32)
         if wav_off is None:
-            wav_off = np.concatenate([[0], np.cumsum(nsamp)[:-1]])
-        self.B = len(nsamp)
-        self.nsamp = nsamp
-        off = (ctypes.c_int64 * self.B)(*[int(o) for o in wav_off])
-        ns = (ctypes.c_int32 * self.B)(*nsamp)
+            wav_off = np.concatenate([[0], np.cumsum(ns_np, dtype=np.int64)[:-1]])
+        off_np = np.ascontiguousarray(wav_off, dtype=np.int64)
+        self.B = len(ns_np)
+        self.nsamp = ns_np.tolist()
+        nsamp = self.nsamp
+        off, ns = off_np.ctypes.data_as(_vp), ns_np.ctypes.data_as(_vp)
         h = _vp()
-        nv.check(nv.lib().svb_batch_create(off, ns, self.B, hop, halo, ctypes.byref(h)))
+        if blobs is None:
+            nv.check(nv.lib().svb_batch_create(off, ns, self.B, hop, halo, ctypes.byref(h)))
+        else:
+            need = nv.lib().svb_batch_blob_bytes(ns, self.B, hop, halo)
+            if need == 0 or blobs[0].numel() < need or blobs[1].numel() < need:
+                raise RuntimeError("plan blobs too small: need %d bytes" % need)
+            nv.check(nv.lib().svb_batch_create_into(off, ns, self.B, hop, halo, blobs[0].data_ptr(), blobs[1].data_ptr(),
+                                                    min(blobs[0].numel(), blobs[1].numel()), nv.stream_ptr(),
+                                                    ctypes.byref(h)))
+            self._blobs = blobs
         self.handle = h
         self.rows = nv.lib().svb_batch_rows(h)
         self.frames = nv.lib().svb_batch_frames(h)
@@ -164,13 +176,28 @@ class EcapaEngine:
         overlap; nothing is copied).  The plan is specific to the offsets and is not cached."""
         if not wav_flat.is_cuda or wav_flat.dtype != torch.float32:
             raise RuntimeError("wave input must be an fp32 CUDA tensor")
-        plan = BatchPlan(nsamp, self.frontend.hop, self.halo, wav_off=wav_off)
-        # freeing a plan is a device-wide sync (cudaFree): retire plans a few launches late so that the copy
-        # stream keeps running ahead of the encoder
-        self._row_plans.append(plan)
-        if len(self._row_plans) > 4:
-            self._row_plans.pop(0)
-        assert max(int(o) + int(n) for o, n in zip(wav_off, nsamp)) <= wav_flat.numel()
+        # per-launch plan in caller-owned blobs (ring of 4 pinned + device pairs): no cudaMalloc / cudaFree / blocking
+        # copy on the critical path, so the copy stream keeps running ahead of the encoder
+        ns_np = np.ascontiguousarray(nsamp, dtype=np.int32)
+        need = int(nv.lib().svb_batch_blob_bytes(ns_np.ctypes.data_as(_vp), len(ns_np), self.frontend.hop, self.halo))
+        if need == 0:
+            nv.check(-1)
+        k = self._ring_pos = (getattr(self, "_ring_pos", -1) + 1) % 4
+        if len(self._row_plans) <= k:
+            self._row_plans.append(None)
+        slot = self._row_plans[k]
+        if slot is not None:
+            slot["done"].synchronize()                       # its upload (4 launches ago) has executed
+            slot["plan"] = None
+        if slot is None or slot["host"].numel() < need:
+            size = max(need, 1 << 21)
+            slot = self._row_plans[k] = {"host": torch.empty(size, dtype=torch.uint8).pin_memory(),
+                                         "dev": torch.empty(size, dtype=torch.uint8, device=self.device),
+                                         "done": torch.cuda.Event(), "plan": None}
+        plan = slot["plan"] = BatchPlan(ns_np, self.frontend.hop, self.halo, wav_off=wav_off,
+                                        blobs=(slot["host"], slot["dev"]))
+        slot["done"].record()
+        assert int((np.asarray(wav_off, dtype=np.int64) + ns_np).max()) <= wav_flat.numel()
         ws = self.workspace(plan)
         if out is None:
             out = torch.empty((plan.B, self.n_out), dtype=torch.float32, device=self.device)

@@ -113,6 +113,8 @@ class ModelHandling(object):
         self.batch_rows = int(kwargs.get("svb_batch_rows", 256))
         self.batch_samples = int(kwargs.get("svb_batch_samples", 256 * 48000))
         self._copy_stream = None
+        self._stage_bufs = None
+        self._pool = None
         if self.gpu == 0:
             nb = sum(p.numel() for p in self.__model__.module.__S__.parameters())
             print("Model information:")
@@ -164,6 +166,22 @@ class ModelHandling(object):
             freed[k].record(main)
         return out
 
+    def _staging(self, t_dt, n_src, n_seg, n_dst):
+        """Grow-only pinned / device staging buffers of the crop/stack pipeline, kept across calls (pinning is slow)."""
+        st = self._stage_bufs
+        need = (n_src, n_seg, n_dst)
+        if st is None or st["dt"] != t_dt or any(x < y for x, y in zip(st["n"], need)):
+            grow = need if st is None or st["dt"] != t_dt else tuple(max(x, y) for x, y in zip(st["n"], need))
+            self._stage_bufs = st = None
+            st = {"dt": t_dt, "n": grow,
+                  "h_pcm": [torch.empty(grow[0], dtype=t_dt).pin_memory() for _ in range(2)],
+                  "h_seg": [torch.empty(grow[1], dtype=torch.uint8).pin_memory() for _ in range(2)],
+                  "d_pcm": [torch.empty(grow[0], dtype=t_dt, device=self.device) for _ in range(2)],
+                  "d_seg": [torch.empty(grow[1], dtype=torch.uint8, device=self.device) for _ in range(2)],
+                  "d_wav": [torch.empty(grow[2], dtype=torch.float32, device=self.device) for _ in range(2)]}
+            self._stage_bufs = st
+        return st["h_pcm"], st["h_seg"], st["d_pcm"], st["d_seg"], st["d_wav"]
+
     def embed_signals(self, signals, num_eval):
         """GPU crop/stack pipeline (replaces loadWAV eval mode + test_data_loader stacking,
         src/processing/audio_loader.py:110-150, src/dataloader.py:275-292): `signals` is a list of 1-D int16 / float32
@@ -197,19 +215,27 @@ class ModelHandling(object):
         max_src = max(int(src_len[a:b].sum()) for a, b in groups)
         max_dst = max(int(dst_len[a:b].sum()) for a, b in groups)
         max_u = max(b - a for a, b in groups)
-        np_dt, t_dt = (np.int16, torch.int16) if i16 else (np.float32, torch.float32)
+        t_dt = torch.int16 if i16 else torch.float32
         seg_dt = np.dtype([("src_off", "<i8"), ("dst_off", "<i8"), ("src_len", "<i4"), ("dst_len", "<i4")])
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=self.device)
+        copy_stream = self._copy_stream
         main = torch.cuda.current_stream(self.device)
-        h_pcm = [torch.empty(max_src, dtype=t_dt).pin_memory() for _ in range(2)]
-        h_seg = [torch.empty(max_u * seg_dt.itemsize, dtype=torch.uint8).pin_memory() for _ in range(2)]
-        d_pcm = [torch.empty(max_src, dtype=t_dt, device=self.device) for _ in range(2)]
-        d_seg = [torch.empty(max_u * seg_dt.itemsize, dtype=torch.uint8, device=self.device) for _ in range(2)]
-        d_wav = [torch.empty(max_dst, dtype=torch.float32, device=self.device) for _ in range(2)]
+        h_pcm, h_seg, d_pcm, d_seg, d_wav = self._staging(t_dt, max_src, max_u * seg_dt.itemsize, max_dst)
         ready = [torch.cuda.Event() for _ in range(2)]
         freed = [torch.cuda.Event() for _ in range(2)]
-        for g, (a, b) in enumerate(groups):
+        if self._pool is None:
+            self._pool = ThreadPoolExecutor(6)
+
+        def fill(k, lo, hi, offs):
+            hp = h_pcm[k].numpy()
+            for u in range(lo, hi):
+                hp[offs[u]:offs[u] + len(signals[u])] = signals[u]
+
+        def stage(g):
+            """Host side of group g (runs on a worker thread, one group ahead of the encoder): PCM of its utterances
+            into pinned buffer g & 1 (parallel memcpy, numpy releases the GIL) and the H2D copies on the copy stream."""
+            a, b = groups[g]
             k = g & 1
             if g >= 2:
                 ready[k].synchronize()                       # the pinned buffers of group g-2 have been consumed
@@ -217,27 +243,34 @@ class ModelHandling(object):
             segs["src_len"], segs["dst_len"] = src_len[a:b], dst_len[a:b]
             segs["src_off"] = np.concatenate([[0], np.cumsum(src_len[a:b])[:-1]])
             segs["dst_off"] = np.concatenate([[0], np.cumsum(dst_len[a:b])[:-1]])
-            hp = h_pcm[k].numpy()
-            for u in range(a, b):
-                o = int(segs["src_off"][u - a])
-                hp[o:o + len(signals[u])] = signals[u]
+            offs = {u: int(segs["src_off"][u - a]) for u in range(a, b)}
+            cuts = np.linspace(a, b, num=min(5, b - a) + 1).astype(int)
+            list(self._pool.map(lambda lh: fill(k, lh[0], lh[1], offs), zip(cuts[:-1], cuts[1:])))
             nsrc = int(src_len[a:b].sum())
             h_seg[k].numpy()[:segs.nbytes] = segs.view(np.uint8)
-            with torch.cuda.stream(self._copy_stream):
+            with torch.cuda.device(self.device), torch.cuda.stream(copy_stream):
                 if g >= 2:
-                    self._copy_stream.wait_event(freed[k])
+                    copy_stream.wait_event(freed[k])
                 d_pcm[k][:nsrc].copy_(h_pcm[k][:nsrc], non_blocking=True)
                 d_seg[k][:segs.nbytes].copy_(h_seg[k][:segs.nbytes], non_blocking=True)
-                ready[k].record(self._copy_stream)
+                ready[k].record(copy_stream)
+            return segs
+
+        fut = self._pool.submit(stage, 0)
+        for g, (a, b) in enumerate(groups):
+            k = g & 1
+            segs = fut.result()
+            if g + 1 < len(groups):
+                fut = self._pool.submit(stage, g + 1)        # freed[(g+1)&1] was recorded when group g-1 was enqueued
             main.wait_event(ready[k])
             nv.check(nv.lib().svb_pcm_stage(nv.ptr(d_pcm[k]), 1 if i16 else 0, nv.ptr(d_seg[k]), b - a,
                                             int(dst_len[a:b].max()), nv.ptr(d_wav[k]), nv.stream_ptr()))
-            offs, lens = [], []
-            for u in range(a, b):
-                base = int(segs["dst_off"][u - a])
-                for st in starts[u]:
-                    offs.append(base + int(st))
-                    lens.append(L if num_eval > 0 else int(dst_len[u]))
+            base = segs["dst_off"]
+            if num_eval > 0:
+                offs = np.concatenate([base[u - a] + starts[u] for u in range(a, b)])
+                lens = np.full(len(offs), L, dtype=np.int64)
+            else:
+                offs, lens = base, dst_len[a:b]
             eng.forward_rows(d_wav[k], offs, lens, out=out[a * n:b * n])
             freed[k].record(main)
         return out.view(U, n, eng.n_out)
