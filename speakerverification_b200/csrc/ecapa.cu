@@ -24,6 +24,7 @@ int fbank_from_power(const Fbank*, const float*, const void*, int, const RowMeta
 int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
+int colsum_finalize(const long long*, const long long*, int, const void*, int, int, float, float*, float*, int, cudaStream_t);
 int small_linear(const float*, int, const float*, const float*, int, const float*, const float*, int, int, int, int,
                  float*, int, float*, cudaStream_t);
 size_t small_linear_ws_floats(int, int, int);
@@ -374,6 +375,9 @@ static Plan make_plan(const Ecapa* e, const Batch* b) {
   p.add("chain_scratch", res2net_scratch_bytes(e->Cs, static_cast<int>(P)));
   p.add("mfa", M * P * e->C3 * 2);
   p.add("att", M * P * e->att * 2);
+  p.add("se_sum", B * e->C * 8);            // fused column statistics (bf16 mode): int64 fixed-point sums
+  p.add("asp_sum", B * e->C3 * 8);
+  p.add("asp_sq", B * e->C3 * 8);
   p.add("se_mean", B * e->C * 4);
   p.add("se_hidden", B * e->se_ch * 4);
   p.add("se_gate", B * e->C * 4);
@@ -401,7 +405,7 @@ struct View { const bf16* p; int ld, plane_cols, cols; };
 static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, const View* x2, int x2_chunks, bf16* out,
                      int out_ld, int out_pc, int store_mode, const float* rowbias, int rowbias_ld, int post_tanh,
                      int out_kind_override, const View* add, bf16* out2, int out2_ld, int out2_pc, int passes,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, long long* colsum = nullptr, long long* colsq = nullptr, int stats_ld = 0) {
   GemmOperands ops{};
   ops.a = x.p; ops.lda = x.ld; ops.a_cols = x.cols;
   if (x2 != nullptr) { ops.a2 = x2->p; ops.lda2 = x2->ld; ops.a2_cols = x2->cols; }
@@ -421,6 +425,8 @@ static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, con
   const bool pointwise = L.k == 1 && store_mode == STORE_ALL && p.out_kind != OUT_F32 && add == nullptr && L.cout % 64 == 0 &&
                          ((L.act == ACT_GELU && rowbias == nullptr && !post_tanh) ||
                           (L.act == ACT_RELU && rowbias != nullptr && post_tanh));
+  p.colsum = colsum; p.colsq = colsq; p.stats_ld = stats_ld;
+  SVB_CHECK(colsum == nullptr || pointwise, "fused column statistics are an option of the pointwise GELU layers");
   if (pointwise) return launch_gemm_pw(ops, p, stream);
   const int bn = L.cout >= 256 ? 256 : (L.cout >= 128 ? 128 : 64);
   return launch_gemm(ops, p, bn, stream);
@@ -481,10 +487,18 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     }
     // tdnn2 (1x1): K chunks of channel group 0 come from U, the rest from R
     View rv{R, P * C, C, P * C}, uv{U, P * C, C, P * C};
+    // (bf16 mode: the SE squeeze -- per-utterance time mean of the output -- is accumulated by the GEMM epilogue)
+    const bool fuse_stats = !e->fp32_mode && C % 256 == 0;
+    long long* se_sum = reinterpret_cast<long long*>(base + pl.off("se_sum"));
+    if (fuse_stats) SVB_CUDA_OK(cudaMemsetAsync(se_sum, 0, static_cast<size_t>(B) * C * 8, stream));
     if (run_layer(e, b, e->tdnn2[i], rv, &uv, Cs / 64, V, P * C, C, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0,
-                  passes, stream)) return -1;
+                  passes, stream, fuse_stats ? se_sum : nullptr, nullptr, C)) return -1;
     // SE: time mean -> C->se->C gate -> gate * V + residual, written into the MFA concat buffer
-    if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
+    if (fuse_stats) {
+      if (colsum_finalize(se_sum, nullptr, C, b->d_uttrows, B, C, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
+    } else if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) {
+      return -1;
+    }
     if (small_linear(e->se_w1[i], C, e->se_b1[i], F("se_mean"), C, nullptr, nullptr, B, e->se_ch, C, LIN_RELU,
                      F("se_hidden"), e->se_ch, F("lin_part"), stream)) return -1;
     if (small_linear(e->se_w2[i], e->se_ch, e->se_b2[i], F("se_hidden"), e->se_ch, nullptr, nullptr, B, C, e->se_ch,
@@ -497,11 +511,19 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   // MFA over the (never materialised separately) concat of the three block outputs
   View xc{XC, P * C3, C3, P * C3};
   bf16* Y = H("mfa");
+  const bool fuse_asp = !e->fp32_mode && C3 % 256 == 0;
+  long long* asp_sum = reinterpret_cast<long long*>(base + pl.off("asp_sum"));
+  long long* asp_sq = reinterpret_cast<long long*>(base + pl.off("asp_sq"));
+  if (fuse_asp) SVB_CUDA_OK(cudaMemsetAsync(asp_sum, 0, 2 * ((static_cast<size_t>(B) * C3 * 8 + 255) / 256 * 256), stream));
   if (run_layer(e, b, e->mfa, xc, nullptr, 0, Y, P * C3, C3, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0, passes,
-                stream)) return -1;
+                stream, fuse_asp ? asp_sum : nullptr, fuse_asp ? asp_sq : nullptr, C3)) return -1;
   // ASP: global mean/std -> per-utterance bias; time-varying 3C->att GEMM; att->3C logits; softmax statistics
   float* st = F("asp_stats");
-  if (col_stats(Y, P * C3, P, C3, b->d_uttrows, B, C3, 1, 1e-12f, st, st + C3, 2 * C3, stream)) return -1;
+  if (fuse_asp) {
+    if (colsum_finalize(asp_sum, asp_sq, C3, b->d_uttrows, B, C3, 1e-12f, st, st + C3, 2 * C3, stream)) return -1;
+  } else if (col_stats(Y, P * C3, P, C3, b->d_uttrows, B, C3, 1, 1e-12f, st, st + C3, 2 * C3, stream)) {
+    return -1;
+  }
   if (small_linear(e->asp_w + C3, 3 * C3, nullptr, st, 2 * C3, nullptr, nullptr, B, e->att, 2 * C3, LIN_NONE,
                    F("asp_rowbias"), e->att, F("lin_part"), stream)) return -1;
   View yv{Y, P * C3, C3, P * C3};

@@ -22,16 +22,23 @@ namespace svb {
 static constexpr int BLOCK_M = 128;
 static constexpr int BLOCK_K = 64;
 static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
-static constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
-static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // one warp's 32 rows x 64 bf16 columns
+// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4.. epilogue.  EW = 8 epilogue warps (two per TMEM lane
+// quadrant, 128B-swizzled 32 x 64 staging boxes) or, for the GELU instances with BN = 256, EW = 16 (four per quadrant,
+// 64B-swizzled 32 x 32 boxes): with K = 1024 the epilogue of 8 warps took 1.5x the MMA time of a tile and is latency
+// bound (2 warps per scheduler); with 16 warps it idles 25 % of the time (profiles/r01_gemm_pw.md), which is the
+// headroom the fused column statistics use.  (Measured and rejected: cp.async.bulk.prefetch.tensor.L2 of the next
+// tile's A rows, burst or interleaved with the loads -- 7-9 % SLOWER on every shape.)
+static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // EW = 8: one warp's 32 rows x 64 bf16 columns
+static constexpr int OUT_BOX64_BYTES = 32 * 32 * 2; // EW = 16: one warp's 32 rows x 32 bf16 columns
 static constexpr int ACT_RAW_F32 = 3;               // epilogue variant: no bias/act/BN, fp32 accumulators stored as is
 
-template <int BN>
+template <int BN, int EW = 8>
 struct PwCfg {
+  static constexpr int NUM_THREADS = 128 + EW * 32;
   static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = (BN == 256) ? 4 : 6;
-  static constexpr int OUT_BYTES = 8 * OUT_BOX_BYTES;
+  static constexpr int OUT_BYTES = (EW == 16) ? 16 * OUT_BOX64_BYTES : 8 * OUT_BOX_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -48,6 +55,9 @@ struct PwParams {
   int rowbias_ld;
   const RowMeta* row_meta;
   int out_plane_cols;    // column offset of the lo plane in the output (HILO instances only)
+  long long* colsum;     // STATS instances: fixed-point per-utterance column sums of the bf16 outputs (valid rows)
+  long long* colsq;      // STATS == 2: and of their squares
+  int stats_ld;
 };
 
 __device__ __forceinline__ float tanh_exact(float x) {
@@ -56,12 +66,12 @@ __device__ __forceinline__ float tanh_exact(float x) {
   return 1.0f - 2.0f * fast_rcp(e + 1.0f);
 }
 
-template <int BN, int ACT, bool RBT, bool HILO>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <int BN, int ACT, bool RBT, bool HILO, int EW, int STATS>
+__global__ void __launch_bounds__(128 + EW * 32, 1)
 gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmOut,
                const PwParams p) {
-  using Cfg = PwCfg<BN>;
+  using Cfg = PwCfg<BN, EW>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES];
@@ -94,7 +104,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&tfull_bar[a]), 1);
-      mbar_init(smem_u32(&tempty_bar[a]), 8);
+      mbar_init(smem_u32(&tempty_bar[a]), EW);
     }
     fence_barrier_init();
   }
@@ -160,6 +170,143 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         umma_commit(smem_u32(&tfull_bar[acc]));
       }
     }
+  } else if (warp >= 4 && EW == 16) {
+    // ===================================================== epilogue, 16 warps: quadrant = warp % 4, 64-column group =
+    // (warp - 4) / 4, processed as two 32 x 32 units: TMEM -> regs -> bias/GELU/BN -> bf16 -> 64B-swizzled 2 KB box
+    // (row = lane, 64 bytes, 16-byte chunk j at j ^ ((lane >> 1) & 3)) -> one TMA store per unit.
+    static_assert(EW != 16 || (BN == 256 && ACT == ACT_GELU && !RBT), "the 16-warp epilogue serves the GELU BN=256 instances");
+    static_assert(!STATS || (EW == 16 && !HILO), "fused column statistics: 16-warp epilogue, single bf16 plane");
+    const int ew = warp - 4;
+    const int quad = ew & 3;
+    const int cgroup = ew >> 2;
+    const uint32_t my_box = out_base + ew * OUT_BOX64_BYTES;
+    const uint32_t my_row = my_box + lane * 64;
+    const int sw = (lane >> 1) & 3;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m0 = (tile / num_n_tiles) * BLOCK_M;
+      const int n0 = (tile % num_n_tiles) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      int my_utt = -1;        // utterance of this lane's row if it is a valid (non-halo) frame
+      unsigned stat_rows = 0;
+      if (STATS) {
+        const long long row = static_cast<long long>(m0) + quad * 32 + lane;
+        if (row < p.M) {
+          const RowMeta rm = p.row_meta[row];
+          if (rm.t >= 0 && rm.t < rm.T) my_utt = rm.utt;
+        }
+        stat_rows = __ballot_sync(0xffffffffu, my_utt >= 0);
+      }
+      mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int u = 0; u < 2; ++u) {
+        const int col0 = cgroup * 64 + u * 32;
+        const int n = n0 + col0;
+        if (n >= p.N) break;
+        uint32_t r[32];
+        tmem_ld32(tmem_base + acc * BN + col0 + (static_cast<uint32_t>(quad * 32) << 16), r);
+        tmem_ld_wait();
+        uint32_t hi[16];
+        uint32_t lo[16];   // dead (eliminated) unless HILO
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n);
+        const float4* s4 = reinterpret_cast<const float4*>(p.scale + n);
+        const float4* h4 = reinterpret_cast<const float4*>(p.shift + n);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 b = __ldg(b4 + i), s = __ldg(s4 + i), h = __ldg(h4 + i);
+          float x0 = gelu_fast(__uint_as_float(r[4 * i]) + b.x), x1 = gelu_fast(__uint_as_float(r[4 * i + 1]) + b.y);
+          float x2 = gelu_fast(__uint_as_float(r[4 * i + 2]) + b.z), x3 = gelu_fast(__uint_as_float(r[4 * i + 3]) + b.w);
+          x0 = fmaf(x0, s.x, h.x); x1 = fmaf(x1, s.y, h.y);
+          x2 = fmaf(x2, s.z, h.z); x3 = fmaf(x3, s.w, h.w);
+          const uint32_t p0 = pack_bf16x2(x0, x1), p1 = pack_bf16x2(x2, x3);
+          hi[2 * i] = p0;
+          hi[2 * i + 1] = p1;
+          if (HILO) {
+            lo[2 * i] = pack_bf16x2(x0 - bf16_lo_f(p0), x1 - bf16_hi_f(p0));
+            lo[2 * i + 1] = pack_bf16x2(x2 - bf16_lo_f(p1), x3 - bf16_hi_f(p1));
+          }
+        }
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(hi[4 * j]),
+                       "r"(hi[4 * j + 1]), "r"(hi[4 * j + 2]), "r"(hi[4 * j + 3])
+                       : "memory");
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmOut, my_box, n, m0 + quad * 32);
+          bulk_commit();
+        }
+        if (STATS) {
+          // column sums of the staged bf16 box over the valid rows of each utterance it touches (usually one): lane =
+          // (row parity h, column pair cp); 16 conflict-free LDS.32 per lane, one shuffle, int64 fixed-point atomics
+          const int h = lane >> 4, cp = lane & 15;
+          const uint32_t col_off = static_cast<uint32_t>((cp & 3) * 4);
+          unsigned todo = stat_rows;
+          while (todo) {
+            const int src = __ffs(todo) - 1;
+            const int utt = __shfl_sync(0xffffffffu, my_utt, src);
+            const unsigned m = __ballot_sync(0xffffffffu, my_utt == utt);
+            todo &= ~m;
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int r = 2 * i + h;
+              if ((m >> r) & 1u) {
+                uint32_t w;
+                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w)
+                             : "r"(my_box + r * 64 + ((((cp >> 2) ^ (i & 3))) << 4) + col_off));
+                const float a = bf16_lo_f(w), b = bf16_hi_f(w);
+                s0 += a; s1 += b;
+                if (STATS == 2) { q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1); }
+              }
+            }
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+            if (STATS == 2) {
+              q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
+              q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+            }
+            if (lane < 16) {
+              const long long o = static_cast<long long>(utt) * p.stats_ld + n + 2 * cp;
+              atomicAdd(reinterpret_cast<unsigned long long*>(p.colsum + o),
+                        static_cast<unsigned long long>(__float2ll_rn(s0 * 4294967296.f)));
+              atomicAdd(reinterpret_cast<unsigned long long*>(p.colsum + o + 1),
+                        static_cast<unsigned long long>(__float2ll_rn(s1 * 4294967296.f)));
+              if (STATS == 2) {
+                atomicAdd(reinterpret_cast<unsigned long long*>(p.colsq + o),
+                          static_cast<unsigned long long>(__float2ll_rn(q0 * 4294967296.f)));
+                atomicAdd(reinterpret_cast<unsigned long long*>(p.colsq + o + 1),
+                          static_cast<unsigned long long>(__float2ll_rn(q1 * 4294967296.f)));
+              }
+            }
+          }
+        }
+        if (HILO) {
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(lo[4 * j]),
+                         "r"(lo[4 * j + 1]), "r"(lo[4 * j + 2]), "r"(lo[4 * j + 3])
+                         : "memory");
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmOut, my_box, p.out_plane_cols + n, m0 + quad * 32);
+            bulk_commit();
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+    }
+    if (lane == 0) bulk_wait<0>();
   } else if (warp >= 4) {
     // ===================================================== epilogue: TMEM -> regs -> swizzled smem -> TMA store
     const int ew = warp - 4;
@@ -289,19 +436,19 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------ host side
-template <int BN, int ACT, bool RBT, bool HILO>
+template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0>
 static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& o,
                        const PwParams& p, cudaStream_t stream) {
-  using Cfg = PwCfg<BN>;
+  using Cfg = PwCfg<BN, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::SMEM_BYTES));
     attr_set = true;
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_pw_kernel<BN, ACT, RBT, HILO><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
+  gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS><<<grid, Cfg::NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -329,11 +476,19 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   }
   if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;
   const long long out_cols = hilo ? static_cast<long long>(g.out_plane_cols) + g.N : g.N;
-  if (make_map(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;
+  if (bn == 256) {   // 16-warp epilogue: 32 x 32 boxes, 64B swizzle
+    if (make_map_sw64(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;
+  } else if (make_map(&mo, g.out, g.M, out_cols, g.out_ld, 32)) {
+    return -1;
+  }
   PwParams p{};
   p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
   p.a2_kc = g.a2_kc; p.w_planes = g.w_planes; p.bias = g.bias; p.scale = g.scale; p.shift = g.shift;
   p.rowbias = g.rowbias; p.rowbias_ld = g.rowbias_ld; p.row_meta = g.row_meta; p.out_plane_cols = g.out_plane_cols;
+  p.colsum = g.colsum; p.colsq = g.colsq; p.stats_ld = g.stats_ld;
+  const int stats = g.colsum == nullptr ? 0 : (g.colsq == nullptr ? 1 : 2);
+  SVB_CHECK(!stats || (bn == 256 && !hilo && !rbt && g.row_meta != nullptr && g.stats_ld % 2 == 0),
+            "fused column statistics need the BN=256 single-plane GELU instance and row_meta");
   if (rbt) {
     SVB_CHECK(g.act == ACT_RELU, "the row-bias instance is ReLU + BN + tanh");
     return hilo ? launch_pw_t<128, ACT_RELU, true, true>(ma, ma2, mw, mo, p, stream)
@@ -341,8 +496,10 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   }
   SVB_CHECK(g.act == ACT_GELU, "the plain pointwise instance is GELU + BN");
   if (bn == 256)
-    return hilo ? launch_pw_t<256, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
-                : launch_pw_t<256, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
+    return hilo         ? launch_pw_t<256, ACT_GELU, false, true, 16>(ma, ma2, mw, mo, p, stream)
+           : stats == 2 ? launch_pw_t<256, ACT_GELU, false, false, 16, 2>(ma, ma2, mw, mo, p, stream)
+           : stats == 1 ? launch_pw_t<256, ACT_GELU, false, false, 16, 1>(ma, ma2, mw, mo, p, stream)
+                        : launch_pw_t<256, ACT_GELU, false, false, 16>(ma, ma2, mw, mo, p, stream);
   return hilo ? launch_pw_t<128, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
               : launch_pw_t<128, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
 }

@@ -333,6 +333,23 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
+// Same matrix with box = [32 cols (64 B), box_rows] and 64B swizzle: the 2 KB store boxes of gemm_pw's 16-warp epilogue.
+int make_map_sw64(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  SVB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  SVB_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0,
+            "TMA operand must be 16-byte aligned (base %p, ld %lld)", base, ld);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t box[2] = {32, static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SVB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (64B swizzle) failed with code %d", static_cast<int>(r));
+  return 0;
+}
+
 // 2D fp32 row-major matrix [rows, ld] exposing `cols` columns; box = [32 cols (128 B), box_rows], 128B swizzle.
 int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();

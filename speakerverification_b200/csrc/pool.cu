@@ -256,6 +256,34 @@ __global__ void l2norm_rows_kernel(const float* __restrict__ in, int in_ld, floa
 }
 
 // ------------------------------------------------------------------ launchers
+// Finalises the fixed-point column sums a GELU GEMM epilogue accumulated (gemm_pw.cu, STATS instances):
+// mean = sum / T, std = sqrt(clamp(sumsq / T - mean^2, eps)) in fp64 (the sums are exact to 2^-32 per 32-row box, so
+// the one-pass variance has no cancellation problem).  Same outputs as col_stats_kernel.
+__global__ void colsum_finalize_kernel(const long long* __restrict__ sum, const long long* __restrict__ sq, int stats_ld,
+                                       const UttRows* __restrict__ utts, int B, int C, float eps,
+                                       float* __restrict__ mean_out, float* __restrict__ std_out, int out_ld) {
+  const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<long long>(B) * C) return;
+  const int b = static_cast<int>(i / C), c = static_cast<int>(i - static_cast<long long>(b) * C);
+  const double inv = 1.0 / (4294967296.0 * static_cast<double>(utts[b].T));
+  const double mean = static_cast<double>(sum[static_cast<long long>(b) * stats_ld + c]) * inv;
+  mean_out[static_cast<long long>(b) * out_ld + c] = static_cast<float>(mean);
+  if (sq != nullptr) {
+    const double ex2 = static_cast<double>(sq[static_cast<long long>(b) * stats_ld + c]) * inv;
+    std_out[static_cast<long long>(b) * out_ld + c] = sqrtf(fmaxf(static_cast<float>(ex2 - mean * mean), eps));
+  }
+}
+
+int colsum_finalize(const long long* sum, const long long* sq, int stats_ld, const void* utts, int B, int C, float eps,
+                    float* mean_out, float* std_out, int out_ld, cudaStream_t stream) {
+  const long long n = static_cast<long long>(B) * C;
+  colsum_finalize_kernel<<<static_cast<int>((n + 255) / 256), 256, 0, stream>>>(
+      sum, sq, stats_ld, static_cast<const UttRows*>(utts), B, C, eps, mean_out, std_out, out_ld);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int col_stats(const bf16* x, int ld, int planes, int plane_cols, const void* utts, int B, int C, int mode, float eps,
               float* mean_out, float* std_out, int out_ld, cudaStream_t stream) {
   SVB_CHECK(C % 8 == 0, "C must be a multiple of 8");

@@ -74,6 +74,10 @@ struct GemmParams {
   void* out; int out_ld; int out_kind; int out_plane_cols;
   const bf16* add_src; int add_ld; int add_planes; int add_plane_cols;
   void* out2; int out2_ld; int out2_plane_cols;
+  // optional fused per-utterance column statistics of the OUTPUT (pointwise GELU layers, bf16 mode): fixed-point
+  // (2^-32) int64 sums [utterances, stats_ld] of the valid rows' bf16 outputs (and of their squares), accumulated with
+  // integer atomics -- order independent, so results stay bit-reproducible.  Buffers must be zeroed by the caller.
+  long long* colsum; long long* colsq; int stats_ld;
 };
 
 // RawNet2 GEMMs (rawnet_gemm.cu): fixed-length utterances, rows [utt][1 zero | T | 1 zero]
@@ -92,6 +96,7 @@ struct RnGemmParams {
 // 2D bf16 row-major matrix [rows, ld] exposing `cols` columns as a TMA map; box = [64 cols, box_rows], 128B swizzle.
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 
+int make_map_sw64(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 // Plain fp32-output GEMM out[M, N] = A * W^T through the TMA-store epilogue of gemm_pw.cu (N % 64 == 0).
 int launch_gemm_f32(const GemmOperands& ops, const GemmParams& p, cudaStream_t stream);

@@ -1,0 +1,9 @@
+#!/bin/bash
+# quick loop: ecapa/tdnn parity + short bench + launch list
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_tdnn_gpu.py tests/test_ecapa_gpu.py -m gpu -x -q 2>&1 | tail -3
+timeout 300 python bench.py --no-e2e --steps 3 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print('emb/s', d['value'], 'ms/step', d['ms_per_step'], 'mfa TF', d['roofline']['achieved'], d['roofline']['kernel_ms'], d['clocks'])"
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_fwd_q.csv python tools/profile_forward.py 256 bf16 2 > /dev/null 2>&1
+python tools/launch_summary.py gpurun_out/launches_fwd_q.csv | head -50
