@@ -586,7 +586,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="svb", choices=["svb", "reference"])
     ap.add_argument("--utts", type=int, default=10000)
-    ap.add_argument("--batch-rows", type=int, default=256)
+    ap.add_argument("--batch-rows", type=int, default=592)   # 4 x 148: whole waves of the per-utterance chain kernel
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2", "eval"])

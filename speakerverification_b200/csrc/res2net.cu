@@ -336,7 +336,11 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
   constexpr int NCOLH = CS / 2;
   constexpr int NG = NCOLH / 32;        // 32-column groups per warp per M tile
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t afull_bar, aempty_bar, wfull_bar, wempty_bar, tfull_bar, tempty_bar, sready_bar;
+  // per-M-tile accumulator / strip barriers: the epilogue of M tile 0 runs while the MMAs of tiles 1 and 2 are still
+  // executing, and the next step's MMAs of tile mt start as soon as the strip rows they read (tiles <= mt + 1) are
+  // rewritten, i.e. while the epilogue of the last tile is still running (the MMA phase, 25 % of a step, is hidden)
+  __shared__ __align__(8) uint64_t afull_bar, aempty_bar, wfull_bar, wempty_bar, tfull_bar[RC_MT], tempty_bar[RC_MT],
+      sready_bar[RC_MT];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
@@ -357,9 +361,11 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
     mbar_init(smem_u32(&aempty_bar), 1);
     mbar_init(smem_u32(&wfull_bar), 1);
     mbar_init(smem_u32(&wempty_bar), 1);
-    mbar_init(smem_u32(&tfull_bar), 1);
-    mbar_init(smem_u32(&tempty_bar), 8);
-    mbar_init(smem_u32(&sready_bar), 8);
+    for (int mt = 0; mt < RC_MT; ++mt) {
+      mbar_init(smem_u32(&tfull_bar[mt]), 1);
+      mbar_init(smem_u32(&tempty_bar[mt]), 8);
+      mbar_init(smem_u32(&sready_bar[mt]), 8);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -405,12 +411,14 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
         for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
           mbar_wait(smem_u32(&wfull_bar), nstep & 1u);
           if (j == 1) mbar_wait(smem_u32(&afull_bar), nitem & 1u);
-          else { mbar_wait(smem_u32(&sready_bar), nsr & 1u); ++nsr; }
-          mbar_wait(smem_u32(&tempty_bar), (nstep & 1u) ^ 1u);
-          tc_fence_after();
           if (p.dbg != nullptr && blockIdx.x == 0 && nstep < 64) p.dbg[nstep * 4 + 0] = clock64();
 #pragma unroll
           for (int mt = 0; mt < RC_MT; ++mt) {
+            // strip rows [mt*128 - d, mt*128 + 128 + d) of this step's input: written by the previous step's epilogue
+            // of tiles <= mt + 1 (epilogue tiles complete in order)
+            if (j > 1) mbar_wait(smem_u32(&sready_bar[mt + 1 < RC_MT ? mt + 1 : RC_MT - 1]), nsr & 1u);
+            mbar_wait(smem_u32(&tempty_bar[mt]), (nstep & 1u) ^ 1u);
+            tc_fence_after();
             uint32_t accf = 0;
 #pragma unroll
             for (int tap = 0; tap < 3; ++tap) {
@@ -422,9 +430,10 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
                 for (int k = 0; k < 4; ++k) { umma_bf16(tmem_base + mt * CS, adesc + 2 * k, bdesc + 2 * k, idesc, accf); accf = 1; }
               }
             }
+            umma_commit(smem_u32(&tfull_bar[mt]));
           }
+          if (j > 1) ++nsr;
           umma_commit(smem_u32(&wempty_bar));
-          umma_commit(smem_u32(&tfull_bar));
           if (j == RC_STEPS) umma_commit(smem_u32(&aempty_bar));
           if (p.dbg != nullptr && blockIdx.x == 0 && nstep < 64) p.dbg[nstep * 4 + 1] = clock64();
         }
@@ -497,11 +506,12 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
           load_x(0, 0, j, xc);
         }
         named_bar_sync(1, 256);
-        mbar_wait(smem_u32(&tfull_bar), nstep & 1u);
-        tc_fence_after();
-        if (p.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0 && nstep < 64) p.dbg[nstep * 4 + 2] = clock64();
+        bool all_mma_done = false;
 #pragma unroll
         for (int mt = 0; mt < RC_MT; ++mt) {
+          mbar_wait(smem_u32(&tfull_bar[mt]), nstep & 1u);
+          tc_fence_after();
+          if (mt == 0 && p.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0 && nstep < 64) p.dbg[nstep * 4 + 2] = clock64();
 #pragma unroll 1
           for (int g = 0; g < NG; ++g) {
             const int col = half * NCOLH + g * 32;
@@ -579,6 +589,12 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
                 for (int q = 0; q < 4; ++q)
                   pk[4 * i + q] = pack_bf16x2(v[8 * i + 2 * q] + bf16_lo_f(w[q]), v[8 * i + 2 * q + 1] + bf16_hi_f(w[q]));
               }
+              if (!all_mma_done) {
+                // the strip is single buffered: this step's MMAs of the later tiles read rows next to (and, through the
+                // reflect mirrors, inside) the rows rewritten here -- all of them must have completed first
+                mbar_wait(smem_u32(&tfull_bar[RC_MT - 1]), nstep & 1u);
+                all_mma_done = true;
+              }
               const uint32_t plane = a_smem + (col >> 6) * RS_PLANE;
               const int ci0 = (col & 63) >> 3;
               const int tg[3] = {own_s[mt] ? lrow[mt] : -1, mir_lo[mt], mir_hi[mt]};
@@ -595,15 +611,16 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
               }
             }
           }
+          // tile mt done: accumulator free, strip rows (and the mirrors they feed) in place
+          tc_fence_before();
+          if (j < RC_STEPS) fence_proxy_async();   // strip stores (generic proxy) -> visible to the tensor core (async proxy)
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(smem_u32(&tempty_bar[mt]));
+            if (j < RC_STEPS) mbar_arrive(smem_u32(&sready_bar[mt]));
+          }
         }
-        tc_fence_before();
         if (p.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0 && nstep < 64) p.dbg[nstep * 4 + 3] = clock64();
-        if (j < RC_STEPS) fence_proxy_async();     // strip stores (generic proxy) -> visible to the tensor core (async proxy)
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(smem_u32(&tempty_bar));
-          if (j < RC_STEPS) mbar_arrive(smem_u32(&sready_bar));
-        }
       }
     }
   }

@@ -110,8 +110,8 @@ class ModelHandling(object):
         self.device = torch.device(f"{device}:{gpu}")
         self.mixedprec = mixedprec
         # rows (crops) per encoder launch and samples per ragged launch
-        self.batch_rows = int(kwargs.get("svb_batch_rows", 256))
-        self.batch_samples = int(kwargs.get("svb_batch_samples", 256 * 48000))
+        self.batch_rows = int(kwargs.get("svb_batch_rows", 592))       # 4 x 148 SMs (sweep: profiles/r01_batch_sweep.md)
+        self.batch_samples = int(kwargs.get("svb_batch_samples", 592 * 48000))
         self._copy_stream = None
         self._stage_bufs = None
         self._pool = None
