@@ -14,6 +14,8 @@
 //     16-byte row stores per warp instruction.
 // Pointwise layers compute halo rows in place (the input halo rows mirror valid rows and the op is
 // per-row), so every row of a tile is stored and no mirror logic is needed.
+#include <stdlib.h>
+
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -66,7 +68,11 @@ __device__ __forceinline__ float tanh_exact(float x) {
   return 1.0f - 2.0f * fast_rcp(e + 1.0f);
 }
 
-template <int BN, int ACT, bool RBT, bool HILO, int EW, int STATS>
+// MC: launched as clusters of two CTAs that work on the two M tiles of an (M-tile pair, N tile) unit at the same time.
+// They need the same W tile, so each loads HALF of it and TMA-multicasts the half into both CTAs: L2 -> SM traffic per
+// CTA and k-block drops from 48 KB to 32 KB.  A stage may be refilled only when BOTH CTAs have consumed it (the peer's
+// multicast lands in it too), so the `empty` barriers count two multicast tcgen05.commit arrivals.
+template <int BN, int ACT, bool RBT, bool HILO, int EW, int STATS, bool MC>
 __global__ void __launch_bounds__(128 + EW * 32, 1)
 gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmOut,
@@ -87,7 +93,11 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int num_m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
   const int num_n_tiles = (p.N + BN - 1) / BN;
-  const int num_tiles = num_m_tiles * num_n_tiles;
+  const uint32_t crank = MC ? cluster_ctarank() : 0u;
+  const int num_tiles = MC ? ((num_m_tiles + 1) >> 1) * num_n_tiles : num_m_tiles * num_n_tiles;   // schedule units
+  const int sched_first = MC ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int sched_stride = MC ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  auto tile_m0 = [&](int t) { const int mt = t / num_n_tiles; return (MC ? 2 * mt + static_cast<int>(crank) : mt) * BLOCK_M; };
   const int kc = p.kc;
   const int num_kb = p.num_pass * kc;
 
@@ -100,7 +110,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(smem_u32(&full_bar[s]), 1);
-      mbar_init(smem_u32(&empty_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), MC ? 2 : 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&tfull_bar[a]), 1);
@@ -114,6 +124,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();      // the peer's barriers are initialised before anything is multicast into this CTA
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
@@ -122,8 +133,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / num_n_tiles) * BLOCK_M;
+      for (int tile = sched_first; tile < num_tiles; tile += sched_stride) {
+        const int m0 = tile_m0(tile);
         const int n0 = (tile % num_n_tiles) * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           const int pass = kb / kc;
@@ -137,7 +148,11 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           tma_load_2d(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, fb, a_col, m0);
-          tma_load_2d(sa + A_STAGE_BYTES, &tmW, fb, w_col, n0);
+          if (MC)
+            tma_load_2d_mc(sa + A_STAGE_BYTES + crank * (Cfg::B_STAGE_BYTES / 2), &tmW, fb, w_col,
+                           n0 + static_cast<int>(crank) * (BN / 2), 0x3);
+          else
+            tma_load_2d(sa + A_STAGE_BYTES, &tmW, fb, w_col, n0);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -149,7 +164,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = sched_first; tile < num_tiles; tile += sched_stride, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
@@ -164,7 +179,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int k = 0; k < BLOCK_K / 16; ++k)
             umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-          umma_commit(smem_u32(&empty_bar[stage]));
+          if (MC) umma_commit_mc(smem_u32(&empty_bar[stage]), 0x3);
+          else umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         umma_commit(smem_u32(&tfull_bar[acc]));
@@ -183,8 +199,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t my_row = my_box + lane * 64;
     const int sw = (lane >> 1) & 3;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m0 = (tile / num_n_tiles) * BLOCK_M;
+    for (int tile = sched_first; tile < num_tiles; tile += sched_stride, ++it) {
+      const int m0 = tile_m0(tile);
       const int n0 = (tile % num_n_tiles) * BN;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
@@ -316,8 +332,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t my_row = my_box + lane * 128;
     const int sw = lane & 7;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m0 = (tile / num_n_tiles) * BLOCK_M;
+    for (int tile = sched_first; tile < num_tiles; tile += sched_stride, ++it) {
+      const int m0 = tile_m0(tile);
       const int n0 = (tile % num_n_tiles) * BN;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
@@ -432,23 +448,41 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();      // no CTA exits while its peer may still multicast data or arrivals into it
   if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
 // ------------------------------------------------------------------ host side
-template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0>
+template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0, bool MC = false>
 static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& o,
                        const PwParams& p, cudaStream_t stream) {
   using Cfg = PwCfg<BN, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS><<<grid, Cfg::NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
+  const int m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M, n_tiles = (p.N + BN - 1) / BN;
+  if (MC) {
+    const int units = ((m_tiles + 1) / 2) * n_tiles;
+    const int clusters = units < num_sms() / 2 ? units : num_sms() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(Cfg::NUM_THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    SVB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC>, a, a2, w, o, p));
+  } else {
+    const int tiles = m_tiles * n_tiles;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
+    gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC><<<grid, Cfg::NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
+  }
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -474,7 +508,10 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   } else {
     ma2 = ma;
   }
-  if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;
+  // cluster pairs with W-tile multicast for the GELU BN=256 layers (SVB_PW_MC=0 selects the single-CTA instances)
+  static const bool mc_enabled = [] { const char* e = getenv("SVB_PW_MC"); return e == nullptr || e[0] != '0'; }();
+  const bool mc = mc_enabled && bn == 256 && !rbt;
+  if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, mc ? bn / 2 : bn)) return -1;
   const long long out_cols = hilo ? static_cast<long long>(g.out_plane_cols) + g.N : g.N;
   if (bn == 256) {   // 16-warp epilogue: 32 x 32 boxes, 64B swizzle
     if (make_map_sw64(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;
@@ -496,10 +533,17 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   }
   SVB_CHECK(g.act == ACT_GELU, "the plain pointwise instance is GELU + BN");
   if (bn == 256)
+  {
+    if (mc)
+      return hilo         ? launch_pw_t<256, ACT_GELU, false, true, 16, 0, true>(ma, ma2, mw, mo, p, stream)
+             : stats == 2 ? launch_pw_t<256, ACT_GELU, false, false, 16, 2, true>(ma, ma2, mw, mo, p, stream)
+             : stats == 1 ? launch_pw_t<256, ACT_GELU, false, false, 16, 1, true>(ma, ma2, mw, mo, p, stream)
+                          : launch_pw_t<256, ACT_GELU, false, false, 16, 0, true>(ma, ma2, mw, mo, p, stream);
     return hilo         ? launch_pw_t<256, ACT_GELU, false, true, 16>(ma, ma2, mw, mo, p, stream)
            : stats == 2 ? launch_pw_t<256, ACT_GELU, false, false, 16, 2>(ma, ma2, mw, mo, p, stream)
            : stats == 1 ? launch_pw_t<256, ACT_GELU, false, false, 16, 1>(ma, ma2, mw, mo, p, stream)
                         : launch_pw_t<256, ACT_GELU, false, false, 16>(ma, ma2, mw, mo, p, stream);
+  }
   return hilo ? launch_pw_t<128, ACT_GELU, false, true>(ma, ma2, mw, mo, p, stream)
               : launch_pw_t<128, ACT_GELU, false, false>(ma, ma2, mw, mo, p, stream);
 }
