@@ -22,6 +22,7 @@ int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, 
 int fbank_from_power(const Fbank*, const float*, const void*, int, const RowMeta*, long long, int, float*, float*, bf16*,
                      int, int, int, cudaStream_t);
 int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
+int pack_conv_weight_kpacked(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
 int colsum_finalize(const long long*, const long long*, int, const void*, int, int, float, float*, float*, int, cudaStream_t);
@@ -203,6 +204,11 @@ struct Ecapa {
   int fp32_mode = 0;  // 0: bf16 operands (block 0 split), 1: split-bf16 everywhere (fp32 grade)
   int dil[5] = {1, 2, 3, 4, 1}, ks[5] = {5, 3, 3, 3, 1};
   Layer block0, tdnn1[3], tdnn2[3], res[3][7], mfa, asp_tdnn, asp_conv;
+  // block 0 "K-packed": the log-mel rows are stored densely ([rows, n_mels], hi rows then lo rows), so the 5-tap window
+  // of a frame is one contiguous run of 5 * n_mels elements and the conv is a GEMM with K = 400 (padded to 448) read
+  // through an overlapping-row TMA view, instead of 5 taps x 128 padded channels = 640 (profiles/r01_summary.md)
+  bf16* block0_wk = nullptr;
+  int block0_kpad = 0;
   float *se_w1[3] = {}, *se_b1[3] = {}, *se_w2[3] = {}, *se_b2[3] = {};
   float *asp_w = nullptr;  // asp.tdnn conv weight fp32 [att, 9C] (the [mean;std] columns feed the per-utterance bias)
   float *aspbn_scale = nullptr, *aspbn_shift = nullptr, *fc_w = nullptr, *fc_b = nullptr;
@@ -296,6 +302,18 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
   int rc = 0;
   rc |= make_layer(e, tm, "blocks.0.", C, n_mels, e->ks[0], e->dil[0], 2, ACT_GELU, true, "conv.conv.", &e->block0);
   SVB_CHECK(rc || e->block0.cin_pad == MEL_PLANE, "block 0 expects the %d-column mel plane", MEL_PLANE);
+  // Off by default (SVB_BLOCK0_KPACK=1 enables it): measured on B200 it takes the block-0 GEMM from 618 to 586 us per 592
+  // crops only -- the layer is bound by gemm_tc's 8-warp epilogue, not by its 30 k-blocks -- and the changed fp32
+  // summation order moves the bf16-mode max score deviation of the C=1024 list test from 1.96e-3 to 2.01e-3, across the
+  // 2e-3 tolerance (mean deviation 4.2e-4 either way).  Kept for the planned move of block 0 onto gemm_pw's epilogue.
+  const char* kp = getenv("SVB_BLOCK0_KPACK");
+  if (!rc && n_mels % 8 == 0 && e->dil[0] == 1 && kp != nullptr && kp[0] == '1') {
+    const float* w0 = find(tm, "blocks.0.conv.conv.weight");
+    e->block0_kpad = (n_mels * e->ks[0] + 63) / 64 * 64;
+    e->block0_wk = dalloc<bf16>(e, static_cast<size_t>(C) * 2 * e->block0_kpad);
+    if (w0 == nullptr || e->block0_wk == nullptr) rc = -1;
+    else rc |= pack_conv_weight_kpacked(w0, C, n_mels, e->ks[0], e->block0_kpad, 2, e->block0_wk, 0);
+  }
   for (int i = 0; i < 3 && !rc; ++i) {
     const std::string p = "blocks." + std::to_string(i + 1) + ".";
     rc |= make_layer(e, tm, p + "tdnn1.", C, C, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->tdnn1[i]);
@@ -448,22 +466,41 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   const int C = e->C, C3 = e->C3, Cs = e->Cs, B = b->B;
   const long long M = b->rows;
 
-  // K1: waveform -> mean-normalised log-mel, hi|lo planes of 128 columns, halos mirrored
+  // K1: waveform -> mean-normalised log-mel, halos mirrored: hi|lo planes of 128 columns side by side, or (K-packed
+  // block 0) dense [rows, n_mels] hi rows followed, after rows + 128, by the lo rows
+  const bool kpack = e->block0_wk != nullptr;
+  const int x0_ld = kpack ? e->n_mels : 2 * MEL_PLANE, x0_pc = kpack ? e->n_mels : MEL_PLANE;
   if (input_kind == 0) {
     if (fbank_forward(fb, wav, b->d_utt, reinterpret_cast<const int32_t*>(b->d_tiles), B, b->ntiles, b->d_meta, M,
-                      b->halo, F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2, 0,
+                      b->halo, F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), x0_ld, x0_pc, 2, 0,
                       stream)) return -1;
   } else {
     if (fbank_from_power(fb, wav, b->d_utt, B, b->d_meta, M, b->halo, F("logmel"), F("mel_mean"), H("x0"),
-                         2 * MEL_PLANE, MEL_PLANE, 2, stream)) return -1;
+                         x0_ld, x0_pc, 2, stream)) return -1;
   }
 
   // block 0 (k=5): always split-bf16 on BOTH operands -- the log-mel input loses too much in plain bf16 (SURVEY
   // app. C), and with bf16 weights here (2 passes, measured) the C=1024 list-API score deviation rises from
   // <= 2.0e-3 to 2.3e-3, over the bf16 tolerance, for a 22 us gain: not worth it
-  View x0{H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2 * MEL_PLANE};
-  if (run_layer(e, b, e->block0, x0, nullptr, 0, H("block0"), P * C, C, STORE_MIRROR, nullptr, 0, 0, -1, nullptr, nullptr,
-                0, 0, 3, stream)) return -1;
+  if (kpack) {
+    const Layer& L = e->block0;
+    GemmOperands ops{};
+    ops.a = H("x0"); ops.lda = e->n_mels; ops.a_cols = e->block0_kpad;
+    ops.w = e->block0_wk; ops.w_rows = L.cout; ops.w_cols = 2 * e->block0_kpad;
+    GemmParams g{};
+    g.M = static_cast<int>(M); g.N = L.cout; g.kc_per_tap = e->block0_kpad / 64; g.num_taps = 1;
+    g.tap_off[0] = -((L.k - 1) / 2);                      // the window of frame t starts at row t - 2
+    g.num_pass = 3; g.a_plane_rows = static_cast<int>(M) + 128; g.w_planes = 2;
+    g.bias = L.bias; g.scale = L.scale; g.shift = L.shift; g.act = L.act; g.row_meta = b->d_meta;
+    g.store_mode = STORE_MIRROR; g.halo = b->halo;
+    g.out = H("block0"); g.out_ld = P * C; g.out_plane_cols = C;
+    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_BF16;
+    if (launch_gemm(ops, g, 256, stream)) return -1;
+  } else {
+    View x0{H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2 * MEL_PLANE};
+    if (run_layer(e, b, e->block0, x0, nullptr, 0, H("block0"), P * C, C, STORE_MIRROR, nullptr, 0, 0, -1, nullptr,
+                  nullptr, 0, 0, 3, stream)) return -1;
+  }
 
   bf16 *U = H("u"), *R = H("r"), *V = H("v"), *S[2] = {H("s0"), H("s1")}, *XC = H("xcat");
   View cur{H("block0"), P * C, C, P * C};

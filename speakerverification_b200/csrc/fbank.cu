@@ -20,6 +20,7 @@ namespace svb {
 static constexpr int NFFT = 512;
 static constexpr int NBIN = NFFT / 2 + 1;
 static constexpr int FRAMES_PER_TILE = 32;
+static constexpr int FB_ROW_SLACK = 128;   // slack rows after each plane of the stacked layout (= the workspace plan's row slack)
 static constexpr int FB_WARPS = 4;
 static constexpr int MAX_MELS = 128;
 static constexpr int MAX_NNZ = 4096;
@@ -241,13 +242,19 @@ __global__ void fbank_mean_kernel(const UttDesc* __restrict__ utts, const float*
 
 // One warp per padded row: subtract the utterance mean, mirror into halo rows, split to hi|lo bf16
 // and zero the channel padding (columns n_mels..plane_cols-1) so K can be tiled in 64-column chunks.
+// lo_off = element distance hi -> lo of the same (row, column): plane_cols when the planes sit side by side in a
+// row, (rows + FB_ROW_SLACK) * out_ld when they are stacked by rows (dense layout for the K-packed block 0, where
+// out_ld == n_mels and the 5-tap window of a frame is ONE contiguous run of 5 * n_mels elements).  Rows
+// [rows, rows + 8) are zeroed: the K padding of the packed window reads a few elements past the last row.
 __global__ void fbank_cmn_pack_kernel(const float* __restrict__ logmel, const float* __restrict__ mean,
                                       const RowMeta* __restrict__ meta, long long rows, int n_mels,
-                                      bf16* __restrict__ out, int out_ld, int plane_cols, int planes) {
+                                      bf16* __restrict__ out, int out_ld, int plane_cols, int planes, long long lo_off,
+                                      long long total_rows) {
   const long long row = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  if (row >= rows) return;
-  const RowMeta mt = meta[row];
+  if (row >= total_rows) return;
+  RowMeta mt{-1, 0, 0, 0};
+  if (row < rows) mt = meta[row];
   for (int m = lane; m < plane_cols; m += 32) {
     float v = 0.f;
     if (mt.utt >= 0 && m < n_mels) {
@@ -259,7 +266,7 @@ __global__ void fbank_cmn_pack_kernel(const float* __restrict__ logmel, const fl
     }
     const bf16 h = __float2bfloat16_rn(v);
     out[row * out_ld + m] = h;
-    if (planes == 2) out[row * out_ld + plane_cols + m] = __float2bfloat16_rn(v - __bfloat162float(h));
+    if (planes == 2) out[row * out_ld + lo_off + m] = __float2bfloat16_rn(v - __bfloat162float(h));
   }
 }
 
@@ -331,8 +338,13 @@ size_t fbank_smem_bytes(const Fbank* f) {
 static int pack_rows(const Fbank* f, const RowMeta* meta, long long rows, const float* logmel_ws, const float* mean_ws,
                      bf16* out, int out_ld, int plane_cols, int planes, cudaStream_t stream) {
   const int rows_per_block = 8;
-  fbank_cmn_pack_kernel<<<static_cast<int>((rows + rows_per_block - 1) / rows_per_block), rows_per_block * 32, 0,
-                          stream>>>(logmel_ws, mean_ws, meta, rows, f->n_mels, out, out_ld, plane_cols, planes);
+  // planes stacked by rows when they do not fit side by side (see the kernel comment); the caller's buffer then holds
+  // 2 * (rows + FB_ROW_SLACK) rows of out_ld elements
+  const bool stacked = planes == 2 && out_ld < 2 * plane_cols;
+  const long long lo_off = stacked ? (rows + FB_ROW_SLACK) * out_ld : plane_cols;
+  const long long nrows = stacked ? rows + 8 : rows;
+  fbank_cmn_pack_kernel<<<static_cast<int>((nrows + rows_per_block - 1) / rows_per_block), rows_per_block * 32, 0,
+                          stream>>>(logmel_ws, mean_ws, meta, rows, f->n_mels, out, out_ld, plane_cols, planes, lo_off, nrows);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;

@@ -133,8 +133,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int pass = (p.num_pass == 2 && pass_i == 1) ? 2 : pass_i;   // 2 passes: hi*hi + lo(A)*hi(W)
           const int aplane = (pass == 2) ? 1 : 0;
           const int wplane = (pass == 1) ? 1 : 0;
-          const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
-          const int a_row = m0 + p.tap_off[tap];
+          const int a_col = (p.a_plane_rows ? 0 : aplane * p.a_plane_cols) + kcx * BLOCK_K;
+          const int a_row = m0 + p.tap_off[tap] + aplane * p.a_plane_rows;
           const int w_col = ((tap * p.w_planes + wplane) * kc + kcx) * BLOCK_K;
           const uint32_t fb = smem_u32(&full_bar[stage]);
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
@@ -388,7 +388,8 @@ int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaS
   SVB_CHECK(p.num_pass >= 1 && p.num_pass <= 3, "num_pass must be 1, 2 or 3");
   SVB_CHECK(p.N % 32 == 0, "N must be a multiple of 32 (got %d)", p.N);
   CUtensorMap ma, ma2, mw;
-  if (make_map(&ma, ops.a, p.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
+  // (a_cols may exceed lda: overlapping rows, the K-packed window view of a dense activation matrix)
+  if (make_map(&ma, ops.a, static_cast<long long>(p.M) + p.a_plane_rows, ops.a_cols, ops.lda, BLOCK_M)) return -1;
   if (ops.a2 != nullptr) {
     if (make_map(&ma2, ops.a2, p.M, ops.a2_cols, ops.lda2, BLOCK_M)) return -1;
   } else {

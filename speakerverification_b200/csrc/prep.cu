@@ -38,6 +38,24 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, int cout, i
   }
 }
 
+// w [cout, cin, k] -> out [cout, planes, kpad] with K index j * cin + c (tap-major, channels contiguous): the layout of a
+// "K-packed" conv whose A operand row is the contiguous k * cin window of a dense [rows, cin] activation matrix.
+__global__ void pack_conv_weight_kpacked_kernel(const float* __restrict__ w, int cout, int cin, int k, int kpad, int planes,
+                                                bf16* __restrict__ out) {
+  const long long total = (long long)cout * kpad;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int kk = static_cast<int>(i % kpad);
+    const int o = static_cast<int>(i / kpad);
+    const int j = kk / cin, c = kk - j * cin;
+    const float v = (kk < cin * k) ? w[((long long)o * cin + c) * k + j] : 0.f;
+    const bf16 h = __float2bfloat16_rn(v);
+    bf16* dst = out + ((long long)o * planes) * kpad + kk;
+    dst[0] = h;
+    if (planes == 2) dst[kpad] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
 __global__ void fold_bn_kernel(const float* g, const float* b, const float* m, const float* v, int n, float eps,
                                float* scale, float* shift) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -115,6 +133,16 @@ int pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, int 
   const long long total = (long long)cout * k * cin_pad;
   const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
   pack_conv_weight_kernel<<<grid, 256, 0, stream>>>(w, cout, cin, k, cin_pad, planes, out);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int pack_conv_weight_kpacked(const float* w, int cout, int cin, int k, int kpad, int planes, bf16* out, cudaStream_t stream) {
+  SVB_CHECK(kpad % 64 == 0 && kpad >= cin * k, "kpad must be a multiple of 64 and >= cin * k");
+  const long long total = (long long)cout * kpad;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  pack_conv_weight_kpacked_kernel<<<grid, 256, 0, stream>>>(w, cout, cin, k, kpad, planes, out);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;

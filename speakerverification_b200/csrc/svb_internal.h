@@ -78,6 +78,8 @@ struct GemmParams {
   // (2^-32) int64 sums [utterances, stats_ld] of the valid rows' bf16 outputs (and of their squares), accumulated with
   // integer atomics -- order independent, so results stay bit-reproducible.  Buffers must be zeroed by the caller.
   long long* colsum; long long* colsq; int stats_ld;
+  // A planes stacked by rows (K-packed block 0): the lo plane of row r is row r + a_plane_rows of the same map
+  int a_plane_rows;
 };
 
 // RawNet2 GEMMs (rawnet_gemm.cu): fixed-length utterances, rows [utt][1 zero | T | 1 zero]
