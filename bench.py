@@ -423,8 +423,9 @@ def run_eval(args, device, rank, world, dist):
     U, N, K, NT = args.eval_utts, 6000, 300, args.eval_trials
     margs = model_args("cuda", args.precision)
     net = WrappedModel(SpeakerEncoder(**margs))
+    # end-to-end launches are smaller than the device-resident ones: finer double buffering of the H2D copies
     handle = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=4096,
-                                       svb_batch_samples=args.batch_rows * L))
+                                       svb_batch_samples=args.e2e_rows * L))
     sd = net.module.state_dict()
     for k, v in synth.ecapa_state_dict(CH, N_OUT).items():
         sd[k].copy_(torch.as_tensor(v))
@@ -447,7 +448,7 @@ def run_eval(args, device, rank, world, dist):
     groups, i, off = [], 0, 0
     while i < len(staged):
         j, tot = i, 0
-        while j < len(staged) and (j == i or tot + len(staged[j]) <= handle.batch_samples):
+        while j < len(staged) and (j == i or tot + len(staged[j]) <= args.batch_rows * L):
             tot += len(staged[j])
             j += 1
         groups.append((i, j, off, tot))
@@ -590,6 +591,7 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2", "eval"])
+    ap.add_argument("--e2e-rows", type=int, default=296)
     ap.add_argument("--eval-utts", type=int, default=2000)
     ap.add_argument("--eval-trials", type=int, default=100000)
     ap.add_argument("--score-utts", type=int, default=200000)

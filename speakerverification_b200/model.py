@@ -111,7 +111,7 @@ class ModelHandling(object):
         self.mixedprec = mixedprec
         # rows (crops) per encoder launch and samples per ragged launch
         self.batch_rows = int(kwargs.get("svb_batch_rows", 592))       # 4 x 148 SMs (sweep: profiles/r01_batch_sweep.md)
-        self.batch_samples = int(kwargs.get("svb_batch_samples", 592 * 48000))
+        self.batch_samples = int(kwargs.get("svb_batch_samples", 296 * 48000))   # ragged launches: finer H2D double buffering
         self._copy_stream = None
         self._stage_bufs = None
         self._pool = None
