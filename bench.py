@@ -764,7 +764,11 @@ def main():
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "roofline": {"kernel": "gemm_pw_kernel<256,GELU> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
                          "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
-                         "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one MFA launch at 592 rows (ncu --set full,
+                         # profiles/r01_summary.md): 1.215 GB + 1.132 GB against 2.267 GB algorithmic
+                         "traffic": 2.347e9 if args.batch_rows == 592 else None,
+                         "traffic_unit": "bytes per launch (ncu capture of the same shape; algorithmic 2.267e9)",
+                         "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
             "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
                             "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
                             "note": "whole step, algorithmic 11.29 GFLOP per utterance vs sustained bf16 peak"},
