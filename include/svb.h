@@ -82,6 +82,12 @@ typedef struct SvbTdnnArgs {
   int32_t add_ld, add_planes, add_plane_cols;
   void* out2; int32_t out2_ld, out2_plane_cols;
   int32_t block_n;         /* 0 = auto */
+  /* optional fused per-utterance column statistics of the OUTPUT (pointwise GELU layers, cout % 256 == 0, bf16 output,
+   * row_meta required): col_sum[utt * stats_ld + c] += round(2^32 * sum over the utterance's valid rows of out[r, c]),
+   * col_sq likewise for out^2.  int64 fixed point, integer atomics (order independent, bit reproducible); the caller
+   * zeroes the buffers.  Replaces the separate time-mean passes of SEBlock (src/models/ECAPA_TDNN.py:171-172) and of
+   * AttentiveStatisticsPooling's global context (src/models/ECAPA_TDNN.py:222-227). */
+  int64_t* col_sum; int64_t* col_sq; int32_t stats_ld;
 } SvbTdnnArgs;
 
 int svb_tdnn_layer(const SvbTdnnArgs* args, void* stream);

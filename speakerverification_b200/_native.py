@@ -35,6 +35,7 @@ class SvbTdnnArgs(_c.Structure):
         ("add_src", _vp), ("add_ld", _i32), ("add_planes", _i32), ("add_plane_cols", _i32),
         ("out2", _vp), ("out2_ld", _i32), ("out2_plane_cols", _i32),
         ("block_n", _i32),
+        ("col_sum", _vp), ("col_sq", _vp), ("stats_ld", _i32),
     ]
 
 
@@ -182,7 +183,7 @@ def tdnn_layer(x, w_packed, cout, cin_pad, k, dilation, bias, bn_scale, bn_shift
                passes=1, w_planes=1, x_plane_cols=0, x_cols=None, x2=None, x2_chunks=0, row_bias=None,
                post_tanh=False, row_meta=None, store_mode=STORE_ALL, halo=0, out_kind=OUT_BF16,
                out_plane_cols=0, add_src=None, add_planes=1, add_plane_cols=0, out2=None,
-               out2_plane_cols=0, block_n=0, rows=None):
+               out2_plane_cols=0, block_n=0, rows=None, col_sum=None, col_sq=None):
     a = SvbTdnnArgs()
     a.rows = x.shape[0] if rows is None else rows
     a.x, a.x_ld = ptr(x), x.stride(0)
@@ -203,5 +204,9 @@ def tdnn_layer(x, w_packed, cout, cin_pad, k, dilation, bias, bn_scale, bn_shift
         a.add_src, a.add_ld, a.add_planes, a.add_plane_cols = ptr(add_src), add_src.stride(0), add_planes, add_plane_cols
         a.out2, a.out2_ld, a.out2_plane_cols = ptr(out2), out2.stride(0), out2_plane_cols
     a.block_n = block_n
+    if col_sum is not None:
+        a.col_sum, a.stats_ld = ptr(col_sum), col_sum.stride(0)
+        if col_sq is not None:
+            a.col_sq = ptr(col_sq)
     check(lib().svb_tdnn_layer(ctypes.byref(a), stream_ptr()))
     return out

@@ -159,6 +159,10 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
   p.out2 = (a->add_src != nullptr) ? a->out2 : nullptr;
   p.out2_ld = a->out2_ld;
   p.out2_plane_cols = a->out2_plane_cols;
+  p.colsum = reinterpret_cast<long long*>(a->col_sum);
+  p.colsq = reinterpret_cast<long long*>(a->col_sq);
+  p.stats_ld = a->stats_ld;
+  SVB_CHECK(a->col_sq == nullptr || a->col_sum != nullptr, "col_sq needs col_sum");
   int bn = a->block_n;
   // pointwise GELU / (ReLU + row-bias + tanh) layers with bf16 output take the lean-epilogue kernel (gemm_pw.cu)
   const bool pointwise = bn == 0 && a->k == 1 && a->store_mode == SVB_STORE_ALL && a->out_kind != SVB_OUT_F32 &&
@@ -166,6 +170,7 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
                          ((a->act == SVB_ACT_GELU && a->row_bias == nullptr && !a->post_tanh) ||
                           (a->act == SVB_ACT_RELU && a->row_bias != nullptr && a->post_tanh && a->row_meta != nullptr));
   if (pointwise) return launch_gemm_pw(ops, p, static_cast<cudaStream_t>(stream));
+  SVB_CHECK(a->col_sum == nullptr, "fused column statistics are an option of the pointwise GELU layers");
   if (bn == 0) bn = (a->cout >= 256) ? 256 : (a->cout >= 128 ? 128 : 64);
   return launch_gemm(ops, p, bn, static_cast<cudaStream_t>(stream));
 }
