@@ -12,6 +12,8 @@
 
 #include <algorithm>
 
+#include <stdlib.h>
+
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -344,16 +346,29 @@ topk_stats_smem_kernel(const float* __restrict__ S, int ld, int N, int K, float*
 // Register-resident variant for N <= NT * 4 * PER4: each thread keeps PER4 float4 of the row in registers (all
 // loads in flight at once, one L2 round trip), so the kernel needs no dynamic shared memory and four CTAs share
 // an SM.  Same algorithm as topk_stats_smem_kernel.
-template <int PER4, int NT>
+// FIXUP instances walk all `rows` with a small grid and redo only the rows the sampled kernel below flagged
+// (sigma < 0): the exact path stays the arbiter for every row the fast path cannot prove.
+template <int PER4, int NT, bool FIXUP>
 __global__ void __launch_bounds__(NT, 2048 / NT / 2 > 0 ? 2048 / NT / 2 : 1)
 topk_stats_reg_kernel(const float* __restrict__ S, int ld, int N, int K, float* __restrict__ mu,
-                      float* __restrict__ sigma) {
+                      float* __restrict__ sigma, int rows) {
+ if (FIXUP) {
+  // usually nothing is flagged: all threads look at the CTA's rows at once and leave
+  int any = 0;
+  for (int r = blockIdx.x + threadIdx.x * gridDim.x; r < rows; r += NT * gridDim.x) any |= !(sigma[r] >= 0.f);
+  if (!__syncthreads_or(any)) return;
+ }
+ for (int rowi = blockIdx.x; rowi < rows; rowi += gridDim.x) {
+  if (FIXUP) {
+    if (sigma[rowi] >= 0.f) continue;      // uniform over the CTA
+    __syncthreads();                       // shared tables of the previous row are no longer read
+  }
   __shared__ uint32_t hist[2048];
   __shared__ float cand[TOPK_CAND];
   __shared__ uint32_t sel[2], ncand_s, wtot[NT / 32];
   __shared__ float red_lo[NT / 32], red_hi[NT / 32];
   __shared__ double red_s[NT / 32], red_q[NT / 32];
-  const float* row = S + static_cast<long long>(blockIdx.x) * ld;
+  const float* row = S + static_cast<long long>(rowi) * ld;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   for (int i = tid; i < 2048; i += NT) hist[i] = 0;
   if (tid == 0) ncand_s = 0;
@@ -455,6 +470,164 @@ topk_stats_reg_kernel(const float* __restrict__ S, int ld, int N, int K, float* 
       ts += copies * kv;
       tq += copies * kv * kv;
     }
+    const double m = ts / K;
+    const double var = fmax(tq / K - m * m, 0.0);
+    mu[rowi] = static_cast<float>(m);
+    sigma[rowi] = static_cast<float>(sqrt(var));
+  }
+ }
+}
+
+
+// Sampled pre-filter + exact selection among the survivors.  The exact kernel above spends ~20 instructions per
+// score, most of them on the 2048-bin shared-memory histogram of ALL N scores.  Only the top K matter: a histogram of
+// every 4th score (the x components of the float4 the thread already holds) estimates a threshold that keeps about
+// K + 8 sqrt(K) scores, the full row is then swept with ONE compare per score, and the exact algorithm (linear
+// histogram, threshold bin, rank by counting) runs on the few hundred survivors in shared memory.  Exactness: the
+// survivors are {v >= thr}, so they contain the K largest whenever there are at least K of them; rows where the
+// estimate fails (fewer than K or more than TOPK_L1 survivors, degenerate ranges, too many ties) are flagged with
+// sigma = -1 and redone by the exact kernel (FIXUP instance).
+#define TOPK_L1 2048
+// The row is NOT kept in registers here (the exact kernel's 24 values per thread fill the register file with one CTA
+// per SM, and a row is a chain of ~10 barrier-separated phases: 8.5 us of latency per row with nothing to overlap it).
+// Only the sample lives in registers; the sweep re-reads the row from L2.  512 threads, 32 registers: four CTAs per SM.
+template <int SAMP4, int NT>
+__global__ void __launch_bounds__(NT, 4)
+topk_stats_sampled_kernel(const float* __restrict__ S, int ld, int N, int K, float* __restrict__ mu,
+                          float* __restrict__ sigma) {
+  __shared__ uint32_t hist[2048];
+  __shared__ float l1[TOPK_L1];
+  __shared__ float cand[NT];
+  __shared__ uint32_t sel[2], n1_s, ncand_s, wtot[NT / 32];
+  __shared__ float red_lo[NT / 32], red_hi[NT / 32];
+  __shared__ double red_s[NT / 32], red_q[NT / 32];
+  const float* row = S + static_cast<long long>(blockIdx.x) * ld;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < 2048; i += NT) hist[i] = 0;
+  if (tid == 0) { n1_s = 0; ncand_s = 0; }
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  const int n4 = N >> 2;                       // whole float4 groups; the (< 4) tail elements are handled in the sweep
+  const float NINF = -INFINITY;
+  // A. sample = every 4th float4 of the row (kept in registers), its range, its histogram
+  float v[SAMP4 * 4];
+  int nsamp = 0;
+#pragma unroll
+  for (int j = 0; j < SAMP4; ++j) {
+    const int i4 = 4 * (tid + NT * j);
+    float4 q = make_float4(NINF, NINF, NINF, NINF);
+    if (i4 < n4) { q = row4[i4]; nsamp += 4; }
+    v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+  }
+  float lo = INFINITY, hi = NINF;
+#pragma unroll
+  for (int j = 0; j < SAMP4 * 4; ++j) {
+    hi = fmaxf(hi, v[j]);
+    lo = fminf(lo, v[j] == NINF ? INFINITY : v[j]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    nsamp += __shfl_xor_sync(0xffffffffu, nsamp, o);
+  }
+  if (lane == 0) { red_lo[wid] = lo; red_hi[wid] = hi; wtot[wid] = static_cast<uint32_t>(nsamp); }
+  __syncthreads();
+  lo = red_lo[0]; hi = red_hi[0];
+  uint32_t total_samp = wtot[0];
+  for (int w = 1; w < NT / 32; ++w) { lo = fminf(lo, red_lo[w]); hi = fmaxf(hi, red_hi[w]); total_samp += wtot[w]; }
+  __syncthreads();                             // wtot is reused by find_bin
+  const float range = hi - lo;
+  const float scale = (range > 0.f && range < INFINITY) ? 2047.f / range : 0.f;
+#pragma unroll
+  for (int j = 0; j < SAMP4 * 4; ++j)
+    if (v[j] != NINF) atomicAdd(&hist[lin_bin(v[j], lo, scale)], 1u);
+  __syncthreads();
+  const int ks4 = (K + 3) / 4;
+  const uint32_t want = static_cast<uint32_t>(ks4 + 6 * static_cast<int>(sqrtf(static_cast<float>(ks4)) + 1.f) + 8);
+  const bool sample_ok = scale > 0.f && want <= total_samp;
+  float thr = lo;
+  if (sample_ok) {
+    find_bin<NT>(hist, 2048, want, 0u, 0, sel, wtot);
+    thr = lo + static_cast<float>(sel[0]) / scale;          // about the lower edge of the threshold bin
+  }
+  __syncthreads();
+  // B. sweep of the whole row (from L2): one compare per score, survivors to shared memory
+  if (sample_ok) {
+    for (int i4 = tid; i4 < n4; i4 += NT) {
+      const float4 q = row4[i4];
+      const float x[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (x[c] >= thr) {
+          const uint32_t slot = atomicAdd(&n1_s, 1u);
+          if (slot < TOPK_L1) l1[slot] = x[c];
+        }
+      }
+    }
+    if (tid < (N & 3)) {
+      const float x = row[4 * n4 + tid];
+      if (x >= thr) {
+        const uint32_t slot = atomicAdd(&n1_s, 1u);
+        if (slot < TOPK_L1) l1[slot] = x;
+      }
+    }
+  }
+  for (int i = tid; i < 2048; i += NT) hist[i] = 0;
+  __syncthreads();
+  const uint32_t n1 = n1_s;
+  if (!sample_ok || n1 < static_cast<uint32_t>(K) || n1 > TOPK_L1) {
+    if (tid == 0) sigma[blockIdx.x] = -1.f;                 // exact kernel redoes this row
+    return;
+  }
+  // C. exact top-K among the survivors: linear histogram over [thr, max], threshold bin, rank inside it
+  float hi1 = NINF;
+  for (int i = tid; i < static_cast<int>(n1); i += NT) hi1 = fmaxf(hi1, l1[i]);
+  for (int o = 16; o > 0; o >>= 1) hi1 = fmaxf(hi1, __shfl_xor_sync(0xffffffffu, hi1, o));
+  if (lane == 0) red_hi[wid] = hi1;
+  __syncthreads();
+  hi1 = red_hi[0];
+  for (int w = 1; w < NT / 32; ++w) hi1 = fmaxf(hi1, red_hi[w]);
+  const float range1 = hi1 - thr;
+  const float scale1 = (range1 > 0.f && range1 < INFINITY) ? 2047.f / range1 : 0.f;
+  for (int i = tid; i < static_cast<int>(n1); i += NT) atomicAdd(&hist[max(0, lin_bin(l1[i], thr, scale1))], 1u);
+  __syncthreads();
+  find_bin<NT>(hist, 2048, static_cast<uint32_t>(K), 0u, 0, sel, wtot);
+  const int bin_sel = static_cast<int>(sel[0]);
+  const uint32_t need = sel[1];
+  __syncthreads();
+  double s = 0.0, q = 0.0;
+  for (int i = tid; i < static_cast<int>(n1); i += NT) {
+    const float x = l1[i];
+    const int b = max(0, lin_bin(x, thr, scale1));
+    if (b > bin_sel) { s += x; q += static_cast<double>(x) * x; }
+    else if (b == bin_sel) {
+      const uint32_t slot = atomicAdd(&ncand_s, 1u);
+      if (slot < NT) cand[slot] = x;
+    }
+  }
+  __syncthreads();
+  const uint32_t ncand = ncand_s;
+  if (ncand > NT) {                                          // heavy ties in the threshold bin: exact kernel
+    if (tid == 0) sigma[blockIdx.x] = -1.f;
+    return;
+  }
+  if (tid < static_cast<int>(ncand)) {
+    const float mine = cand[tid];
+    uint32_t rank = 0;
+    for (int i = 0; i < static_cast<int>(ncand); ++i) {
+      const float c = cand[i];
+      rank += (c > mine || (c == mine && i < tid)) ? 1u : 0u;
+    }
+    if (rank < need) { s += mine; q += static_cast<double>(mine) * mine; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) { red_s[wid] = s; red_q[wid] = q; }
+  __syncthreads();
+  if (tid == 0) {
+    double ts = 0.0, tq = 0.0;
+    for (int w = 0; w < NT / 32; ++w) { ts += red_s[w]; tq += red_q[w]; }
     const double m = ts / K;
     const double var = fmax(tq / K - m * m, 0.0);
     mu[blockIdx.x] = static_cast<float>(m);
@@ -590,10 +763,27 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
     g.a_plane_cols = Dp; g.w_planes = 2; g.bias = zeros; g.scale = ones; g.shift = zeros;
     g.act = ACT_NONE; g.store_mode = STORE_ALL; g.out = S; g.out_ld = Np; g.out_kind = OUT_F32;
     if (launch_gemm_f32(ops, g, stream)) return -1;
-    if (N <= 512 * 16)
-      topk_stats_reg_kernel<4, 512><<<rows, 512, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
-    else if (N <= 1024 * 24)
-      topk_stats_reg_kernel<6, 1024><<<rows, 1024, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+    static const bool sampled = [] { const char* e = getenv("SVB_TOPK_SAMPLED"); return e == nullptr || e[0] != '0'; }();
+    const bool fast = sampled && K >= 16 && 8 * K <= N;        // the pre-filter pays when K << N
+    if (N <= 512 * 16) {
+      if (fast) {
+        topk_stats_sampled_kernel<1, 512><<<rows, 512, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+        topk_stats_reg_kernel<4, 512, true><<<std::min(rows, 2 * num_sms()), 512, 0, stream>>>(S, Np, N, K, mu + u0,
+                                                                                              sigma + u0, rows);
+        count_launch();
+      } else {
+        topk_stats_reg_kernel<4, 512, false><<<rows, 512, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0, rows);
+      }
+    } else if (N <= 1024 * 24) {
+      if (fast) {
+        topk_stats_sampled_kernel<3, 512><<<rows, 512, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
+        topk_stats_reg_kernel<6, 1024, true><<<std::min(rows, num_sms()), 1024, 0, stream>>>(S, Np, N, K, mu + u0,
+                                                                                             sigma + u0, rows);
+        count_launch();
+      } else {
+        topk_stats_reg_kernel<6, 1024, false><<<rows, 1024, 0, stream>>>(S, Np, N, K, mu + u0, sigma + u0, rows);
+      }
+    }
     else if (smem_rows)
       topk_stats_smem_kernel<<<rows, 512, static_cast<size_t>(Np) * 4, stream>>>(S, Np, N, K, mu + u0, sigma + u0);
     else
