@@ -94,3 +94,37 @@ def test_scoring_sweep_properties():
     assert (s_ab - s_perm).abs().max().item() < 1e-4                 # cohort order is irrelevant
     same = U.score_trials(emb, ia, ia, "cosine")
     assert (same - 1).abs().max().item() < 1e-6
+
+
+@pytest.mark.parametrize("N,K", [(20000, 300), (6000, 300), (8000, 100)])
+def test_topk_sampled_prefilter_adversarial_rows(N, K):
+    """The sampled pre-filter select against numpy's full sort on rows built to break its estimate: one-hot embeddings
+    pick cohort COLUMNS as score rows.  Ties everywhere, the top-K hidden from / concentrated in the sampled positions
+    (every 4th float4), thousands of copies of the maximum, bimodal, sorted and random rows: every row must come out
+    exact, through the fast path or through the exact-kernel fix-up."""
+    from speakerverification_b200 import utils as U
+    rng = np.random.default_rng(N + K)
+    D = 64
+    cols = []
+    idx = np.arange(N)
+    sampled = (idx // 4) % 4 == 0
+    base = 0.01 * rng.standard_normal(N)
+    cols.append(np.full(N, 0.25))                                            # all equal
+    c1 = base.copy(); c1[np.flatnonzero(sampled)[:K]] = 0.5 + 0.1 * rng.random(K); cols.append(c1)     # top-K only in the sample
+    c2 = base.copy(); c2[np.flatnonzero(~sampled)[:K]] = 0.5 + 0.1 * rng.random(K); cols.append(c2)    # top-K hidden from the sample
+    c3 = base.copy(); c3[rng.permutation(N)[:5000]] = 0.75; cols.append(c3)  # 5000 copies of the maximum
+    c4 = np.full(N, -0.125); c4[rng.permutation(N)[:K - 1]] = 0.5 + 0.1 * rng.random(K - 1); cols.append(c4)   # bimodal, K-th is a tie
+    cols.append(rng.standard_normal(N) * 0.1)                                # plain
+    cols.append(np.linspace(-0.5, 0.5, N))                                   # sorted ascending
+    cols.append(np.linspace(0.5, -0.5, N))                                   # sorted descending
+    c8 = base.copy(); c8[:2 * K] = 1e3 * (1 + rng.random(2 * K)); cols.append(c8)    # huge dynamic range
+    c = np.zeros((N, D), dtype=np.float32)
+    for j, col in enumerate(cols):
+        c[:, j] = col.astype(np.float32)
+    e = np.zeros((len(cols), D), dtype=np.float32)
+    e[np.arange(len(cols)), np.arange(len(cols))] = 1.0
+    mu, sg = U.asnorm_stats(torch.from_numpy(e).cuda(), torch.from_numpy(c).cuda(), K)
+    S = np.sort(c[:, :len(cols)].T.astype(np.float64), axis=1)[:, ::-1][:, :K]
+    scale = np.maximum(1.0, np.abs(S).max(1))
+    assert (np.abs(mu.cpu().numpy() - S.mean(1)) <= 4e-6 * scale).all(), (mu.cpu().numpy(), S.mean(1))
+    assert (np.abs(sg.cpu().numpy() - S.std(1)) <= 4e-6 * scale).all(), (sg.cpu().numpy(), S.std(1))
