@@ -225,7 +225,9 @@ class ModelHandling(object):
         ready = [torch.cuda.Event() for _ in range(2)]
         freed = [torch.cuda.Event() for _ in range(2)]
         if self._pool is None:
-            self._pool = ThreadPoolExecutor(6)
+            # one stager + pinned-fill workers; the ranks of one box share its host cores
+            local_world = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
+            self._pool = ThreadPoolExecutor(max(2, min(6, (os.cpu_count() or 8) // max(local_world, 1))))
 
         def fill(k, lo, hi, offs):
             hp = h_pcm[k].numpy()
