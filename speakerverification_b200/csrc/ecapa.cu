@@ -25,6 +25,7 @@ int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t)
 int pack_conv_weight_kpacked(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
+int mirror_halo_rows(bf16*, int, int, const void*, int, int, cudaStream_t);
 int colsum_finalize(const long long*, const long long*, int, const void*, int, int, float, float*, float*, int, cudaStream_t);
 int small_linear(const float*, int, const float*, const float*, int, const float*, const float*, int, int, int, int,
                  float*, int, float*, cudaStream_t);
@@ -496,6 +497,24 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     g.out = H("block0"); g.out_ld = P * C; g.out_plane_cols = C;
     g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_BF16;
     if (launch_gemm(ops, g, 256, stream)) return -1;
+  } else if (C % 256 == 0 && getenv("SVB_BLOCK0_TC") == nullptr) {
+    // same K order (tap, pass, chunk) and the same exact-erf GELU as gemm_tc, i.e. bit-identical outputs, but through
+    // gemm_pw's 16-warp TMA-store epilogue (gemm_tc's 8-warp row-store epilogue bounded this layer: tensor pipe 56 %);
+    // every row is stored in place and the reflect halos are then copied from the valid frames
+    const Layer& L = e->block0;
+    GemmOperands ops{};
+    ops.a = H("x0"); ops.lda = 2 * MEL_PLANE; ops.a_cols = 2 * MEL_PLANE;
+    ops.w = L.w; ops.w_rows = L.cout; ops.w_cols = L.k * L.planes * L.cin_pad;
+    GemmParams g{};
+    g.M = static_cast<int>(M); g.N = L.cout; g.kc_per_tap = L.cin_pad / 64; g.num_taps = L.k;
+    for (int j = 0; j < L.k; ++j) g.tap_off[j] = (j - (L.k - 1) / 2) * L.dil;
+    g.num_pass = 3; g.a_plane_cols = MEL_PLANE; g.w_planes = L.planes;
+    g.bias = L.bias; g.scale = L.scale; g.shift = L.shift; g.act = L.act; g.row_meta = b->d_meta;
+    g.store_mode = STORE_ALL; g.halo = b->halo;
+    g.out = H("block0"); g.out_ld = P * C; g.out_plane_cols = C;
+    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_BF16;
+    if (launch_gemm_pw(ops, g, stream)) return -1;
+    if (mirror_halo_rows(H("block0"), P * C, P * C, b->d_uttrows, B, b->halo, stream)) return -1;
   } else {
     View x0{H("x0"), 2 * MEL_PLANE, MEL_PLANE, 2 * MEL_PLANE};
     if (run_layer(e, b, e->block0, x0, nullptr, 0, H("block0"), P * C, C, STORE_MIRROR, nullptr, 0, 0, -1, nullptr,

@@ -33,6 +33,8 @@ static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // EW = 8: one warp's 32 rows x 64 bf16 columns
 static constexpr int OUT_BOX64_BYTES = 32 * 32 * 2; // EW = 16: one warp's 32 rows x 32 bf16 columns
 static constexpr int ACT_RAW_F32 = 3;               // epilogue variant: no bias/act/BN, fp32 accumulators stored as is
+static constexpr int ACT_GELU_ERF = 4;              // GELU through erff: the k > 1 layer (block 0) keeps gemm_tc's exact numerics
+__device__ __forceinline__ float gelu_erf_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
 template <int BN, int EW = 8>
 struct PwCfg {
@@ -57,6 +59,8 @@ struct PwParams {
   int rowbias_ld;
   const RowMeta* row_meta;
   int out_plane_cols;    // column offset of the lo plane in the output (HILO instances only)
+  int num_taps;          // k > 1: the K loop runs tap-major over row-shifted A loads (same order as gemm_tc.cu)
+  int tap_off[5];
   long long* colsum;     // STATS instances: fixed-point per-utterance column sums of the bf16 outputs (valid rows)
   long long* colsq;      // STATS == 2: and of their squares
   int stats_ld;
@@ -99,7 +103,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int sched_stride = MC ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   auto tile_m0 = [&](int t) { const int mt = t / num_n_tiles; return (MC ? 2 * mt + static_cast<int>(crank) : mt) * BLOCK_M; };
   const int kc = p.kc;
-  const int num_kb = p.num_pass * kc;
+  const int kb_per_tap = p.num_pass * kc;
+  const int num_kb = p.num_taps * kb_per_tap;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -137,17 +142,20 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int m0 = tile_m0(tile);
         const int n0 = (tile % num_n_tiles) * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
-          const int pass = kb / kc;
-          const int kcx = kb - pass * kc;
+          const int tap = kb / kb_per_tap;
+          const int rem = kb - tap * kb_per_tap;
+          const int pass = rem / kc;
+          const int kcx = rem - pass * kc;
           const int aplane = (pass == 2) ? 1 : 0;
           const int wplane = (pass == 1) ? 1 : 0;
           const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
-          const int w_col = (wplane * kc + kcx) * BLOCK_K;
+          const int w_col = ((tap * p.w_planes + wplane) * kc + kcx) * BLOCK_K;
+          const int a_row = m0 + p.tap_off[tap];
           const uint32_t fb = smem_u32(&full_bar[stage]);
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
           mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
-          tma_load_2d(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, fb, a_col, m0);
+          tma_load_2d(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, fb, a_col, a_row);
           if (MC)
             tma_load_2d_mc(sa + A_STAGE_BYTES + crank * (Cfg::B_STAGE_BYTES / 2), &tmW, fb, w_col,
                            n0 + static_cast<int>(crank) * (BN / 2), 0x3);
@@ -190,7 +198,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================================================== epilogue, 16 warps: quadrant = warp % 4, 64-column group =
     // (warp - 4) / 4, processed as two 32 x 32 units: TMEM -> regs -> bias/GELU/BN -> bf16 -> 64B-swizzled 2 KB box
     // (row = lane, 64 bytes, 16-byte chunk j at j ^ ((lane >> 1) & 3)) -> one TMA store per unit.
-    static_assert(EW != 16 || (BN == 256 && ACT == ACT_GELU && !RBT), "the 16-warp epilogue serves the GELU BN=256 instances");
+    static_assert(EW != 16 || (BN == 256 && (ACT == ACT_GELU || ACT == ACT_GELU_ERF) && !RBT),
+                  "the 16-warp epilogue serves the GELU BN=256 instances");
     static_assert(!STATS || (EW == 16 && !HILO), "fused column statistics: 16-warp epilogue, single bf16 plane");
     const int ew = warp - 4;
     const int quad = ew & 3;
@@ -232,8 +241,13 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const float4 b = __ldg(b4 + i), s = __ldg(s4 + i), h = __ldg(h4 + i);
-          float x0 = gelu_fast(__uint_as_float(r[4 * i]) + b.x), x1 = gelu_fast(__uint_as_float(r[4 * i + 1]) + b.y);
-          float x2 = gelu_fast(__uint_as_float(r[4 * i + 2]) + b.z), x3 = gelu_fast(__uint_as_float(r[4 * i + 3]) + b.w);
+          float x0 = __uint_as_float(r[4 * i]) + b.x, x1 = __uint_as_float(r[4 * i + 1]) + b.y;
+          float x2 = __uint_as_float(r[4 * i + 2]) + b.z, x3 = __uint_as_float(r[4 * i + 3]) + b.w;
+          if (ACT == ACT_GELU_ERF) {
+            x0 = gelu_erf_exact(x0); x1 = gelu_erf_exact(x1); x2 = gelu_erf_exact(x2); x3 = gelu_erf_exact(x3);
+          } else {
+            x0 = gelu_fast(x0); x1 = gelu_fast(x1); x2 = gelu_fast(x2); x3 = gelu_fast(x3);
+          }
           x0 = fmaf(x0, s.x, h.x); x1 = fmaf(x1, s.y, h.y);
           x2 = fmaf(x2, s.z, h.z); x3 = fmaf(x3, s.w, h.w);
           const uint32_t p0 = pack_bf16x2(x0, x1), p1 = pack_bf16x2(x2, x3);
@@ -492,7 +506,8 @@ static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtens
 // store_mode STORE_ALL, bf16 output).  Supported: GELU layers with N % 256-tileable outputs (tdnn1/tdnn2/mfa)
 // and the ReLU + row-bias + tanh attention layer (asp.tdnn).
 int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t stream) {
-  SVB_CHECK(g.num_taps == 1 && g.tap_off[0] == 0 && g.store_mode == STORE_ALL, "launch_gemm_pw handles pointwise layers only");
+  SVB_CHECK(g.store_mode == STORE_ALL && g.num_taps >= 1 && g.num_taps <= 5 && (g.num_taps > 1 || g.tap_off[0] == 0),
+            "launch_gemm_pw stores every row (k > 1 layers need a halo fix-up by the caller)");
   SVB_CHECK(g.out_kind == OUT_BF16 || g.out_kind == OUT_BF16_HILO, "launch_gemm_pw writes bf16");
   SVB_CHECK(g.N % 64 == 0 && g.out2 == nullptr, "launch_gemm_pw: N must be a multiple of 64 and there is no second output");
   SVB_CHECK(g.num_pass == 1 || g.num_pass == 3, "num_pass must be 1 or 3");
@@ -522,6 +537,8 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
   p.a2_kc = g.a2_kc; p.w_planes = g.w_planes; p.bias = g.bias; p.scale = g.scale; p.shift = g.shift;
   p.rowbias = g.rowbias; p.rowbias_ld = g.rowbias_ld; p.row_meta = g.row_meta; p.out_plane_cols = g.out_plane_cols;
+  p.num_taps = g.num_taps;
+  for (int j = 0; j < g.num_taps; ++j) p.tap_off[j] = g.tap_off[j];
   p.colsum = g.colsum; p.colsq = g.colsq; p.stats_ld = g.stats_ld;
   const int stats = g.colsum == nullptr ? 0 : (g.colsq == nullptr ? 1 : 2);
   SVB_CHECK(!stats || (bn == 256 && !hilo && !rbt && g.row_meta != nullptr && g.stats_ld % 2 == 0),
@@ -532,6 +549,14 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
                 : launch_pw_t<128, ACT_RELU, true, false>(ma, ma2, mw, mo, p, stream);
   }
   SVB_CHECK(g.act == ACT_GELU, "the plain pointwise instance is GELU + BN");
+  SVB_CHECK(g.num_taps == 1 || (bn == 256 && !stats && g.a2_kc == 0), "k > 1 runs on the BN=256 instances without statistics");
+  if (g.num_taps > 1) {   // block 0: exact-erf GELU, bit-identical to the gemm_tc path it replaces
+    if (mc)
+      return hilo ? launch_pw_t<256, ACT_GELU_ERF, false, true, 16, 0, true>(ma, ma2, mw, mo, p, stream)
+                  : launch_pw_t<256, ACT_GELU_ERF, false, false, 16, 0, true>(ma, ma2, mw, mo, p, stream);
+    return hilo ? launch_pw_t<256, ACT_GELU_ERF, false, true, 16>(ma, ma2, mw, mo, p, stream)
+                : launch_pw_t<256, ACT_GELU_ERF, false, false, 16>(ma, ma2, mw, mo, p, stream);
+  }
   if (bn == 256)
   {
     if (mc)
@@ -560,7 +585,7 @@ int launch_gemm_f32(const GemmOperands& ops, const GemmParams& g, cudaStream_t s
   if (make_map_f32(&mo, g.out, g.M, g.N, g.out_ld, 32)) return -1;
   PwParams p{};
   p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
-  p.a2_kc = 0; p.w_planes = g.w_planes;
+  p.a2_kc = 0; p.w_planes = g.w_planes; p.num_taps = 1; p.tap_off[0] = 0;
   return bn == 256 ? launch_pw_t<256, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream)
                    : launch_pw_t<128, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream);
 }

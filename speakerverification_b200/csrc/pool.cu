@@ -284,6 +284,30 @@ int colsum_finalize(const long long* sum, const long long* sq, int stats_ld, con
   return 0;
 }
 
+// Reflect-halo fix-up after a k > 1 layer that stored every row in place (gemm_pw): halo row -h of every utterance
+// becomes a copy of frame h, halo row T-1+h a copy of frame T-1-h (F.pad(..., 'reflect'), src/models/layers/cnn.py:157),
+// exactly what gemm_tc's STORE_MIRROR epilogue writes.  grid (utterances, 2 * halo), 16-byte copies of the whole row.
+__global__ void mirror_halo_rows_kernel(bf16* __restrict__ x, int ld, int row_bytes, const UttRows* __restrict__ utts,
+                                        int halo) {
+  const UttRows u = utts[blockIdx.x];
+  const int h = static_cast<int>(blockIdx.y % halo) + 1;
+  const bool tail = static_cast<int>(blockIdx.y) >= halo;
+  const long long dst = tail ? u.row0 + u.T - 1 + h : u.row0 - h;
+  const long long src = tail ? u.row0 + u.T - 1 - h : u.row0 + h;
+  const uint4* s4 = reinterpret_cast<const uint4*>(x + src * ld);
+  uint4* d4 = reinterpret_cast<uint4*>(x + dst * ld);
+  for (int i = threadIdx.x; i < row_bytes / 16; i += blockDim.x) d4[i] = s4[i];
+}
+
+int mirror_halo_rows(bf16* x, int ld, int cols, const void* utts, int B, int halo, cudaStream_t stream) {
+  SVB_CHECK((cols * 2) % 16 == 0 && (ld * 2) % 16 == 0, "mirror_halo_rows copies 16-byte chunks");
+  if (halo == 0) return 0;
+  mirror_halo_rows_kernel<<<dim3(B, 2 * halo), 256, 0, stream>>>(x, ld, cols * 2, static_cast<const UttRows*>(utts), halo);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int col_stats(const bf16* x, int ld, int planes, int plane_cols, const void* utts, int B, int C, int mode, float eps,
               float* mean_out, float* std_out, int out_ld, cudaStream_t stream) {
   SVB_CHECK(C % 8 == 0, "C must be a multiple of 8");
