@@ -36,12 +36,12 @@ static constexpr int ACT_RAW_F32 = 3;               // epilogue variant: no bias
 static constexpr int ACT_GELU_ERF = 4;              // GELU through erff: the k > 1 layer (block 0) keeps gemm_tc's exact numerics
 __device__ __forceinline__ float gelu_erf_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
-template <int BN, int EW = 8>
+template <int BN, int EW = 8, bool TWO = false>
 struct PwCfg {
   static constexpr int NUM_THREADS = 128 + EW * 32;
-  static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+  static constexpr int B_STAGE_BYTES = (TWO ? BN / 2 : BN) * BLOCK_K * 2;   // TWO: this CTA's half of the W tile
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int STAGES = (BN == 256 && !TWO) ? 4 : 6;
   static constexpr int OUT_BYTES = (EW == 16) ? 16 * OUT_BOX64_BYTES : 8 * OUT_BOX_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN;
@@ -76,13 +76,20 @@ __device__ __forceinline__ float tanh_exact(float x) {
 // They need the same W tile, so each loads HALF of it and TMA-multicasts the half into both CTAs: L2 -> SM traffic per
 // CTA and k-block drops from 48 KB to 32 KB.  A stage may be refilled only when BOTH CTAs have consumed it (the peer's
 // multicast lands in it too), so the `empty` barriers count two multicast tcgen05.commit arrivals.
-template <int BN, int ACT, bool RBT, bool HILO, int EW, int STATS, bool MC>
+// TWO (implies the cluster schedule of MC): the pair runs ONE tcgen05.mma.cta_group::2 of M = 256 per k-step.  Each CTA
+// stages its own 128 x 64 A tile and only its HALF of the W tile (128 of the 256 N rows), so a stage is 32 KB instead of
+// 48 KB (6 stages instead of 4, a third less L2 -> SM traffic, half the shared-memory operand reads per CTA).  The
+// leader (cluster rank 0) owns the `full` barriers (both producers arrive.expect_tx on them, both CTAs' TMA loads
+// complete_tx on them), issues every MMA and multicasts its commits to the `empty` / `tfull` barriers of both CTAs; the
+// peer's epilogue warps release the accumulator on the leader's `tempty` barrier.
+template <int BN, int ACT, bool RBT, bool HILO, int EW, int STATS, bool MC, bool TWO = false>
 __global__ void __launch_bounds__(128 + EW * 32, 1)
 gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmOut,
                const PwParams p) {
-  using Cfg = PwCfg<BN, EW>;
+  using Cfg = PwCfg<BN, EW, TWO>;
   constexpr int STAGES = Cfg::STAGES;
+  static_assert(!TWO || (MC && BN == 256), "the 2-SM MMA instances use the cluster schedule");
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES];
   __shared__ __align__(8) uint64_t empty_bar[STAGES];
@@ -114,18 +121,18 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(smem_u32(&full_bar[s]), 1);
-      mbar_init(smem_u32(&empty_bar[s]), MC ? 2 : 1);
+      mbar_init(smem_u32(&full_bar[s]), TWO ? 2 : 1);             // TWO: one arrive.expect_tx per producer of the pair
+      mbar_init(smem_u32(&empty_bar[s]), (MC && !TWO) ? 2 : 1);   // TWO: one multicast commit from the leader
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&tfull_bar[a]), 1);
-      mbar_init(smem_u32(&tempty_bar[a]), EW);
+      mbar_init(smem_u32(&tempty_bar[a]), TWO ? 2 * EW : EW);   // TWO: the epilogue warps of both CTAs
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(smem_u32(&tmem_slot), Cfg::TMEM_COLS);
-    tmem_relinquish();
+    if (TWO) { tmem_alloc_2sm(smem_u32(&tmem_slot), Cfg::TMEM_COLS); tmem_relinquish_2sm(); }
+    else { tmem_alloc(smem_u32(&tmem_slot), Cfg::TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
@@ -153,8 +160,16 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int a_row = m0 + p.tap_off[tap];
           const uint32_t fb = smem_u32(&full_bar[stage]);
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
-          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          if (TWO) {
+            const uint32_t lfb = fb & 0xFEFFFFFFu;          // the leader's barrier (bit 24 = rank inside the CTA pair)
+            mbar_arrive_expect_tx_cluster(lfb, Cfg::STAGE_BYTES);
+            tma_load_2d_2sm(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, lfb, a_col, a_row);
+            tma_load_2d_2sm(sa + A_STAGE_BYTES, &tmW, lfb, w_col, n0 + static_cast<int>(crank) * (BN / 2));
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            continue;
+          }
+          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           tma_load_2d(sa, (kcx < p.a2_kc) ? &tmA2 : &tmA, fb, a_col, a_row);
           if (MC)
             tma_load_2d_mc(sa + A_STAGE_BYTES + crank * (Cfg::B_STAGE_BYTES / 2), &tmW, fb, w_col,
@@ -165,10 +180,10 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================================================== MMA issuer
+  } else if (warp == 1 && (!TWO || crank == 0)) {
+    // ===================================================== MMA issuer (TWO: the leader CTA only, M = 256 over the pair)
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      constexpr uint32_t idesc = umma_idesc_bf16(TWO ? 2 * BLOCK_M : BLOCK_M, BN);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -185,13 +200,17 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint64_t adesc = umma_desc_sw128(sa);
           const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-          if (MC) umma_commit_mc(smem_u32(&empty_bar[stage]), 0x3);
+          for (int k = 0; k < BLOCK_K / 16; ++k) {
+            if (TWO) umma_bf16_2sm(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          }
+          if (TWO) umma_commit_2sm(smem_u32(&empty_bar[stage]), 0x3);
+          else if (MC) umma_commit_mc(smem_u32(&empty_bar[stage]), 0x3);
           else umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));
+        if (TWO) umma_commit_2sm(smem_u32(&tfull_bar[acc]), 0x3);
+        else umma_commit(smem_u32(&tfull_bar[acc]));
       }
     }
   } else if (warp >= 4 && EW == 16) {
@@ -334,7 +353,10 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      if (lane == 0) {
+        if (TWO) mbar_arrive_cluster(smem_u32(&tempty_bar[acc]) & 0xFEFFFFFFu);   // the leader issues the pair's MMAs
+        else mbar_arrive(smem_u32(&tempty_bar[acc]));
+      }
     }
     if (lane == 0) bulk_wait<0>();
   } else if (warp >= 4) {
@@ -463,17 +485,20 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   if (MC) cluster_sync_all();      // no CTA exits while its peer may still multicast data or arrivals into it
-  if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if (warp == 2) {
+    if (TWO) tmem_dealloc_2sm(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
 }
 
 // ------------------------------------------------------------------ host side
-template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0, bool MC = false>
+template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0, bool MC = false, bool TWO = false>
 static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& o,
                        const PwParams& p, cudaStream_t stream) {
-  using Cfg = PwCfg<BN, EW>;
+  using Cfg = PwCfg<BN, EW, TWO>;
   static bool attr_set = false;
   if (!attr_set) {
-    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::SMEM_BYTES));
     attr_set = true;
   }
@@ -491,11 +516,11 @@ static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtens
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    SVB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC>, a, a2, w, o, p));
+    SVB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC, TWO>, a, a2, w, o, p));
   } else {
     const int tiles = m_tiles * n_tiles;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC><<<grid, Cfg::NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
+    gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC, TWO><<<grid, Cfg::NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, a2, w, o, p);
   }
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
@@ -559,6 +584,11 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   }
   if (bn == 256)
   {
+    static const bool two_enabled = [] { const char* e = getenv("SVB_PW_2SM"); return e == nullptr || e[0] != '0'; }();
+    if (mc && two_enabled && !hilo)
+      return stats == 2 ? launch_pw_t<256, ACT_GELU, false, false, 16, 2, true, true>(ma, ma2, mw, mo, p, stream)
+           : stats == 1 ? launch_pw_t<256, ACT_GELU, false, false, 16, 1, true, true>(ma, ma2, mw, mo, p, stream)
+                        : launch_pw_t<256, ACT_GELU, false, false, 16, 0, true, true>(ma, ma2, mw, mo, p, stream);
     if (mc)
       return hilo         ? launch_pw_t<256, ACT_GELU, false, true, 16, 0, true>(ma, ma2, mw, mo, p, stream)
              : stats == 2 ? launch_pw_t<256, ACT_GELU, false, false, 16, 2, true>(ma, ma2, mw, mo, p, stream)
