@@ -42,7 +42,7 @@ struct PwCfg {
   static constexpr int B_STAGE_BYTES = (TWO ? BN / 2 : BN) * BLOCK_K * 2;   // TWO: this CTA's half of the W tile
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = (BN == 256 && !TWO) ? 4 : 6;
-  static constexpr int OUT_BYTES = (EW == 16) ? 16 * OUT_BOX64_BYTES : 8 * OUT_BOX_BYTES;
+  static constexpr int OUT_BYTES = 8 * OUT_BOX_BYTES;   // EW = 16: one 32 x 64 box per warp PAIR
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -214,18 +214,23 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp >= 4 && EW == 16) {
-    // ===================================================== epilogue, 16 warps: quadrant = warp % 4, 64-column group =
-    // (warp - 4) / 4, processed as two 32 x 32 units: TMEM -> regs -> bias/GELU/BN -> bf16 -> 64B-swizzled 2 KB box
-    // (row = lane, 64 bytes, 16-byte chunk j at j ^ ((lane >> 1) & 3)) -> one TMA store per unit.
+    // ===================================================== epilogue, 16 warps: quadrant = warp % 4; the two warps of a
+    // PAIR (same quadrant, column groups 2P and 2P+1) cover 128 columns and fill, per unit, the left / right half of ONE
+    // 32 x 64 box with 128-byte rows (128B swizzle), stored by one TMA instruction: 128-byte store requests instead of
+    // the 64-byte rows of per-warp 32 x 32 boxes (the L2 path of these kernels is request bound: every extra request
+    // stream tried, e.g. the L2 prefetch, cost 8-10 %).  TMEM -> regs -> bias/GELU/BN -> bf16 -> box -> TMA store.
     static_assert(EW != 16 || (BN == 256 && (ACT == ACT_GELU || ACT == ACT_GELU_ERF) && !RBT),
                   "the 16-warp epilogue serves the GELU BN=256 instances");
     static_assert(!STATS || (EW == 16 && !HILO), "fused column statistics: 16-warp epilogue, single bf16 plane");
     const int ew = warp - 4;
     const int quad = ew & 3;
     const int cgroup = ew >> 2;
-    const uint32_t my_box = out_base + ew * OUT_BOX64_BYTES;
-    const uint32_t my_row = my_box + lane * 64;
-    const int sw = (lane >> 1) & 3;
+    const int pr = cgroup >> 1, pos = cgroup & 1;          // pair of column groups, position inside the pair
+    const int pair = quad + 4 * pr;                        // 0..7: named barrier 1 + pair, box `pair`
+    const bool issuer = pos == 0;
+    const uint32_t my_box = out_base + pair * OUT_BOX_BYTES;
+    const uint32_t my_row = my_box + lane * 128;
+    const int sw = lane & 7;
     int it = 0;
     for (int tile = sched_first; tile < num_tiles; tile += sched_stride, ++it) {
       const int m0 = tile_m0(tile);
@@ -246,9 +251,10 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
 #pragma unroll 1
       for (int u = 0; u < 2; ++u) {
-        const int col0 = cgroup * 64 + u * 32;
+        const int col0 = pr * 128 + u * 64 + pos * 32;
         const int n = n0 + col0;
-        if (n >= p.N) break;
+        const int n_box = n0 + pr * 128 + u * 64;          // first column of the pair's box (N % 64 == 0)
+        if (n_box >= p.N) break;                           // uniform over the pair
         uint32_t r[32];
         tmem_ld32(tmem_base + acc * BN + col0 + (static_cast<uint32_t>(quad * 32) << 16), r);
         tmem_ld_wait();
@@ -277,17 +283,17 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             lo[2 * i + 1] = pack_bf16x2(x2 - bf16_lo_f(p1), x3 - bf16_hi_f(p1));
           }
         }
-        if (lane == 0) bulk_wait_read<0>();
-        __syncwarp();
+        if (issuer && lane == 0) bulk_wait_read<0>();      // the previous store has finished reading the box
+        named_bar_sync(1 + pair, 64);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(hi[4 * j]),
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((pos * 4 + j) ^ sw) << 4)), "r"(hi[4 * j]),
                        "r"(hi[4 * j + 1]), "r"(hi[4 * j + 2]), "r"(hi[4 * j + 3])
                        : "memory");
         fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_2d(&tmOut, my_box, n, m0 + quad * 32);
+        named_bar_sync(1 + pair, 64);
+        if (issuer && lane == 0) {
+          tma_store_2d(&tmOut, my_box, n_box, m0 + quad * 32);
           bulk_commit();
         }
         if (STATS) {
@@ -308,7 +314,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if ((m >> r) & 1u) {
                 uint32_t w;
                 asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w)
-                             : "r"(my_box + r * 64 + ((((cp >> 2) ^ (i & 3))) << 4) + col_off));
+                             : "r"(my_box + r * 128 + (((pos * 4 + (cp >> 2)) ^ (r & 7)) << 4) + col_off));
                 const float a = bf16_lo_f(w), b = bf16_hi_f(w);
                 s0 += a; s1 += b;
                 if (STATS == 2) { q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1); }
@@ -336,17 +342,17 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         if (HILO) {
-          if (lane == 0) bulk_wait_read<0>();
-          __syncwarp();
+          if (issuer && lane == 0) bulk_wait_read<0>();
+          named_bar_sync(1 + pair, 64);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(lo[4 * j]),
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((pos * 4 + j) ^ sw) << 4)), "r"(lo[4 * j]),
                          "r"(lo[4 * j + 1]), "r"(lo[4 * j + 2]), "r"(lo[4 * j + 3])
                          : "memory");
           fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmOut, my_box, p.out_plane_cols + n, m0 + quad * 32);
+          named_bar_sync(1 + pair, 64);
+          if (issuer && lane == 0) {
+            tma_store_2d(&tmOut, my_box, p.out_plane_cols + n_box, m0 + quad * 32);
             bulk_commit();
           }
         }
@@ -553,11 +559,7 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   const bool mc = mc_enabled && bn == 256 && !rbt;
   if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, mc ? bn / 2 : bn)) return -1;
   const long long out_cols = hilo ? static_cast<long long>(g.out_plane_cols) + g.N : g.N;
-  if (bn == 256) {   // 16-warp epilogue: 32 x 32 boxes, 64B swizzle
-    if (make_map_sw64(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;
-  } else if (make_map(&mo, g.out, g.M, out_cols, g.out_ld, 32)) {
-    return -1;
-  }
+  if (make_map(&mo, g.out, g.M, out_cols, g.out_ld, 32)) return -1;   // 32 x 64 boxes, 128B swizzle (8 and 16 warps)
   PwParams p{};
   p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
   p.a2_kc = g.a2_kc; p.w_planes = g.w_planes; p.bias = g.bias; p.scale = g.scale; p.shift = g.shift;
