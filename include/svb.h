@@ -225,6 +225,16 @@ int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int 
 int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b,
                       int64_t n_trials, const float* mu, const float* sigma, float* out, void* stream);
 
+/* ------------------------------------------------------------------ nearest-enrolment search
+ * The --predict statistic of src/inference.py:284-294 for Q query utterances at once:
+ *   dist[q, s] = mean_i || query[q, i, :] - bank[i, :, s] + eps ||_2   (F.pairwise_distance over the feature axis)
+ * query: [Q, n_per_utt, D] fp32 crop embeddings (embed_utterance, src/model.py:675-704); bank: [n_per_utt, D, S] fp32,
+ * the layout prepare('embed') saves as embeds.pt (src/model.py:634-641).  dist: [Q, S] out.  topk (0..8) > 0
+ * additionally returns np.argsort(dist[q])[:topk] (ties to the lower index) in top_idx [Q, topk] with the distances
+ * in top_dist [Q, topk]; the reference's score is 1 - dist^2 / 2 (host side). */
+int svb_enrol_nearest(const float* query, const float* bank, int Q, int n_per_utt, int D, int S, float eps,
+                      int topk, float* dist, float* top_dist, int32_t* top_idx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,6 +103,7 @@ _EXTRA_SIGS = {
     "svb_ecapa_forward_mel": ([_vp, _vp, _vp, _vp, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
     "svb_cosine_trials": ([_vp, _i32, _i32, _vp, _vp, _i64, _vp, _vp], _i32),
     "svb_mean_embeddings": ([_vp, _i32, _i32, _i32, _i32, _vp, _vp], _i32),
+    "svb_enrol_nearest": ([_vp, _vp, _i32, _i32, _i32, _i32, _c.c_float, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
     "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
     "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),

@@ -39,6 +39,7 @@ int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, int, v
                   cudaStream_t);
 int cosine_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float*, cudaStream_t);
 int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
+int enrol_nearest(const float*, const float*, int, int, int, int, float, int, float*, float*, int32_t*, cudaStream_t);
 size_t asnorm_workspace_bytes(int, int, int, int*);
 int asnorm_stats(const float*, int, const float*, int, int, int, float*, float*, void*, size_t, cudaStream_t);
 int asnorm_trials(const float*, int, const int32_t*, const int32_t*, long long, const float*, const float*, float*,
@@ -274,6 +275,14 @@ int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int norma
   if (check_device()) return -1;
   SVB_CHECK(emb && out && U >= 1 && n_per_utt >= 1, "bad argument");
   return mean_rows(emb, U, n_per_utt, D, normalize, out, static_cast<cudaStream_t>(stream));
+}
+int svb_enrol_nearest(const float* query, const float* bank, int Q, int n_per_utt, int D, int S, float eps, int topk,
+                      float* dist, float* top_dist, int32_t* top_idx, void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(query && bank && dist && Q >= 0 && n_per_utt >= 1 && D >= 1 && S >= 1, "bad argument");
+  SVB_CHECK(topk >= 0 && topk <= 8 && topk <= S && (topk == 0 || (top_dist && top_idx)), "topk must be 0..min(8, S)");
+  return enrol_nearest(query, bank, Q, n_per_utt, D, S, eps, topk, dist, top_dist, top_idx,
+                       static_cast<cudaStream_t>(stream));
 }
 size_t svb_asnorm_workspace_bytes(int U, int N, int D) { return asnorm_workspace_bytes(U, N, D, nullptr); }
 int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu, float* sigma,

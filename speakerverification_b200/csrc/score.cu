@@ -650,6 +650,93 @@ __global__ void asnorm_trials_kernel(const float* __restrict__ emean, int D, con
   if (lane == 0) out[tr] = 0.5f * ((s - mu[a]) / sigma[a] + (s - mu[b]) / sigma[b]);
 }
 
+// ---------------------------------------------------------------- nearest-enrolment search (--predict)
+// The statistic of src/inference.py:284-294: dist[s] = mean_i || q_i - e_(i,s) + eps ||_2 over the n index-paired crops
+// (torch's pairwise_distance adds eps to the difference), enrolment bank in the reference's saved layout
+// [n, D, S] (src/model.py:634-641: per-speaker mean crop embeddings concatenated on the LAST axis).  Thread = speaker
+// (coalesced bank reads), ENROL_QT queries per block share every bank element from a register; the crop's query
+// vectors sit in shared memory.  fp32 throughout, direct differences (no ||a||^2 + ||b||^2 - 2ab cancellation).
+static constexpr int ENROL_QT = 8;
+static constexpr int ENROL_NT = 128;
+__global__ void __launch_bounds__(ENROL_NT) enrol_dist_kernel(const float* __restrict__ query, const float* __restrict__ bank,
+                                                              int Q, int n, int D, int S, float eps,
+                                                              float* __restrict__ dist) {
+  extern __shared__ float qs[];   // [ENROL_QT][D]
+  const int s = blockIdx.x * ENROL_NT + threadIdx.x;
+  const int q0 = blockIdx.y * ENROL_QT;
+  float tot[ENROL_QT];
+#pragma unroll
+  for (int q = 0; q < ENROL_QT; ++q) tot[q] = 0.f;
+  for (int i = 0; i < n; ++i) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < ENROL_QT * D; k += ENROL_NT) {
+      const int q = q0 + k / D;
+      qs[k] = q < Q ? query[(static_cast<long long>(q) * n + i) * D + (k % D)] + eps : 0.f;
+    }
+    __syncthreads();
+    if (s < S) {
+      float acc[ENROL_QT];
+#pragma unroll
+      for (int q = 0; q < ENROL_QT; ++q) acc[q] = 0.f;
+      const float* b = bank + static_cast<long long>(i) * D * S + s;
+      for (int d = 0; d < D; ++d) {
+        const float e = __ldg(b + static_cast<long long>(d) * S);
+#pragma unroll
+        for (int q = 0; q < ENROL_QT; ++q) {
+          const float df = qs[q * D + d] - e;
+          acc[q] = fmaf(df, df, acc[q]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < ENROL_QT; ++q) tot[q] += sqrtf(acc[q]);
+    }
+  }
+  if (s < S) {
+#pragma unroll
+    for (int q = 0; q < ENROL_QT; ++q)
+      if (q0 + q < Q) dist[static_cast<long long>(q0 + q) * S + s] = tot[q] / static_cast<float>(n);
+  }
+}
+
+// The k nearest speakers of one query (k <= 8; np.argsort(dist)[:k], ties to the lower index): k rounds of a block
+// arg-min over the query's distance row, each round excluding everything at or before the previous winner in
+// (distance, index) order.
+__global__ void __launch_bounds__(256) enrol_topk_kernel(const float* __restrict__ dist, int S, int k,
+                                                         float* __restrict__ out_d, int32_t* __restrict__ out_i) {
+  __shared__ float rv[8];
+  __shared__ int ri[8];
+  const float* row = dist + static_cast<long long>(blockIdx.x) * S;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float pv = -INFINITY;
+  int pi = -1;
+  for (int r = 0; r < k; ++r) {
+    float bv = INFINITY;
+    int bi = 0x7fffffff;
+    for (int s = threadIdx.x; s < S; s += 256) {
+      const float v = row[s];
+      const bool after = v > pv || (v == pv && s > pi);
+      if (after && (v < bv || (v == bv && s < bi))) { bv = v; bi = s; }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { rv[warp] = bv; ri[warp] = bi; }
+    __syncthreads();
+    bv = rv[0]; bi = ri[0];
+    for (int w = 1; w < 8; ++w)
+      if (rv[w] < bv || (rv[w] == bv && ri[w] < bi)) { bv = rv[w]; bi = ri[w]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      out_d[static_cast<long long>(blockIdx.x) * k + r] = bv;
+      out_i[static_cast<long long>(blockIdx.x) * k + r] = bi == 0x7fffffff ? -1 : bi;
+    }
+    pv = bv; pi = bi;
+  }
+}
+
 __global__ void fill_kernel(float* p, int n, float v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -669,6 +756,23 @@ int mean_rows(const float* emb, int U, int n, int D, int normalize, float* out, 
   mean_rows_kernel<<<(U + 7) / 8, 256, 0, stream>>>(emb, U, n, D, normalize, out);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int enrol_nearest(const float* query, const float* bank, int Q, int n, int D, int S, float eps, int k, float* dist,
+                  float* out_d, int32_t* out_i, cudaStream_t stream) {
+  if (Q == 0) return 0;
+  const size_t smem = static_cast<size_t>(ENROL_QT) * D * sizeof(float);
+  if (smem > 48 * 1024) { set_error("enrol_nearest: embedding size above 1536"); return -1; }
+  dim3 grid((S + ENROL_NT - 1) / ENROL_NT, (Q + ENROL_QT - 1) / ENROL_QT);
+  enrol_dist_kernel<<<grid, ENROL_NT, smem, stream>>>(query, bank, Q, n, D, S, eps, dist);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  if (k > 0) {
+    enrol_topk_kernel<<<Q, 256, 0, stream>>>(dist, S, k, out_d, out_i);
+    count_launch();
+    SVB_CUDA_OK(cudaGetLastError());
+  }
   return 0;
 }
 

@@ -489,6 +489,31 @@ class ModelHandling(object):
             if save_path:
                 np.save(save_path, cohort)
             return True
+        if prepare_type == "embed" and isinstance(source, (str, Path)):
+            # src/model.py:615-645: one directory per known speaker; bank [n, D, S] = per-speaker mean over its files
+            # of the crop embeddings, speakers on the LAST axis (embeds.pt), classes = {index: directory name}.
+            # All files go through the batched crop/stack pipeline in one pass (directories in sorted order).
+            dirs = sorted(x for x in Path(source).iterdir() if x.is_dir())
+            classes = {i: d.stem for i, d in enumerate(dirs)}
+            flat, owner = [], []
+            for i, d in enumerate(dirs):
+                for f in sorted(d.glob("*.wav")):
+                    flat.append(str(f))
+                    owner.append(i)
+            if not flat or len(set(owner)) != len(dirs):
+                raise ValueError("every speaker directory under %s needs at least one .wav file" % source)
+            emb = self._embed_files(flat, num_eval)                                    # [files, n, D]
+            if self.__model__.module.test_normalize:
+                emb = F.normalize(emb, p=2, dim=2)
+            owner_t = torch.tensor(owner, device=self.device)
+            S = len(dirs)
+            sums = torch.zeros((S,) + tuple(emb.shape[1:]), device=self.device).index_add_(0, owner_t, emb)
+            cnt = torch.bincount(owner_t, minlength=S).to(sums.dtype)
+            embeds = (sums / cnt[:, None, None]).permute(1, 2, 0).contiguous().cpu()   # [n, D, S]
+            if save_path:
+                torch.save(embeds, Path(save_path, "embeds.pt"))
+                np.save(str(Path(save_path, "classes.npy")), classes)
+            return True
         if prepare_type == "embed" and isinstance(source, list):
             embs = [self.embed_utterance(a, num_eval=num_eval, normalize=self.__model__.module.test_normalize)
                     for a in source]
@@ -497,6 +522,28 @@ class ModelHandling(object):
                 torch.save(mean_embed, Path(save_path, "embeds.pt"))
             return mean_embed
         raise NotImplementedError("prepare_type=%r with source type %s" % (prepare_type, type(source).__name__))
+
+    def predict(self, sources, embeds, classes=None, num_eval=10, topk=3):
+        """The ``--predict`` loop of src/inference.py:254-327 as one batched call: every file of ``sources`` is
+        embedded (``embed_utterance`` semantics: ``num_eval`` crops, normalised when the loss asks for it), compared
+        with the enrolment bank ``embeds`` [n, D, S] (tensor or path of embeds.pt) by the mean-over-crops L2 distance,
+        and the ``topk`` nearest speakers are returned: dict(dist [Q, S], top_dist [Q, k], top_idx [Q, k],
+        score = 1 - top_dist**2 / 2 (:293), names = classes[top_idx] when ``classes`` (dict or classes.npy path) is
+        given).  The reference's console report (same_smallest_score / diff_biggest_score) is host logic on these."""
+        from .utils import enrol_nearest
+        if isinstance(embeds, (str, Path)):
+            embeds = torch.load(embeds)
+        if isinstance(classes, (str, Path)):
+            classes = np.load(str(classes), allow_pickle=True).item()
+        emb = self._embed_files([str(f) for f in sources], num_eval)                   # [Q, n, D] on the device
+        if self.__model__.module.test_normalize:
+            emb = F.normalize(emb, p=2, dim=2)
+        dist, td, ti = enrol_nearest(emb.contiguous(), embeds.to(self.device), topk=topk)
+        out = dict(dist=dist.cpu().numpy(), top_dist=td.cpu().numpy(), top_idx=ti.cpu().numpy())
+        out["score"] = 1.0 - out["top_dist"] ** 2 / 2
+        if classes is not None:
+            out["names"] = [[classes[int(i)] for i in row] for row in out["top_idx"]]
+        return out
 
     def embed_utterance(self, source, num_eval=20, normalize=False):
         """src/model.py:675-704: path or ndarray -> CPU tensor [num_eval, D]."""

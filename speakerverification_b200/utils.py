@@ -56,6 +56,24 @@ def asnorm_trials(emean, idx_a, idx_b, mu, sigma):
     return out
 
 
+def enrol_nearest(query, bank, topk=3, eps=1e-6):
+    """The --predict statistic of src/inference.py:284-294 for all query utterances at once: query [Q, n, D] crop
+    embeddings, bank [n, D, S] (embeds.pt layout of src/model.py:634-641) -> (dist [Q, S] = mean over crops of the
+    L2 distance with torch's pairwise_distance eps, top_dist [Q, k], top_idx [Q, k] = np.argsort(dist)[:k])."""
+    query, bank = _dev(query), _dev(bank, query.device if torch.is_tensor(query) and query.is_cuda else None)
+    Q, n, D = query.shape
+    if tuple(bank.shape[:2]) != (n, D):
+        raise ValueError("bank %s does not match query crops %s" % (tuple(bank.shape), tuple(query.shape)))
+    S = bank.shape[2]
+    k = min(int(topk), S)
+    dist = torch.empty((Q, S), dtype=torch.float32, device=query.device)
+    td = torch.empty((Q, k), dtype=torch.float32, device=query.device)
+    ti = torch.empty((Q, k), dtype=torch.int32, device=query.device)
+    nv.check(nv.lib().svb_enrol_nearest(nv.ptr(query), nv.ptr(bank), Q, n, D, S, float(eps), k, nv.ptr(dist),
+                                        nv.ptr(td), nv.ptr(ti), nv.stream_ptr()))
+    return dist, td, ti
+
+
 def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200, normalize=True):
     """All trials at once.  emb [U, n, D] (raw crop embeddings); returns a CUDA fp32 vector.
     'cosine' = utils.cosine_similarity per trial; 'norm' = utils.ZT_norm_similarity(top)."""
