@@ -48,9 +48,14 @@ struct AspParams {
   float* pooled; int pooled_ld;
   float eps;
   int y_plane_cols;      // column offset of the lo plane of Y
+  const float* bound;    // FIXMAX: per-channel upper bound of logit * log2(e) (att = tanh(.) lies in [-1, 1])
 };
 
-template <bool SPLIT>
+// FIXMAX: the softmax is shift invariant and the logits are bounded by the L1 norm of their weight row (|att| <= 1),
+// so that bound replaces the running maximum: no chunk-maximum pass over the logits (one TMEM read and one FMNMX per
+// element less), no rescaling of the partial sums, and both warpgroups accumulate on the same scale.  The host picks
+// this instance only when every bound is small enough for exp2(logit - bound) to stay far from fp32 underflow.
+template <bool SPLIT, bool FIXMAX>
 __global__ void __launch_bounds__(ASP_THREADS, 1)
 asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constant__ CUtensorMap tmY,
                  const __grid_constant__ CUtensorMap tmW, const AspParams p) {
@@ -220,7 +225,8 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
       const UttRows u = p.utts[b];
       const int c = cb * 128 + ch_local;
       const float gm = __ldg(p.gmean + static_cast<long long>(b) * p.gmean_ld + c);
-      float m = -INFINITY, l = 0.f, s1 = 0.f, s2 = 0.f;   // m is kept in log2 units (logit * log2 e)
+      float m = FIXMAX ? __ldg(p.bound + c) : -INFINITY;   // m is kept in log2 units (logit * log2 e)
+      float l = 0.f, s1 = 0.f, s2 = 0.f;
       const int nch = (u.T + CH_N - 1) / CH_N;
       for (int ch = 0; ch < nch; ++ch, ++g) {
         if ((g & 1u) != static_cast<uint32_t>(wg)) continue;
@@ -230,25 +236,27 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
         const uint32_t t_log = tmem_base + wg * 2 * CH_N + lane_sel;
         const uint32_t t_x = t_log + CH_N;
         const int ngrp = (nvalid + 31) >> 5;
-        // pass 1: chunk maximum
-        float cmax = -INFINITY;
-        for (int grp = 0; grp < ngrp; ++grp) {
-          uint32_t r[32];
-          tmem_ld32(t_log + grp * 32, r);
-          tmem_ld_wait();
-          const int lim = nvalid - grp * 32;
-          if (lim >= 32) {
+        if (!FIXMAX) {
+          // pass 1: chunk maximum
+          float cmax = -INFINITY;
+          for (int grp = 0; grp < ngrp; ++grp) {
+            uint32_t r[32];
+            tmem_ld32(t_log + grp * 32, r);
+            tmem_ld_wait();
+            const int lim = nvalid - grp * 32;
+            if (lim >= 32) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, __uint_as_float(r[i]));
-          } else {
+              for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, __uint_as_float(r[i]));
+            } else {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, i < lim ? __uint_as_float(r[i]) : -INFINITY);
+              for (int i = 0; i < 32; ++i) cmax = fmaxf(cmax, i < lim ? __uint_as_float(r[i]) : -INFINITY);
+            }
           }
+          const float mz = fmaxf(m, cmax * LOG2E);
+          const float corr = fast_ex2(m - mz);
+          l *= corr; s1 *= corr; s2 *= corr;
+          m = mz;
         }
-        const float mz = fmaxf(m, cmax * LOG2E);
-        const float corr = fast_ex2(m - mz);
-        l *= corr; s1 *= corr; s2 *= corr;
-        m = mz;
         // pass 2: e = exp(logit - max); accumulate sum e, sum e (x - g), sum e (x - g)^2
         for (int grp = 0; grp < ngrp; ++grp) {
           uint32_t r[32], xr[32];
@@ -306,27 +314,28 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
 }
 
 // ------------------------------------------------------------------ host side
-template <bool SPLIT>
+template <bool SPLIT, bool FIXMAX>
 static int launch_asp(const CUtensorMap& ma, const CUtensorMap& my, const CUtensorMap& mw, const AspParams& p,
                       cudaStream_t stream) {
   using Cfg = AspCfg<SPLIT>;
   static bool attr_set = false;
   if (!attr_set) {
-    SVB_CUDA_OK(cudaFuncSetAttribute(asp_fused_kernel<SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    SVB_CUDA_OK(cudaFuncSetAttribute(asp_fused_kernel<SPLIT, FIXMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
   const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
-  asp_fused_kernel<SPLIT><<<grid, ASP_THREADS, Cfg::SMEM_BYTES, stream>>>(ma, my, mw, p);
+  asp_fused_kernel<SPLIT, FIXMAX><<<grid, ASP_THREADS, Cfg::SMEM_BYTES, stream>>>(ma, my, mw, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 // att [rows, planes*128] bf16 (tanh output of asp.tdnn), y [rows, y_ld] bf16 MFA output (hi | lo at +y_plane_cols),
+// bound [C3] or nullptr (see FIXMAX);
 // wc packed asp.conv weight [C3, planes*128]; gmean [B, gmean_ld] global time means; pooled [B, pooled_ld] = [mean | std].
 int asp_fused(const bf16* att, const bf16* y, int y_ld, int y_plane_cols, const bf16* wc, int planes, long long rows,
               const void* utts, int B, int C3, const float* gmean, int gmean_ld, float eps, float* pooled, int pooled_ld,
-              cudaStream_t stream) {
+              const float* bound, cudaStream_t stream) {
   SVB_CHECK(C3 % 128 == 0, "ASP channels must be a multiple of 128 (got %d)", C3);
   SVB_CHECK(planes == 1 || planes == 2, "planes must be 1 or 2");
   const int chn = planes == 2 ? 32 : 128;
@@ -339,7 +348,10 @@ int asp_fused(const bf16* att, const bf16* y, int y_ld, int y_plane_cols, const 
   p.utts = static_cast<const UttRows*>(utts);
   p.gmean = gmean; p.gmean_ld = gmean_ld; p.pooled = pooled; p.pooled_ld = pooled_ld; p.eps = eps;
   p.y_plane_cols = y_plane_cols;
-  return planes == 2 ? launch_asp<true>(ma, my, mw, p, stream) : launch_asp<false>(ma, my, mw, p, stream);
+  p.bound = bound;
+  if (bound != nullptr)
+    return planes == 2 ? launch_asp<true, true>(ma, my, mw, p, stream) : launch_asp<false, true>(ma, my, mw, p, stream);
+  return planes == 2 ? launch_asp<true, false>(ma, my, mw, p, stream) : launch_asp<false, false>(ma, my, mw, p, stream);
 }
 
 }  // namespace svb

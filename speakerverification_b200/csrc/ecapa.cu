@@ -33,7 +33,7 @@ size_t small_linear_ws_floats(int, int, int);
 int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, const RowMeta*, long long, int, int, bf16*,
              int, int, cudaStream_t);
 int asp_fused(const bf16*, const bf16*, int, int, const bf16*, int, long long, const void*, int, int, const float*, int, float,
-              float*, int, cudaStream_t);
+              float*, int, const float*, cudaStream_t);
 int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
 size_t res2net_scratch_bytes(int, int);
 int res2net_seg_frames();
@@ -211,6 +211,7 @@ struct Ecapa {
   bf16* block0_wk = nullptr;
   int block0_kpad = 0;
   float *se_w1[3] = {}, *se_b1[3] = {}, *se_w2[3] = {}, *se_b2[3] = {};
+  float *asp_bound = nullptr;  // per-channel bound of the asp.conv logits in log2 units, or nullptr (asp_fused.cu, FIXMAX)
   float *asp_w = nullptr;  // asp.tdnn conv weight fp32 [att, 9C] (the [mean;std] columns feed the per-utterance bias)
   float *aspbn_scale = nullptr, *aspbn_shift = nullptr, *fc_w = nullptr, *fc_b = nullptr;
   std::vector<void*> owned;
@@ -343,6 +344,25 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
       e->aspbn_scale = dalloc<float>(e, 2 * e->C3); e->aspbn_shift = dalloc<float>(e, 2 * e->C3);
       rc |= fold_bn(g, b, m, v, 2 * e->C3, 1e-5f, e->aspbn_scale, e->aspbn_shift, 0);
       e->fc_w = dcopy(e, fw, static_cast<size_t>(n_out) * 2 * e->C3); e->fc_b = dcopy(e, fb, n_out);
+    }
+    // |att| <= 1 (tanh), so |logit_c - bias_c| <= sum_k |W[c, k]|: the softmax of asp_fused uses that bound in place of
+    // a running maximum when it is small enough that exp2(logit - bound) >= 2^-2*bound stays far above fp32 underflow
+    const float* cw = find(tm, "asp.conv.conv.weight");
+    if (!rc && cw != nullptr && getenv("SVB_ASP_TWOPASS") == nullptr) {
+      std::vector<float> hw(static_cast<size_t>(e->C3) * att), bound(e->C3);
+      if (cudaMemcpy(hw.data(), cw, hw.size() * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess) {
+        float worst = 0.f;
+        for (int c = 0; c < e->C3; ++c) {
+          double a = 0.0;
+          for (int k = 0; k < att; ++k) a += fabs(static_cast<double>(hw[static_cast<size_t>(c) * att + k]));
+          bound[c] = static_cast<float>(a * 1.4426950408889634 * 1.01 + 0.05);   // 1 %: bf16 weight / activation rounding
+          worst = fmaxf(worst, bound[c]);
+        }
+        if (worst <= 40.f) {
+          e->asp_bound = dalloc<float>(e, e->C3);
+          if (e->asp_bound) cudaMemcpy(e->asp_bound, bound.data(), e->C3 * sizeof(float), cudaMemcpyHostToDevice);
+        }
+      }
     }
   }
   if (!rc && cudaDeviceSynchronize() != cudaSuccess) { set_error("weight packing failed: %s", cudaGetErrorString(cudaGetLastError())); rc = -2; }
@@ -587,7 +607,7 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
                 nullptr, nullptr, 0, 0, passes, stream)) return -1;
   // asp.conv + softmax over time + weighted mean / std in one kernel (logits never reach HBM)
   if (asp_fused(H("att"), Y, P * C3, C3, e->asp_conv.w, P, M, b->d_uttrows, B, C3, st, 2 * C3, 1e-12f, F("pooled"), 2 * C3,
-                stream)) return -1;
+                e->asp_bound, stream)) return -1;
   // asp_bn + fc
   float* dst = l2norm ? F("emb_raw") : emb;
   const int dst_ld = l2norm ? e->n_out : emb_ld;

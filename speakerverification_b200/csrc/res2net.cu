@@ -480,13 +480,21 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
       for (int mt = 0; mt < RC_MT; ++mt) m_out[mt] = __ballot_sync(0xffffffffu, out_r[mt]);
       const int crow = lane >> 2, cchk = lane & 3;
       const long long gq = g0 + quad * 32;     // global row of this warp's first row in M tile 0
-      auto load_x = [&](int mt, int g, int j, uint4 (&xc)[4]) {
-        const int colx = (j + 1) * CS + half * NCOLH + g * 32 + cchk * 8;
+      // per-item 64-bit bases; everything inside the step loops is 32-bit offset arithmetic from them
+      const bf16* xbase = p.U + (gq + crow) * static_cast<long long>(p.u_ld) + half * NCOLH + cchk * 8;
+      bf16* rbase0 = p.R + (gq + crow) * static_cast<long long>(p.r_ld) + half * NCOLH + cchk * 8;
+      uint32_t xmask = 0;                      // bit mt * 4 + i: row gq + mt * 128 + 8 i + crow lies inside the buffer
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const long long row = gq + mt * 128 + 8 * i + crow;
-          xc[i] = (row >= 0 && row < p.M) ? __ldg(reinterpret_cast<const uint4*>(p.U + row * p.u_ld + colx)) : make_uint4(0, 0, 0, 0);
-        }
+      for (int q = 0; q < 4 * RC_MT; ++q) {
+        const long long row = gq + (q >> 2) * 128 + 8 * (q & 3) + crow;
+        if (row >= 0 && row < p.M) xmask |= 1u << q;
+      }
+      auto load_x = [&](int mt, int g, int j, uint4 (&xc)[4]) {
+        const int off = mt * 128 * p.u_ld + (j + 1) * CS + g * 32;
+        const uint32_t vm = xmask >> (mt * 4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          xc[i] = ((vm >> i) & 1u) ? __ldg(reinterpret_cast<const uint4*>(xbase + (off + 8 * i * p.u_ld))) : make_uint4(0, 0, 0, 0);
       };
       for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
         // this step's bias / BN scale / BN shift -> shared memory (double buffered by step parity)
@@ -554,7 +562,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + lane * RS_PITCH + i * 16), "r"(pk[4 * i]),
                            "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
             __syncwarp();
-            bf16* rbase = p.R + (gq + mt * 128) * p.r_ld + j * CS + col + cchk * 8;
+            bf16* rbase = rbase0 + (mt * 128 * p.r_ld + j * CS + g * 32);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const int rr = 8 * i + crow;
@@ -562,7 +570,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
                 uint4 o;
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
                              : "r"(stg + rr * RS_PITCH + cchk * 16) : "memory");
-                *reinterpret_cast<uint4*>(rbase + static_cast<long long>(rr) * p.r_ld) = o;
+                *reinterpret_cast<uint4*>(rbase + 8 * i * p.r_ld) = o;
               }
             }
             if (out_r[mt] && (mir_lo[mt] >= 0 || mir_hi[mt] >= 0)) {
