@@ -9,3 +9,9 @@ timeout 300 python bench.py --no-e2e --steps 3 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); print('emb/s', d['value'], 'ms/step', d['ms_per_step'], 'mfa TF', d['roofline']['achieved'], d['roofline']['kernel_ms'], d['clocks'])"
 done
+echo "--- SVB_PDL=0"
+for i in 1 2; do
+SVB_PDL=0 timeout 300 python bench.py --no-e2e --steps 3 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print('emb/s', d['value'], 'ms/step', d['ms_per_step'], 'mfa TF', d['roofline']['achieved'], d['roofline']['kernel_ms'], d['clocks'])"
+done
