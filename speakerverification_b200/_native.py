@@ -10,7 +10,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsvb.so")
+LIB_PATH = os.environ.get("SVB_LIB", os.path.join(_HERE, "libsvb.so"))   # SVB_LIB: A/B builds of the same ABI
 
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
 OUT_BF16, OUT_BF16_HILO, OUT_F32 = 0, 1, 2

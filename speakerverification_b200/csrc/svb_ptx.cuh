@@ -39,14 +39,20 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
+// suspend-time hint of try_wait: the waiting thread sleeps in hardware until the phase completes or the hint expires,
+// instead of re-issuing the poll (17 % of the instructions executed by the Res2Net chain kernel were this loop; the
+// step runs power capped, so polling costs clock)
+#ifndef SVB_MBAR_SUSPEND_NS
+#define SVB_MBAR_SUSPEND_NS 20000u
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.b32 %0, 1, 0, p;\n\t}\n"
       : "=r"(done)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(SVB_MBAR_SUSPEND_NS)
       : "memory");
   return done != 0;
 }
