@@ -578,6 +578,9 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   SVB_CHECK(g.act == ACT_GELU, "the plain pointwise instance is GELU + BN");
   SVB_CHECK(g.num_taps == 1 || (bn == 256 && !stats && g.a2_kc == 0), "k > 1 runs on the BN=256 instances without statistics");
   if (g.num_taps > 1) {   // block 0: exact-erf GELU, bit-identical to the gemm_tc path it replaces
+    static const bool two_b0 = [] { const char* e = getenv("SVB_PW_2SM"); return e == nullptr || e[0] != '0'; }();
+    if (mc && two_b0 && !hilo)
+      return launch_pw_t<256, ACT_GELU_ERF, false, false, 16, 0, true, true>(ma, ma2, mw, mo, p, stream);
     if (mc)
       return hilo ? launch_pw_t<256, ACT_GELU_ERF, false, true, 16, 0, true>(ma, ma2, mw, mo, p, stream)
                   : launch_pw_t<256, ACT_GELU_ERF, false, false, 16, 0, true>(ma, ma2, mw, mo, p, stream);
