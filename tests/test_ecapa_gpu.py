@@ -125,3 +125,24 @@ def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
         want = eo.embed(np.stack([waves[i, :n], waves[i, :n]]), sd).numpy()[0]
         c = float((got[i] * want).sum() / np.linalg.norm(got[i]) / np.linalg.norm(want))
         assert c > 0.9995, (i, c)
+
+
+def test_extreme_lengths_fp32(golden_c512):
+    """Shortest supported utterance (9 frames: the reflect halo of 4 frames per side must not overlap), a 16-frame one,
+    multi-segment Res2Net windows (1025 and 2001 frames = 20 s) in ONE ragged launch against the oracle; one frame
+    less than the minimum fails loudly."""
+    from oracle import ecapa_oracle as eo, synth
+    from speakerverification_b200.engine import EcapaEngine
+    sd, state = _state(CH512, golden_c512)
+    eng = EcapaEngine(state, CH512, 80, 192, _frontend(), precision="fp32")
+    f0, env = synth.speaker_bank(4, seed=5)
+    lens = [1280, 2400 + 37, 1024 * 160 + 5, 320000]
+    sig = [synth.utterance(f0[i], env[i], n, 900 + i) for i, n in enumerate(lens)]
+    got = eng.forward_flat(torch.from_numpy(np.concatenate(sig)).cuda(), lens).cpu().numpy()
+    assert np.isfinite(got).all()
+    for i, n in enumerate(lens):
+        want = eo.embed(np.stack([sig[i], sig[i]]), sd).numpy()[0]
+        c = float((got[i] * want).sum() / np.linalg.norm(got[i]) / np.linalg.norm(want))
+        assert c >= 0.9999, (n, c)
+    with pytest.raises(RuntimeError, match="frames"):
+        eng.forward_flat(torch.from_numpy(sig[0][:1279]).cuda(), [1279])
