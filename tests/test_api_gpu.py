@@ -195,6 +195,60 @@ def test_plugin_interfaces_and_test_from_list(workdir, golden_c512):
     assert rows[0] == "audio_1,audio_2,pred_label,score" and len(rows) == 51
 
 
+def test_benchmark_consumer_flow(workdir, golden_c512):
+    """The call sequence of the reference's integration consumer src/benchmark/benmark_model.py:55-125:
+    evaluateFromList -> tuneThresholdfromScore over 50 target-FA points -> best sum rate / EER / g-mean threshold ->
+    evaluation_results.txt -> testFromList at that threshold; every decision checked against the same flow run on the
+    reference's own scores (tests/golden)."""
+    import csv
+    from speakerverification_b200 import utils as U
+    net, h, args = _handle(workdir, "fp32")
+    sc, lab, trials = h.evaluateFromList(listfilename=workdir["trials"], distributed=False,
+                                         dataloader_options=args["dataloader_options"], cohorts_path=workdir["cohorts"],
+                                         num_eval=2, scoring_mode="cosine")
+    target_fa = np.linspace(5, 0, num=50)
+    res = U.tuneThresholdfromScore(sc, lab, target_fa)
+    ref = U.tuneThresholdfromScore(list(golden_c512["scores_cos"]), lab, target_fa)
+    assert set(res) == {"gmean", "roc", "prec_recall"} and len(res["roc"][0]) == 50
+
+    def best(r):
+        rates = [row[1] + row[2] for row in r["roc"][0]]
+        return int(np.argmin(rates)), min(rates)
+    assert abs(best(res)[1] - best(ref)[1]) <= 0.25       # best FA + FR sum rate in %, one trial = 0.1-1 %
+    assert round(float(res["roc"][1]), 4) == round(float(ref["roc"][1]), 4)            # EER, 4 decimals
+    assert abs(res["roc"][2] - ref["roc"][2]) <= 1e-2     # AUC (x100 scale): scores within 1e-4 may swap neighbouring ranks
+    assert res["gmean"][0] == ref["gmean"][0] and abs(res["gmean"][2] - ref["gmean"][2]) <= 1e-4
+    thr = res["gmean"][-1]
+    out = workdir["tmp"] / "evaluation_results.txt"
+    with open(out, "w", newline="") as wf:
+        w = csv.writer(wf, delimiter=",")
+        w.writerow(["audio_1", "audio_2", "label", "predict_label", "score"])
+        for score, label, pair in zip(sc, lab, trials):
+            com, refp = pair.strip().split(" ")
+            w.writerow([com, refp, label, int(score >= thr), score])
+    preds = np.asarray(sc) >= thr
+    gold = golden_c512["scores_cos"]
+    clear = np.abs(gold - ref["gmean"][-1]) > 2e-4
+    assert clear.sum() >= 990 and np.array_equal(preds[clear], (gold >= ref["gmean"][-1])[clear])
+    # the verification list goes through testFromList at the tuned threshold
+    csv_in = str(workdir["tmp"] / "verify.csv")
+    with open(csv_in, "w") as f:
+        f.write("audio_1,audio_2\n")
+        for pair in trials[:200]:
+            a, b = pair.split(" ")
+            f.write("%s,%s\n" % (a, b))
+    out_csv = str(workdir["tmp"] / "verify_result.csv")
+    got = h.testFromList(csv_in, thresh_score=thr, distributed=False, dataloader_options=args["dataloader_options"],
+                         cohorts_path=workdir["cohorts"], num_eval=2, scoring_mode="cosine", output_file=out_csv)
+    assert len(got) == 200
+    with open(out_csv) as f:
+        rows = list(csv.reader(f))[1:]
+    for k, row in enumerate(rows):
+        assert abs(float(row[3]) - gold[k]) <= 1e-4
+        if clear[k]:
+            assert row[2] == ("1" if gold[k] >= ref["gmean"][-1] else "0")
+
+
 def test_no_cpu_path(workdir):
     from speakerverification_b200.model import SpeakerEncoder
     with pytest.raises(RuntimeError):
