@@ -46,9 +46,11 @@ def crop_plan(src_len, audio_spec, num_eval):
     src_len = np.asarray(src_len, dtype=np.int64)
     dst_len = np.where(src_len <= L, L + 1, src_len)
     if num_eval == 0:
-        return dst_len, [np.zeros(1, dtype=np.int64) for _ in src_len], L
-    starts = [np.array([int(s) for s in np.linspace(0, n - L, num=num_eval)], dtype=np.int64) for n in dst_len]
-    return dst_len, starts, L
+        return dst_len, list(np.zeros((len(dst_len), 1), dtype=np.int64)), L
+    # np.linspace with an array-valued stop evaluates the same expression per column as the scalar call of the
+    # reference (arange * (stop / div), last point = stop); int() truncation = astype on the non-negative values
+    starts = np.linspace(0, dst_len - L, num=num_eval, axis=1).astype(np.int64)
+    return dst_len, list(starts), L
 
 
 def normalize_audio_amp(signal):

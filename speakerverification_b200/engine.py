@@ -52,7 +52,7 @@ class Frontend:
         self.handle = h
 
     def __del__(self):
-        if getattr(self, "handle", None) and nv._lib is not None:
+        if getattr(self, "handle", None) and nv is not None and getattr(nv, "_lib", None) is not None:   # nv is None at interpreter shutdown
             nv._lib.svb_fbank_destroy(self.handle)
             self.handle = None
 
@@ -97,7 +97,7 @@ class BatchPlan:
         return torch.cat(idx)
 
     def __del__(self):
-        if getattr(self, "handle", None) and nv._lib is not None:
+        if getattr(self, "handle", None) and nv is not None and getattr(nv, "_lib", None) is not None:   # nv is None at interpreter shutdown
             nv._lib.svb_batch_destroy(self.handle)
             self.handle = None
 
@@ -221,7 +221,7 @@ class EcapaEngine:
         return self._ws[off:off + n * esz].view(dtype).view(plan.rows, planes * cols)
 
     def __del__(self):
-        if getattr(self, "handle", None) and nv._lib is not None:
+        if getattr(self, "handle", None) and nv is not None and getattr(nv, "_lib", None) is not None:   # nv is None at interpreter shutdown
             nv._lib.svb_ecapa_destroy(self.handle)
             self.handle = None
 

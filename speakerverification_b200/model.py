@@ -11,6 +11,7 @@ and plotting are out of scope and raise.
 import csv
 import itertools
 import os
+import time
 from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
 
@@ -182,6 +183,8 @@ class ModelHandling(object):
             self._stage_bufs = st
         return st["h_pcm"], st["h_seg"], st["d_pcm"], st["d_seg"], st["d_wav"]
 
+    stage_trace = None   # set to a list to collect per-group host staging times of embed_signals
+
     def embed_signals(self, signals, num_eval):
         """GPU crop/stack pipeline (replaces loadWAV eval mode + test_data_loader stacking,
         src/processing/audio_loader.py:110-150, src/dataloader.py:275-292): `signals` is a list of 1-D int16 / float32
@@ -202,18 +205,22 @@ class ModelHandling(object):
         src_len = np.array([len(s) for s in signals], dtype=np.int64)
         dst_len, starts, L = crop_plan(src_len, self.audio_spec, num_eval)
         # groups of utterances per encoder launch
+        # (plain Python ints and prefix sums: this prologue runs before the first byte moves, nothing overlaps it)
+        dl = dst_len.tolist()
         groups, i = [], 0
         while i < U:
             j, rows, samples = i, 0, 0
             while j < U and (j == i or (rows + n <= self.batch_rows and
-                                        (num_eval > 0 or samples + dst_len[j] <= self.batch_samples))):
+                                        (num_eval > 0 or samples + dl[j] <= self.batch_samples))):
                 rows += n
-                samples += int(dst_len[j])
+                samples += dl[j]
                 j += 1
             groups.append((i, j))
             i = j
-        max_src = max(int(src_len[a:b].sum()) for a, b in groups)
-        max_dst = max(int(dst_len[a:b].sum()) for a, b in groups)
+        csrc = np.concatenate([[0], np.cumsum(src_len)])
+        cdst = np.concatenate([[0], np.cumsum(dst_len)])
+        max_src = max(int(csrc[b] - csrc[a]) for a, b in groups)
+        max_dst = max(int(cdst[b] - cdst[a]) for a, b in groups)
         max_u = max(b - a for a, b in groups)
         t_dt = torch.int16 if i16 else torch.float32
         seg_dt = np.dtype([("src_off", "<i8"), ("dst_off", "<i8"), ("src_len", "<i4"), ("dst_len", "<i4")])
@@ -239,8 +246,10 @@ class ModelHandling(object):
             into pinned buffer g & 1 (parallel memcpy, numpy releases the GIL) and the H2D copies on the copy stream."""
             a, b = groups[g]
             k = g & 1
+            t_in = time.perf_counter()
             if g >= 2:
                 ready[k].synchronize()                       # the pinned buffers of group g-2 have been consumed
+            t_sync = time.perf_counter()
             segs = np.zeros(b - a, dtype=seg_dt)
             segs["src_len"], segs["dst_len"] = src_len[a:b], dst_len[a:b]
             segs["src_off"] = np.concatenate([[0], np.cumsum(src_len[a:b])[:-1]])
@@ -249,6 +258,7 @@ class ModelHandling(object):
             cuts = np.linspace(a, b, num=min(5, b - a) + 1).astype(int)
             list(self._pool.map(lambda lh: fill(k, lh[0], lh[1], offs), zip(cuts[:-1], cuts[1:])))
             nsrc = int(src_len[a:b].sum())
+            t_fill = time.perf_counter()
             h_seg[k].numpy()[:segs.nbytes] = segs.view(np.uint8)
             with torch.cuda.device(self.device), torch.cuda.stream(copy_stream):
                 if g >= 2:
@@ -256,6 +266,9 @@ class ModelHandling(object):
                 d_pcm[k][:nsrc].copy_(h_pcm[k][:nsrc], non_blocking=True)
                 d_seg[k][:segs.nbytes].copy_(h_seg[k][:segs.nbytes], non_blocking=True)
                 ready[k].record(copy_stream)
+            if self.stage_trace is not None:                 # diagnostics: (group, wait, fill, enqueue) in ms
+                t_out = time.perf_counter()
+                self.stage_trace.append((g, 1e3 * (t_sync - t_in), 1e3 * (t_fill - t_sync), 1e3 * (t_out - t_fill)))
             return segs
 
         fut = self._pool.submit(stage, 0)

@@ -7,7 +7,7 @@ from speakerverification_b200 import synth
 from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
 margs = bench.model_args("cuda", "bf16")
 net = WrappedModel(SpeakerEncoder(**margs))
-h = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=4096, svb_batch_samples=256 * 48000))
+h = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=592, svb_batch_samples=296 * 48000))
 net.eval()
 lengths = synth.ragged_lengths(2000, seed=2)
 signals = bench.eval_signals(lengths, seed=50)
