@@ -280,6 +280,7 @@ int svb_enrol_nearest(const float* query, const float* bank, int Q, int n_per_ut
                       float* dist, float* top_dist, int32_t* top_idx, void* stream) {
   if (check_device()) return -1;
   SVB_CHECK(query && bank && dist && Q >= 0 && n_per_utt >= 1 && D >= 1 && S >= 1, "bad argument");
+  SVB_CHECK(Q <= 8 * 65535, "at most %d query utterances per call", 8 * 65535);   // grid.y of the distance kernel
   SVB_CHECK(topk >= 0 && topk <= 8 && topk <= S && (topk == 0 || (top_dist && top_idx)), "topk must be 0..min(8, S)");
   return enrol_nearest(query, bank, Q, n_per_utt, D, S, eps, topk, dist, top_dist, top_idx,
                        static_cast<cudaStream_t>(stream));
