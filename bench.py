@@ -766,8 +766,8 @@ def main():
                          "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one MFA launch at 592 rows (ncu --set full,
                          # profiles/r01_summary.md): 1.215 GB + 1.132 GB against 2.267 GB algorithmic
-                         "traffic": 2.347e9 if args.batch_rows == 592 else None,
-                         "traffic_unit": "bytes per launch (ncu capture of the same shape; algorithmic 2.267e9)",
+                         "traffic": 2.487e9 if args.batch_rows == 592 else None,
+                         "traffic_unit": "bytes per launch (dram read + write of the ncu --set full capture of this kernel at this shape, profiles/r01_ncu_final.md; algorithmic 2.267e9)",
                          "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
             "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
                             "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
