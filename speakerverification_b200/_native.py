@@ -123,8 +123,38 @@ def check(rc):
         raise RuntimeError("libsvb: %s (code %d)" % (lib().svb_last_error().decode(), rc))
 
 
-def stream_ptr():
-    return _vp(torch.cuda.current_stream().cuda_stream)
+def stream_ptr(device=None):
+    """Raw handle of torch's current stream on `device` (default: the current device).  libsvb launches on the
+    CURRENT CUDA context, so a call for another device must run inside ``on_device``."""
+    return _vp(torch.cuda.current_stream(device).cuda_stream)
+
+
+def on_device(device):
+    """Context manager that makes `device` the current CUDA device for the library calls inside it: libsvb never
+    calls cudaSetDevice itself (its launches, cudaMalloc and TMA maps use the current context), so handles built for
+    cuda:N must be driven with cuda:N current (src/model.py:55-56,171-172: the reference's gpu=N selects cuda:N)."""
+    return torch.cuda.device(device)
+
+
+def device_method(fn):
+    """Decorator for methods of objects that carry ``self.device``: runs the body with that device current."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(self, *a, **k):
+        with torch.cuda.device(self.device):
+            return fn(self, *a, **k)
+    return wrapped
+
+
+def require_current(device):
+    """Raises unless `device` is the current CUDA device (a launch on another device would run device-N pointers on
+    device 0's context)."""
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    if dev.type != "cuda" or idx != torch.cuda.current_device():
+        raise RuntimeError("libsvb call for %s while cuda:%d is current; wrap the call in torch.cuda.device(%s)"
+                           % (dev, torch.cuda.current_device(), idx))
 
 
 def ptr(t):

@@ -1,5 +1,6 @@
 // Operand preparation kernels: fp32 -> bf16 hi/lo planes, Conv1d weight packing, BN folding,
 // and the row bookkeeping table of the time-major-with-halos layout.
+#include <algorithm>
 #include <vector>
 
 #include "svb_internal.h"
@@ -99,20 +100,61 @@ int pcm_stage(const void* pcm, int sample_kind, const PcmSeg* segs, int U, int m
   return 0;
 }
 
+// row_meta from per-utterance frame counts without any stream synchronisation: the (tiny) prefix table is written to a
+// slot of a library-owned ring of page-locked buffers and uploaded / expanded on the stream; a slot is reused only
+// after the event recorded behind its last kernel has completed (4 calls later: in practice never a wait).
+__global__ void row_meta_kernel(const long long* __restrict__ row0, int B, int halo, RowMeta* __restrict__ meta,
+                                long long total_rows) {
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < total_rows;
+       r += (long long)gridDim.x * blockDim.x) {
+    int lo = 0, hi = B;                    // largest b with row0[b] <= r  (row0[B] = rows in use)
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (row0[mid] <= r) lo = mid; else hi = mid;
+    }
+    if (r >= row0[B]) { meta[r] = RowMeta{-1, 0, 0, 0}; continue; }
+    const int T = static_cast<int>(row0[lo + 1] - row0[lo]) - 2 * halo;
+    meta[r] = RowMeta{lo, static_cast<int>(r - row0[lo]) - halo, T, 0};
+  }
+}
+
+namespace {
+struct MetaSlot { long long* host = nullptr; long long* dev = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; bool used = false; };
+MetaSlot g_meta_ring[4];
+int g_meta_pos = 0;
+}  // namespace
+
 int build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row_meta, long long total_rows,
                    cudaStream_t stream) {
-  std::vector<RowMeta> h(static_cast<size_t>(total_rows), RowMeta{-1, 0, 0, 0});
+  SVB_CHECK(B > 0 && halo >= 0, "bad row_meta arguments");
+  MetaSlot& sl = g_meta_ring[g_meta_pos];
+  g_meta_pos = (g_meta_pos + 1) & 3;
+  if (sl.used) SVB_CUDA_OK(cudaEventSynchronize(sl.done));     // its upload of 4 calls ago has executed
+  const size_t need = static_cast<size_t>(B) + 1;
+  if (sl.cap < need) {
+    if (sl.host) cudaFreeHost(sl.host);
+    if (sl.dev) cudaFree(sl.dev);
+    sl.cap = need < 1024 ? 1024 : 2 * need;
+    SVB_CUDA_OK(cudaMallocHost(reinterpret_cast<void**>(&sl.host), sl.cap * sizeof(long long)));
+    SVB_CUDA_OK(cudaMalloc(reinterpret_cast<void**>(&sl.dev), sl.cap * sizeof(long long)));
+  }
+  if (sl.done == nullptr) SVB_CUDA_OK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
   long long r = 0;
   for (int b = 0; b < B; ++b) {
     const int T = frames_host[b];
     SVB_CHECK(T > 2 * halo, "utterance %d has %d frames; need more than 2*halo = %d", b, T, 2 * halo);
-    for (int t = -halo; t < T + halo; ++t, ++r) {
-      SVB_CHECK(r < total_rows, "row_meta buffer too small");
-      h[static_cast<size_t>(r)] = RowMeta{b, t, T, 0};
-    }
+    sl.host[b] = r;
+    r += T + 2 * halo;
   }
-  SVB_CUDA_OK(cudaMemcpyAsync(row_meta, h.data(), h.size() * sizeof(RowMeta), cudaMemcpyHostToDevice, stream));
-  SVB_CUDA_OK(cudaStreamSynchronize(stream));  // h goes out of scope
+  sl.host[B] = r;
+  SVB_CHECK(r <= total_rows, "row_meta buffer too small");
+  SVB_CUDA_OK(cudaMemcpyAsync(sl.dev, sl.host, need * sizeof(long long), cudaMemcpyHostToDevice, stream));
+  const int grid = static_cast<int>(std::min<long long>((total_rows + 255) / 256, 148 * 8));
+  row_meta_kernel<<<grid < 1 ? 1 : grid, 256, 0, stream>>>(sl.dev, B, halo, reinterpret_cast<RowMeta*>(row_meta), total_rows);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  SVB_CUDA_OK(cudaEventRecord(sl.done, stream));
+  sl.used = true;
   return 0;
 }
 

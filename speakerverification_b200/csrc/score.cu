@@ -848,7 +848,7 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
   const size_t Upad = (static_cast<size_t>(U) + 127) / 128 * 128;
   SVB_CUDA_OK(cudaMemsetAsync(a16, 0, Upad * 2 * Dp * 2, stream));
   if (split_bf16(emean, U, D, D, a16, 2 * Dp, 2, Dp, stream)) return -1;
-  const bool smem_rows = N <= TOPK_SMEM_MAX_N;
+  const bool smem_rows = Np <= TOPK_SMEM_MAX_N;   // the launch asks for Np * 4 bytes (N rounded up to 64)
   if (smem_rows) {
     static bool attr_set = false;
     if (!attr_set) {

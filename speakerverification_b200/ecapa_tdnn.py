@@ -78,7 +78,9 @@ class ECAPA_TDNN(nn.Module):
         self.att, self.se, self.scale = attention_channels, se_channels, res2net_scale
         self.kwargs = kwargs
         if precision is None:
-            precision = kwargs.get("svb_precision") or ("bf16" if kwargs.get("mixedprec") else "fp32")
+            # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
+            # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
+            precision = kwargs.get("svb_precision") or "fp32"
         self.precision = precision
         C = channels
         self.blocks = nn.ModuleList([_TDNN(input_size, C[0], kernel_sizes[0])])
@@ -143,8 +145,9 @@ class ECAPA_TDNN(nn.Module):
         rows[plan.valid_row_index(x.device)] = x.float().transpose(1, 2).reshape(-1, M)
         ws = eng.workspace(plan)
         out = torch.empty((B, self.n_out), dtype=torch.float32, device=x.device)
-        nv.check(nv.lib().svb_ecapa_forward_mel(eng.handle, eng.frontend.handle, plan.handle, nv.ptr(rows), nv.ptr(ws),
-                                                ws.numel(), nv.ptr(out), out.stride(0), 0, nv.stream_ptr()))
+        with nv.on_device(x.device):
+            nv.check(nv.lib().svb_ecapa_forward_mel(eng.handle, eng.frontend.handle, plan.handle, nv.ptr(rows), nv.ptr(ws),
+                                                    ws.numel(), nv.ptr(out), out.stride(0), 0, nv.stream_ptr()))
         return out.squeeze()
 
 

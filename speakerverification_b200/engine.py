@@ -134,13 +134,15 @@ class EcapaEngine:
         arr_p = (_vp * len(ptrs))(*ptrs)
         h = _vp()
         torch.cuda.synchronize(self.device)
-        nv.check(nv.lib().svb_ecapa_create(ctypes.byref(cfg), arr_n, arr_p, len(names), ctypes.byref(h)))
+        with nv.on_device(self.device):      # the library allocates / launches on the current device
+            nv.check(nv.lib().svb_ecapa_create(ctypes.byref(cfg), arr_n, arr_p, len(names), ctypes.byref(h)))
         self.handle = h
         self.halo = nv.lib().svb_ecapa_halo(h)
         self._plans = {}
         self._row_plans = []
         self._ws = None
 
+    @nv.device_method
     def plan(self, nsamp):
         key = tuple(int(n) for n in nsamp)
         p = self._plans.get(key)
@@ -157,6 +159,7 @@ class EcapaEngine:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._ws
 
+    @nv.device_method
     def forward_flat(self, wav_flat, nsamp, l2norm=False, out=None):
         """wav_flat: 1-D fp32 CUDA tensor holding the utterances back to back; returns [B, n_out] fp32."""
         if not wav_flat.is_cuda or wav_flat.dtype != torch.float32:
@@ -171,6 +174,7 @@ class EcapaEngine:
                                             nv.stream_ptr()))
         return out
 
+    @nv.device_method
     def forward_rows(self, wav_flat, wav_off, nsamp, l2norm=False, out=None):
         """Rows given as (offset, length) views into one staged fp32 CUDA buffer (crops of the same utterance may
         overlap; nothing is copied).  The plan is specific to the offsets and is not cached."""

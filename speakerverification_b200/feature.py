@@ -77,11 +77,13 @@ class MelFrontend(nn.Sequential):
         fe = self.frontend()
         x = x.contiguous().float()
         B, L = x.shape
-        plan = BatchPlan([L] * B, fe.hop, 0)
+        with nv.on_device(x.device):
+            plan = BatchPlan([L] * B, fe.hop, 0)
         mel = torch.empty((plan.rows, fe.n_mels), dtype=torch.float32, device=x.device)
         tsum = torch.empty((plan.tiles, fe.n_mels), dtype=torch.float32, device=x.device)
-        nv.check(nv.lib().svb_fbank_power(fe.handle, plan.handle, nv.ptr(x), nv.ptr(mel), nv.ptr(tsum),
-                                          nv.stream_ptr()))
+        with nv.on_device(x.device):
+            nv.check(nv.lib().svb_fbank_power(fe.handle, plan.handle, nv.ptr(x), nv.ptr(mel), nv.ptr(tsum),
+                                              nv.stream_ptr()))
         return mel.view(B, plan.T[0], fe.n_mels).transpose(1, 2)
 
 

@@ -115,6 +115,7 @@ class ModelHandling(object):
         self.batch_samples = int(kwargs.get("svb_batch_samples", 296 * 48000))   # ragged launches: finer H2D double buffering
         self._copy_stream = None
         self._stage_bufs = None
+        self._batch_bufs = None
         self._pool = None
         if self.gpu == 0:
             nb = sum(p.numel() for p in self.__model__.module.__S__.parameters())
@@ -148,23 +149,34 @@ class ModelHandling(object):
             for r0 in range(0, R, bs):
                 eng.forward(waves[r0:r0 + bs], out=out[r0:r0 + bs])
             return out
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        main = torch.cuda.current_stream(self.device)
-        bufs = [torch.empty((bs, L), dtype=torch.float32, device=self.device) for _ in range(2)]
-        ready = [torch.cuda.Event() for _ in range(2)]
-        freed = [torch.cuda.Event() for _ in range(2)]
-        for i, r0 in enumerate(range(0, R, bs)):
-            k = i & 1
-            n = min(bs, R - r0)
-            with torch.cuda.stream(self._copy_stream):
-                if i >= 2:
-                    self._copy_stream.wait_event(freed[k])
-                bufs[k][:n].copy_(waves[r0:r0 + n], non_blocking=True)
-                ready[k].record(self._copy_stream)
-            main.wait_event(ready[k])
-            eng.forward(bufs[k][:n], out=out[r0:r0 + n])
-            freed[k].record(main)
+        with torch.cuda.device(self.device):
+            if self._copy_stream is None:
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+            main = torch.cuda.current_stream(self.device)
+            # the two device input buffers and their events live across calls (2 x 114 MB at 592 x 48 000): the
+            # `freed` event of a buffer's last use in the PREVIOUS call is waited on like one of this call
+            bb = self._batch_bufs
+            if bb is None or bb["shape"][0] < bs or bb["shape"][1] != L:
+                self._batch_bufs = bb = None
+                bb = self._batch_bufs = {"shape": (bs, L),
+                                         "bufs": [torch.empty((bs, L), dtype=torch.float32, device=self.device)
+                                                  for _ in range(2)],
+                                         "ready": [torch.cuda.Event() for _ in range(2)],
+                                         "freed": [None, None]}
+            bufs, ready, freed = bb["bufs"], bb["ready"], bb["freed"]
+            for i, r0 in enumerate(range(0, R, bs)):
+                k = i & 1
+                n = min(bs, R - r0)
+                with torch.cuda.stream(self._copy_stream):
+                    if freed[k] is not None:
+                        self._copy_stream.wait_event(freed[k])
+                    bufs[k][:n].copy_(waves[r0:r0 + n], non_blocking=True)
+                    ready[k].record(self._copy_stream)
+                main.wait_event(ready[k])
+                eng.forward(bufs[k][:n], out=out[r0:r0 + n])
+                if freed[k] is None:
+                    freed[k] = torch.cuda.Event()
+                freed[k].record(main)
         return out
 
     def _staging(self, t_dt, n_src, n_seg, n_dst):
@@ -173,15 +185,17 @@ class ModelHandling(object):
         need = (n_src, n_seg, n_dst)
         if st is None or st["dt"] != t_dt or any(x < y for x, y in zip(st["n"], need)):
             grow = need if st is None or st["dt"] != t_dt else tuple(max(x, y) for x, y in zip(st["n"], need))
+            if st is not None:
+                torch.cuda.synchronize(self.device)          # in-flight copies / kernels still use the old buffers
             self._stage_bufs = st = None
-            st = {"dt": t_dt, "n": grow,
+            st = {"dt": t_dt, "n": grow, "ready": [None, None], "freed": [None, None],
                   "h_pcm": [torch.empty(grow[0], dtype=t_dt).pin_memory() for _ in range(2)],
                   "h_seg": [torch.empty(grow[1], dtype=torch.uint8).pin_memory() for _ in range(2)],
                   "d_pcm": [torch.empty(grow[0], dtype=t_dt, device=self.device) for _ in range(2)],
                   "d_seg": [torch.empty(grow[1], dtype=torch.uint8, device=self.device) for _ in range(2)],
                   "d_wav": [torch.empty(grow[2], dtype=torch.float32, device=self.device) for _ in range(2)]}
             self._stage_bufs = st
-        return st["h_pcm"], st["h_seg"], st["d_pcm"], st["d_seg"], st["d_wav"]
+        return st
 
     stage_trace = None   # set to a list to collect per-group host staging times of embed_signals
 
@@ -228,9 +242,12 @@ class ModelHandling(object):
             self._copy_stream = torch.cuda.Stream(device=self.device)
         copy_stream = self._copy_stream
         main = torch.cuda.current_stream(self.device)
-        h_pcm, h_seg, d_pcm, d_seg, d_wav = self._staging(t_dt, max_src, max_u * seg_dt.itemsize, max_dst)
-        ready = [torch.cuda.Event() for _ in range(2)]
-        freed = [torch.cuda.Event() for _ in range(2)]
+        st = self._staging(t_dt, max_src, max_u * seg_dt.itemsize, max_dst)
+        h_pcm, h_seg, d_pcm, d_seg, d_wav = st["h_pcm"], st["h_seg"], st["d_pcm"], st["d_seg"], st["d_wav"]
+        # `ready[k]` (H2D copies of slot k executed) and `freed[k]` (the encoder finished with slot k) persist with the
+        # staging buffers: the first two groups of THIS call wait on the last uses of the PREVIOUS call, which may still
+        # be queued (embed_signals returns without a synchronisation)
+        ready, freed = st["ready"], st["freed"]
         if self._pool is None:
             # one stager + pinned-fill workers; the ranks of one box share its host cores
             local_world = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
@@ -247,8 +264,8 @@ class ModelHandling(object):
             a, b = groups[g]
             k = g & 1
             t_in = time.perf_counter()
-            if g >= 2:
-                ready[k].synchronize()                       # the pinned buffers of group g-2 have been consumed
+            if ready[k] is not None:
+                ready[k].synchronize()                       # the pinned buffers' previous contents have been copied out
             t_sync = time.perf_counter()
             segs = np.zeros(b - a, dtype=seg_dt)
             segs["src_len"], segs["dst_len"] = src_len[a:b], dst_len[a:b]
@@ -261,10 +278,12 @@ class ModelHandling(object):
             t_fill = time.perf_counter()
             h_seg[k].numpy()[:segs.nbytes] = segs.view(np.uint8)
             with torch.cuda.device(self.device), torch.cuda.stream(copy_stream):
-                if g >= 2:
-                    copy_stream.wait_event(freed[k])
+                if freed[k] is not None:
+                    copy_stream.wait_event(freed[k])         # the previous user of d_pcm[k] / d_seg[k] has run
                 d_pcm[k][:nsrc].copy_(h_pcm[k][:nsrc], non_blocking=True)
                 d_seg[k][:segs.nbytes].copy_(h_seg[k][:segs.nbytes], non_blocking=True)
+                if ready[k] is None:
+                    ready[k] = torch.cuda.Event()
                 ready[k].record(copy_stream)
             if self.stage_trace is not None:                 # diagnostics: (group, wait, fill, enqueue) in ms
                 t_out = time.perf_counter()
@@ -272,22 +291,25 @@ class ModelHandling(object):
             return segs
 
         fut = self._pool.submit(stage, 0)
-        for g, (a, b) in enumerate(groups):
-            k = g & 1
-            segs = fut.result()
-            if g + 1 < len(groups):
-                fut = self._pool.submit(stage, g + 1)        # freed[(g+1)&1] was recorded when group g-1 was enqueued
-            main.wait_event(ready[k])
-            nv.check(nv.lib().svb_pcm_stage(nv.ptr(d_pcm[k]), 1 if i16 else 0, nv.ptr(d_seg[k]), b - a,
-                                            int(dst_len[a:b].max()), nv.ptr(d_wav[k]), nv.stream_ptr()))
-            base = segs["dst_off"]
-            if num_eval > 0:
-                offs = np.concatenate([base[u - a] + starts[u] for u in range(a, b)])
-                lens = np.full(len(offs), L, dtype=np.int64)
-            else:
-                offs, lens = base, dst_len[a:b]
-            eng.forward_rows(d_wav[k], offs, lens, out=out[a * n:b * n])
-            freed[k].record(main)
+        with torch.cuda.device(self.device):
+            for g, (a, b) in enumerate(groups):
+                k = g & 1
+                segs = fut.result()
+                if g + 1 < len(groups):
+                    fut = self._pool.submit(stage, g + 1)    # freed[(g+1)&1] was recorded when group g-1 was enqueued
+                main.wait_event(ready[k])
+                nv.check(nv.lib().svb_pcm_stage(nv.ptr(d_pcm[k]), 1 if i16 else 0, nv.ptr(d_seg[k]), b - a,
+                                                int(dst_len[a:b].max()), nv.ptr(d_wav[k]), nv.stream_ptr()))
+                base = segs["dst_off"]
+                if num_eval > 0:
+                    offs = np.concatenate([base[u - a] + starts[u] for u in range(a, b)])
+                    lens = np.full(len(offs), L, dtype=np.int64)
+                else:
+                    offs, lens = base, dst_len[a:b]
+                eng.forward_rows(d_wav[k], offs, lens, out=out[a * n:b * n])
+                if freed[k] is None:
+                    freed[k] = torch.cuda.Event()
+                freed[k].record(main)
         return out.view(U, n, eng.n_out)
 
     def _embed_ragged(self, signals):

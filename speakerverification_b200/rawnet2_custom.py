@@ -84,8 +84,9 @@ class RawNet2Engine:
         self.device = keep[0].device
         h = _vp()
         torch.cuda.synchronize(self.device)
-        nv.check(nv.lib().svb_rawnet2_create(ctypes.byref(cfg), (ctypes.c_char_p * len(names))(*names),
-                                             (_vp * len(ptrs))(*ptrs), len(names), ctypes.byref(h)))
+        with nv.on_device(self.device):      # the library allocates / launches on the current device
+            nv.check(nv.lib().svb_rawnet2_create(ctypes.byref(cfg), (ctypes.c_char_p * len(names))(*names),
+                                                 (_vp * len(ptrs))(*ptrs), len(names), ctypes.byref(h)))
         self.handle = h
         self.planes = 2 if precision == "fp32" else 1
         self._ws = None
@@ -97,6 +98,12 @@ class RawNet2Engine:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._ws
 
+    def forward_flat(self, *a, **k):
+        raise NotImplementedError("RawNet2 embeds fixed-length crops only (ln.gamma / ln.beta have n_samples entries, "
+                                  "src/models/RawNet_baseline.py:13-24): whole-utterance embedding (num_eval=0) has no "
+                                  "meaning for this encoder")
+
+    @nv.device_method
     def forward(self, wav, l2norm=False, out=None):
         """wav: [B, n_samples] fp32 CUDA tensor -> [B, n_out] fp32."""
         if not wav.is_cuda or wav.dtype != torch.float32:
@@ -129,7 +136,7 @@ class RawNet2Engine:
         return v[:, 1:T + 1]
 
     def __del__(self):
-        if getattr(self, "handle", None) and nv._lib is not None:
+        if getattr(self, "handle", None) and nv is not None and getattr(nv, "_lib", None) is not None:   # nv is None at interpreter shutdown
             nv._lib.svb_rawnet2_destroy(self.handle)
             self.handle = None
 
@@ -161,7 +168,9 @@ class RawNet2(nn.Module):
         self.fc_after_gru = nn.Linear(gru_node, code_dim)
         self.fc = nn.Linear(nb_filters[5] * 2, code_dim)      # unused by the gru head; kept for the checkpoint layout
         if precision is None:
-            precision = kwargs.get("svb_precision") or ("bf16" if kwargs.get("mixedprec") else "fp32")
+            # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
+            # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
+            precision = kwargs.get("svb_precision") or "fp32"
         self.precision = precision
         self._engine, self._fingerprint = None, None
         for p in self.parameters():

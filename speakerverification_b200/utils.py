@@ -19,7 +19,19 @@ def _dev(t, device=None):
     return t.contiguous()
 
 
+def _on_arg_device(fn):
+    """Runs a scoring op with its first tensor argument's device current (libsvb launches on the current device)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(t, *a, **k):
+        with torch.cuda.device(t.device):
+            return fn(t, *a, **k)
+    return wrapped
+
+
 # ------------------------------------------------------------------ batched device scoring
+@_on_arg_device
 def cosine_trials(emb, idx_a, idx_b):
     """emb [U, n, D] CUDA fp32; int32 index tensors -> [trials] fp32 (mean_i |cos(a_i, b_i)|)."""
     U, n, D = emb.shape
@@ -29,6 +41,7 @@ def cosine_trials(emb, idx_a, idx_b):
     return out
 
 
+@_on_arg_device
 def mean_embeddings(emb, normalize):
     U, n, D = emb.shape
     out = torch.empty((U, D), dtype=torch.float32, device=emb.device)
@@ -36,6 +49,7 @@ def mean_embeddings(emb, normalize):
     return out
 
 
+@_on_arg_device
 def asnorm_stats(emean, cohorts, top):
     """Per-utterance (mu, sigma) of the `top` largest cohort scores; emean [U, D], cohorts [N, D]."""
     U, D = emean.shape
@@ -49,6 +63,7 @@ def asnorm_stats(emean, cohorts, top):
     return mu, sg
 
 
+@_on_arg_device
 def asnorm_trials(emean, idx_a, idx_b, mu, sigma):
     out = torch.empty(idx_a.numel(), dtype=torch.float32, device=emean.device)
     nv.check(nv.lib().svb_asnorm_trials(nv.ptr(emean), emean.shape[1], nv.ptr(idx_a), nv.ptr(idx_b), idx_a.numel(),
@@ -69,8 +84,9 @@ def enrol_nearest(query, bank, topk=3, eps=1e-6):
     dist = torch.empty((Q, S), dtype=torch.float32, device=query.device)
     td = torch.empty((Q, k), dtype=torch.float32, device=query.device)
     ti = torch.empty((Q, k), dtype=torch.int32, device=query.device)
-    nv.check(nv.lib().svb_enrol_nearest(nv.ptr(query), nv.ptr(bank), Q, n, D, S, float(eps), k, nv.ptr(dist),
-                                        nv.ptr(td), nv.ptr(ti), nv.stream_ptr()))
+    with torch.cuda.device(query.device):
+        nv.check(nv.lib().svb_enrol_nearest(nv.ptr(query), nv.ptr(bank), Q, n, D, S, float(eps), k, nv.ptr(dist),
+                                            nv.ptr(td), nv.ptr(ti), nv.stream_ptr()))
     return dist, td, ti
 
 
