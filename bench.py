@@ -558,13 +558,14 @@ def gemm_roofline(device, batch_rows, halo=4):
     C3 = CH[4]
     T = 1 + L // 160
     M = batch_rows * (T + 2 * halo)
-    a = torch.randn((M, C3), device=device).to(torch.bfloat16)
+    a = torch.randn((M, C3), device=device).to(torch.float16)
     w = torch.randn((C3, C3, 1), device=device) / C3 ** 0.5
-    wp = nv.pack_conv_weight(w, planes=1)
+    wp = nv.pack_conv_weight(w, planes=1, f16=True)
     z = torch.zeros(C3, device=device)
     o = torch.ones(C3, device=device)
-    out = torch.empty((M, C3), dtype=torch.bfloat16, device=device)
-    run = lambda: nv.tdnn_layer(a, wp, C3, C3, 1, 1, z, o, z, out, act=nv.ACT_GELU)
+    out = torch.empty((M, C3), dtype=torch.float16, device=device)
+    run = lambda: nv.tdnn_layer(a, wp, C3, C3, 1, 1, z, o, z, out, act=nv.ACT_GELU, out_kind=nv.OUT_F16, w_f16=True,
+                                x_f16=True)
     for _ in range(3):
         run()
     torch.cuda.synchronize()

@@ -44,10 +44,16 @@ int svb_build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row
 /* fp32 [rows, cols] (ld_in) -> bf16 planes: hi at out[r*ld_out + c], optional lo at +plane_cols. */
 int svb_split_bf16(const float* x, int64_t rows, int cols, int ld_in, void* out, int ld_out,
                    int planes, int plane_cols, void* stream);
+/* fp32 [rows, cols] (ld_in) -> one plane of IEEE half (saturating), the activation format of the 16-bit mode. */
+int svb_to_f16(const float* x, int64_t rows, int cols, int ld_in, void* out, int ld_out, void* stream);
 /* Conv1d weight [cout, cin, k] fp32 (nn.Conv1d layout, src/models/layers/cnn.py:79-88) ->
  * packed bf16 [cout, k, planes, cin_pad] (cin_pad multiple of 64, zero filled; planes: hi[, lo]). */
 int svb_pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, int planes,
                          void* out, void* stream);
+/* Same layout with the weights stored as IEEE half (one plane): the weight operand of a tensor-core layer may be fp16
+ * while the activations stay bf16 (SvbTdnnArgs.w_f16 = 1, passes = 1) -- same MMA rate, 11 instead of 8 significant
+ * weight bits.  This is what bf16 mode of the ECAPA / RawNet2 engines uses for every single-plane layer. */
+int svb_pack_conv_weight_f16(const float* w, int cout, int cin, int k, int cin_pad, void* out, void* stream);
 /* BatchNorm1d(eval) -> per-channel scale/shift (src/models/layers/normalization.py:62-68, eps 1e-5). */
 int svb_fold_bn(const float* gamma, const float* beta, const float* mean, const float* var, int n,
                 float eps, float* scale, float* shift, void* stream);
@@ -57,7 +63,8 @@ int svb_fold_bn(const float* gamma, const float* beta, const float* mean, const 
  *   out = BN(act(conv_reflect_same(x) + bias))          src/models/ECAPA_TDNN.py:68-69
  * replaces F.pad(reflect) + nn.Conv1d + activation + BatchNorm1d (4 library kernels). */
 enum { SVB_ACT_NONE = 0, SVB_ACT_RELU = 1, SVB_ACT_GELU = 2 };
-enum { SVB_OUT_BF16 = 0, SVB_OUT_BF16_HILO = 1, SVB_OUT_F32 = 2 };
+/* output storage: one bf16 plane, bf16 hi|lo planes (fp32 grade), fp32, or one plane of IEEE half (16-bit mode) */
+enum { SVB_OUT_BF16 = 0, SVB_OUT_BF16_HILO = 1, SVB_OUT_F32 = 2, SVB_OUT_F16 = 3 };
 enum { SVB_STORE_ALL = 0, SVB_STORE_MIRROR = 1 };
 
 typedef struct SvbTdnnArgs {
@@ -88,6 +95,9 @@ typedef struct SvbTdnnArgs {
    * zeroes the buffers.  Replaces the separate time-mean passes of SEBlock (src/models/ECAPA_TDNN.py:171-172) and of
    * AttentiveStatisticsPooling's global context (src/models/ECAPA_TDNN.py:222-227). */
   int64_t* col_sum; int64_t* col_sq; int32_t stats_ld;
+  int32_t w_f16;           /* w was packed by svb_pack_conv_weight_f16 (w_planes = 1, passes = 1) */
+  int32_t x_f16;           /* x (x2, add_src) hold ONE plane of IEEE half instead of bf16 (passes = 1): the activation
+                            * format of the 16-bit mode, i.e. what an SVB_OUT_F16 layer wrote */
 } SvbTdnnArgs;
 
 int svb_tdnn_layer(const SvbTdnnArgs* args, void* stream);
@@ -217,6 +227,13 @@ int svb_rawnet2_forward(const SvbRawnet2* e, const float* wav, int64_t wav_ld, i
  * svb_asnorm_trials     = S-norm combination (src/utils.py:148-156) for all trials at once. */
 int svb_cosine_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b,
                       int64_t n_trials, float* out, void* stream);
+/* svb_pnorm_trials      = utils.pnorm_similarity (src/utils.py:167-169; dispatched as 'pnorm' at :129-130, called with
+ *                         p=2 from src/model.py:442-444,546-548) for all trials at once:
+ *                         mean_i || a_i - b_i + eps ||_p over index-paired crops (F.pairwise_distance, eps 1e-6 added to
+ *                         the difference); normalize != 0 L2-normalises every crop row first (src/model.py:421-423).
+ *                         p = INFINITY selects the max norm. */
+int svb_pnorm_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b,
+                     int64_t n_trials, float p, float eps, int normalize, float* out, void* stream);
 int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int normalize, float* out,
                         void* stream);
 size_t svb_asnorm_workspace_bytes(int U, int N, int D);

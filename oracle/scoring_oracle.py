@@ -20,6 +20,17 @@ def cosine_score(ref, com, eps=1e-5):
     return float(np.mean(np.abs(num / den)))
 
 
+def pnorm_score(ref, com, p=2, eps=1e-6):
+    """src/utils.py:167-169: np.mean(F.pairwise_distance(ref, com, p=p, eps=1e-06, keepdim=True)) -- the eps is added
+    to the DIFFERENCE (torch.nn.functional.pairwise_distance), index-paired crops."""
+    d = np.abs(np.asarray(ref, np.float32) - np.asarray(com, np.float32) + np.float32(eps)).astype(np.float64)
+    if np.isinf(p):
+        n = d.max(-1)
+    else:
+        n = (d ** p).sum(-1) ** (1.0 / p)
+    return float(np.mean(n.astype(np.float32)))
+
+
 def _zt(ref, com, cohorts, top):
     # src/utils.py:140-150
     S = np.mean(np.inner(cohorts, ref), axis=1)

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SVB_LIB", os.path.join(_HERE, "libsvb.so"))   # SVB_LIB: A/B builds of the same ABI
 
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
-OUT_BF16, OUT_BF16_HILO, OUT_F32 = 0, 1, 2
+OUT_BF16, OUT_BF16_HILO, OUT_F32, OUT_F16 = 0, 1, 2, 3
 STORE_ALL, STORE_MIRROR = 0, 1
 
 _c = ctypes
@@ -36,6 +36,7 @@ class SvbTdnnArgs(_c.Structure):
         ("out2", _vp), ("out2_ld", _i32), ("out2_plane_cols", _i32),
         ("block_n", _i32),
         ("col_sum", _vp), ("col_sq", _vp), ("stats_ld", _i32),
+        ("w_f16", _i32), ("x_f16", _i32),
     ]
 
 
@@ -61,6 +62,8 @@ def _declare(L):
     L.svb_build_row_meta.argtypes = [_vp, _i32, _i32, _vp, _i64, _vp]
     L.svb_split_bf16.argtypes = [_vp, _i64, _i32, _i32, _vp, _i32, _i32, _i32, _vp]
     L.svb_pack_conv_weight.argtypes = [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]
+    L.svb_to_f16.argtypes = [_vp, _i64, _i32, _i32, _vp, _i32, _vp]
+    L.svb_pack_conv_weight_f16.argtypes = [_vp, _i32, _i32, _i32, _i32, _vp, _vp]
     L.svb_fold_bn.argtypes = [_vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _vp]
     L.svb_tdnn_layer.argtypes = [_c.POINTER(SvbTdnnArgs), _vp]
     for name, (args, res) in _EXTRA_SIGS.items():
@@ -102,6 +105,7 @@ _EXTRA_SIGS = {
     "svb_fbank_power": ([_vp, _vp, _vp, _vp, _vp, _vp], _i32),
     "svb_ecapa_forward_mel": ([_vp, _vp, _vp, _vp, _vp, _c.c_size_t, _vp, _i32, _i32, _vp], _i32),
     "svb_cosine_trials": ([_vp, _i32, _i32, _vp, _vp, _i64, _vp, _vp], _i32),
+    "svb_pnorm_trials": ([_vp, _i32, _i32, _vp, _vp, _i64, _c.c_float, _c.c_float, _i32, _vp, _vp], _i32),
     "svb_mean_embeddings": ([_vp, _i32, _i32, _i32, _i32, _vp, _vp], _i32),
     "svb_enrol_nearest": ([_vp, _vp, _i32, _i32, _i32, _i32, _c.c_float, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
@@ -190,12 +194,25 @@ def split_bf16(x, planes=1, out=None, plane_cols=None):
     return out
 
 
-def pack_conv_weight(w, planes, cin_pad=None):
-    """nn.Conv1d weight [cout, cin, k] fp32 -> packed bf16 [cout, k*planes*cin_pad]."""
+def to_f16(x):
+    """fp32 [rows, cols] -> one plane of IEEE half (saturating): the activation format of the 16-bit mode."""
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    out = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    check(lib().svb_to_f16(ptr(x), x.shape[0], x.shape[1], x.stride(0), ptr(out), out.stride(0), stream_ptr()))
+    return out
+
+
+def pack_conv_weight(w, planes, cin_pad=None, f16=False):
+    """nn.Conv1d weight [cout, cin, k] fp32 -> packed bf16 [cout, k*planes*cin_pad] (f16: one plane of IEEE half)."""
     w = w.contiguous().float()
     cout, cin, k = w.shape
     if cin_pad is None:
         cin_pad = (cin + 63) // 64 * 64
+    if f16:
+        assert planes == 1
+        out = torch.empty((cout, k * cin_pad), dtype=torch.float16, device=w.device)
+        check(lib().svb_pack_conv_weight_f16(ptr(w), cout, cin, k, cin_pad, ptr(out), stream_ptr()))
+        return out
     out = torch.empty((cout, k * planes * cin_pad), dtype=torch.bfloat16, device=w.device)
     check(lib().svb_pack_conv_weight(ptr(w), cout, cin, k, cin_pad, planes, ptr(out), stream_ptr()))
     return out
@@ -214,8 +231,9 @@ def tdnn_layer(x, w_packed, cout, cin_pad, k, dilation, bias, bn_scale, bn_shift
                passes=1, w_planes=1, x_plane_cols=0, x_cols=None, x2=None, x2_chunks=0, row_bias=None,
                post_tanh=False, row_meta=None, store_mode=STORE_ALL, halo=0, out_kind=OUT_BF16,
                out_plane_cols=0, add_src=None, add_planes=1, add_plane_cols=0, out2=None,
-               out2_plane_cols=0, block_n=0, rows=None, col_sum=None, col_sq=None):
+               out2_plane_cols=0, block_n=0, rows=None, col_sum=None, col_sq=None, w_f16=False, x_f16=False):
     a = SvbTdnnArgs()
+    a.w_f16, a.x_f16 = int(w_f16), int(x_f16)
     a.rows = x.shape[0] if rows is None else rows
     a.x, a.x_ld = ptr(x), x.stride(0)
     a.x_cols = x.shape[1] if x_cols is None else x_cols

@@ -112,7 +112,7 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
   if (threadIdx.x < 128) {
     const int r = threadIdx.x, c = r;
     const uint32_t addr = i_smem + (c >> 6) * 16384 + r * 128 + ((((c & 63) >> 3) ^ (r & 7)) << 4) + (c & 7) * 2;
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<unsigned short>(0x3f80)) : "memory");
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<unsigned short>(SPLIT ? 0x3f80 : 0x3c00)) : "memory");   // 1.0 as bf16 / as IEEE half
   }
   fence_proxy_async();
   tc_fence_before();
@@ -158,7 +158,10 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, CH_N);
+      // split mode: every operand is a bf16 plane; 16-bit mode: every operand (asp.conv weights, the identity, att, Y)
+      // is IEEE half.  A kind::f16 UMMA cannot mix the two: a_format != b_format raises an illegal-instruction error
+      // on sm_100a (measured, profiles/r02_precision.md), although the descriptor has two fields.
+      constexpr uint32_t idesc = umma_idesc_f16(128, CH_N, !SPLIT, !SPLIT);
       int stage = 0, cur_cb = -1;
       uint32_t phase = 0, wchg = 0, g = 0;
       for (int item = item_begin; item < item_end; ++item) {

@@ -8,8 +8,8 @@ const char* last_error();
 long long launches();
 void reset_launches();
 int build_row_meta(const int32_t*, int, int, int32_t*, long long, cudaStream_t);
+int to_f16(const float*, long long, int, int, void*, int, cudaStream_t);
 int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStream_t);
-int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int pcm_stage(const void*, int, const PcmSeg*, int, int, float*, cudaStream_t);
 struct Fbank; struct Batch; struct Ecapa;
@@ -38,6 +38,7 @@ long long ecapa_ws_offset(const Ecapa*, const Batch*, const char*);
 int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, int, void*, size_t, float*, int, int,
                   cudaStream_t);
 int cosine_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float*, cudaStream_t);
+int pnorm_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float, float, int, float*, cudaStream_t);
 int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
 int enrol_nearest(const float*, const float*, int, int, int, int, float, int, float*, float*, int32_t*, cudaStream_t);
 size_t asnorm_workspace_bytes(int, int, int, int*);
@@ -103,6 +104,16 @@ int svb_pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, 
                           static_cast<cudaStream_t>(stream));
 }
 
+int svb_to_f16(const float* x, int64_t rows, int cols, int ld_in, void* out, int ld_out, void* stream) {
+  if (check_device()) return -1;
+  return to_f16(x, rows, cols, ld_in, out, ld_out, static_cast<cudaStream_t>(stream));
+}
+
+int svb_pack_conv_weight_f16(const float* w, int cout, int cin, int k, int cin_pad, void* out, void* stream) {
+  if (check_device()) return -1;
+  return pack_conv_weight(w, cout, cin, k, cin_pad, 1, static_cast<bf16*>(out), static_cast<cudaStream_t>(stream), 1);
+}
+
 int svb_fold_bn(const float* gamma, const float* beta, const float* mean, const float* var, int n, float eps,
                 float* scale, float* shift, void* stream) {
   if (check_device()) return -1;
@@ -128,6 +139,10 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
   ops.w = static_cast<const bf16*>(a->w);
   ops.w_rows = a->cout;
   ops.w_cols = a->k * a->w_planes * a->cin_pad;
+  ops.w_f16 = a->w_f16;
+  ops.a_f16 = a->x_f16;
+  SVB_CHECK(!a->x_f16 || (a->passes == 1 && (a->add_src == nullptr || a->add_planes == 1)),
+            "fp16 activations (x_f16) are single plane: passes = 1");
   GemmParams p{};
   p.M = static_cast<int>(a->rows);
   p.N = a->cout;
@@ -165,8 +180,10 @@ int svb_tdnn_layer(const SvbTdnnArgs* a, void* stream) {
   p.stats_ld = a->stats_ld;
   SVB_CHECK(a->col_sq == nullptr || a->col_sum != nullptr, "col_sq needs col_sum");
   int bn = a->block_n;
-  // pointwise GELU / (ReLU + row-bias + tanh) layers with bf16 output take the lean-epilogue kernel (gemm_pw.cu)
-  const bool pointwise = bn == 0 && a->k == 1 && a->store_mode == SVB_STORE_ALL && a->out_kind != SVB_OUT_F32 &&
+  // pointwise GELU / (ReLU + row-bias + tanh) layers with fp16 or bf16 hi|lo output take the lean-epilogue kernel
+  // (gemm_pw.cu); single-plane bf16 output stays on the generic kernel
+  const bool pointwise = bn == 0 && a->k == 1 && a->store_mode == SVB_STORE_ALL &&
+                         (a->out_kind == SVB_OUT_F16 || a->out_kind == SVB_OUT_BF16_HILO) &&
                          p.out2 == nullptr && a->cout % 64 == 0 && p.num_pass != 2 &&
                          ((a->act == SVB_ACT_GELU && a->row_bias == nullptr && !a->post_tanh) ||
                           (a->act == SVB_ACT_RELU && a->row_bias != nullptr && a->post_tanh && a->row_meta != nullptr));
@@ -265,6 +282,12 @@ int svb_ecapa_forward_mel(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* 
 
 
 // ---------------------------------------------------------------- scoring
+int svb_pnorm_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b, int64_t n_trials,
+                     float p, float eps, int normalize, float* out, void* stream) {
+  if (check_device()) return -1;
+  return pnorm_trials(emb, n_per_utt, D, idx_a, idx_b, n_trials, p, eps, normalize, out, static_cast<cudaStream_t>(stream));
+}
+
 int svb_cosine_trials(const float* emb, int n_per_utt, int D, const int32_t* idx_a, const int32_t* idx_b,
                       int64_t n_trials, float* out, void* stream) {
   if (check_device()) return -1;

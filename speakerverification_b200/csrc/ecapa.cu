@@ -21,7 +21,6 @@ int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, 
                   float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
 int fbank_from_power(const Fbank*, const float*, const void*, int, const RowMeta*, long long, int, float*, float*, bf16*,
                      int, int, int, cudaStream_t);
-int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int pack_conv_weight_kpacked(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
@@ -38,7 +37,7 @@ int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
 size_t res2net_scratch_bytes(int, int);
 int res2net_seg_frames();
 int res2net_chain(const bf16*, bf16*, int, int, long long, const bf16* const*, const float* const*, const float* const*,
-                  const float* const*, int, int, const void*, int, const void*, void*, cudaStream_t);
+                  const float* const*, int, int, const void*, int, const void*, void*, cudaStream_t, int);
 
 enum { LIN_NONE = 0, LIN_RELU = 1, LIN_SIGMOID = 2 };
 static constexpr int FRAMES_PER_TILE = 32;
@@ -198,11 +197,15 @@ struct Layer {
   bf16* w = nullptr;
   float *bias = nullptr, *scale = nullptr, *shift = nullptr;
   int cout = 0, cin = 0, cin_pad = 0, k = 1, dil = 1, planes = 1, act = ACT_NONE;
+  int w_f16 = 0;   // single-plane weights stored as IEEE half (bf16 mode; see pack_conv_weight)
 };
 
 struct Ecapa {
   int C = 0, C3 = 0, Cs = 0, n_mels = 0, n_out = 0, att = 128, se_ch = 128, scale = 8, halo = 0;
-  int fp32_mode = 0;  // 0: bf16 operands (block 0 split), 1: split-bf16 everywhere (fp32 grade)
+  int fp32_mode = 0;  // 0: 16-bit operands (block 0 split-bf16), 1: split-bf16 everywhere (fp32 grade)
+  // 16-bit mode stores activations AND weights of the single-plane layers as IEEE half: kind::f16 UMMAs run fp16 at the
+  // bf16 rate, and 11 instead of 8 significant bits take the all-pairs score deviation from 2.1e-3 (bf16 operands,
+  // round 1) to 2.4e-4 (CPU model, profiles/r02_precision.md).  Stores saturate at +-65504 (BN outputs are O(1-10)).
   int dil[5] = {1, 2, 3, 4, 1}, ks[5] = {5, 3, 3, 3, 1};
   Layer block0, tdnn1[3], tdnn2[3], res[3][7], mfa, asp_tdnn, asp_conv;
   // block 0 "K-packed": the log-mel rows are stored densely ([rows, n_mels], hi rows then lo rows), so the 5-tap window
@@ -246,6 +249,15 @@ static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int c
   const float* b = find(tm, p + conv_key + "bias");
   if (w == nullptr || b == nullptr) return -1;
   L->cout = cout; L->cin = cin; L->k = k; L->dil = dil; L->planes = planes; L->act = act;
+  L->w_f16 = 0;
+  if (planes == 1) {
+    // 16-bit mode: the weights share the activations' format (a kind::f16 UMMA cannot mix bf16 and fp16 operands)
+    float amax = 0.f;
+    if (absmax_host(w, static_cast<long long>(cout) * cin * k, &amax)) return -1;
+    SVB_CHECK(amax == amax && amax <= 65504.f, "%sweight: |w| up to %g does not fit IEEE half; use the fp32-grade mode",
+              (p + conv_key).c_str(), static_cast<double>(amax));
+    L->w_f16 = 1;
+  }
   const int cu = cin_used < 0 ? cin : cin_used;   // pack only the first `cu` input channels
   L->cin_pad = (cu + 63) / 64 * 64;
   L->w = dalloc<bf16>(e, static_cast<size_t>(cout) * k * planes * L->cin_pad);
@@ -254,7 +266,7 @@ static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int c
   L->shift = dalloc<float>(e, cout);
   SVB_CHECK(L->w && L->bias && L->scale && L->shift, "cudaMalloc failed while packing %s", p.c_str());
   if (cu == cin) {
-    if (pack_conv_weight(w, cout, cin, k, L->cin_pad, planes, L->w, 0)) return -1;
+    if (pack_conv_weight(w, cout, cin, k, L->cin_pad, planes, L->w, 0, L->w_f16)) return -1;
   } else {
     // strided sub-matrix (k == 1): copy the first cu columns to a dense temporary first
     SVB_CHECK(k == 1, "partial input packing only for k=1");
@@ -262,7 +274,7 @@ static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int c
     SVB_CUDA_OK(cudaMalloc(&tmp, static_cast<size_t>(cout) * cu * sizeof(float)));
     SVB_CUDA_OK(cudaMemcpy2D(tmp, cu * sizeof(float), w, cin * sizeof(float), cu * sizeof(float), cout,
                              cudaMemcpyDeviceToDevice));
-    const int rc = pack_conv_weight(tmp, cout, cu, 1, L->cin_pad, planes, L->w, 0);
+    const int rc = pack_conv_weight(tmp, cout, cu, 1, L->cin_pad, planes, L->w, 0, L->w_f16);
     cudaDeviceSynchronize();
     cudaFree(tmp);
     if (rc) return -1;
@@ -304,12 +316,11 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
   const int P = fp32_mode ? 2 : 1;
   int rc = 0;
   rc |= make_layer(e, tm, "blocks.0.", C, n_mels, e->ks[0], e->dil[0], 2, ACT_GELU, true, "conv.conv.", &e->block0);
-  // Off by default (SVB_BLOCK0_KPACK=1 enables it): measured on B200 it takes the block-0 GEMM from 618 to 586 us per 592
-  // crops only -- the layer is bound by gemm_tc's 8-warp epilogue, not by its 30 k-blocks -- and the changed fp32
-  // summation order moves the bf16-mode max score deviation of the C=1024 list test from 1.96e-3 to 2.01e-3, across the
-  // 2e-3 tolerance (mean deviation 4.2e-4 either way).  Kept for the planned move of block 0 onto gemm_pw's epilogue.
+  // K-packed block 0 (K = 5 * n_mels = 400 -> 448 instead of 5 taps x 128 padded channels = 640 per pass): -160 us per
+  // 592 crops.  It changes the fp32 summation order of the layer, which round 1 could not afford (bf16-mode list test at
+  // 1.96e-3 of 2e-3); with fp16 weights the margin is there.  SVB_BLOCK0_KPACK=0 selects the tap-major layout.
   const char* kp = getenv("SVB_BLOCK0_KPACK");
-  if (!rc && n_mels % 8 == 0 && e->dil[0] == 1 && kp != nullptr && kp[0] == '1') {
+  if (!rc && n_mels % 8 == 0 && e->dil[0] == 1 && (kp == nullptr || kp[0] != '0')) {
     const float* w0 = find(tm, "blocks.0.conv.conv.weight");
     e->block0_kpad = (n_mels * e->ks[0] + 63) / 64 * 64;
     e->block0_wk = dalloc<bf16>(e, static_cast<size_t>(C) * 2 * e->block0_kpad);
@@ -448,7 +459,8 @@ static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, con
   GemmOperands ops{};
   ops.a = x.p; ops.lda = x.ld; ops.a_cols = x.cols;
   if (x2 != nullptr) { ops.a2 = x2->p; ops.lda2 = x2->ld; ops.a2_cols = x2->cols; }
-  ops.w = L.w; ops.w_rows = L.cout; ops.w_cols = L.k * L.planes * L.cin_pad;
+  ops.w = L.w; ops.w_rows = L.cout; ops.w_cols = L.k * L.planes * L.cin_pad; ops.w_f16 = L.w_f16;
+  ops.a_f16 = (!e->fp32_mode && passes == 1) ? 1 : 0;   // single-plane activations are IEEE half (block 0's input is split)
   GemmParams p{};
   p.M = static_cast<int>(b->rows); p.N = L.cout; p.kc_per_tap = L.cin_pad / 64; p.num_taps = L.k;
   for (int j = 0; j < L.k; ++j) p.tap_off[j] = (j - (L.k - 1) / 2) * L.dil;
@@ -456,7 +468,7 @@ static int run_layer(const Ecapa* e, const Batch* b, const Layer& L, View x, con
   p.bias = L.bias; p.scale = L.scale; p.shift = L.shift; p.rowbias = rowbias; p.rowbias_ld = rowbias_ld;
   p.act = L.act; p.post_tanh = post_tanh; p.row_meta = b->d_meta; p.store_mode = store_mode; p.halo = b->halo;
   p.out = out; p.out_ld = out_ld; p.out_plane_cols = out_pc;
-  p.out_kind = out_kind_override >= 0 ? out_kind_override : (e->fp32_mode ? OUT_BF16_HILO : OUT_BF16);
+  p.out_kind = out_kind_override >= 0 ? out_kind_override : (e->fp32_mode ? OUT_BF16_HILO : OUT_F16);
   if (add != nullptr) {
     p.add_src = add->p; p.add_ld = add->ld; p.add_planes = e->fp32_mode ? 2 : 1; p.add_plane_cols = add->plane_cols;
     p.out2 = out2; p.out2_ld = out2_ld; p.out2_plane_cols = out2_pc;
@@ -513,10 +525,19 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     g.tap_off[0] = -((L.k - 1) / 2);                      // the window of frame t starts at row t - 2
     g.num_pass = 3; g.a_plane_rows = static_cast<int>(M) + 128; g.w_planes = 2;
     g.bias = L.bias; g.scale = L.scale; g.shift = L.shift; g.act = L.act; g.row_meta = b->d_meta;
-    g.store_mode = STORE_MIRROR; g.halo = b->halo;
+    g.halo = b->halo;
     g.out = H("block0"); g.out_ld = P * C; g.out_plane_cols = C;
-    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_BF16;
-    if (launch_gemm(ops, g, 256, stream)) return -1;
+    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_F16;
+    if (C % 256 == 0 && getenv("SVB_BLOCK0_TC") == nullptr) {
+      // gemm_pw's 16-warp TMA-store epilogue (cta_group::2 instance in bf16 mode): every row is stored in place,
+      // then the reflect halos are copied from the valid frames
+      g.store_mode = STORE_ALL;
+      if (launch_gemm_pw(ops, g, stream)) return -1;
+      if (mirror_halo_rows(H("block0"), P * C, P * C, b->d_uttrows, B, b->halo, stream)) return -1;
+    } else {
+      g.store_mode = STORE_MIRROR;
+      if (launch_gemm(ops, g, 256, stream)) return -1;
+    }
   } else if (C % 256 == 0 && getenv("SVB_BLOCK0_TC") == nullptr) {
     // same K order (tap, pass, chunk) and the same exact-erf GELU as gemm_tc, i.e. bit-identical outputs, but through
     // gemm_pw's 16-warp TMA-store epilogue (gemm_tc's 8-warp row-store epilogue bounded this layer: tensor pipe 56 %);
@@ -532,7 +553,7 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     g.bias = L.bias; g.scale = L.scale; g.shift = L.shift; g.act = L.act; g.row_meta = b->d_meta;
     g.store_mode = STORE_ALL; g.halo = b->halo;
     g.out = H("block0"); g.out_ld = P * C; g.out_plane_cols = C;
-    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_BF16;
+    g.out_kind = e->fp32_mode ? OUT_BF16_HILO : OUT_F16;
     if (launch_gemm_pw(ops, g, stream)) return -1;
     if (mirror_halo_rows(H("block0"), P * C, P * C, b->d_uttrows, B, b->halo, stream)) return -1;
   } else {
@@ -553,7 +574,7 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
       const bf16* w[7]; const float *bs[7], *sc[7], *sh[7];
       for (int j = 0; j < 7; ++j) { w[j] = e->res[i][j].w; bs[j] = e->res[i][j].bias; sc[j] = e->res[i][j].scale; sh[j] = e->res[i][j].shift; }
       if (res2net_chain(U, R, C, P, M, w, bs, sc, sh, e->dil[i + 1], b->halo, b->d_segs, b->nsegs, b->d_uttrows,
-                        base + pl.off("chain_scratch"), stream)) return -1;
+                        base + pl.off("chain_scratch"), stream, e->res[i][0].w_f16)) return -1;
     }
     for (int j = 1; j < 8 && !fused_chain; ++j) {
       View xin = (j == 1) ? View{U + Cs, P * C, C, P * C - Cs} : View{S[(j - 1) & 1], P * Cs, Cs, P * Cs};

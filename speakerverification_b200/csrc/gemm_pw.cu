@@ -12,6 +12,8 @@
 //   * results are packed to bf16 in registers, staged per warp in a 4 KB 128B-swizzled smem box and
 //     written with ONE TMA store per 32 x 64 block (coalesced, asynchronous) instead of 32 uncoalesced
 //     16-byte row stores per warp instruction.
+// Output storage: HILO instances write bf16 hi|lo planes (fp32-grade mode); the single-plane instances write IEEE half
+// (16-bit mode, OUT_F16) -- there is no single-plane bf16 variant of this kernel (gemm_tc.cu keeps one).
 // Pointwise layers compute halo rows in place (the input halo rows mirror valid rows and the op is
 // per-row), so every row of a tile is stored and no mirror logic is needed.
 #include <stdlib.h>
@@ -64,6 +66,9 @@ struct PwParams {
   long long* colsum;     // STATS instances: fixed-point per-utterance column sums of the bf16 outputs (valid rows)
   long long* colsq;      // STATS == 2: and of their squares
   int stats_ld;
+  int w_f16;             // the W operand is IEEE half (b_format = F16) instead of bf16
+  int a_f16;             // the A operand is IEEE half (a_format = F16): activations of the 16-bit mode
+  int a_plane_rows;      // > 0: the lo plane of A row r is row r + a_plane_rows of the same map (K-packed block 0)
 };
 
 __device__ __forceinline__ float tanh_exact(float x) {
@@ -157,7 +162,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int wplane = (pass == 1) ? 1 : 0;
           const int a_col = aplane * p.a_plane_cols + kcx * BLOCK_K;
           const int w_col = ((tap * p.w_planes + wplane) * kc + kcx) * BLOCK_K;
-          const int a_row = m0 + p.tap_off[tap];
+          const int a_row = m0 + p.tap_off[tap] + aplane * p.a_plane_rows;
           const uint32_t fb = smem_u32(&full_bar[stage]);
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
@@ -183,7 +188,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1 && (!TWO || crank == 0)) {
     // ===================================================== MMA issuer (TWO: the leader CTA only, M = 256 over the pair)
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(TWO ? 2 * BLOCK_M : BLOCK_M, BN);
+      const uint32_t idesc = umma_idesc_f16(TWO ? 2 * BLOCK_M : BLOCK_M, BN, p.a_f16 != 0, p.w_f16 != 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -275,7 +280,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           x0 = fmaf(x0, s.x, h.x); x1 = fmaf(x1, s.y, h.y);
           x2 = fmaf(x2, s.z, h.z); x3 = fmaf(x3, s.w, h.w);
-          const uint32_t p0 = pack_bf16x2(x0, x1), p1 = pack_bf16x2(x2, x3);
+          const uint32_t p0 = pack16x2<!HILO>(x0, x1), p1 = pack16x2<!HILO>(x2, x3);
           hi[2 * i] = p0;
           hi[2 * i + 1] = p1;
           if (HILO) {
@@ -315,7 +320,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 uint32_t w;
                 asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w)
                              : "r"(my_box + r * 128 + (((pos * 4 + (cp >> 2)) ^ (r & 7)) << 4) + col_off));
-                const float a = bf16_lo_f(w), b = bf16_hi_f(w);
+                const float a = f16_lo_f(w), b = f16_hi_f(w);      // STATS instances are single plane = IEEE half
                 s0 += a; s1 += b;
                 if (STATS == 2) { q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1); }
               }
@@ -442,7 +447,7 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             x0 = fmaf(x0, s.x, h.x); x1 = fmaf(x1, s.y, h.y);
             x2 = fmaf(x2, s.z, h.z); x3 = fmaf(x3, s.w, h.w);
             if (RBT) { x0 = tanh_exact(x0); x1 = tanh_exact(x1); x2 = tanh_exact(x2); x3 = tanh_exact(x3); }
-            const uint32_t p0 = pack_bf16x2(x0, x1), p1 = pack_bf16x2(x2, x3);
+            const uint32_t p0 = pack16x2<!HILO>(x0, x1), p1 = pack16x2<!HILO>(x2, x3);
             hi[hh * 16 + 2 * i] = p0;
             hi[hh * 16 + 2 * i + 1] = p1;
             if (HILO) {
@@ -537,9 +542,13 @@ static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtens
 // store_mode STORE_ALL, bf16 output).  Supported: GELU layers with N % 256-tileable outputs (tdnn1/tdnn2/mfa)
 // and the ReLU + row-bias + tanh attention layer (asp.tdnn).
 int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t stream) {
-  SVB_CHECK(g.store_mode == STORE_ALL && g.num_taps >= 1 && g.num_taps <= 5 && (g.num_taps > 1 || g.tap_off[0] == 0),
+  SVB_CHECK(g.store_mode == STORE_ALL && g.num_taps >= 1 && g.num_taps <= 5 &&
+                (g.num_taps > 1 || g.tap_off[0] == 0 || g.a_plane_rows > 0),
             "launch_gemm_pw stores every row (k > 1 layers need a halo fix-up by the caller)");
-  SVB_CHECK(g.out_kind == OUT_BF16 || g.out_kind == OUT_BF16_HILO, "launch_gemm_pw writes bf16");
+  SVB_CHECK(g.a_plane_rows == 0 || (g.num_taps == 1 && g.a_plane_cols == 0 && ops.a2 == nullptr),
+            "row-stacked A planes come with the single-tap K-packed window view");
+  SVB_CHECK(g.out_kind == OUT_F16 || g.out_kind == OUT_BF16_HILO,
+            "launch_gemm_pw writes one plane of IEEE half or bf16 hi|lo planes");
   SVB_CHECK(g.N % 64 == 0 && g.out2 == nullptr, "launch_gemm_pw: N must be a multiple of 64 and there is no second output");
   SVB_CHECK(g.num_pass == 1 || g.num_pass == 3, "num_pass must be 1 or 3");
   const bool rbt = g.rowbias != nullptr;
@@ -548,7 +557,8 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   const bool hilo = g.out_kind == OUT_BF16_HILO;
   const int bn = (g.N >= 256 && !rbt) ? 256 : 128;
   CUtensorMap ma, ma2, mw, mo;
-  if (make_map(&ma, ops.a, g.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
+  // (a_cols may exceed lda: overlapping rows, the K-packed window view of a dense activation matrix)
+  if (make_map(&ma, ops.a, static_cast<long long>(g.M) + g.a_plane_rows, ops.a_cols, ops.lda, BLOCK_M)) return -1;
   if (ops.a2 != nullptr) {
     if (make_map(&ma2, ops.a2, g.M, ops.a2_cols, ops.lda2, BLOCK_M)) return -1;
   } else {
@@ -567,6 +577,11 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
   p.num_taps = g.num_taps;
   for (int j = 0; j < g.num_taps; ++j) p.tap_off[j] = g.tap_off[j];
   p.colsum = g.colsum; p.colsq = g.colsq; p.stats_ld = g.stats_ld;
+  p.w_f16 = ops.w_f16; p.a_f16 = ops.a_f16; p.a_plane_rows = g.a_plane_rows;
+  SVB_CHECK(ops.a_f16 == ops.w_f16, "activations and weights of a layer share one 16-bit format: a kind::f16 UMMA "
+            "with a_format != b_format is an illegal instruction on sm_100a");
+  SVB_CHECK(!ops.a_f16 || g.num_pass == 1, "fp16 activations are single plane / single pass");
+  SVB_CHECK(!ops.w_f16 || (g.num_pass == 1 && g.w_planes == 1), "fp16 weights are single plane / single pass");
   const int stats = g.colsum == nullptr ? 0 : (g.colsq == nullptr ? 1 : 2);
   SVB_CHECK(!stats || (bn == 256 && !hilo && !rbt && g.row_meta != nullptr && g.stats_ld % 2 == 0),
             "fused column statistics need the BN=256 single-plane GELU instance and row_meta");

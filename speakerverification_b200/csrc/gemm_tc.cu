@@ -52,7 +52,7 @@ __device__ __forceinline__ void store32(void* base, int ld, int plane_cols, long
     bf16* p = reinterpret_cast<bf16*>(base) + row * ld + col;
     uint32_t hi[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) hi[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+    for (int i = 0; i < 16; ++i) hi[i] = pack16x2<KIND == OUT_F16>(v[2 * i], v[2 * i + 1]);
     uint4* dst = reinterpret_cast<uint4*>(p);
 #pragma unroll
     for (int i = 0; i < 4; ++i) dst[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
@@ -149,7 +149,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================================================== MMA issuer (one elected lane)
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      const uint32_t idesc = umma_idesc_f16(BLOCK_M, BN, p.a_f16 != 0, p.w_f16 != 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -250,6 +250,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           for (int j = 0; j < tg.n; ++j) {
             if (p.out_kind == OUT_BF16) store32<OUT_BF16>(p.out, p.out_ld, 0, tg.r[j], n, v);
+            else if (p.out_kind == OUT_F16) store32<OUT_F16>(p.out, p.out_ld, 0, tg.r[j], n, v);
             else if (p.out_kind == OUT_BF16_HILO) store32<OUT_BF16_HILO>(p.out, p.out_ld, p.out_plane_cols, tg.r[j], n, v);
             else store32<OUT_F32>(p.out, p.out_ld, 0, tg.r[j], n, v);
           }
@@ -263,8 +264,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
-                v[8 * i + 2 * q] += bf16_lo_f(w[q]);
-                v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
+                v[8 * i + 2 * q] += p.a_f16 ? f16_lo_f(w[q]) : bf16_lo_f(w[q]);      // add_src shares A's format
+                v[8 * i + 2 * q + 1] += p.a_f16 ? f16_hi_f(w[q]) : bf16_hi_f(w[q]);
               }
             }
             if (p.add_planes == 2) {
@@ -281,6 +282,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             for (int j = 0; j < tg.n; ++j) {
               if (p.out_kind == OUT_BF16) store32<OUT_BF16>(p.out2, p.out2_ld, 0, tg.r[j], n, v);
+              else if (p.out_kind == OUT_F16) store32<OUT_F16>(p.out2, p.out2_ld, 0, tg.r[j], n, v);
               else store32<OUT_BF16_HILO>(p.out2, p.out2_ld, p.out2_plane_cols, tg.r[j], n, v);
             }
           }
@@ -383,7 +385,13 @@ static int launch_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorM
   return 0;
 }
 
-int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream) {
+int launch_gemm(const GemmOperands& ops, const GemmParams& p_in, int block_n, cudaStream_t stream) {
+  GemmParams p = p_in;
+  p.w_f16 = ops.w_f16; p.a_f16 = ops.a_f16;
+  SVB_CHECK(ops.a_f16 == ops.w_f16, "activations and weights of a layer share one 16-bit format: a kind::f16 UMMA "
+            "with a_format != b_format is an illegal instruction on sm_100a");
+  SVB_CHECK(!p.a_f16 || (p.num_pass == 1 && p.add_planes <= 1), "fp16 activations are single plane / single pass");
+  SVB_CHECK(!p.w_f16 || (p.num_pass == 1 && p.w_planes == 1), "fp16 weights are single plane / single pass");
   SVB_CHECK(p.M > 0 && p.N > 0 && p.kc_per_tap > 0 && p.num_taps >= 1 && p.num_taps <= 5, "bad GEMM shape");
   SVB_CHECK(p.num_pass >= 1 && p.num_pass <= 3, "num_pass must be 1, 2 or 3");
   SVB_CHECK(p.N % 32 == 0, "N must be a multiple of 32 (got %d)", p.N);

@@ -3,7 +3,8 @@
 //   AttentiveStatisticsPooling  src/models/ECAPA_TDNN.py:213-260 (global mean/std, softmax over time,
 //                               attention-weighted mean/std)
 //   asp_bn + fc head   src/models/ECAPA_TDNN.py:496-500
-// All statistics are fp32; activations are read from bf16 hi(+lo) planes.
+// All statistics are fp32; activations are read from bf16 hi|lo planes (planes == 2, fp32-grade mode) or from ONE plane
+// of IEEE half (planes == 1, 16-bit mode).
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -14,6 +15,11 @@ struct UttRows { long long row0; int T; int pad; };  // first VALID row and fram
 __device__ __forceinline__ void load8(const bf16* p, int planes, int plane_cols, float (&v)[8]) {
   const uint4 u = *reinterpret_cast<const uint4*>(p);
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+  if (planes == 1) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { v[2 * q] = f16_lo_f(w[q]); v[2 * q + 1] = f16_hi_f(w[q]); }
+    return;
+  }
 #pragma unroll
   for (int q = 0; q < 4; ++q) { v[2 * q] = bf16_lo_f(w[q]); v[2 * q + 1] = bf16_hi_f(w[q]); }
   if (planes == 2) {
@@ -22,6 +28,11 @@ __device__ __forceinline__ void load8(const bf16* p, int planes, int plane_cols,
 #pragma unroll
     for (int q = 0; q < 4; ++q) { v[2 * q] += bf16_lo_f(z[q]); v[2 * q + 1] += bf16_hi_f(z[q]); }
   }
+}
+
+__device__ __forceinline__ float load1(const bf16* p, int planes, int plane_cols) {
+  if (planes == 1) return __half2float(*reinterpret_cast<const __half*>(p));
+  return __bfloat162float(p[0]) + __bfloat162float(p[plane_cols]);
 }
 
 // grid (C/256, B), block 256: warp w sweeps rows w, w+8, ...; lane owns 8 consecutive channels.
@@ -61,8 +72,7 @@ col_stats_kernel(const bf16* __restrict__ x, int ld, int planes, int plane_cols,
   const float d = s * inv;
   float shift = 0.f;
   if (mode == 1) {
-    shift = __bfloat162float(x[u.row0 * ld + c]);
-    if (planes == 2) shift += __bfloat162float(x[u.row0 * ld + plane_cols + c]);
+    shift = load1(x + u.row0 * ld + c, planes, plane_cols);
   }
   mean_out[static_cast<long long>(blockIdx.y) * out_ld + c] = shift + d;
   if (mode == 1) std_out[static_cast<long long>(blockIdx.y) * out_ld + c] = sqrtf(fmaxf(q * inv - d * d, eps));
@@ -177,6 +187,7 @@ se_apply_kernel(const bf16* __restrict__ x, int x_ld, int x_pc, const bf16* __re
     for (int q = 0; q < 4; ++q) {
       const float a = fmaf(g[2 * q], v[2 * q], r[2 * q]);
       const float b = fmaf(g[2 * q + 1], v[2 * q + 1], r[2 * q + 1]);
+      if (planes == 1) { hi[q] = pack_f16x2(a, b); continue; }
       hi[q] = pack_bf16x2(a, b);
       lo[q] = pack_bf16x2(a - bf16_lo_f(hi[q]), b - bf16_hi_f(hi[q]));
     }
@@ -200,8 +211,7 @@ asp_pool_kernel(const float* __restrict__ logits, int l_ld, const bf16* __restri
   for (int t = ty; t < u.T; t += 4) {
     const long long row = u.row0 + t;
     const float lg = logits[row * l_ld + c];
-    float xv = __bfloat162float(x[row * x_ld + c]);
-    if (planes == 2) xv += __bfloat162float(x[row * x_ld + plane_cols + c]);
+    const float xv = load1(x + row * x_ld + c, planes, plane_cols);
     const float mn = fmaxf(m, lg);
     const float corr = expf(m - mn), e = expf(lg - mn);
     l = l * corr + e;
@@ -227,8 +237,7 @@ asp_pool_kernel(const float* __restrict__ logits, int l_ld, const bf16* __restri
   for (int t = ty; t < u.T; t += 4) {
     const long long row = u.row0 + t;
     const float lg = logits[row * l_ld + c];
-    float xv = __bfloat162float(x[row * x_ld + c]);
-    if (planes == 2) xv += __bfloat162float(x[row * x_ld + plane_cols + c]);
+    const float xv = load1(x + row * x_ld + c, planes, plane_cols);
     const float d = xv - mu;
     s2 = fmaf(expf(lg - M), d * d, s2);
   }

@@ -1,5 +1,8 @@
 // Operand preparation kernels: fp32 -> bf16 hi/lo planes, Conv1d weight packing, BN folding,
 // and the row bookkeeping table of the time-major-with-halos layout.
+#include <cuda_fp16.h>
+#include <string.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -22,7 +25,31 @@ __global__ void split_bf16_kernel(const float* __restrict__ x, long long rows, i
   }
 }
 
-// w [cout, cin, k] -> out [cout, k, planes, cin_pad]
+__global__ void to_f16_kernel(const float* __restrict__ x, long long rows, int cols, int ld_in, __half* __restrict__ out,
+                              int ld_out) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = static_cast<int>(i - r * cols);
+    const uint32_t pk = pack_f16x2(x[r * ld_in + c], 0.f);
+    out[r * ld_out + c] = __ushort_as_half(static_cast<unsigned short>(pk & 0xffffu));
+  }
+}
+
+int to_f16(const float* x, long long rows, int cols, int ld_in, void* out, int ld_out, cudaStream_t stream) {
+  const long long total = rows * cols;
+  if (total == 0) return 0;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  to_f16_kernel<<<grid, 256, 0, stream>>>(x, rows, cols, ld_in, static_cast<__half*>(out), ld_out);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// w [cout, cin, k] -> out [cout, k, planes, cin_pad].  F16: single-plane IEEE half instead of bf16 (the B operand of a
+// kind::f16 UMMA may be .f16 while A stays .bf16: three more mantissa bits for the weights at the same MMA rate).
+template <bool F16>
 __global__ void pack_conv_weight_kernel(const float* __restrict__ w, int cout, int cin, int k, int cin_pad,
                                         int planes, bf16* __restrict__ out) {
   const long long total = (long long)cout * k * cin_pad;
@@ -32,11 +59,40 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, int cout, i
     const int j = static_cast<int>((i / cin_pad) % k);
     const int o = static_cast<int>(i / ((long long)cin_pad * k));
     const float v = (c < cin) ? w[((long long)o * cin + c) * k + j] : 0.f;
-    const bf16 h = __float2bfloat16_rn(v);
     bf16* dst = out + ((long long)(o * k + j) * planes) * cin_pad + c;
+    if (F16) {
+      *reinterpret_cast<__half*>(dst) = __float2half_rn(v);
+      continue;
+    }
+    const bf16 h = __float2bfloat16_rn(v);
     dst[0] = h;
     if (planes == 2) dst[cin_pad] = __float2bfloat16_rn(v - __bfloat162float(h));
   }
+}
+
+// max |x| over n floats (engine creation: does a weight tensor fit the fp16 range?)
+__global__ void absmax_kernel(const float* __restrict__ x, long long n, unsigned* __restrict__ out) {
+  float m = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float a = fabsf(x[i]);
+    m = (a > m || a != a) ? a : m;         // NaN propagates
+  }
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));   // non-negative floats order like their bit patterns
+}
+
+int absmax_host(const float* x, long long n, float* result_host) {
+  unsigned* d = nullptr;
+  SVB_CUDA_OK(cudaMalloc(reinterpret_cast<void**>(&d), sizeof(unsigned)));
+  SVB_CUDA_OK(cudaMemset(d, 0, sizeof(unsigned)));
+  const int grid = static_cast<int>(std::min<long long>((n + 255) / 256, 148 * 8));
+  absmax_kernel<<<grid < 1 ? 1 : grid, 256>>>(x, n, d);
+  unsigned h = 0;
+  const cudaError_t e = cudaMemcpy(&h, d, sizeof(unsigned), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  SVB_CUDA_OK(e);
+  memcpy(result_host, &h, sizeof(float));
+  return 0;
 }
 
 // w [cout, cin, k] -> out [cout, planes, kpad] with K index j * cin + c (tap-major, channels contiguous): the layout of a
@@ -170,11 +226,13 @@ int split_bf16(const float* x, long long rows, int cols, int ld_in, bf16* out, i
 }
 
 int pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, int planes, bf16* out,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, int f16) {
   SVB_CHECK(cin_pad % 64 == 0 && cin_pad >= cin, "cin_pad must be a multiple of 64 and >= cin");
+  SVB_CHECK(!f16 || planes == 1, "fp16 weights are single plane");
   const long long total = (long long)cout * k * cin_pad;
   const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  pack_conv_weight_kernel<<<grid, 256, 0, stream>>>(w, cout, cin, k, cin_pad, planes, out);
+  if (f16) pack_conv_weight_kernel<true><<<grid, 256, 0, stream>>>(w, cout, cin, k, cin_pad, planes, out);
+  else pack_conv_weight_kernel<false><<<grid, 256, 0, stream>>>(w, cout, cin, k, cin_pad, planes, out);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;

@@ -24,7 +24,6 @@
 
 namespace svb {
 
-int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStream_t);
 int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);

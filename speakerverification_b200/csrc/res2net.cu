@@ -58,6 +58,7 @@ struct ChainParams {
   const float* bias[RC_STEPS];
   const float* scale[RC_STEPS];
   const float* shift[RC_STEPS];
+  int w_f16;                // single-plane weights are IEEE half (b_format = F16), see pack_conv_weight
   long long* dbg;           // optional phase timestamps of CTA 0 (SVB_CHAIN_DBG=1): [step][4] clock64 values
 };
 
@@ -307,7 +308,7 @@ res2net_chain_kernel(const __grid_constant__ ChainMaps tm, const ChainParams p) 
 }
 
 // ------------------------------------------------------------------ shared-memory resident variant (1 plane)
-// bf16 mode: the step input never leaves the SM.  The activation strip (400 rows x Cs channels, K-major,
+// 16-bit mode (single plane = IEEE half activations, fp16 or bf16 weights): the step input never leaves the SM.  The activation strip (400 rows x Cs channels, K-major,
 // 128B swizzle, one plane per 64-channel K chunk) stays in shared memory for the whole chain; the epilogue
 // writes x_{j+1} + y_j straight into it in the UMMA operand layout and the three dilated taps are the SAME
 // strip read through descriptors whose start address is shifted by +-d rows (d * 128 bytes).  A hardware
@@ -405,7 +406,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, CS);
+      const uint32_t idesc = umma_idesc_f16(128, CS, true, p.w_f16 != 0);      // activations of the 1-plane path are IEEE half
       uint32_t nitem = 0, nstep = 0, nsr = 0;
       for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++nitem) {
         for (int j = 1; j <= RC_STEPS; ++j, ++nstep) {
@@ -555,7 +556,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
             }
             uint32_t pk[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+            for (int i = 0; i < 16; ++i) pk[i] = pack_f16x2(v[2 * i], v[2 * i + 1]);
             // y_j -> R: own row into staging, then coalesced stores of the segment's output rows
 #pragma unroll
             for (int i = 0; i < 4; ++i)
@@ -595,7 +596,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
                 const uint32_t w[4] = {xrow[i].x, xrow[i].y, xrow[i].z, xrow[i].w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                  pk[4 * i + q] = pack_bf16x2(v[8 * i + 2 * q] + bf16_lo_f(w[q]), v[8 * i + 2 * q + 1] + bf16_hi_f(w[q]));
+                  pk[4 * i + q] = pack_f16x2(v[8 * i + 2 * q] + f16_lo_f(w[q]), v[8 * i + 2 * q + 1] + f16_hi_f(w[q]));
               }
               if (!all_mma_done) {
                 // the strip is single buffered: this step's MMAs of the later tiles read rows next to (and, through the
@@ -678,8 +679,9 @@ static int launch_chain(const ChainMaps& tm, const ChainParams& p, cudaStream_t 
 // with segments of res2net_seg_frames() frames; scratch: res2net_scratch_bytes(Cs, planes) bytes.
 int res2net_chain(const bf16* U, bf16* R, int C, int planes, long long rows, const bf16* const* w, const float* const* bias,
                   const float* const* scale, const float* const* shift, int dil, int halo, const void* items, int n_items,
-                  const void* utts, void* scratch, cudaStream_t stream) {
+                  const void* utts, void* scratch, cudaStream_t stream, int w_f16) {
   const int Cs = C / 8;
+  SVB_CHECK(!w_f16 || planes == 1, "fp16 weights are single plane");
   SVB_CHECK(Cs == 64 || Cs == 128, "the fused Res2Net chain supports C = 512 or 1024 (Res2Net chunks of 64 / 128 channels)");
   SVB_CHECK(dil >= 1 && dil <= RC_GUARD && halo >= dil && RC_SEG + 2 * RC_STEPS * dil <= RC_WIN, "unsupported dilation %d", dil);
   if (planes == 1) {
@@ -690,7 +692,7 @@ int res2net_chain(const bf16* U, bf16* R, int C, int planes, long long rows, con
     ChainParams q{};
     q.M = rows; q.n_items = n_items; q.items = static_cast<const SegItem*>(items);
     q.utts = static_cast<const UttRows*>(utts);
-    q.C = C; q.P = 1; q.dil = dil; q.halo = halo;
+    q.C = C; q.P = 1; q.dil = dil; q.halo = halo; q.w_f16 = w_f16;
     q.U = U; q.u_ld = C; q.R = R; q.r_ld = C;
     for (int j = 0; j < RC_STEPS; ++j) { q.bias[j] = bias[j]; q.scale[j] = scale[j]; q.shift[j] = shift[j]; }
     if (getenv("SVB_CHAIN_DBG") != nullptr) {

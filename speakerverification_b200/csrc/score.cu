@@ -20,7 +20,6 @@
 namespace svb {
 
 int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStream_t);
-int pack_conv_weight(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 
 // ---------------------------------------------------------------- cosine trials
 // emb [U, n, D] fp32; one warp per trial.
@@ -41,6 +40,40 @@ __global__ void cosine_trials_kernel(const float* __restrict__ emb, int n, int D
     }
     ab = warp_sum(ab); aa = warp_sum(aa); bb = warp_sum(bb);
     acc += fabsf(ab / (fmaxf(sqrtf(aa), eps) * fmaxf(sqrtf(bb), eps)));
+  }
+  if (lane == 0) out[tr] = acc / static_cast<float>(n);
+}
+
+// pnorm trials (utils.pnorm_similarity, src/utils.py:167-169): mean_i || a_i - b_i + eps ||_p over index-paired
+// crops (F.pairwise_distance adds eps to the DIFFERENCE), rows optionally L2-normalised first (test_normalize,
+// src/model.py:421-423).  pmode 0: general p (powf), 1: p = 1, 2: p = 2, 3: p = inf.  One warp per trial.
+__global__ void pnorm_trials_kernel(const float* __restrict__ emb, int n, int D, const int32_t* __restrict__ ia,
+                                    const int32_t* __restrict__ ib, long long ntrials, float pw, int pmode, float eps,
+                                    int normalize, float* __restrict__ out) {
+  const long long tr = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (tr >= ntrials) return;
+  const float* a = emb + static_cast<long long>(ia[tr]) * n * D;
+  const float* b = emb + static_cast<long long>(ib[tr]) * n * D;
+  float acc = 0.f;
+  for (int i = 0; i < n; ++i) {
+    float ia_ = 1.f, ib_ = 1.f;
+    if (normalize) {
+      float aa = 0.f, bb = 0.f;
+      for (int c = lane; c < D; c += 32) { const float x = a[i * D + c], y = b[i * D + c]; aa = fmaf(x, x, aa); bb = fmaf(y, y, bb); }
+      aa = warp_sum(aa); bb = warp_sum(bb);
+      ia_ = 1.f / fmaxf(sqrtf(aa), 1e-12f); ib_ = 1.f / fmaxf(sqrtf(bb), 1e-12f);
+    }
+    float s = 0.f;
+    for (int c = lane; c < D; c += 32) {
+      const float d = fabsf(a[i * D + c] * ia_ - b[i * D + c] * ib_ + eps);
+      if (pmode == 2) s = fmaf(d, d, s);
+      else if (pmode == 1) s += d;
+      else if (pmode == 3) s = fmaxf(s, d);
+      else s += powf(d, pw);
+    }
+    s = (pmode == 3) ? warp_max(s) : warp_sum(s);
+    acc += (pmode == 2) ? sqrtf(s) : ((pmode == 1 || pmode == 3) ? s : powf(s, 1.f / pw));
   }
   if (lane == 0) out[tr] = acc / static_cast<float>(n);
 }
@@ -747,6 +780,18 @@ int cosine_trials(const float* emb, int n, int D, const int32_t* ia, const int32
                   cudaStream_t stream) {
   if (ntrials == 0) return 0;
   cosine_trials_kernel<<<static_cast<int>((ntrials + 7) / 8), 256, 0, stream>>>(emb, n, D, ia, ib, ntrials, 1e-5f, out);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int pnorm_trials(const float* emb, int n, int D, const int32_t* ia, const int32_t* ib, long long ntrials, float pw,
+                 float eps, int normalize, float* out, cudaStream_t stream) {
+  if (ntrials == 0) return 0;
+  SVB_CHECK(pw > 0.f, "pnorm needs p > 0 (got %g)", static_cast<double>(pw));
+  const int pmode = isinf(pw) ? 3 : (pw == 2.f ? 2 : (pw == 1.f ? 1 : 0));
+  pnorm_trials_kernel<<<static_cast<int>((ntrials + 7) / 8), 256, 0, stream>>>(emb, n, D, ia, ib, ntrials, pw, pmode, eps,
+                                                                             normalize, out);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;

@@ -43,7 +43,10 @@ struct PcmSeg { long long src_off, dst_off; int src_len, dst_len; };
 
 // ------------------------------------------------------------------ tensor-core GEMM
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
-enum { OUT_BF16 = 0, OUT_BF16_HILO = 1, OUT_F32 = 2 };
+// Activation storage: two bf16 planes hi|lo (fp32-grade mode), ONE plane of IEEE half (16-bit mode: OUT_F16; fp16
+// operands run at the bf16 tensor-core rate with 3 more mantissa bits -- the score deviation of the 16-bit mode drops
+// from ~2e-3 to ~2e-4), fp32, or one plane of bf16 (generic gemm_tc path, RawNet2).
+enum { OUT_BF16 = 0, OUT_BF16_HILO = 1, OUT_F32 = 2, OUT_F16 = 3 };
 enum { STORE_ALL = 0, STORE_MIRROR = 1 };
 
 struct GemmOperands {
@@ -52,6 +55,8 @@ struct GemmOperands {
   const bf16* a2; int lda2; int a2_cols; int a2_kc;
   int a_plane_cols;                            // column distance hi-plane -> lo-plane in A (and A2)
   const bf16* w; int w_rows; int w_cols;       // packed weights [N, taps*planes*kc*64]
+  int w_f16;                                   // weights are IEEE half (single plane) instead of bf16
+  int a_f16;                                   // A (and A2, add_src) are IEEE half (single plane) instead of bf16
 };
 
 struct GemmParams {
@@ -80,6 +85,7 @@ struct GemmParams {
   long long* colsum; long long* colsq; int stats_ld;
   // A planes stacked by rows (K-packed block 0): the lo plane of row r is row r + a_plane_rows of the same map
   int a_plane_rows;
+  int w_f16, a_f16;      // filled by launch_gemm from GemmOperands (b_format / a_format of the UMMA)
 };
 
 // RawNet2 GEMMs (rawnet_gemm.cu): fixed-length utterances, rows [utt][1 zero | T | 1 zero]
@@ -94,6 +100,13 @@ struct RnGemmParams {
   bf16* out; int out_ld, out_planes, out_plane_cols;
   bf16* out2; int out2_ld, out2_planes, out2_plane_cols;
 };
+
+// Conv1d weight [cout, cin, k] fp32 -> packed [cout, k, planes, cin_pad] bf16 hi(|lo) planes, or (f16 != 0, one plane)
+// IEEE half: weights are the B operand of kind::f16 UMMAs, whose a_format / b_format are independent, so bf16
+// activations x fp16 weights run at the bf16 rate with 11 instead of 8 significant weight bits.
+int pack_conv_weight(const float* w, int cout, int cin, int k, int cin_pad, int planes, bf16* out, cudaStream_t stream,
+                     int f16 = 0);
+int absmax_host(const float* x, long long n, float* result_host);   // synchronous; engine creation only
 
 // 2D bf16 row-major matrix [rows, ld] exposing `cols` columns as a TMA map; box = [64 cols, box_rows], 128B swizzle.
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);

@@ -1,6 +1,7 @@
 // Thin inline-PTX wrappers for the sm_100a features the kernels use:
 // mbarrier, TMA (cp.async.bulk.tensor), tcgen05 (alloc / mma / commit / ld) and fences.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -245,6 +246,12 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
          (static_cast<uint32_t>(m >> 4) << 24);
 }
 
+// Same with the operand formats chosen per operand (F32F16Format: 0 = F16, 1 = BF16).
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int m, int n, bool a_f16, bool b_f16) {
+  return (1u << 4) | ((a_f16 ? 0u : 1u) << 7) | ((b_f16 ? 0u : 1u) << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(m >> 4) << 24);
+}
+
 // ---------------------------------------------------------------- misc
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -252,6 +259,25 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo_f(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi_f(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+// IEEE half pairs: the storage format of single-plane ("16-bit mode") activations.  One F2FP to pack two values
+// (saturating at +-65504: no inf is ever stored), one HADD2.F32 to decode one -- the same instruction counts as bf16.
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ float f16_lo_f(uint32_t u) {
+  return __half2float(__ushort_as_half(static_cast<unsigned short>(u & 0xffffu)));
+}
+__device__ __forceinline__ float f16_hi_f(uint32_t u) {
+  return __half2float(__ushort_as_half(static_cast<unsigned short>(u >> 16)));
+}
+// 16-bit pair helpers selected by format (F16: IEEE half, else bf16)
+template <bool F16> __device__ __forceinline__ uint32_t pack16x2(float lo, float hi) {
+  return F16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi);
+}
+template <bool F16> __device__ __forceinline__ float lo16_f(uint32_t u) { return F16 ? f16_lo_f(u) : bf16_lo_f(u); }
+template <bool F16> __device__ __forceinline__ float hi16_f(uint32_t u) { return F16 ? f16_hi_f(u) : bf16_hi_f(u); }
 
 // GELU(x) = x * Phi(x) with the exact-erf definition (nn.GELU() default), evaluated branch-free as
 //   relu(x) - |x| * h,   h = 0.5 * erfc(|x| / sqrt(2)) = 0.5 * t * P(t) * exp(-x^2 / 2),  t = 1 / (1 + p |x| / sqrt 2)

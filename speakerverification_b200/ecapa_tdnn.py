@@ -10,7 +10,7 @@ import torch
 import torch.nn as nn
 
 from . import _native as nv
-from .engine import EcapaEngine, Frontend
+from .engine import EcapaEngine, Frontend, normalize_precision
 
 
 class _Conv(nn.Module):          # key: <p>.conv.{weight,bias}          (layers/cnn.py Conv1d wrapper)
@@ -81,7 +81,7 @@ class ECAPA_TDNN(nn.Module):
             # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
             # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
             precision = kwargs.get("svb_precision") or "fp32"
-        self.precision = precision
+        self.precision = normalize_precision(precision)
         C = channels
         self.blocks = nn.ModuleList([_TDNN(input_size, C[0], kernel_sizes[0])])
         for i in range(1, len(C) - 1):
@@ -124,7 +124,7 @@ class ECAPA_TDNN(nn.Module):
         return self._engine
 
     def set_precision(self, precision):
-        assert precision in ("bf16", "fp32")
+        precision = normalize_precision(precision)
         if precision != self.precision:
             self.precision, self._engine = precision, None
 

@@ -102,13 +102,24 @@ class BatchPlan:
             self.handle = None
 
 
+def normalize_precision(precision):
+    """'fp32' = split-bf16 operands, 3 tensor-core passes (fp32-grade parity mode); 'f16' = the 16-bit throughput mode:
+    IEEE-half activations and weights, fp32 accumulation and epilogues (same tcgen05 kind::f16 rate as bf16, 11 instead
+    of 8 significant bits).  'bf16' is accepted as a name for the 16-bit mode (BASELINE.json calls the config that)."""
+    if precision in ("f16", "fp16", "bf16", "half"):
+        return "f16"
+    if precision == "fp32":
+        return "fp32"
+    raise ValueError("precision must be 'fp32' or 'f16' (alias 'bf16'); got %r" % (precision,))
+
+
 class EcapaEngine:
     """Packed ECAPA-TDNN weights + forward (svb_ecapa_*).  `state` maps reference state-dict names
     (without the '__S__.' prefix) to fp32 CUDA tensors."""
 
     def __init__(self, state, channels, n_mels, n_out, frontend, attention_channels=128, se_channels=128,
-                 res2net_scale=8, kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), precision="bf16"):
-        assert precision in ("bf16", "fp32")
+                 res2net_scale=8, kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), precision="f16"):
+        precision = normalize_precision(precision)
         C = int(channels[0])
         if list(channels[:4]) != [C] * 4 or int(channels[4]) != 3 * C:
             raise ValueError("ECAPA channels must be [C, C, C, C, 3C]; got %s" % (list(channels),))
@@ -215,8 +226,11 @@ class EcapaEngine:
         wav = wav.contiguous()
         return self.forward_flat(wav.view(-1), [wav.shape[1]] * wav.shape[0], l2norm=l2norm, out=out)
 
-    def stage(self, plan, name, cols, dtype=torch.bfloat16, planes=1):
-        """View of a named intermediate inside the workspace: [rows, planes*cols] (tests, profiling)."""
+    def stage(self, plan, name, cols, dtype=None, planes=1):
+        """View of a named intermediate inside the workspace: [rows, planes*cols] (tests, profiling); bf16 hi|lo planes
+        in fp32 mode, one plane of IEEE half in the 16-bit mode."""
+        if dtype is None:
+            dtype = torch.bfloat16 if planes == 2 else torch.float16
         off = nv.lib().svb_ecapa_ws_offset(self.handle, plan.handle, name.encode())
         if off < 0:
             raise KeyError(name)

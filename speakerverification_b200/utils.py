@@ -42,6 +42,17 @@ def cosine_trials(emb, idx_a, idx_b):
 
 
 @_on_arg_device
+def pnorm_trials(emb, idx_a, idx_b, p=2, normalize=False, eps=1e-6):
+    """emb [U, n, D] CUDA fp32 -> [trials] fp32: mean_i ||a_i - b_i + eps||_p (utils.pnorm_similarity, src/utils.py:167-169),
+    rows L2-normalised first when `normalize` (test_normalize, src/model.py:421-423)."""
+    U, n, D = emb.shape
+    out = torch.empty(idx_a.numel(), dtype=torch.float32, device=emb.device)
+    nv.check(nv.lib().svb_pnorm_trials(nv.ptr(emb), n, D, nv.ptr(idx_a), nv.ptr(idx_b), idx_a.numel(), float(p), float(eps),
+                                       int(normalize), nv.ptr(out), nv.stream_ptr()))
+    return out
+
+
+@_on_arg_device
 def mean_embeddings(emb, normalize):
     U, n, D = emb.shape
     out = torch.empty((U, D), dtype=torch.float32, device=emb.device)
@@ -90,9 +101,12 @@ def enrol_nearest(query, bank, topk=3, eps=1e-6):
     return dist, td, ti
 
 
-def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200, normalize=True):
+def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200, normalize=True, p=2):
     """All trials at once.  emb [U, n, D] (raw crop embeddings); returns a CUDA fp32 vector.
-    'cosine' = utils.cosine_similarity per trial; 'norm' = utils.ZT_norm_similarity(top)."""
+    'cosine' = utils.cosine_similarity per trial; 'norm' = utils.ZT_norm_similarity(top); 'pnorm' =
+    utils.pnorm_similarity(p) (the three branches of src/model.py:433-444)."""
+    if scoring_mode == "pnorm":
+        return pnorm_trials(emb, idx_a, idx_b, p=p, normalize=normalize)
     if scoring_mode == "cosine":
         return cosine_trials(emb, idx_a, idx_b)      # cosine is scale invariant: normalisation is a no-op
     if scoring_mode == "norm":
@@ -101,7 +115,8 @@ def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200
         em = mean_embeddings(emb, normalize)
         mu, sg = asnorm_stats(em, _dev(cohorts, emb.device), top)
         return asnorm_trials(em, idx_a, idx_b, mu, sg)
-    raise NotImplementedError("scoring_mode %r (only 'cosine' and 'norm' are on the hot path)" % (scoring_mode,))
+    raise ValueError("scoring_mode %r: the reference knows 'cosine', 'norm' and 'pnorm' (src/model.py:433-444)"
+                     % (scoring_mode,))
 
 
 # ------------------------------------------------------------------ per-trial reference signatures
@@ -121,6 +136,14 @@ def ZT_norm_similarity(ref, com, cohorts, top=-1):
     return float(asnorm_trials(em, i0, i0 + 1, mu, sg).item())
 
 
+def pnorm_similarity(ref, com, p=2, **kwargs):
+    """src/utils.py:167-169: np.mean(F.pairwise_distance(ref, com, p=p, eps=1e-06, keepdim=True))."""
+    ref, com = _dev(ref), _dev(com)
+    emb = torch.stack([ref.view(-1, ref.shape[-1]), com.view(-1, com.shape[-1])])
+    i0 = torch.zeros(1, dtype=torch.int32, device=emb.device)
+    return float(pnorm_trials(emb, i0, i0 + 1, p=p, normalize=False).item())
+
+
 def similarity_measure(method="cosine", ref=None, com=None, *args, **kwargs):
     """Same dispatch as src/utils.py:126-132.  Unlike the reference, extra positionals are accepted,
     so the call site src/model.py:434-438 (zt_norm with the cohort passed positionally) works."""
@@ -128,7 +151,9 @@ def similarity_measure(method="cosine", ref=None, com=None, *args, **kwargs):
         return cosine_similarity(ref, com, **kwargs)
     if method == "zt_norm":
         return ZT_norm_similarity(ref, com, *args, **kwargs)
-    raise NotImplementedError("similarity method %r is not on the accelerated path" % (method,))
+    if method == "pnorm":
+        return pnorm_similarity(ref, com, **kwargs)
+    return None      # src/utils.py:126-132 falls through (returns None) for an unknown method
 
 
 # ------------------------------------------------------------------ metrics (host, fp64)

@@ -103,29 +103,43 @@ def test_evaluate_from_list_fp32(workdir, golden_c512):
     assert devn <= 5e-3
 
 
-def test_evaluate_from_list_bf16_c1024(workdir1024, golden_c1024):
-    """BASELINE.json configs[1] (C=1024, bf16): trial scores agree with the reference fp32 path to <= 2e-3."""
+def test_evaluate_from_list_f16_c1024(workdir1024, golden_c1024):
+    """BASELINE.json configs[1] (C=1024, 16-bit mode = what bench.py times): trial scores agree with the reference fp32
+    path to <= 2e-3 (north star) -- asserted at 5e-4, the CPU model of the data flow says 2.0e-4 -- and EER / minDCF
+    equal the reference's at four decimals.  (The decisive score gap at the EER threshold of this list is 7e-5, trials
+    936 / 501: bf16 operands, deviation ~3e-4 there, flipped the EER by one ROC step; see profiles/r02_precision.md.)"""
     from speakerverification_b200 import utils as U
-    net, h, args = _handle(workdir1024, "bf16")
+    net, h, args = _handle(workdir1024, "f16")
     sc, lab, _ = h.evaluateFromList(workdir1024["trials"], distributed=False,
                                     dataloader_options=args["dataloader_options"],
                                     cohorts_path=workdir1024["cohorts"], num_eval=2, scoring_mode="cosine")
     d = np.abs(np.asarray(sc) - golden_c1024["scores_cos"])
-    print("bf16 C=1024 list-API cosine score dev: max", d.max(), "mean", d.mean())
-    assert d.max() <= 2e-3
+    print("f16 C=1024 list-API cosine score dev: max", d.max(), "mean", d.mean())
+    assert d.max() <= 5e-4
+    # EER / minDCF at the benchmark's precision equal the reference's at four decimals (north star)
     res = U.tuneThresholdfromScore(sc, lab, [1, 0.1])
-    print("bf16 C=1024 EER", res["roc"][1], "reference", float(golden_c1024["eer/scores_cos"]))
+    fn, fp, th = U.ComputeErrorRates(sc, lab)
+    dcf, _ = U.ComputeMinDcf(fn, fp, th, 0.05, 1, 1)
+    print("f16 C=1024 EER", res["roc"][1], "reference", float(golden_c1024["eer/scores_cos"]),
+          "minDCF", dcf, "reference", float(golden_c1024["mindcf/scores_cos"]))
+    assert round(float(res["roc"][1]), 4) == round(float(golden_c1024["eer/scores_cos"]), 4)
+    assert round(dcf, 4) == round(float(golden_c1024["mindcf/scores_cos"]), 4)
 
 
-def test_evaluate_from_list_bf16_c512(workdir, golden_c512):
-    """C=512 in bf16 sits at the edge of the budget (1.9e-3 .. 2.4e-3 for bf16 operands
-    with fp32 accumulation/epilogues); asserted at 2.5e-3 and reported."""
-    net, h, args = _handle(workdir, "bf16")
+def test_evaluate_from_list_f16_c512(workdir, golden_c512):
+    """C=512 in the 16-bit mode: the north-star score tolerance with margin, plus EER / minDCF at four decimals."""
+    from speakerverification_b200 import utils as U
+    net, h, args = _handle(workdir, "f16")
     sc, lab, _ = h.evaluateFromList(workdir["trials"], distributed=False, dataloader_options=args["dataloader_options"],
                                     cohorts_path=workdir["cohorts"], num_eval=2, scoring_mode="cosine")
     d = np.abs(np.asarray(sc) - golden_c512["scores_cos"])
-    print("bf16 C=512 list-API cosine score dev: max", d.max(), "mean", d.mean())
-    assert d.max() <= 2.5e-3
+    print("f16 C=512 list-API cosine score dev: max", d.max(), "mean", d.mean())
+    assert d.max() <= 5e-4
+    res = U.tuneThresholdfromScore(sc, lab, [1, 0.1])
+    fn, fp, th = U.ComputeErrorRates(sc, lab)
+    dcf, _ = U.ComputeMinDcf(fn, fp, th, 0.05, 1, 1)
+    assert round(float(res["roc"][1]), 4) == round(float(golden_c512["eer/scores_cos"]), 4)
+    assert round(dcf, 4) == round(float(golden_c512["mindcf/scores_cos"]), 4)
 
 
 def test_embed_utterance_prepare_and_checkpoint(workdir, golden_c512):

@@ -56,10 +56,11 @@ def test_fbank_matches_oracle():
 
 
 # fp32 mode: BASELINE tolerances (cos >= 0.9999, scores <= 1e-4) on ALL 2016 single-crop pairs.
-# bf16 mode: the <= 2e-3 tolerance is stated on trial scores and is asserted on the reference's own
-# trial list in tests/test_api_gpu.py; the all-pairs single-crop maximum asserted here (3e-3) is a
-# stricter-population diagnostic (measured 2.15e-3; the fp32-epilogue bf16 design point).
-@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("bf16", 0.9995, 3e-3)])
+# 16-bit mode (IEEE-half activations and weights, fp32 accumulation / epilogues; BASELINE's "bf16" config): the north
+# star's <= 2e-3 score tolerance with a 3x margin on ALL 2016 single-crop pairs (a stricter population than the
+# 1000-trial list of tests/test_api_gpu.py).  CPU model of the data flow (tools/bf16_ablation.py, profiles/
+# r02_precision.md): 2.7e-4 (C=512), 2.4e-4 (C=1024); bf16 operands gave 1.9e-3 / 2.1e-3 (round 1: 2.15e-3 measured).
+@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("f16", 0.99995, 6e-4)])
 def test_ecapa_c512_matches_reference(golden_c512, precision, cos_min, tol):
     from oracle import synth
     from speakerverification_b200.engine import EcapaEngine
@@ -103,20 +104,20 @@ def test_ecapa_stages_fp32(golden_c512):
     np.testing.assert_allclose(stage("mfa", 1536)[::16], golden_c512["stage/mfa"], atol=3e-4, rtol=1e-4)
 
 
-def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
+def test_ecapa_c1024_f16_and_ragged(golden_c1024):
     from oracle import ecapa_oracle as eo, synth
     from speakerverification_b200.engine import EcapaEngine
     waves, _ = synth.utterance_set(16, 4, L + 1)
     sd, state = _state(CH1024, golden_c1024)
-    eng = EcapaEngine(state, CH1024, 80, 192, _frontend(), precision="bf16")
+    eng = EcapaEngine(state, CH1024, 80, 192, _frontend(), precision="f16")
     emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda()).cpu().numpy()
     ref = golden_c1024["emb_batch"]
     en = emb / np.linalg.norm(emb, axis=1, keepdims=True)
     rn = ref / np.linalg.norm(ref, axis=1, keepdims=True)
-    assert (en * rn).sum(1).min() > 0.9995
+    assert (en * rn).sum(1).min() > 0.99995
     dev = np.abs(en @ en.T - rn @ rn.T).max()
-    print("C=1024 bf16: min cos", (en * rn).sum(1).min(), "max all-pairs score dev", dev)
-    assert dev <= 3e-3
+    print("C=1024 f16: min cos", (en * rn).sum(1).min(), "max all-pairs score dev", dev)
+    assert dev <= 6e-4
     # ragged batch: every utterance keeps its own length (no padding), checked against the oracle
     lens = [16000, 48000, 23456, 40000]
     flat = torch.from_numpy(np.concatenate([waves[i, :n] for i, n in enumerate(lens)])).cuda()
@@ -124,7 +125,7 @@ def test_ecapa_c1024_bf16_and_ragged(golden_c1024):
     for i, n in enumerate(lens):
         want = eo.embed(np.stack([waves[i, :n], waves[i, :n]]), sd).numpy()[0]
         c = float((got[i] * want).sum() / np.linalg.norm(got[i]) / np.linalg.norm(want))
-        assert c > 0.9995, (i, c)
+        assert c > 0.9999, (i, c)
 
 
 def test_extreme_lengths_fp32(golden_c512):

@@ -128,3 +128,25 @@ def test_topk_sampled_prefilter_adversarial_rows(N, K):
     scale = np.maximum(1.0, np.abs(S).max(1))
     assert (np.abs(mu.cpu().numpy() - S.mean(1)) <= 4e-6 * scale).all(), (mu.cpu().numpy(), S.mean(1))
     assert (np.abs(sg.cpu().numpy() - S.std(1)) <= 4e-6 * scale).all(), (sg.cpu().numpy(), S.std(1))
+
+
+def test_pnorm_trials_match_reference(golden_c512):
+    """'pnorm' scoring (utils.pnorm_similarity, src/utils.py:167-169; the third branch of src/model.py:433-444) for all
+    trials at once against the reference function's own outputs (tests/golden/pnorm.npz), p = 2 (the call sites'
+    value), 1 and 3, normalised and raw rows, plus the per-trial reference signatures."""
+    import os
+    from speakerverification_b200 import utils as U
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pnorm.npz"))
+    emb = torch.from_numpy(golden_c512["emb_list"]).cuda()
+    ia, ib = torch.from_numpy(g["ti"]).cuda(), torch.from_numpy(g["tj"]).cuda()
+    for p in (2, 1, 3):
+        got = U.score_trials(emb, ia, ib, "pnorm", normalize=True, p=p).cpu().numpy()
+        ref = g["scores_p%d" % p]
+        assert np.abs(got - ref).max() <= 1e-5 * max(1.0, float(ref.max())), (p, np.abs(got - ref).max())
+    raw = U.pnorm_trials(emb, ia, ib, p=2, normalize=False).cpu().numpy()
+    assert np.abs(raw - g["scores_p2_raw"]).max() <= 1e-5 * float(g["scores_p2_raw"].max())
+    en = torch.nn.functional.normalize(emb, dim=2)
+    s = U.similarity_measure("pnorm", en[int(g["ti"][0])], en[int(g["tj"][0])], p=2)
+    assert abs(s - float(g["scores_p2"][0])) <= 1e-5
+    assert abs(U.pnorm_similarity(en[int(g["ti"][1])].cpu(), en[int(g["tj"][1])].cpu()) - float(g["scores_p2"][1])) <= 1e-5
+    assert U.similarity_measure("no_such_method", en[0], en[1]) is None        # src/utils.py:126-132 falls through
