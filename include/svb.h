@@ -168,7 +168,11 @@ typedef struct SvbEcapaCfg {
   int32_t channels;        /* C (channels[0..3]); channels[4] must be 3*C */
   int32_t n_mels, n_out, attention_channels, se_channels, res2net_scale;
   int32_t kernel_sizes[5], dilations[5];
-  int32_t fp32_mode;       /* 0: bf16 tensor-core operands; 1: split-bf16 (fp32-grade parity mode) */
+  int32_t fp32_mode;       /* 0: 16-bit mode (IEEE-half activations and weights, fp32 accumulation and epilogues);
+                            * 1: split-bf16 (fp32-grade parity mode, 3 tensor-core passes) */
+  int32_t input_norm;      /* input_norm=True of src/models/ECAPA_TDNN.py:406-408,477-478 (the ECAPA branch of the
+                            * Raw3_ECAPA hybrid, src/models/Raw3_ECAPA.py:21-24): InstanceNorm1d(n_mels, affine) after the
+                            * log / mean normalisation; needs the tensors "instance_norm.weight" / ".bias" */
 } SvbEcapaCfg;
 int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n,
                      SvbEcapa** out);

@@ -79,6 +79,13 @@ def log_cmn(mel):
 
 
 # ------------------------------------------------------------------ encoder
+def input_instance_norm(x, weight, bias, eps=1e-5):
+    """nn.InstanceNorm1d(affine=True, track_running_stats=False) on [B, C, T] (src/models/ECAPA_TDNN.py:406-408)."""
+    m = x.mean(dim=2, keepdim=True)
+    v = ((x - m) ** 2).mean(dim=2, keepdim=True)
+    return (x - m) / torch.sqrt(v + eps) * weight[None, :, None] + bias[None, :, None]
+
+
 def _conv_same_reflect(x, w, b, dilation):
     # src/models/layers/cnn.py:104-108,157 + get_padding_elem :787-805 (stride 1)
     k = w.shape[-1]
@@ -157,6 +164,10 @@ def ecapa_forward(feat, sd, dilations=(1, 2, 3, 4, 1), prefix="__S__.", stages=N
     """src/models/ECAPA_TDNN.py:460-502: [B, n_mels, T] power-mel -> [B, nOut]."""
     sd = {k: torch.as_tensor(v) for k, v in sd.items()}
     x = log_cmn(feat)
+    if prefix + "instance_norm.weight" in sd:
+        # input_norm=True (src/models/ECAPA_TDNN.py:406-408,477-478): nn.InstanceNorm1d(n_mels, affine=True, eps=1e-5,
+        # track_running_stats=False) = per (utterance, mel) biased statistics over time
+        x = input_instance_norm(x, sd[prefix + "instance_norm.weight"], sd[prefix + "instance_norm.bias"])
     if stages is not None:
         stages["logmel"] = x
     xl = []

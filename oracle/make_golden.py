@@ -121,6 +121,37 @@ def make(channels, n_out, tag, n_spk=16, per_spk=4, n_trials=1000, n_cohort=300,
     print("wrote", path, os.path.getsize(path) // 1024, "KiB")
 
 
+def make_inorm(tag="cfg1_c512_inorm", channels=(512, 512, 512, 512, 1536), n_out=192):
+    """ECAPA-TDNN with input_norm=True (nn.InstanceNorm1d(n_mels, affine=True) after the log / mean normalisation,
+    src/models/ECAPA_TDNN.py:406-408,477-478) -- the configuration the Raw3_ECAPA hybrid builds its ECAPA branch
+    with (src/models/Raw3_ECAPA.py:21-24).  The affine parameters are seeded non-trivial values."""
+    ref_loader.load()
+    net, handle, args = ref_loader.build(list(channels), n_out, input_norm=True)
+    sd = synth.ecapa_state_dict(list(channels), n_out, seed=1234)
+    rng = np.random.default_rng(4321)
+    sd["__S__.instance_norm.weight"] = (1.0 + 0.3 * rng.standard_normal(80)).astype(np.float32)
+    sd["__S__.instance_norm.bias"] = (0.2 * rng.standard_normal(80)).astype(np.float32)
+    _load_weights(net, sd)
+    waves, spk = synth.utterance_set(16, 4, L + 1)
+    bn = _calibrate_bn(net, waves[:, :L])
+    out = {"bn/" + k: v for k, v in bn.items()}
+    out["instance_norm.weight"], out["instance_norm.bias"] = sd["__S__.instance_norm.weight"], sd["__S__.instance_norm.bias"]
+    store = {}
+    hooks = _stage_hooks(net, store)
+    with torch.no_grad():
+        emb = net(torch.from_numpy(waves[:, :L]))
+    for h in hooks:
+        h.remove()
+    out["emb_batch"] = emb.numpy()
+    out["stage/block0"] = store["block0"][0, ::16].numpy()
+    _, ref_utils = ref_loader.load()
+    lab, ti, tj = synth.trial_list(spk, 1000)
+    out["scores_cos"] = np.asarray([float(ref_utils.cosine_similarity(emb[i:i + 1], emb[j:j + 1])) for i, j in zip(ti, tj)])
+    path = os.path.join(GOLD, "%s.npz" % tag)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB")
+
+
 def make_rawnet(tag="cfg4_rawnet2", n_spk=4, per_spk=4, n_out=512, L4=64000):
     """RawNet2_custom (sinc + GRU, 4 s crops): embeddings through the reference's
     SpeakerEncoder(features='raw') and strided per-stage dumps for utterance 0."""
@@ -169,3 +200,5 @@ if __name__ == "__main__":
         make([1024, 1024, 1024, 1024, 3072], 192, "cfg2_c1024")
     if "cfg4" in which:
         make_rawnet()
+    if "cfg1i" in which:
+        make_inorm()

@@ -51,9 +51,10 @@ def load():
 
 
 def reference_args(channels, n_out, sentence_len=3.0, features="melspectrogram",
-                   model_name="ECAPA_TDNN"):
-    """Config dict the reference constructors need."""
-    return dict(
+                   model_name="ECAPA_TDNN", **extra):
+    """Config dict the reference constructors need; `extra` keys (e.g. input_norm=True) reach
+    the encoder's MainModel(**kwargs) like any other YAML key."""
+    return dict(extra, 
         device="cpu", gpu=0, seed=0, save_folder="/tmp/svb_ref",
         model={"name": model_name, "nOut": n_out}, channels=list(channels),
         criterion={"name": "AAmSoftmaxAP", "margin": 0.2, "scale": 30}, nClasses=10,

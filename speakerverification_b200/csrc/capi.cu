@@ -16,7 +16,7 @@ struct Fbank; struct Batch; struct Ecapa;
 int fbank_create(const float*, int, int, int, const float*, int, int, float, float, Fbank**);
 void fbank_destroy(Fbank*);
 int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
-                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
+                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t, const float*, const float*, float, float*);
 int batch_create(const int64_t*, const int32_t*, int, int, int, Batch**);
 int batch_create_into(const int64_t*, const int32_t*, int, int, int, void*, void*, size_t, cudaStream_t, Batch**);
 size_t batch_blob_bytes(const int32_t*, int, int, int);
@@ -29,7 +29,7 @@ int batch_B(const Batch*);
 int batch_halo(const Batch*);
 const void* batch_utt_tab(const Batch*);
 const int32_t* batch_tile_tab(const Batch*);
-int ecapa_create(int, int, int, int, int, int, const int*, const int*, int, const char* const*, const void* const*, int,
+int ecapa_create(int, int, int, int, int, int, const int*, const int*, int, int, const char* const*, const void* const*, int,
                  Ecapa**);
 void ecapa_destroy(Ecapa*);
 int ecapa_halo(const Ecapa*);
@@ -234,7 +234,7 @@ int svb_fbank_forward(const SvbFbank* f, const SvbBatch* b, const float* wav, vo
   return fbank_forward(reinterpret_cast<const Fbank*>(f), wav, batch_utt_tab(bt), batch_tile_tab(bt), batch_B(bt),
                        batch_tiles(bt), reinterpret_cast<const RowMeta*>(batch_row_meta(bt)), batch_rows(bt),
                        batch_halo(bt), logmel_ws, tile_sums_ws, mean_ws, static_cast<bf16*>(out), out_ld, plane_cols,
-                       planes, 0, static_cast<cudaStream_t>(stream));
+                       planes, 0, static_cast<cudaStream_t>(stream), nullptr, nullptr, 0.f, nullptr);
 }
 
 int svb_fbank_power(const SvbFbank* f, const SvbBatch* b, const float* wav, float* mel_rows, float* tile_sums_ws,
@@ -245,14 +245,14 @@ int svb_fbank_power(const SvbFbank* f, const SvbBatch* b, const float* wav, floa
   return fbank_forward(reinterpret_cast<const Fbank*>(f), wav, batch_utt_tab(bt), batch_tile_tab(bt), batch_B(bt),
                        batch_tiles(bt), reinterpret_cast<const RowMeta*>(batch_row_meta(bt)), batch_rows(bt),
                        batch_halo(bt), mel_rows, tile_sums_ws, nullptr, nullptr, 0, 0, 0, 1,
-                       static_cast<cudaStream_t>(stream));
+                       static_cast<cudaStream_t>(stream), nullptr, nullptr, 0.f, nullptr);
 }
 
 int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n, SvbEcapa** out) {
   if (check_device()) return -1;
   SVB_CHECK(cfg && names && ptrs && out, "null argument");
   return ecapa_create(cfg->channels, cfg->n_mels, cfg->n_out, cfg->attention_channels, cfg->se_channels,
-                      cfg->res2net_scale, cfg->kernel_sizes, cfg->dilations, cfg->fp32_mode, names, ptrs, n,
+                      cfg->res2net_scale, cfg->kernel_sizes, cfg->dilations, cfg->fp32_mode, cfg->input_norm, names, ptrs, n,
                       reinterpret_cast<Ecapa**>(out));
 }
 void svb_ecapa_destroy(SvbEcapa* e) { ecapa_destroy(reinterpret_cast<Ecapa*>(e)); }

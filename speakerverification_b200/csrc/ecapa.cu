@@ -18,9 +18,9 @@ struct Fbank;
 int fbank_n_mels(const Fbank*);
 int fbank_hop(const Fbank*);
 int fbank_forward(const Fbank*, const float*, const void*, const int32_t*, int, int, const RowMeta*, long long, int,
-                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t);
+                  float*, float*, float*, bf16*, int, int, int, int, cudaStream_t, const float*, const float*, float, float*);
 int fbank_from_power(const Fbank*, const float*, const void*, int, const RowMeta*, long long, int, float*, float*, bf16*,
-                     int, int, int, cudaStream_t);
+                     int, int, int, cudaStream_t, const float*, const float*, float, float*);
 int pack_conv_weight_kpacked(const float*, int, int, int, int, int, bf16*, cudaStream_t);
 int fold_bn(const float*, const float*, const float*, const float*, int, float, float*, float*, cudaStream_t);
 int col_stats(const bf16*, int, int, int, const void*, int, int, int, float, float*, float*, int, cudaStream_t);
@@ -217,6 +217,7 @@ struct Ecapa {
   float *asp_bound = nullptr;  // per-channel bound of the asp.conv logits in log2 units, or nullptr (asp_fused.cu, FIXMAX)
   float *asp_w = nullptr;  // asp.tdnn conv weight fp32 [att, 9C] (the [mean;std] columns feed the per-utterance bias)
   float *aspbn_scale = nullptr, *aspbn_shift = nullptr, *fc_w = nullptr, *fc_b = nullptr;
+  float *inorm_w = nullptr, *inorm_b = nullptr;   // input_norm=True: InstanceNorm1d affine parameters [n_mels]
   std::vector<void*> owned;
 };
 
@@ -293,7 +294,7 @@ static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int c
 }
 
 int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scale, const int* kernel_sizes,
-                 const int* dilations, int fp32_mode, const char* const* names, const void* const* ptrs, int n,
+                 const int* dilations, int fp32_mode, int input_norm, const char* const* names, const void* const* ptrs, int n,
                  Ecapa** out) {
   SVB_CHECK(C % 512 == 0, "channels must be a multiple of 512 (Res2Net chunks are tiled in 64-column K blocks); got %d", C);
   SVB_CHECK(res2_scale == 8 && att == 128 && se_ch % 4 == 0 && n_mels <= MEL_PLANE,
@@ -339,6 +340,11 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
     if (!w1 || !b1 || !w2 || !b2) { rc = -1; break; }
     e->se_w1[i] = dcopy(e, w1, static_cast<size_t>(se_ch) * C); e->se_b1[i] = dcopy(e, b1, se_ch);
     e->se_w2[i] = dcopy(e, w2, static_cast<size_t>(C) * se_ch); e->se_b2[i] = dcopy(e, b2, C);
+  }
+  if (!rc && input_norm) {
+    const float *iw = find(tm, "instance_norm.weight"), *ib = find(tm, "instance_norm.bias");
+    if (!iw || !ib) rc = -1;
+    else { e->inorm_w = dcopy(e, iw, n_mels); e->inorm_b = dcopy(e, ib, n_mels); if (!e->inorm_w || !e->inorm_b) rc = -1; }
   }
   if (!rc) rc |= make_layer(e, tm, "mfa.", e->C3, e->C3, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->mfa);
   // asp.tdnn: only the first 3C input channels vary over time; the rest become a per-utterance bias
@@ -414,6 +420,7 @@ static Plan make_plan(const Ecapa* e, const Batch* b) {
   p.add("logmel", M * e->n_mels * 4);
   p.add("tile_sums", static_cast<size_t>(b->ntiles) * e->n_mels * 4);
   p.add("mel_mean", B * e->n_mels * 4);
+  p.add("mel_scale", B * e->n_mels * 4);    // input_norm=True: per (utterance, mel) InstanceNorm scale
   p.add("x0", M * 2 * MEL_PLANE * 2);
   p.add("block0", M * P * e->C * 2);
   p.add("xcat", M * P * e->C3 * 2);
@@ -506,10 +513,10 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   if (input_kind == 0) {
     if (fbank_forward(fb, wav, b->d_utt, reinterpret_cast<const int32_t*>(b->d_tiles), B, b->ntiles, b->d_meta, M,
                       b->halo, F("logmel"), F("tile_sums"), F("mel_mean"), H("x0"), x0_ld, x0_pc, 2, 0,
-                      stream)) return -1;
+                      stream, e->inorm_w, e->inorm_b, 1e-5f, F("mel_scale"))) return -1;
   } else {
     if (fbank_from_power(fb, wav, b->d_utt, B, b->d_meta, M, b->halo, F("logmel"), F("mel_mean"), H("x0"),
-                         x0_ld, x0_pc, 2, stream)) return -1;
+                         x0_ld, x0_pc, 2, stream, e->inorm_w, e->inorm_b, 1e-5f, F("mel_scale"))) return -1;
   }
 
   // block 0 (k=5): always split-bf16 on BOTH operands -- the log-mel input loses too much in plain bf16 (SURVEY

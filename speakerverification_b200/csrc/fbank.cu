@@ -249,7 +249,9 @@ __global__ void fbank_mean_kernel(const UttDesc* __restrict__ utts, const float*
 // row, (rows + FB_ROW_SLACK) * out_ld when they are stacked by rows (dense layout for the K-packed block 0, where
 // out_ld == n_mels and the 5-tap window of a frame is ONE contiguous run of 5 * n_mels elements).  Rows
 // [rows, rows + 8) are zeroed: the K padding of the packed window reads a few elements past the last row.
+// (inorm_scale / inorm_bias != nullptr: input_norm=True, v = (x - mean) * scale[utt, m] + bias[m], see fbank_inorm_kernel)
 __global__ void fbank_cmn_pack_kernel(const float* __restrict__ logmel, const float* __restrict__ mean,
+                                      const float* __restrict__ inorm_scale, const float* __restrict__ inorm_bias,
                                       const RowMeta* __restrict__ meta, long long rows, int n_mels,
                                       bf16* __restrict__ out, int out_ld, int plane_cols, int planes, long long lo_off,
                                       long long total_rows) {
@@ -266,10 +268,34 @@ __global__ void fbank_cmn_pack_kernel(const float* __restrict__ logmel, const fl
       if (t >= mt.T) t = 2 * (mt.T - 1) - t;
       const long long src = row + (t - mt.t);
       v = logmel[src * n_mels + m] - mean[mt.utt * n_mels + m];
+      if (inorm_scale != nullptr) v = fmaf(v, inorm_scale[mt.utt * n_mels + m], inorm_bias[m]);
     }
     const bf16 h = __float2bfloat16_rn(v);
     out[row * out_ld + m] = h;
     if (planes == 2) out[row * out_ld + lo_off + m] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+// input_norm=True of ECAPA_TDNN (nn.InstanceNorm1d(n_mels, affine=True, eps, track_running_stats=False) applied to the
+// mean-normalised log-mel, src/models/ECAPA_TDNN.py:406-408,477-478): per (utterance, mel) scale = weight / sqrt(var +
+// eps) with the biased variance over the utterance's frames (the mean is the CMN mean).  One block per utterance; the
+// fp32 log-mel rows it re-reads (96 KB per 3 s crop) are still L2 resident.
+__global__ void fbank_inorm_kernel(const float* __restrict__ logmel, const float* __restrict__ mean,
+                                   const UttDesc* __restrict__ utts, int halo, int n_mels, const float* __restrict__ weight,
+                                   float eps, float* __restrict__ scale) {
+  const UttDesc u = utts[blockIdx.x];
+  for (int m = threadIdx.x; m < n_mels; m += blockDim.x) {
+    const float mu = mean[blockIdx.x * n_mels + m];
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int t = 0;
+    for (; t + 3 < u.T; t += 4) {
+      const float* r = logmel + (u.row_base + halo + t) * n_mels + m;
+      const float d0 = r[0] - mu, d1 = r[n_mels] - mu, d2 = r[2 * n_mels] - mu, d3 = r[3 * n_mels] - mu;
+      s0 = fmaf(d0, d0, s0); s1 = fmaf(d1, d1, s1); s2 = fmaf(d2, d2, s2); s3 = fmaf(d3, d3, s3);
+    }
+    for (; t < u.T; ++t) { const float d = logmel[(u.row_base + halo + t) * n_mels + m] - mu; s0 = fmaf(d, d, s0); }
+    const float var = ((s0 + s1) + (s2 + s3)) / static_cast<float>(u.T);
+    scale[blockIdx.x * n_mels + m] = weight[m] / sqrtf(var + eps);
   }
 }
 
@@ -338,8 +364,20 @@ size_t fbank_smem_bytes(const Fbank* f) {
          (static_cast<size_t>(f->hop) * (FRAMES_PER_TILE - 1) + NFFT) * sizeof(float);
 }
 
+struct InputNorm { const float* weight; const float* bias; float eps; float* scale_ws; };   // weight == nullptr: off
+
 static int pack_rows(const Fbank* f, const RowMeta* meta, long long rows, const float* logmel_ws, const float* mean_ws,
-                     bf16* out, int out_ld, int plane_cols, int planes, cudaStream_t stream) {
+                     bf16* out, int out_ld, int plane_cols, int planes, cudaStream_t stream, const void* utt_tab = nullptr,
+                     int B = 0, int halo = 0, const InputNorm* in = nullptr) {
+  const float *in_scale = nullptr, *in_bias = nullptr;
+  if (in != nullptr && in->weight != nullptr) {
+    SVB_CHECK(in->bias != nullptr && in->scale_ws != nullptr && utt_tab != nullptr, "input_norm needs weight, bias and scratch");
+    fbank_inorm_kernel<<<B, 128, 0, stream>>>(logmel_ws, mean_ws, static_cast<const UttDesc*>(utt_tab), halo, f->n_mels,
+                                             in->weight, in->eps, in->scale_ws);
+    count_launch();
+    SVB_CUDA_OK(cudaGetLastError());
+    in_scale = in->scale_ws; in_bias = in->bias;
+  }
   const int rows_per_block = 8;
   // planes stacked by rows when they do not fit side by side (see the kernel comment); the caller's buffer then holds
   // 2 * (rows + FB_ROW_SLACK) rows of out_ld elements
@@ -347,7 +385,8 @@ static int pack_rows(const Fbank* f, const RowMeta* meta, long long rows, const 
   const long long lo_off = stacked ? (rows + FB_ROW_SLACK) * out_ld : plane_cols;
   const long long nrows = stacked ? rows + 8 : rows;
   fbank_cmn_pack_kernel<<<static_cast<int>((nrows + rows_per_block - 1) / rows_per_block), rows_per_block * 32, 0,
-                          stream>>>(logmel_ws, mean_ws, meta, rows, f->n_mels, out, out_ld, plane_cols, planes, lo_off, nrows);
+                          stream>>>(logmel_ws, mean_ws, in_scale, in_bias, meta, rows, f->n_mels, out, out_ld, plane_cols, planes,
+                                    lo_off, nrows);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -356,7 +395,7 @@ static int pack_rows(const Fbank* f, const RowMeta* meta, long long rows, const 
 // power-mel rows [rows, n_mels] (time-major, valid rows filled) -> packed mean-normalised log-mel
 int fbank_from_power(const Fbank* f, const float* power_rows, const void* utt_tab, int B, const RowMeta* meta,
                      long long rows, int halo, float* logmel_ws, float* mean_ws, bf16* out, int out_ld, int plane_cols,
-                     int planes, cudaStream_t stream) {
+                     int planes, cudaStream_t stream, const float* in_w, const float* in_b, float in_eps, float* in_scale_ws) {
   SVB_CHECK(plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
   const long long n = rows * f->n_mels;
   log_rows_kernel<<<static_cast<int>(std::min<long long>((n + 255) / 256, 148 * 16)), 256, 0, stream>>>(
@@ -364,13 +403,15 @@ int fbank_from_power(const Fbank* f, const float* power_rows, const void* utt_ta
   utt_mean_f32_kernel<<<B, 128, 0, stream>>>(logmel_ws, static_cast<const UttDesc*>(utt_tab), halo, f->n_mels, mean_ws);
   count_launch(2);
   SVB_CUDA_OK(cudaGetLastError());
-  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream);
+  const InputNorm in{in_w, in_b, in_eps, in_scale_ws};
+  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream, utt_tab, B, halo, &in);
 }
 
 // mode 0: full front-end (log, mean normalisation, bf16 pack); mode 1: power-mel rows only (logmel_ws receives them)
 int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const int32_t* tile_tab, int B, int ntiles,
                   const RowMeta* meta, long long rows, int halo, float* logmel_ws, float* tile_sums_ws,
-                  float* mean_ws, bf16* out, int out_ld, int plane_cols, int planes, int mode, cudaStream_t stream) {
+                  float* mean_ws, bf16* out, int out_ld, int plane_cols, int planes, int mode, cudaStream_t stream,
+                  const float* in_w, const float* in_b, float in_eps, float* in_scale_ws) {
   SVB_CHECK(mode == 1 || plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
   const size_t smem = fbank_smem_bytes(f);
   static bool attr_set = false;
@@ -389,7 +430,8 @@ int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const i
   fbank_mean_kernel<<<B, 128, 0, stream>>>(static_cast<const UttDesc*>(utt_tab), tile_sums_ws, f->n_mels, mean_ws);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
-  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream);
+  const InputNorm in{in_w, in_b, in_eps, in_scale_ws};
+  return pack_rows(f, meta, rows, logmel_ws, mean_ws, out, out_ld, plane_cols, planes, stream, utt_tab, B, halo, &in);
 }
 
 }  // namespace svb

@@ -68,8 +68,8 @@ class ECAPA_TDNN(nn.Module):
         super().__init__()
         assert len(channels) == len(kernel_sizes) == len(dilations)
         assert input_size == kwargs["n_mels"], "inappropriate input size, should equal feature_dim"
-        if input_norm or not global_context:
-            raise NotImplementedError("input_norm=True / global_context=False are outside the ECAPA_TDNN hot path")
+        if not global_context:
+            raise NotImplementedError("global_context=False is outside the ECAPA_TDNN hot path")
         if str(kwargs.get("features", "melspectrogram")).strip() != "melspectrogram":
             raise NotImplementedError("the libsvb encoder consumes mel-spectrogram features only")
         self.channels = list(channels)
@@ -77,6 +77,10 @@ class ECAPA_TDNN(nn.Module):
         self.n_mels, self.n_out = input_size, lin_neurons
         self.att, self.se, self.scale = attention_channels, se_channels, res2net_scale
         self.kwargs = kwargs
+        self.input_norm = bool(input_norm)
+        if self.input_norm:      # src/models/ECAPA_TDNN.py:406-408: keys instance_norm.{weight,bias}
+            self.instance_norm = nn.InstanceNorm1d(input_size, affine=True, eps=1e-05, momentum=0.1,
+                                                   track_running_stats=False)
         if precision is None:
             # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
             # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
@@ -119,7 +123,7 @@ class ECAPA_TDNN(nn.Module):
             self._engine = EcapaEngine(state, self.channels, self.n_mels, self.n_out, self.frontend(),
                                        attention_channels=self.att, se_channels=self.se, res2net_scale=self.scale,
                                        kernel_sizes=self.kernel_sizes, dilations=self.dilations,
-                                       precision=self.precision)
+                                       precision=self.precision, input_norm=self.input_norm)
             self._fingerprint = fp
         return self._engine
 

@@ -118,7 +118,8 @@ class EcapaEngine:
     (without the '__S__.' prefix) to fp32 CUDA tensors."""
 
     def __init__(self, state, channels, n_mels, n_out, frontend, attention_channels=128, se_channels=128,
-                 res2net_scale=8, kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), precision="f16"):
+                 res2net_scale=8, kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), precision="f16",
+                 input_norm=False):
         precision = normalize_precision(precision)
         C = int(channels[0])
         if list(channels[:4]) != [C] * 4 or int(channels[4]) != 3 * C:
@@ -130,6 +131,7 @@ class EcapaEngine:
         cfg.kernel_sizes = (ctypes.c_int32 * 5)(*kernel_sizes)
         cfg.dilations = (ctypes.c_int32 * 5)(*dilations)
         cfg.fp32_mode = 1 if precision == "fp32" else 0
+        cfg.input_norm = 1 if input_norm else 0
         keep, names, ptrs = [], [], []
         for k, v in state.items():
             if not torch.is_tensor(v) or not v.is_floating_point():

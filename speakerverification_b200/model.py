@@ -20,12 +20,13 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from . import ecapa_tdnn, feature, rawnet2_custom
+from . import ecapa_tdnn, feature, raw3_ecapa, rawnet2_custom
 from . import utils as svb_utils
 from . import _native as nv
 from .audio_loader import crop_plan, loadWAV, read_pcm
 
-_ENCODERS = {"ECAPA_TDNN": ecapa_tdnn.MainModel, "RawNet2_custom": rawnet2_custom.MainModel}
+_ENCODERS = {"ECAPA_TDNN": ecapa_tdnn.MainModel, "RawNet2_custom": rawnet2_custom.MainModel,
+             "Raw3_ECAPA": raw3_ecapa.MainModel}
 # losses of the reference whose constructor sets test_normalize = False (src/losses/Prototypical.py:21)
 # or leaves it unset (AttributeError -> False at src/model.py:90-94); every other loss sets True.
 _NO_TEST_NORMALIZE = {"Prototypical", "AngularPenaltySMLoss", "CircleLoss", "CircleLossV2", "GE2ELoss",

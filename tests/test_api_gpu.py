@@ -100,7 +100,8 @@ def test_evaluate_from_list_fp32(workdir, golden_c512):
     print("fp32 list-API AS-norm score max dev", devn)
     # normalised scores amplify embedding error by 1/sigma (sigma ~ 0.03-0.1): 1e-4 holds for the scoring
     # kernels on identical embeddings (test_scoring_gpu.py); end to end the bound is 1e-4 / sigma_min.
-    assert devn <= 5e-3
+    # Measured on B200 (round 2): 2.5e-4 with a raw-cosine deviation of 4.9e-5; asserted at 2x.
+    assert devn <= 5e-4
 
 
 def test_evaluate_from_list_f16_c1024(workdir1024, golden_c1024):
@@ -267,3 +268,50 @@ def test_no_cpu_path(workdir):
     from speakerverification_b200.model import SpeakerEncoder
     with pytest.raises(RuntimeError):
         SpeakerEncoder(**dict(_args(workdir["tmp"], "fp32"), device="cpu"))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+def test_ragged_eval_asnorm_scores_vs_oracle(workdir, golden_c512, precision):
+    """BASELINE.json configs[2] at test size, score level: 16 ragged 2-20 s utterances -> embed_signals(num_eval=0)
+    (whole-utterance embeddings, int16 PCM in) -> AS-norm against a 6000-row cohort, top-300 -> all 120 pair scores,
+    against oracle.ecapa_oracle.embed + oracle.scoring_oracle (cosine_score / asnorm_score) on the same signals.
+    The cohort bank is an INPUT of the scoring stage (6000 one-second synthetic utterances embedded once, fp32 mode)
+    and is handed to both sides.  Tolerances: raw cosine <= 1e-4 (fp32) / 2e-3 north star, asserted 5e-4 (16-bit mode);
+    AS-norm divides by the cohort sigma, so its bound is the cosine bound / sigma_min (computed by the oracle)."""
+    from oracle import ecapa_oracle as eo, scoring_oracle as so, synth
+    from speakerverification_b200 import utils as U
+    net, h, args = _handle(workdir, precision)
+    sd = synth.ecapa_state_dict(CH512, 192, bn_stats={k[3:]: v for k, v in golden_c512.items() if k.startswith("bn/")})
+    lengths = synth.ragged_lengths(16, seed=21)
+    lengths[0], lengths[1] = 32000, 320000                       # both ends of the configs[2] range
+    f0, env = synth.speaker_bank(6, seed=31)
+    sig = [synth.utterance(f0[i % 6], env[i % 6], int(n), 700 + i) for i, n in enumerate(lengths)]
+    pcm = [np.round(s / np.abs(s).max() * 20000).astype(np.int16) for s in sig]
+    emb = h.embed_signals(pcm, 0)                                # [16, 1, 192]
+    # cohort: 6000 one-second utterances of 300 cohort speakers, embedded in fp32 mode (input data for both sides)
+    hc = h if precision == "fp32" else _handle(workdir, "fp32")[1]
+    hc.audio_spec = dict(hc.audio_spec, sentence_len=1.0)
+    cf0, cenv = synth.speaker_bank(300, seed=77)
+    rng = np.random.default_rng(8)
+    base = [synth.utterance(cf0[s], cenv[s], 16001, 60000 + s) for s in range(300)]
+    coh_sig = [np.round((base[i % 300] * rng.uniform(0.3, 1.0) + 0.02 * rng.standard_normal(16001)) * 30000).astype(np.int16)
+               for i in range(6000)]
+    cohort = torch.nn.functional.normalize(hc.embed_signals(coh_sig, 1)[:, 0], dim=1).cpu().numpy()
+    hc.audio_spec = dict(hc.audio_spec, sentence_len=3.0)
+    ti, tj = np.triu_indices(16, 1)
+    ia, ib = torch.from_numpy(ti.astype(np.int32)).cuda(), torch.from_numpy(tj.astype(np.int32)).cuda()
+    got_cos = U.score_trials(emb, ia, ib, "cosine").cpu().numpy()
+    got_as = U.score_trials(emb, ia, ib, "norm", cohort, top=300, normalize=True).cpu().numpy()
+    # oracle: one forward per whole utterance (src/model.py:380-396), then the per-trial scoring functions
+    # (loadWAV wrap-pads signals of <= sentence_len to sentence_len + 1 sample, src/processing/audio_loader.py:126-129)
+    whole = [eo.load_wav_eval(p.astype(np.float32) / 32768.0, 3.0, 16000, 0)[0] for p in pcm]
+    ref = np.stack([eo.embed(np.stack([x, x]), sd).numpy()[0] for x in whole])
+    rn = so.l2_normalize(ref)
+    want_cos = np.array([so.cosine_score(ref[i][None], ref[j][None]) for i, j in zip(ti, tj)])
+    want_as = np.array([so.asnorm_score(rn[i][None], rn[j][None], cohort, 300) for i, j in zip(ti, tj)])
+    _, sigma = so.asnorm_stats(rn, cohort, 300)
+    tol = 1e-4 if precision == "fp32" else 5e-4
+    dc, da = np.abs(got_cos - want_cos).max(), np.abs(got_as - want_as).max()
+    print("ragged eval", precision, "cosine dev", dc, "AS-norm dev", da, "sigma_min", sigma.min(), "bound", 2 * tol / sigma.min())
+    assert dc <= tol, dc
+    assert da <= 2 * tol / sigma.min(), (da, sigma.min())

@@ -147,3 +147,80 @@ def test_extreme_lengths_fp32(golden_c512):
         assert c >= 0.9999, (n, c)
     with pytest.raises(RuntimeError, match="frames"):
         eng.forward_flat(torch.from_numpy(sig[0][:1279]).cuda(), [1279])
+
+
+@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("f16", 0.99995, 6e-4)])
+def test_input_norm_matches_reference(precision, cos_min, tol):
+    """input_norm=True (nn.InstanceNorm1d(n_mels, affine=True) after the log / mean normalisation,
+    src/models/ECAPA_TDNN.py:406-408,477-478): the ECAPA branch of the Raw3_ECAPA hybrid, against the reference's own
+    embeddings and 1000 cosine trial scores (tests/golden/cfg1_c512_inorm.npz, oracle/make_golden.py cfg1i)."""
+    import os
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    from speakerverification_b200.engine import EcapaEngine
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "cfg1_c512_inorm.npz")))
+    _, state = _state(CH512, g)
+    state["instance_norm.weight"] = torch.from_numpy(g["instance_norm.weight"]).cuda()
+    state["instance_norm.bias"] = torch.from_numpy(g["instance_norm.bias"]).cuda()
+    waves, spk = synth.utterance_set(16, 4, L + 1)
+    eng = EcapaEngine(state, CH512, 80, 192, _frontend(), precision=precision, input_norm=True)
+    emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda())
+    e = emb.cpu().numpy()
+    ref = g["emb_batch"]
+    cos = (e * ref).sum(1) / np.linalg.norm(e, axis=1) / np.linalg.norm(ref, axis=1)
+    assert cos.min() >= cos_min, cos.min()
+    lab, ti, tj = synth.trial_list(spk, 1000)
+    sc = U.cosine_trials(emb.unsqueeze(1).contiguous(), torch.from_numpy(ti.astype(np.int32)).cuda(),
+                         torch.from_numpy(tj.astype(np.int32)).cuda()).cpu().numpy()
+    dev = np.abs(sc - g["scores_cos"]).max()
+    print("input_norm", precision, "min cos", cos.min(), "max score dev", dev)
+    assert dev <= tol, dev
+    if precision == "fp32":
+        plan = eng.plan([L] * 64)
+        t = eng.stage(plan, "block0", 512, planes=2)[plan.halo:plan.halo + plan.T[0]].float()
+        got = (t[:, :512] + t[:, 512:]).t().cpu().numpy()[::16]
+        np.testing.assert_allclose(got, g["stage/block0"], atol=2e-4, rtol=1e-4)
+    # without the flag the same checkpoint is refused only when the tensors are missing
+    with pytest.raises(RuntimeError, match="instance_norm"):
+        EcapaEngine({k: v for k, v in state.items() if not k.startswith("instance_norm")}, CH512, 80, 192, _frontend(),
+                    precision=precision, input_norm=True)
+
+
+def test_raw3_ecapa_hybrid_plumbing(tmp_path):
+    """Raw3_ECAPA (src/models/Raw3_ECAPA.py:21-47): ECAPA(C=512, nOut=192, input_norm=True) on libsvb concatenated with
+    a caller-supplied second raw-waveform encoder (the reference's RawNet3 needs asteroid_filterbanks: unpinned here),
+    through the SpeakerEncoder plugin registry with the reference's parameter names."""
+    import os
+    from oracle import synth
+    from speakerverification_b200.model import SpeakerEncoder, WrappedModel
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "cfg1_c512_inorm.npz")))
+
+    class Second(torch.nn.Module):                      # stand-in for models.RawNet3.MainModel(nOut = 512 - 192)
+        def __init__(self):
+            super().__init__()
+            self.proj = torch.nn.Linear(100, 320, bias=False)
+
+        def forward(self, x):
+            return self.proj(x[:, :48000].reshape(x.shape[0], 100, 480).mean(2))
+    args = dict(device="cuda", gpu=0, model={"name": "Raw3_ECAPA", "nOut": 512}, criterion={"name": "AAmSoftmaxAP"},
+                features="raw", n_mels=80, sr=16000, n_fft=512, win_length=400, hop_length=160, lib="torchaudio",
+                audio_spec={"sample_rate": 16000, "sentence_len": 3.0, "win_len": 0.025, "hop_len": 0.01},
+                dataloader_options={"nPerSpeaker": 2}, svb_precision="fp32", svb_second_encoder=Second())
+    net = WrappedModel(SpeakerEncoder(**args))
+    tgt = net.module.state_dict()
+    sd = synth.ecapa_state_dict(CH512, 192, bn_stats=_bn(g))
+    sd["__S__.instance_norm.weight"], sd["__S__.instance_norm.bias"] = g["instance_norm.weight"], g["instance_norm.bias"]
+    for k, v in sd.items():
+        tgt["__S__.ECAPA_TDNN." + k[len("__S__."):]].copy_(torch.as_tensor(v))
+    assert "__S__.rawnet.proj.weight" in tgt and "__S__.compute_features.1.mel_scale.fb" in tgt
+    waves, _ = synth.utterance_set(16, 4, L + 1)
+    w = torch.from_numpy(waves[:6, :L])
+    out = net(w)
+    assert tuple(out.shape) == (6, 512)
+    ref = torch.from_numpy(g["emb_batch"][:6])
+    assert torch.nn.functional.cosine_similarity(out[:, :192].cpu(), ref, dim=1).min().item() >= 0.9999
+    with torch.no_grad():
+        want2 = net.module.__S__.rawnet(w.cuda())
+    assert torch.allclose(out[:, 192:], want2, atol=1e-6)
+    with pytest.raises(NotImplementedError, match="asteroid_filterbanks"):
+        SpeakerEncoder(**dict(args, svb_second_encoder=None))

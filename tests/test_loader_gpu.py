@@ -78,3 +78,35 @@ def test_embed_signals_matches_host_crop_path(golden_c512):
             want = net.module.engine().forward(torch.from_numpy(np.ascontiguousarray(crops)).cuda()).cpu().numpy()
             assert got[i].shape == want.shape
             assert np.abs(got[i] - want).max() <= 1e-5 * max(1.0, np.abs(want).max()), (num_eval, i)
+
+
+def test_embed_signals_back_to_back_calls():
+    """Two embed_signals calls without a synchronisation in between (>= 4 launch groups each) reuse the persistent pinned
+    / device staging buffers: the second call must wait for the copies and kernels of the first (the first
+    groups of a call used to skip the ready / freed events of the previous call's last groups)."""
+    import torch
+    from oracle import synth
+    from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
+    CH = [512, 512, 512, 512, 1536]
+    args = dict(device="cuda", gpu=0, save_folder="/tmp/svb_t", model={"name": "ECAPA_TDNN", "nOut": 192}, channels=CH,
+                criterion={"name": "AAmSoftmaxAP"}, features="melspectrogram", n_mels=80, sr=16000, n_fft=512,
+                win_length=400, hop_length=160,
+                audio_spec={"sample_rate": 16000, "sentence_len": 1.0, "win_len": 0.025, "hop_len": 0.01},
+                dataloader_options={"nPerSpeaker": 2}, svb_precision="f16", svb_batch_rows=8)
+    net = WrappedModel(SpeakerEncoder(**args))
+    h = ModelHandling(net, **dict(args, T_max=10))
+    tgt = net.module.state_dict()
+    for k, v in synth.ecapa_state_dict(CH, 192).items():
+        tgt[k].copy_(torch.as_tensor(v))
+    rng = np.random.default_rng(5)
+    sigs_a = [np.round(3000 * rng.standard_normal(int(n))).astype(np.int16) for n in rng.integers(16000, 40000, 20)]
+    sigs_b = [np.round(3000 * rng.standard_normal(int(n))).astype(np.int16) for n in rng.integers(16000, 40000, 20)]
+    want_a = h.embed_signals(sigs_a, 2).clone()
+    torch.cuda.synchronize()
+    want_b = h.embed_signals(sigs_b, 2).clone()
+    torch.cuda.synchronize()
+    got_a = h.embed_signals(sigs_a, 2)          # 5 groups of 4 utterances x 2 crops; no sync before the next call
+    got_b = h.embed_signals(sigs_b, 2)
+    got_a2 = h.embed_signals(sigs_a, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(got_a, want_a) and torch.equal(got_b, want_b) and torch.equal(got_a2, want_a)
