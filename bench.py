@@ -28,6 +28,9 @@ N_OUT = 192
 L = 48000
 FLOP_PER_UTT = 11.29e9          # 37.50 MFLOP/frame x 301 frames (C=1024, 3 s crop)
 MFA_MAC_PER_FRAME = 9437184     # SURVEY.md 8a GEMM table, mfa row (3C x 3C)
+# dram__bytes_read.sum + dram__bytes_write.sum of one MFA launch at 592 rows (ncu --set full, profiles/r01_ncu_final.md:
+# 1.215 GB + 1.132 GB; fp16 operands have the same footprint as bf16) against 2.267 GB algorithmic
+MFA_DRAM_BYTES = 2.487e9
 
 
 def model_args(device, precision):
@@ -133,9 +136,11 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def synth_waves(n, device, seed):
-    """n distinct 3 s utterances: speaker-like harmonic signals (oracle/synth.py) mixed, shifted and scaled on the GPU."""
+def synth_waves(n, device, seed, length=None):
+    """n distinct utterances of `length` samples (default 3 s): speaker-like harmonic signals (synth.py) mixed, shifted
+    and scaled on the GPU."""
     from speakerverification_b200 import synth
+    L = length or globals()["L"]
     pool, _ = synth.utterance_set(8, 4, L)
     pool = torch.from_numpy(pool).to(device)
     g = torch.Generator(device=device).manual_seed(seed)
@@ -285,7 +290,7 @@ def cpu_scoring_rate(e, c, ia, ib, top, min_seconds):
     t0 = time.perf_counter()
     n = 0
     while time.perf_counter() - t0 < min_seconds or n < 8:
-        so.asnorm_score(e[ia[n]][None], e[ib[n]][None], c, top)
+        so.asnorm_score(e[ia[n % len(ia)]][None], e[ib[n % len(ib)]][None], c, top)
         n += 1
     dt = time.perf_counter() - t0
     return n / dt, n, dt
@@ -412,7 +417,7 @@ def cpu_eval_rate(signals, cohort, top, min_seconds):
     return t_emb, t_trial, len(embs), nt, secs
 
 
-def run_eval(args, device, rank, world, dist):
+def run_eval(args, device, rank, world, dist, steps):
     """cfg3: ragged 2-20 s utterances -> whole-utterance embeddings (num_eval = 0) -> AS-norm (6 000 cohort, top-300)
     -> trial scores.  Utterances are sharded length-balanced (ModelHandling.shard_balanced); the exchange steps are the
     all-gathers of the embedding shards, of the (mu, sigma) shards and of the score slices."""
@@ -457,7 +462,6 @@ def run_eval(args, device, rank, world, dist):
     emb = torch.empty((len(signals), N_OUT), dtype=torch.float32, device=device)
 
     def score(e_local):
-        e_local = torch.nn.functional.normalize(e_local, dim=1)
         full = ModelHandling.gather_assigned(e_local, parts, rank, world) if world > 1 else e_local
         mu, sg = SU.asnorm_stats(e_local, coh, K)
         if world > 1:
@@ -472,7 +476,7 @@ def run_eval(args, device, rank, world, dist):
 
     def step():
         for (a, b, o, tot) in groups:
-            eng.forward_flat(flat[o:o + tot], [len(x) for x in staged[a:b]], out=emb[a:b])
+            eng.forward_flat(flat[o:o + tot], [len(x) for x in staged[a:b]], l2norm=True, out=emb[a:b])   # F.normalize fused
         return score(emb)
 
     for _ in range(max(args.warmup, 3)):
@@ -486,27 +490,23 @@ def run_eval(args, device, rank, world, dist):
     nv.lib().svb_reset_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         out = step()
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    ms = e0.elapsed_time(e1)
     launches = int(nv.lib().svb_launch_count())
     clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        t = torch.tensor([ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms, per_rank = rank_stats(e0.elapsed_time(e1), {"device": device, "world": world, "dist": dist})
     # end to end: int16 PCM on the host -> GPU crop/stack stage -> encoder -> gathers -> scores on the host
     handle.embed_signals(signals[:64], 0)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_emb = handle.embed_signals(signals, 0).view(len(signals), N_OUT)
+    for _ in range(steps):
+        e2e_emb = torch.nn.functional.normalize(handle.embed_signals(signals, 0).view(len(signals), N_OUT), dim=1)
         hs = score(e2e_emb).cpu()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
@@ -521,35 +521,39 @@ def run_eval(args, device, rank, world, dist):
     audio_s = float(lengths.sum()) / 16000.0
     frames = float((1 + lengths // 160).sum())
     hbm, tf_burst, tf_sust, src = peaks()
-    tfl = frames * 37.50e6 * args.steps / (ms * 1e-3) / 1e12 / world
+    tfl = frames * 37.50e6 * steps / (ms * 1e-3) / 1e12 / world
     line = {"metric": "full-length eval utterances/sec (2-20 s utt, fbank + ECAPA + AS-norm)",
-            "value": world * U * args.steps / (ms * 1e-3), "unit": "utterances/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)",
+            "value": world * U * steps / (ms * 1e-3), "unit": "utterances/s", "n_gpus": world, "steps": steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None,
+            "dtype": "f16 (IEEE-half tensor-core operands, fp32 accumulate)" if args.precision != "fp32" else "bf16x3 (split, fp32 grade)",
             "data": "synthetic",
             "config": {"workload": "full-length eval (configs[2]): %d ragged U(2,20) s utterances per GPU, whole-utterance "
                                    "ECAPA-TDNN C=1024 embeddings, AS-norm vs 6000-cohort top-300, %d trials per GPU"
                                    % (U, NT),
                        "parallelism": "utterances length-balanced over %d GPU(s); all-gather of embeddings, (mu, sigma) "
                                       "and score slices" % world,
-                       "audio_seconds_per_s": audio_s * args.steps / (ms * 1e-3),
-                       "equiv_3s_embeddings_per_s": frames / 301.0 * args.steps / (ms * 1e-3),
+                       "audio_seconds_per_s": audio_s * steps / (ms * 1e-3),
+                       "equiv_3s_embeddings_per_s": frames / 301.0 * steps / (ms * 1e-3),
                        "l2": "inputs larger than L2 (%.2f GB of samples per GPU per step)" % (flat.numel() * 4 / 1e9)},
-            "e2e": {"value": world * U * args.steps / dt, "unit": "utterances/s",
+            "e2e": {"value": world * U * steps / dt, "unit": "utterances/s",
                     "h2d_bytes_per_step": int(sum(len(x) for x in signals)) * 2, "d2h_bytes_per_step": world * NT * 4,
                     "api": "ModelHandling.embed_signals(int16 PCM list, num_eval=0) -> gathers -> utils.asnorm_* -> .cpu()"},
             "gpu_launches": launches, "clocks": clocks,
             "roofline": {"kernel": "whole step (tensor-bound encoder), algorithmic 37.50 MFLOP per frame", "bound": "tensor",
                          "achieved": tfl, "peak": tf_sust, "unit": "TFLOP/s", "frac": tfl / tf_sust, "traffic": None,
                          "peak_source": src + " (sustained)"}}
+    if per_rank is not None:
+        line["per_rank_ms_per_step"] = {k: (v / steps if not isinstance(v, list) else [x / steps for x in v])
+                                        for k, v in per_rank.items()}
     if world == 1:
-        t_emb, t_trial, ne, nt, secs = cpu_eval_rate(signals, cohort, K, 12.0)
+        t_emb, t_trial, ne, nt, secs = cpu_eval_rate(signals, cohort, K, 12.0 if args.workload == "eval" else 6.0)
         per_utt = t_emb * (audio_s / U) / (secs / ne) + t_trial * NT / U
         line["cpu_baseline"] = {"value": 1.0 / per_utt, "unit": "utterances/s", "cores": os.cpu_count(), "kind": "port",
                                 "sample": "%d whole utterances (%.0f s of audio) + %d AS-norm trials, torch/numpy oracle "
                                           "port; composed per utterance at the workload's mean length and trials per "
                                           "utterance" % (ne, secs, nt)}
-    emit(json.dumps(line))
+    return line
 
 
 def gemm_roofline(device, batch_rows, halo=4):
@@ -581,64 +585,27 @@ def gemm_roofline(device, batch_rows, halo=4):
     return flops / (ms * 1e-3) / 1e12, ms
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="svb", choices=["svb", "reference"])
-    ap.add_argument("--utts", type=int, default=10000)
-    ap.add_argument("--batch-rows", type=int, default=592)   # 4 x 148: whole waves of the per-utterance chain kernel
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="embed", choices=["embed", "scoring", "rawnet2", "eval"])
-    ap.add_argument("--e2e-rows", type=int, default=296)
-    ap.add_argument("--eval-utts", type=int, default=2000)
-    ap.add_argument("--eval-trials", type=int, default=100000)
-    ap.add_argument("--score-utts", type=int, default=200000)
-    ap.add_argument("--score-cohort", type=int, default=20000)
-    ap.add_argument("--score-trials", type=int, default=1000000)
-    args = ap.parse_args()
-    quiet_stdout()
-    if args.impl == "reference":
-        return run_reference(args)
+def rank_stats(ms_local, ctx):
+    """(max over ranks, {min, median, max, per_rank}) of a per-rank device time; every rank calls it."""
+    if ctx["world"] == 1:
+        return ms_local, None
+    t = torch.tensor([ms_local], device=ctx["device"])
+    allt = [torch.empty_like(t) for _ in range(ctx["world"])]
+    ctx["dist"].all_gather(allt, t)
+    v = sorted(float(x.item()) for x in allt)
+    return v[-1], {"min": v[0], "median": float(np.median(v)), "max": v[-1], "per_rank": [float(x.item()) for x in allt]}
 
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    rank = int(os.environ.get("RANK", 0))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=device)
 
-    if args.workload == "scoring":
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
-        res = run_scoring(args, device, rank, world, dist, args.steps)
-        if rank == 0:
-            res["warmup"] = 3
-            res["clocks"] = sampler.stop()
-            emit(json.dumps(res))
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
-    if args.workload == "eval":
-        run_eval(args, device, rank, world, dist)
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
+def bench_encoder(args, ctx, rawnet):
+    """Embedding extraction (configs[1] ECAPA-TDNN C=1024 3 s crops, or configs[3] RawNet2 4 s crops): `value` with the
+    waveforms resident in HBM, `e2e` through ModelHandling.embed_batches from pinned host memory.  Returns the JSON line
+    (rank 0) or None."""
     from speakerverification_b200 import _native as nv
     from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
     from speakerverification_b200 import synth
-    rawnet = args.workload == "rawnet2"
-    global L, N_OUT, FLOP_PER_UTT
-    if rawnet:
-        L, N_OUT, FLOP_PER_UTT = 64000, 512, 13.96e9        # 13.96 GFLOP per 4 s crop
+    device, rank, world, dist = ctx["device"], ctx["rank"], ctx["world"], ctx["dist"]
+    Lw, n_out, flop_per_utt = (64000, 512, 13.96e9) if rawnet else (L, N_OUT, FLOP_PER_UTT)   # SURVEY.md 8a (a13, a26)
+    steps = args.steps if not rawnet or args.workload == "rawnet2" else max(10, min(args.steps, 10))
     margs = rawnet_args("cuda", args.precision) if rawnet else model_args("cuda", args.precision)
     net = WrappedModel(SpeakerEncoder(**margs))
     handle = ModelHandling(net, **dict(margs, T_max=10, svb_batch_rows=args.batch_rows))
@@ -650,47 +617,71 @@ def main():
     eng = net.module.engine()
 
     U = args.utts
-    waves = synth_waves(U, device, seed=100 + rank)
-    emb = torch.empty((U, N_OUT), dtype=torch.float32, device=device)
-    gathered = torch.empty((world * U, N_OUT), dtype=torch.float32, device=device) if world > 1 else None
+    waves = synth_waves(U, device, seed=100 + rank, length=Lw)
+    emb = torch.empty((U, n_out), dtype=torch.float32, device=device)
+    gathered = torch.empty((world * U, n_out), dtype=torch.float32, device=device) if world > 1 else None
 
-    def step():
-        for r0 in range(0, U, args.batch_rows):
-            eng.forward(waves[r0:r0 + args.batch_rows], out=emb[r0:r0 + args.batch_rows])
-        if world > 1:
+    def step(n_utts=U, gather=True):
+        for r0 in range(0, n_utts, args.batch_rows):
+            r1 = min(n_utts, r0 + args.batch_rows)
+            eng.forward(waves[r0:r1], out=emb[r0:r1])
+        if world > 1 and gather:
             dist.all_gather_into_tensor(gathered, emb)          # the path's one exchange step
+
+    def timed(n_steps, **kw):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_steps):
+            step(**kw)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        return e0.elapsed_time(e1)
 
     for _ in range(max(args.warmup, 3)):
         step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(ctx["local"])
     if rank == 0:
         sampler.start()
     nv.lib().svb_reset_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    ms = e0.elapsed_time(e1)
+    ms_local = timed(steps)
     launches = int(nv.lib().svb_launch_count())
     clocks = sampler.stop() if rank == 0 else None
+    ms, per_rank = rank_stats(ms_local, ctx)
+    value = world * U * steps / (ms * 1e-3)
+
+    # strong scaling: ONE set of U utterances split over the ranks (weak scaling is the headline)
+    strong = None
     if world > 1:
-        t = torch.tensor([ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = world * U * args.steps / (ms * 1e-3)
+        share = (U + world - 1) // world
+        emb_s = torch.empty((world * share, n_out), dtype=torch.float32, device=device)
+
+        def strong_step():
+            for r0 in range(0, share, args.batch_rows):
+                r1 = min(share, r0 + args.batch_rows)
+                eng.forward(waves[r0:r1], out=emb[r0:r1])
+            dist.all_gather_into_tensor(emb_s, emb[:share])
+        strong_step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            strong_step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms_s, _ = rank_stats(e0.elapsed_time(e1), ctx)
+        strong = {"value": world * share * steps / (ms_s * 1e-3), "unit": "embeddings/s", "ms_per_step": ms_s / steps,
+                  "utterances_total": world * share, "scaling": "strong"}
 
     # end to end through the public API from pinned host buffers
     e2e = None
     if not args.no_e2e:
-        host = torch.empty((U, L), dtype=torch.float32).pin_memory()
+        host = torch.empty((U, Lw), dtype=torch.float32).pin_memory()
         host.copy_(waves)
         torch.cuda.synchronize()
         handle.embed_batches(host[:4 * args.batch_rows]).cpu()  # warm-up
@@ -698,7 +689,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             out = handle.embed_batches(host).cpu()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
@@ -706,12 +697,29 @@ def main():
             t = torch.tensor([dt], device=device)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {"value": world * U * args.steps / dt, "unit": "embeddings/s", "h2d_bytes_per_step": U * L * 4,
-               "d2h_bytes_per_step": U * N_OUT * 4, "api": "ModelHandling.embed_batches(pinned host [U, L]) -> .cpu()"}
-        assert out.shape == (U, N_OUT) and bool(torch.isfinite(out).all())
-
-    if rank == 0 and rawnet:
-        hbm, tf_burst, tf_sust, src = peaks()
+        e2e = {"value": world * U * steps / dt, "unit": "embeddings/s", "h2d_bytes_per_step": U * Lw * 4,
+               "d2h_bytes_per_step": U * n_out * 4, "api": "ModelHandling.embed_batches(pinned host [U, L]) -> .cpu()"}
+        # the e2e embeddings are the device-resident pass's embeddings (same kernels, same inputs)
+        cos = torch.nn.functional.cosine_similarity(out.to(device), emb, dim=1)
+        assert out.shape == (U, n_out) and bool(torch.isfinite(out).all()) and float(cos.min()) > 0.99999, float(cos.min())
+        del host
+    if rank != 0:
+        return None
+    hbm, tf_burst, tf_sust, src = peaks()
+    dtype = "f16 (IEEE-half tensor-core operands, fp32 accumulate)" if args.precision != "fp32" else "bf16x3 (split, fp32 grade)"
+    line = {"metric": "RawNet2 embeddings/sec (4 s utt)" if rawnet else "ECAPA embeddings/sec (3 s utt)",
+            "value": value, "unit": "embeddings/s", "n_gpus": world, "steps": steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
+            "data": "synthetic", "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+    if per_rank is not None:
+        line["per_rank_ms_per_step"] = {k: (v / steps if not isinstance(v, list) else [x / steps for x in v])
+                                        for k, v in per_rank.items()}
+    if strong is not None:
+        line["strong_scaling"] = strong
+    line["step_tensor"] = {"achieved_tflops": value / world * flop_per_utt / 1e12, "peak": tf_sust,
+                           "frac": value / world * flop_per_utt / 1e12 / tf_sust,
+                           "note": "whole step, algorithmic %.2f GFLOP per utterance vs sustained bf16 peak" % (flop_per_utt / 1e9)}
+    if rawnet:
         # dominant kernel: the sliding-window sinc GEMM (front end = LayerNorm + sinc GEMM, timed alone)
         os.environ["SVB_RAWNET_STOP"] = "-1"
         wv = waves[:args.batch_rows]
@@ -726,65 +734,221 @@ def main():
         del os.environ["SVB_RAWNET_STOP"]
         front_ms = ev[0].elapsed_time(ev[1]) / 10
         ach = 4.10e9 * wv.shape[0] / (front_ms * 1e-3) / 1e12
-        line = {
-            "metric": "RawNet2 embeddings/sec (4 s utt)", "value": value, "unit": "embeddings/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)", "data": "synthetic",
-            "config": {"workload": "RawNet2_custom (sinc front-end + 8 residual blocks + GRU) nOut=512, %d synthetic 4 s "
-                                   "16 kHz utterances per GPU (configs[3])" % U,
-                       "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
-                       "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * L * 4 / 1e9)},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "roofline": {"kernel": "rn_gemm_kernel<192,EPI_SINC> (+ LayerNorm kernel) of one %d-utterance launch" % wv.shape[0],
-                         "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
-                         "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": front_ms,
-                         "note": "algorithmic 4.10 GFLOP per utterance (SURVEY 8a a23); the GEMM executes 1.27x that "
-                                 "(K padded 251 -> 320)"},
-            "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
-                            "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
-                            "note": "whole step, algorithmic 13.96 GFLOP per utterance vs sustained bf16 peak"},
-        }
-        if world == 1:
+        line["config"] = {"workload": "RawNet2_custom (sinc front-end + 8 residual blocks + GRU) nOut=512, %d synthetic 4 s "
+                                      "16 kHz utterances per GPU (configs[3])" % U,
+                          "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
+                          "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * Lw * 4 / 1e9)}
+        line["roofline"] = {"kernel": "rn_gemm_kernel<EPI_SINC> (+ LayerNorm kernel) of one %d-utterance launch" % wv.shape[0],
+                            "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
+                            "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": front_ms,
+                            "note": "algorithmic 4.10 GFLOP per utterance (SURVEY 8a a23)"}
+        if world == 1 and args.workload == "rawnet2":
             rate, n, dt = cpu_rawnet_rate(12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port (%.1f s)" % (n, dt)}
-        emit(json.dumps(line))
-    elif rank == 0:
-        hbm, tf_burst, tf_sust, src = peaks()
+    else:
         ach, gemm_ms = gemm_roofline(device, args.batch_rows)
-        line = {
-            "metric": "ECAPA embeddings/sec (3 s utt)", "value": value, "unit": "embeddings/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16" if args.precision == "bf16" else "bf16x3 (split, fp32 grade)", "data": "synthetic",
-            "config": {"workload": "ECAPA-TDNN C=1024 nOut=192, 80-mel fbank (16 kHz, n_fft 512, win 400, hop 160), "
-                                   "%d synthetic 3 s utterances per GPU (configs[1])" % U,
-                       "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
-                       "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * L * 4 / 1e9)},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "roofline": {"kernel": "gemm_pw_kernel<256,GELU> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
-                         "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one MFA launch at 592 rows (ncu --set full,
-                         # profiles/r01_summary.md): 1.215 GB + 1.132 GB against 2.267 GB algorithmic
-                         "traffic": 2.487e9 if args.batch_rows == 592 else None,
-                         "traffic_unit": "bytes per launch (dram read + write of the ncu --set full capture of this kernel at this shape, profiles/r01_ncu_final.md; algorithmic 2.267e9)",
-                         "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms},
-            "step_tensor": {"achieved_tflops": value / world * FLOP_PER_UTT / 1e12, "peak": tf_sust,
-                            "frac": value / world * FLOP_PER_UTT / 1e12 / tf_sust,
-                            "note": "whole step, algorithmic 11.29 GFLOP per utterance vs sustained bf16 peak"},
-        }
-        if world == 1:
-            del waves, emb
-            torch.cuda.empty_cache()
-            sc = run_scoring(args, device, rank, world, dist, max(args.steps, 3), full_line=False)
-            line["scoring"] = {k: sc[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "roofline")}
+        line["config"] = {"workload": "ECAPA-TDNN C=1024 nOut=192, 80-mel fbank (16 kHz, n_fft 512, win 400, hop 160), "
+                                      "%d synthetic 3 s utterances per GPU (configs[1])" % U,
+                          "batch_rows": args.batch_rows, "parallelism": "utterance-sharded x%d" % world,
+                          "l2": "inputs larger than L2 (%.2f GB of waveforms per step)" % (U * Lw * 4 / 1e9)}
+        line["roofline"] = {"kernel": "gemm_pw_kernel<256,GELU> (MFA layer 3C x 3C of one %d-utterance launch)" % args.batch_rows,
+                            "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
+                            "traffic": MFA_DRAM_BYTES if args.batch_rows == 592 else None,
+                            "traffic_unit": "bytes per launch: dram__bytes_read.sum + dram__bytes_write.sum of the ncu --set "
+                                            "full capture of this kernel at this shape (profiles/); algorithmic 2.267e9",
+                            "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": gemm_ms}
+    del waves, emb, eng, handle, net
+    torch.cuda.empty_cache()
+    return line
+
+
+def gpu_library_baseline(device, batch=592, reps=3):
+    """SURVEY 8d 'secondary baseline (the library kernels to beat)': the reference's forward as PyTorch eager launches it
+    on this same B200 -- oracle.ecapa_oracle.embed (the functional restatement of SpeakerEncoder.forward, pinned to the
+    reference to <= 1e-5) moved to CUDA: cuFFT + cuBLAS + cuDNN kernels, fp32 and under torch.autocast(bfloat16).
+    Baseline leg only (nothing under speakerverification_b200/ can import it).  Same model (C=1024), same 3 s crops,
+    same launch size; CUDA-event timed."""
+    from oracle import ecapa_oracle as eo
+    from speakerverification_b200 import synth
+    sd = {k: torch.as_tensor(v).to(device) for k, v in synth.ecapa_state_dict(CH, N_OUT).items()}
+    wav = synth_waves(batch, device, seed=7)
+    out = {"batch": batch, "model": "ECAPA-TDNN C=1024, 3 s crops, torch %s eager (cuFFT / cuBLAS / cuDNN)" % torch.__version__}
+    for name, ctxmgr in (("fp32", None), ("autocast_bf16", torch.autocast("cuda", dtype=torch.bfloat16))):
+        def run():
+            if ctxmgr is None:
+                return eo.embed(wav, sd)
+            with ctxmgr:
+                return eo.embed(wav, sd)
+        try:
+            for _ in range(2):
+                e = run()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                e = run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            out[name] = {"value": batch / (ms * 1e-3), "unit": "embeddings/s", "ms_per_launch": ms,
+                         "finite": bool(torch.isfinite(e.float()).all())}
+        except Exception as ex:                                  # e.g. out of memory on a shared box: report, do not fail
+            out[name] = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+        torch.cuda.empty_cache()
+    return out
+
+
+def api_distributed_check(ctx, precision):
+    """evaluateFromList(distributed=True) on `world` ranks returns, on rank 0, the scores of the
+    single-GPU call (bit-equal for cosine, <= 1e-6 for AS-norm) and ([], [], []) on the other ranks, as
+    src/model.py:400-450 prescribes.  C=512 model, 24 synthetic wav files, 200 trials, 300-row cohort."""
+    from scipy.io import wavfile
+    from speakerverification_b200 import synth
+    from speakerverification_b200.model import ModelHandling, SpeakerEncoder, WrappedModel
+    rank, world, dist, device = ctx["rank"], ctx["world"], ctx["dist"], ctx["device"]
+    root = "/tmp/svb_bench_api"
+    ch = [512, 512, 512, 512, 1536]
+    margs = dict(model_args("cuda", precision), channels=ch, save_folder=root)
+    waves, spk = synth.utterance_set(6, 4, L + 1)
+    lab, ti, tj = synth.trial_list(spk, 200)
+    names = [os.path.join(root, "utt%03d.wav" % i) for i in range(len(waves))]
+    if rank == 0:
+        os.makedirs(root, exist_ok=True)
+        for n, w in zip(names, waves):
+            wavfile.write(n, 16000, w)
+        with open(os.path.join(root, "trials.txt"), "w") as f:
+            for a, i, j in zip(lab, ti, tj):
+                f.write("%d %s %s\n" % (a, names[i], names[j]))
+        coh, _ = synth.scoring_embeddings(300, 50, seed=5)
+        np.save(os.path.join(root, "cohorts.npy"), coh)
+    dist.barrier()
+    net = WrappedModel(SpeakerEncoder(**margs))
+    h = ModelHandling(net, **dict(margs, T_max=10))
+    sd = net.module.state_dict()
+    for k, v in synth.ecapa_state_dict(ch, N_OUT).items():
+        sd[k].copy_(torch.as_tensor(v))
+    net.eval()
+    res = {}
+    ok_empty = True
+    for mode in ("cosine", "norm"):
+        sc, lb, tr = h.evaluateFromList(os.path.join(root, "trials.txt"), distributed=True, dataloader_options={"num_workers": 0},
+                                        cohorts_path=os.path.join(root, "cohorts.npy"), num_eval=2, scoring_mode=mode, top=200)
+        if rank == 0:
+            s1, l1, t1 = h.evaluateFromList(os.path.join(root, "trials.txt"), distributed=False,
+                                            dataloader_options={"num_workers": 0},
+                                            cohorts_path=os.path.join(root, "cohorts.npy"), num_eval=2, scoring_mode=mode, top=200)
+            d = float(np.abs(np.asarray(sc) - np.asarray(s1)).max())
+            res[mode] = {"max_abs_dev_vs_single_gpu": d, "bit_equal": bool(np.array_equal(np.asarray(sc), np.asarray(s1))),
+                         "labels_trials_equal": lb == l1 and tr == t1, "n_trials": len(sc)}
+        else:
+            ok_empty = ok_empty and (sc, lb, tr) == ([], [], [])
+    flag = torch.tensor([1 if ok_empty else 0], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank != 0:
+        return None
+    res["other_ranks_returned_empty"] = bool(flag.item())
+    res["passed"] = bool(res["cosine"]["bit_equal"] and res["norm"]["max_abs_dev_vs_single_gpu"] <= 1e-6 and
+                         res["cosine"]["labels_trials_equal"] and res["other_ranks_returned_empty"])
+    return res
+
+
+SUB_KEYS = ("metric", "value", "unit", "steps", "ms_per_step", "dtype", "config", "e2e", "roofline", "gpu_launches",
+            "per_rank_ms_per_step", "strong_scaling", "step_tensor", "cpu_baseline", "parity_check")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="svb", choices=["svb", "reference"])
+    ap.add_argument("--utts", type=int, default=10000)
+    ap.add_argument("--batch-rows", type=int, default=592)   # 4 x 148: whole waves of the per-utterance chain kernel
+    ap.add_argument("--precision", default="f16", choices=["f16", "bf16", "fp32"])   # 'bf16' = the 16-bit mode's alias
+    ap.add_argument("--no-e2e", action="store_true")
+    # 'all' (default): the headline line is configs[1] (embed) and carries configs[2] / [3] / [4] as sub-objects
+    ap.add_argument("--workload", default="all", choices=["all", "embed", "scoring", "rawnet2", "eval"])
+    ap.add_argument("--e2e-rows", type=int, default=296)
+    ap.add_argument("--eval-utts", type=int, default=2000)
+    ap.add_argument("--eval-trials", type=int, default=100000)
+    ap.add_argument("--score-utts", type=int, default=200000)
+    ap.add_argument("--score-cohort", type=int, default=20000)
+    ap.add_argument("--score-trials", type=int, default=1000000)
+    ap.add_argument("--no-library-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.precision == "bf16":
+        args.precision = "f16"
+    quiet_stdout()
+    if args.impl == "reference":
+        if args.workload == "all":
+            args.workload = "embed"
+        return run_reference(args)
+
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    ctx = {"device": device, "rank": rank, "world": world, "local": local, "dist": dist}
+    sub_steps = max(10, min(args.steps, 10))
+
+    def finish(line):
+        if rank == 0 and line is not None:
+            emit(json.dumps(line))
+        if world > 1:
+            dist.destroy_process_group()
+
+    if args.workload == "scoring":
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        res = run_scoring(args, device, rank, world, dist, args.steps)
+        if rank == 0:
+            res["warmup"] = 3
+            res["clocks"] = sampler.stop()
+        return finish(res if rank == 0 else None)
+    if args.workload == "eval":
+        return finish(run_eval(args, device, rank, world, dist, args.steps))
+    if args.workload in ("embed", "rawnet2"):
+        line = bench_encoder(args, ctx, rawnet=args.workload == "rawnet2")
+        if line is not None and world == 1 and args.workload == "embed":
             rate, n, dt = cpu_reference_rate(64, min_seconds=12.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}
-        emit(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+        return finish(line)
+
+    # ---- default: every BASELINE.json config in one driver-observed line
+    line = bench_encoder(args, ctx, rawnet=False)                       # configs[1]: the headline keys
+    torch.cuda.empty_cache()
+    ev = run_eval(args, device, rank, world, dist, sub_steps)           # configs[2]
+    torch.cuda.empty_cache()
+    rn = bench_encoder(args, ctx, rawnet=True)                          # configs[3]
+    torch.cuda.empty_cache()
+    sc = run_scoring(args, device, rank, world, dist, sub_steps, full_line=True)   # configs[4]
+    torch.cuda.empty_cache()
+    api = api_distributed_check(ctx, args.precision) if world > 1 else None
+    if rank == 0:
+        line["eval"] = {k: ev[k] for k in SUB_KEYS if k in ev}
+        line["rawnet2"] = {k: rn[k] for k in SUB_KEYS if k in rn}
+        line["scoring"] = {k: sc[k] for k in SUB_KEYS if k in sc}
+        if api is not None:
+            line["api_distributed_check"] = api
+        if world == 1:
+            if not args.no_library_baseline:
+                lib = gpu_library_baseline(device, args.batch_rows)
+                for k in ("fp32", "autocast_bf16"):
+                    if "value" in lib.get(k, {}):
+                        lib[k]["svb_speedup"] = line["value"] / lib[k]["value"]
+                line["gpu_library_baseline"] = lib
+            rate, n, dt = cpu_reference_rate(64, min_seconds=12.0)
+            line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "%d x 3 s utterances, batch 16, torch fp32 oracle port (%.1f s)" % (n, dt)}
+    finish(line)
 
 
 if __name__ == "__main__":

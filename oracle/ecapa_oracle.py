@@ -62,14 +62,14 @@ def power_mel(x, sr=16000, n_fft=512, win_length=400, hop_length=160, n_mels=80,
     pad = n_fft // 2
     xp = F.pad(x.unsqueeze(1), (pad, pad), mode="reflect").squeeze(1)
     frames = xp.unfold(-1, n_fft, hop_length)                       # [B, T, n_fft]
-    win = torch.zeros(n_fft)
+    win = torch.zeros(n_fft, device=x.device)
     lo = (n_fft - win_length) // 2
-    win[lo:lo + win_length] = torch.hamming_window(win_length, periodic=True)
+    win[lo:lo + win_length] = torch.hamming_window(win_length, periodic=True).to(x.device)
     spec = torch.fft.rfft(frames * win, dim=-1)
     power = spec.real ** 2 + spec.imag ** 2                         # [B, T, n_fft/2+1]
     if fb is None:
         fb = mel_filterbank(n_fft // 2 + 1, f_min, f_max if f_max else sr / 2.0, n_mels, sr)
-    return torch.matmul(power, fb).transpose(1, 2).contiguous()
+    return torch.matmul(power, fb.to(x.device)).transpose(1, 2).contiguous()
 
 
 def log_cmn(mel):
@@ -150,7 +150,7 @@ def attentive_stats_pool(x, sd, p, eps=1e-12):
         std = torch.sqrt((m * (x - mean.unsqueeze(2)).pow(2)).sum(2).clamp(eps))
         return mean, std
 
-    m0 = torch.full((x.shape[0], 1, L), 1.0 / L)
+    m0 = torch.full((x.shape[0], 1, L), 1.0 / L, device=x.device, dtype=x.dtype)
     mean, std = stats(x, m0)
     attn = torch.cat([x, mean.unsqueeze(2).expand(-1, -1, L), std.unsqueeze(2).expand(-1, -1, L)], 1)
     attn = tdnn_block(attn, sd, p + "tdnn.", 1, "relu")
@@ -192,7 +192,8 @@ def ecapa_forward(feat, sd, dilations=(1, 2, 3, 4, 1), prefix="__S__.", stages=N
 
 
 def embed(wave, sd, stages=None, **fb_kw):
-    """src/model.py:104-129: waveform rows [B, L] -> embeddings [B, nOut] (fp32, CPU)."""
+    """src/model.py:104-129: waveform rows [B, L] -> embeddings [B, nOut] (fp32; on the device `wave` and `sd` live on:
+    the CPU for parity work, a CUDA device for bench.py's library-kernel baseline leg)."""
     with torch.no_grad():
         wave = torch.as_tensor(wave, dtype=torch.float32)
         mel = power_mel(wave, **fb_kw)

@@ -109,14 +109,14 @@ def rawnet2_forward(wave, sd, prefix="__S__.", stages=None, sample_rate=16000):
     return out.squeeze()
 
 
-# ------------------------------------------------------------------ bf16-operand emulation
+# ------------------------------------------------------------------ 16-bit-operand emulation
 def _r(t):
-    return t.to(torch.bfloat16).to(torch.float32)
+    return t.to(torch.float16).to(torch.float32)
 
 
-def rawnet2_forward_bf16emu(wave, sd, prefix="__S__.", sample_rate=16000):
-    """The same network with every stored activation and every tensor-core weight rounded to bfloat16 exactly
-    where libsvb's bf16 mode rounds (fp32 accumulation, fp32 BN / AFMS / GRU-gate arithmetic, fp32-grade GRU
+def rawnet2_forward_f16emu(wave, sd, prefix="__S__.", sample_rate=16000):
+    """The same network with every stored activation and every tensor-core weight rounded to IEEE half exactly
+    where libsvb's 16-bit mode rounds (fp32 accumulation, fp32 BN / AFMS / GRU-gate arithmetic, fp32-grade GRU
     recurrence).  It separates two things the fp32 comparison mixes: whether
     the kernels compute what bf16 operands imply (this function, tight tolerance) and how far bf16 operands drift
     from fp32 on a given checkpoint (a property of the checkpoint, loose tolerance)."""

@@ -19,6 +19,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -44,10 +46,17 @@ static const char* RN_NAME[NB] = {"layer1.0", "layer2.0", "layer3.0", "layer4.0"
 // ------------------------------------------------------------------ elementwise kernels
 __device__ __forceinline__ float lrelu03(float x) { return x > 0.f ? x : 0.3f * x; }
 
-// 8 consecutive channels of one row: hi (+ lo) planes -> fp32
+// 8 consecutive channels of one row -> fp32: bf16 hi + lo planes (planes == 2, fp32-grade mode) or ONE plane of IEEE
+// half (planes == 1, 16-bit mode; the CPU model of the data flow puts its trial-score deviation at 1.4e-3 against
+// 1.0e-2 for bf16 operands, profiles/r02_precision.md)
 __device__ __forceinline__ void load8(const bf16* p, int planes, int plane_cols, float (&v)[8]) {
   const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+  if (planes == 1) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { v[2 * q] = f16_lo_f(w[q]); v[2 * q + 1] = f16_hi_f(w[q]); }
+    return;
+  }
 #pragma unroll
   for (int q = 0; q < 4; ++q) { v[2 * q] = bf16_lo_f(w[q]); v[2 * q + 1] = bf16_hi_f(w[q]); }
   if (planes == 2) {
@@ -60,7 +69,7 @@ __device__ __forceinline__ void load8(const bf16* p, int planes, int plane_cols,
 __device__ __forceinline__ void store8(bf16* p, int planes, int plane_cols, const float (&v)[8]) {
   uint32_t hi[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) hi[q] = pack_bf16x2(v[2 * q], v[2 * q + 1]);
+  for (int q = 0; q < 4; ++q) hi[q] = planes == 1 ? pack_f16x2(v[2 * q], v[2 * q + 1]) : pack_bf16x2(v[2 * q], v[2 * q + 1]);
   *reinterpret_cast<uint4*>(p) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
   if (planes == 2) {
     uint32_t lo[4];
@@ -100,9 +109,10 @@ rn_ln_kernel(const float* __restrict__ wav, long long wav_ld, int L, int Lp, con
   for (int i = tid; i < Lp; i += 1024) {
     float v = 0.f;
     if (i < L) v = gamma[i] * (x[i] - mean) * inv + beta[i];
+    if (planes == 1) { reinterpret_cast<__half*>(hi)[i] = __float2half_rn(v); continue; }
     const bf16 h = __float2bfloat16_rn(v);
     hi[i] = h;
-    if (planes == 2) hi[i + plane_dist] = __float2bfloat16_rn(v - __bfloat162float(h));
+    hi[i + plane_dist] = __float2bfloat16_rn(v - __bfloat162float(h));
   }
 }
 
@@ -323,7 +333,7 @@ static bf16* make_conv(Rawnet2* e, const TensorMap& tm, const std::string& key, 
   if (!w) return nullptr;
   bf16* d = dalloc<bf16>(e, static_cast<size_t>(cout) * k * e->planes * cin);
   if (d == nullptr) { set_error("out of device memory"); return nullptr; }
-  if (pack_conv_weight(w, cout, cin, k, cin, e->planes, d, 0)) return nullptr;
+  if (pack_conv_weight(w, cout, cin, k, cin, e->planes, d, 0, e->planes == 1 ? 1 : 0)) return nullptr;
   return d;
 }
 
@@ -371,9 +381,14 @@ static int build_sinc(Rawnet2* e, const float* low_d, const float* band_d, int F
         const int j = 3 * jg + ph;
         for (int k = 0; k < K; ++k) {
           const float v = h[static_cast<size_t>(f) * K + k];
+          if (planes == 1) {       // 16-bit mode: IEEE half (shares the activations' format)
+            const __half hv = __float2half(v);
+            memcpy(&w[n * planes * SINC_K + j + k], &hv, sizeof(hv));
+            continue;
+          }
           const bf16 hi = __float2bfloat16(v);
           w[n * planes * SINC_K + j + k] = hi;
-          if (planes == 2) w[n * planes * SINC_K + SINC_K + j + k] = __float2bfloat16(v - __bfloat162float(hi));
+          w[n * planes * SINC_K + SINC_K + j + k] = __float2bfloat16(v - __bfloat162float(hi));
         }
       }
   e->sinc_w = dalloc<bf16>(e, w.size());
@@ -430,7 +445,7 @@ int rawnet2_create(int n_samples, int n_out, int gru_node, int sample_rate, int 
     e->w_ih = dalloc<bf16>(e, static_cast<size_t>(3 * H) * e->planes * 512);
     e->w_hh = dalloc<bf16>(e, static_cast<size_t>(3 * H) * 2 * H);
     if (!e->w_ih || !e->w_hh) { set_error("out of device memory"); break; }
-    if (pack_conv_weight(wih, 3 * H, 512, 1, 512, e->planes, e->w_ih, 0)) break;
+    if (pack_conv_weight(wih, 3 * H, 512, 1, 512, e->planes, e->w_ih, 0, e->planes == 1 ? 1 : 0)) break;
     if (pack_conv_weight(whh, 3 * H, H, 1, H, 2, e->w_hh, 0)) break;     // the recurrence is always fp32 grade
     e->b_ih = dcopy(e, bih, 3 * H); e->b_hh = dcopy(e, bhh, 3 * H);
     e->fcg_w = dcopy(e, fw, static_cast<size_t>(n_out) * H); e->fcg_b = dcopy(e, fb, n_out);
@@ -556,12 +571,10 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
 
   // ---- front: LayerNorm -> sinc GEMM (+abs, maxpool3, first_bn, lrelu, layer1.bn1, lrelu)
   const long long plane_dist = (static_cast<long long>(B) * e->Lp + 63) / 64 * 64;
-  // The normalised signal is written as hi|lo planes.  fp32-grade mode runs the three split passes; bf16 mode
-  // uses the hi plane only (one pass).  Measured on the synthetic speech set (tools/rawnet_bf16_err.py): adding the
-  // lo(A) pass lowers the front-end error from 3.3e-3 to 2.6e-3 rms (the rest is the bf16 rounding of the stored
-  // output) and does not change the embedding error, for +0.9 ms per 256 utterances; SVB_SINC_PASSES=2 enables it.
+  // The normalised signal is written as bf16 hi|lo planes (fp32-grade mode, three split passes) or as one plane of
+  // IEEE half (16-bit mode, one pass).
   SVB_CUDA_OK(cudaMemsetAsync(xn, 0, (static_cast<size_t>(B) * e->Lp * 2 + 4096) * 2, st));
-  rn_ln_kernel<<<B, 1024, 0, st>>>(wav, wav_ld, e->L, e->Lp, e->ln_g, e->ln_b, 1e-6f, xn, plane_dist, 2);
+  rn_ln_kernel<<<B, 1024, 0, st>>>(wav, wav_ld, e->L, e->Lp, e->ln_g, e->ln_b, 1e-6f, xn, plane_dist, P);
   count_launch();
   // the first block's padding rows must be zero: the sinc epilogue writes valid rows only
   rn_zero_halo_kernel<<<2 * B, 64, 0, st>>>(ab[0], P * 128, e->T[0], B);
@@ -569,7 +582,7 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
   {
     RnGemmParams g{};
     g.M = B * e->Mu; g.N = 16 * 128 * 3; g.kc_per_tap = SINC_K / 64; g.num_taps = 1; g.tap_off[0] = 0;
-    g.num_pass = P == 2 ? 3 : (getenv("SVB_SINC_PASSES") ? atoi(getenv("SVB_SINC_PASSES")) : 1); g.a_plane_cols = static_cast<int>(plane_dist); g.w_planes = P;
+    g.num_pass = P == 2 ? 3 : 1; g.a_plane_cols = static_cast<int>(plane_dist); g.w_planes = P;
     g.T = e->T[0]; g.Tp = e->T[0] + 2; g.Mu = e->Mu; g.B = B;
     g.s1 = e->fbn_s; g.h1 = e->fbn_h; g.s2 = e->blk[0].s1; g.h2 = e->blk[0].h1;
     g.out = xb[0]; g.out_ld = PX * 128; g.out_planes = PX; g.out_plane_cols = 128;
@@ -629,6 +642,7 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     GemmOperands ops{};
     ops.a = ab[cur]; ops.lda = P * 512; ops.a_cols = P * 512;
     ops.w = e->w_ih; ops.w_rows = 3 * H; ops.w_cols = P * 512;
+    ops.a_f16 = ops.w_f16 = (P == 1) ? 1 : 0;
     GemmParams g{};
     g.M = B * (Tg + 2); g.N = 3 * H; g.kc_per_tap = 512 / 64; g.num_taps = 1; g.tap_off[0] = 0;
     g.num_pass = P == 2 ? 3 : 1; g.a_plane_cols = 512; g.w_planes = P;

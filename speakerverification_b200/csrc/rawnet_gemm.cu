@@ -57,12 +57,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "memory");
 }
 
-// n consecutive fp32 values -> bf16 hi (and lo = v - hi) planes at dst / dst + plane_cols (N multiple of 8)
+// n consecutive fp32 values -> bf16 hi and lo = v - hi planes at dst / dst + plane_cols (planes == 2), or ONE plane of
+// IEEE half (planes == 1, the 16-bit mode); N multiple of 8
 template <int N>
 __device__ __forceinline__ void store_planes(bf16* dst, int planes, int plane_cols, const float (&v)[N]) {
   uint32_t hi[N / 2];
 #pragma unroll
-  for (int i = 0; i < N / 2; ++i) hi[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+  for (int i = 0; i < N / 2; ++i)
+    hi[i] = planes == 1 ? pack_f16x2(v[2 * i], v[2 * i + 1]) : pack_bf16x2(v[2 * i], v[2 * i + 1]);
   uint4* d = reinterpret_cast<uint4*>(dst);
 #pragma unroll
   for (int i = 0; i < N / 8; ++i) d[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
@@ -158,7 +160,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      // single plane = IEEE half on both operands (a kind::f16 UMMA cannot mix formats); split mode = bf16 planes
+      const uint32_t idesc = umma_idesc_f16(BLOCK_M, BN, p.w_planes == 1, p.w_planes == 1);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -269,8 +272,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
-                v[8 * i + 2 * q] = __uint_as_float(r[8 * i + 2 * q]) + bf16_lo_f(w[q]);
-                v[8 * i + 2 * q + 1] = __uint_as_float(r[8 * i + 2 * q + 1]) + bf16_hi_f(w[q]);
+                v[8 * i + 2 * q] = __uint_as_float(r[8 * i + 2 * q]) + (p.add_planes == 1 ? f16_lo_f(w[q]) : bf16_lo_f(w[q]));
+                v[8 * i + 2 * q + 1] = __uint_as_float(r[8 * i + 2 * q + 1]) + (p.add_planes == 1 ? f16_hi_f(w[q]) : bf16_hi_f(w[q]));
               }
             }
             if (p.add_planes == 2) {

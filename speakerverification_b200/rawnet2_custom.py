@@ -67,8 +67,9 @@ class RawNet2Engine:
     """Packed RawNet2 weights + forward (svb_rawnet2_*).  `state` maps reference state-dict names (without
     the '__S__.' prefix) to fp32 CUDA tensors."""
 
-    def __init__(self, state, n_samples, n_out, gru_node=1024, sample_rate=16000, precision="bf16"):
-        assert precision in ("bf16", "fp32")
+    def __init__(self, state, n_samples, n_out, gru_node=1024, sample_rate=16000, precision="f16"):
+        from .engine import normalize_precision
+        precision = normalize_precision(precision)
         self.n_samples, self.n_out, self.precision = int(n_samples), int(n_out), precision
         cfg = nv.SvbRawnet2Cfg(self.n_samples, self.n_out, int(gru_node), int(sample_rate), 1 if precision == "fp32" else 0)
         keep, names, ptrs = [], [], []
@@ -132,7 +133,8 @@ class RawNet2Engine:
         T = self.frames(level)
         planes = self.planes
         n = B * (T + 2) * planes * channels
-        v = self._ws[off:off + 2 * n].view(torch.bfloat16).view(B, T + 2, planes, channels).float().sum(2)
+        dt = torch.bfloat16 if planes == 2 else torch.float16        # bf16 hi|lo planes / one plane of IEEE half
+        v = self._ws[off:off + 2 * n].view(dt).view(B, T + 2, planes, channels).float().sum(2)
         return v[:, 1:T + 1]
 
     def __del__(self):
@@ -171,7 +173,8 @@ class RawNet2(nn.Module):
             # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
             # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
             precision = kwargs.get("svb_precision") or "fp32"
-        self.precision = precision
+        from .engine import normalize_precision
+        self.precision = normalize_precision(precision)
         self._engine, self._fingerprint = None, None
         for p in self.parameters():
             p.requires_grad_(False)
@@ -196,7 +199,8 @@ class RawNet2(nn.Module):
         return self._engine
 
     def set_precision(self, precision):
-        assert precision in ("bf16", "fp32")
+        from .engine import normalize_precision
+        precision = normalize_precision(precision)
         if precision != self.precision:
             self.precision, self._engine = precision, None
 

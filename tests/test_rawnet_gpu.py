@@ -47,7 +47,7 @@ NEXT_BN = ["layer2.0.bn1.", "layer3.0.bn1.", "layer4.0.bn1.", "layer4.1.bn1.", "
 COUT = [128, 128, 256, 256, 256, 512, 512, 512]
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("bf16", 0.08)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("f16", 4e-3)])
 def test_front_end(setup, precision, tol):
     """LayerNorm + sinc conv + |.| + maxpool3 + first_bn + lrelu (RawNet2_custom.py:171-176) and layer1's bn1+lrelu."""
     sd, state, waves, st, _ = setup
@@ -62,6 +62,7 @@ def test_front_end(setup, precision, tol):
     got = eng.stage(2, "x0", 0, 128).cpu().numpy()
     assert got.shape == want.shape == (2, 21250, 128)
     scale = np.abs(want).max()
+    print("RawNet2 front end", precision, "max err / scale", np.abs(got - want).max() / scale)
     assert np.abs(got - want).max() <= tol * scale, np.abs(got - want).max() / scale
     got_a = eng.stage(2, "a0", 0, 128).cpu().numpy()
     want_a = _pre(st["front"], sd, "__S__.layer1.0.bn1.")
@@ -116,24 +117,30 @@ def test_rawnet2_fp32_matches_reference(setup, golden_rawnet):
     assert np.abs(s - golden_rawnet["scores_cos"]).max() <= 1e-4, np.abs(s - golden_rawnet["scores_cos"]).max()
 
 
-def test_rawnet2_bf16_mode(setup, golden_rawnet):
-    """bf16 mode.  (1) Against the oracle with bf16 rounding at the same points (rawnet2_forward_bf16emu): the
-    kernels compute exactly what bf16 operands imply -- cos >= 0.9995 (the randomly initialised network amplifies
-    any perturbation ~1.4x per residual block, tools/rawnet_bf16_err.py, so summation-order noise is visible).
-    (2) Against the fp32 reference: bounded drift; on this checkpoint the drift of bf16 operands themselves
-    (emulation vs fp32 reference) is of the same size, i.e. it is the checkpoint's conditioning, not the kernels."""
-    from oracle import rawnet_oracle as ro
+def test_rawnet2_f16_mode(setup, golden_rawnet):
+    """16-bit mode (IEEE-half activations and weights, the mode bench.py times): (1) cosine trial scores agree with the
+    reference's own scores to <= 2e-3 (north-star 16-bit tolerance; the CPU model of the data flow, oracle
+    rawnet2_forward_f16emu, says 1.4e-3 -- bf16 operands gave 1.0e-2, which is why the mode moved to fp16); (2) the
+    kernels compute what fp16 operands imply: cos >= 0.9999 against the emulation with rounding at the same points."""
+    from oracle import rawnet_oracle as ro, synth
+    from speakerverification_b200 import utils as U
     sd, state, waves, st, emb_oracle = setup
-    eng = _engine(state, "bf16")
-    got = eng.forward(torch.from_numpy(waves[:4]).cuda()).cpu().numpy()
-    with torch.no_grad():
-        emu = ro.rawnet2_forward_bf16emu(waves[:4], sd).numpy()
-    ref = golden_rawnet["emb_batch"][:4]
+    eng = _engine(state, "f16")
+    got_t = eng.forward(torch.from_numpy(waves).cuda())
+    got = got_t.cpu().numpy()
+    ref = golden_rawnet["emb_batch"]
     cos = lambda a, b: (a * b).sum(1) / np.linalg.norm(a, axis=1) / np.linalg.norm(b, axis=1)
-    assert cos(got, emu).min() >= 0.9995, cos(got, emu)
-    drift_kernel, drift_emu = 1 - cos(got, ref), 1 - cos(emu, ref)
-    assert cos(got, ref).min() >= 0.99, cos(got, ref)
-    assert drift_kernel.max() <= 3 * drift_emu.max() + 1e-4, (drift_kernel, drift_emu)
+    spk = np.repeat(np.arange(4), 4)
+    lab, ti, tj = synth.trial_list(spk, 120)
+    s = U.cosine_trials(got_t.unsqueeze(1).contiguous(), torch.from_numpy(ti.astype(np.int32)).cuda(),
+                        torch.from_numpy(tj.astype(np.int32)).cuda()).cpu().numpy()
+    dev = np.abs(s - golden_rawnet["scores_cos"]).max()
+    print("RawNet2 f16: min cos vs reference", cos(got, ref).min(), "max trial-score dev", dev)
+    assert dev <= 2e-3, dev
+    assert cos(got, ref).min() >= 0.9995, cos(got, ref)
+    with torch.no_grad():
+        emu = ro.rawnet2_forward_f16emu(waves[:4], sd).numpy()
+    assert cos(got[:4], emu).min() >= 0.9999, cos(got[:4], emu)
 
 
 def test_rawnet2_batch_invariance_and_api(setup):
