@@ -243,6 +243,9 @@ int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int norma
 size_t svb_asnorm_workspace_bytes(int U, int N, int D);
 int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu,
                      float* sigma, void* ws, size_t ws_bytes, void* stream);
+/* Diagnostic, synchronous: rows of the last svb_asnorm_stats call on `ws` that the fused pre-filter could not prove and
+ * the exact fix-up kernel redid (-1: the call used the store-and-select path). */
+int svb_asnorm_fixup_rows(const void* ws, int U, int N, int D, int topk);
 int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b,
                       int64_t n_trials, const float* mu, const float* sigma, float* out, void* stream);
 

@@ -110,6 +110,7 @@ _EXTRA_SIGS = {
     "svb_enrol_nearest": ([_vp, _vp, _i32, _i32, _i32, _i32, _c.c_float, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
     "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
+    "svb_asnorm_fixup_rows": ([_vp, _i32, _i32, _i32, _i32], _i32),
     "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),
     "svb_rawnet2_create": ([_c.POINTER(SvbRawnet2Cfg), _c.POINTER(_c.c_char_p), _c.POINTER(_vp), _i32, _pp], _i32),
     "svb_rawnet2_destroy": ([_vp], None),

@@ -38,6 +38,7 @@ long long ecapa_ws_offset(const Ecapa*, const Batch*, const char*);
 int ecapa_forward(const Ecapa*, const Fbank*, const Batch*, const float*, int, void*, size_t, float*, int, int,
                   cudaStream_t);
 int cosine_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float*, cudaStream_t);
+int asnorm_fixup_rows(const void*, int, int, int, int);
 int pnorm_trials(const float*, int, int, const int32_t*, const int32_t*, long long, float, float, int, float*, cudaStream_t);
 int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
 int enrol_nearest(const float*, const float*, int, int, int, int, float, int, float*, float*, int32_t*, cudaStream_t);
@@ -315,6 +316,8 @@ int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int 
   SVB_CHECK(emean && cohort && mu && sigma && U >= 1 && N >= 1 && D >= 1, "bad argument");
   return asnorm_stats(emean, U, cohort, N, D, topk, mu, sigma, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
+int svb_asnorm_fixup_rows(const void* ws, int U, int N, int D, int topk) { return asnorm_fixup_rows(ws, U, N, D, topk); }
+
 int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b, int64_t n_trials,
                       const float* mu, const float* sigma, float* out, void* stream) {
   if (check_device()) return -1;

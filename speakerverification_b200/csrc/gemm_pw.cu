@@ -35,6 +35,7 @@ static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 static constexpr int OUT_BOX_BYTES = 32 * 64 * 2;   // EW = 8: one warp's 32 rows x 64 bf16 columns
 static constexpr int OUT_BOX64_BYTES = 32 * 32 * 2; // EW = 16: one warp's 32 rows x 32 bf16 columns
 static constexpr int ACT_RAW_F32 = 3;               // epilogue variant: no bias/act/BN, fp32 accumulators stored as is
+static constexpr int ACT_FILTER = 5;                // epilogue variant: nothing is stored but the accumulators >= a per-row threshold
 static constexpr int ACT_GELU_ERF = 4;              // GELU through erff: the k > 1 layer (block 0) keeps gemm_tc's exact numerics
 __device__ __forceinline__ float gelu_erf_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
@@ -69,6 +70,9 @@ struct PwParams {
   int w_f16;             // the W operand is IEEE half (b_format = F16) instead of bf16
   int a_f16;             // the A operand is IEEE half (a_format = F16): activations of the 16-bit mode
   int a_plane_rows;      // > 0: the lo plane of A row r is row r + a_plane_rows of the same map (K-packed block 0)
+  // ACT_FILTER (AS-norm cohort scores, score.cu): accumulators >= filt_thr[row] of columns < filt_ncols are appended
+  // to the row's candidate list cand[row * filt_cap + slot], slot = atomicAdd(&filt_cnt[row], hits)
+  const float* filt_thr; unsigned* filt_cnt; float* filt_cand; int filt_cap, filt_ncols;
 };
 
 __device__ __forceinline__ float tanh_exact(float x) {
@@ -218,13 +222,13 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         else umma_commit(smem_u32(&tfull_bar[acc]));
       }
     }
-  } else if (warp >= 4 && EW == 16) {
+  } else if (warp >= 4 && EW == 16 && ACT != ACT_FILTER) {
     // ===================================================== epilogue, 16 warps: quadrant = warp % 4; the two warps of a
     // PAIR (same quadrant, column groups 2P and 2P+1) cover 128 columns and fill, per unit, the left / right half of ONE
     // 32 x 64 box with 128-byte rows (128B swizzle), stored by one TMA instruction: 128-byte store requests instead of
     // the 64-byte rows of per-warp 32 x 32 boxes (the L2 path of these kernels is request bound: every extra request
     // stream tried, e.g. the L2 prefetch, cost 8-10 %).  TMEM -> regs -> bias/GELU/BN -> bf16 -> box -> TMA store.
-    static_assert(EW != 16 || (BN == 256 && (ACT == ACT_GELU || ACT == ACT_GELU_ERF) && !RBT),
+    static_assert(EW != 16 || ACT == ACT_FILTER || (BN == 256 && (ACT == ACT_GELU || ACT == ACT_GELU_ERF) && !RBT),
                   "the 16-warp epilogue serves the GELU BN=256 instances");
     static_assert(!STATS || (EW == 16 && !HILO), "fused column statistics: 16-warp epilogue, single bf16 plane");
     const int ew = warp - 4;
@@ -374,7 +378,8 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================================================== epilogue: TMEM -> regs -> swizzled smem -> TMA store
     const int ew = warp - 4;
     const int quad = ew & 3;   // == warp % 4: the TMEM lane quadrant this warp may read
-    const int half = ew >> 2;  // column half of the tile
+    const int half = ew >> 2;  // column half of the tile (ACT_FILTER with EW = 16: column quarter)
+    constexpr int PARTS = EW / 4;      // warps per lane quadrant = column parts of a tile
     const uint32_t my_box = out_base + ew * OUT_BOX_BYTES;
     const uint32_t my_row = my_box + lane * 128;
     const int sw = lane & 7;
@@ -390,10 +395,61 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int utt = (row < p.M) ? p.row_meta[row].utt : -1;
         rb = p.rowbias + static_cast<long long>(utt < 0 ? 0 : utt) * p.rowbias_ld;
       }
+      float f_thr = INFINITY;      // ACT_FILTER: this lane's row threshold (rows past M never pass)
+      long long f_row = 0;
+      if (ACT == ACT_FILTER) {
+        f_row = static_cast<long long>(m0) + quad * 32 + lane;
+        if (f_row < p.M) f_thr = __ldg(p.filt_thr + f_row);
+      }
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
+      if (ACT == ACT_FILTER) {
+        // Fused top-K pre-filter: the score tile never leaves the SM.  Pass 1 reads this thread's BN / 2 accumulators
+        // of its row and keeps only hit MASKS; one atomic per (row, tile half) reserves the slots; pass 2 re-reads the
+        // strips from TMEM (on chip, cheap) and stores the ~2.5 % of the scores that pass.  A single atomic round trip
+        // per tile hides under the next tile's MMAs; one per 32-column strip (first version) made the epilogue the
+        // bottleneck (622 TFLOP/s against 890 for the plain store epilogue).
+        constexpr int NSTRIP = BN / PARTS / 32;              // 32-column strips per thread
+        uint32_t masks[NSTRIP];
+        int total = 0;
+#pragma unroll
+        for (int st = 0; st < NSTRIP; ++st) {
+          const int col0 = half * (BN / PARTS) + st * 32;
+          uint32_t r[32];
+          tmem_ld32(tmem_base + acc * BN + col0 + (static_cast<uint32_t>(quad * 32) << 16), r);
+          tmem_ld_wait();
+          uint32_t mask = 0;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mask |= (__uint_as_float(r[i]) >= f_thr ? 1u : 0u) << i;
+          const int ncols = p.filt_ncols - (n0 + col0);      // valid (non-padding) columns of this strip
+          if (ncols < 32) mask &= ncols <= 0 ? 0u : ((1u << ncols) - 1u);
+          masks[st] = mask;
+          total += __popc(mask);
+        }
+        if (__any_sync(0xffffffffu, total > 0)) {            // tcgen05.ld is warp collective: uniform branch
+          uint32_t slot = 0;
+          if (total > 0) slot = atomicAdd(p.filt_cnt + f_row, static_cast<unsigned>(total));
+          float* dst = p.filt_cand + f_row * p.filt_cap;
+#pragma unroll
+          for (int st = 0; st < NSTRIP; ++st) {
+            if (!__any_sync(0xffffffffu, masks[st] != 0u)) continue;
+            const int col0 = half * (BN / PARTS) + st * 32;
+            uint32_t r[32];
+            tmem_ld32(tmem_base + acc * BN + col0 + (static_cast<uint32_t>(quad * 32) << 16), r);
+            tmem_ld_wait();
+            const uint32_t mask = masks[st];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              if ((mask >> i) & 1u) {
+                if (slot < static_cast<uint32_t>(p.filt_cap)) dst[slot] = __uint_as_float(r[i]);
+                ++slot;
+              }
+            }
+          }
+        }
+      }
 #pragma unroll 1
-      for (int c = 0; c < BN / 128; ++c) {
+      for (int c = 0; c < BN / 128 && ACT != ACT_FILTER; ++c) {
         const int col0 = half * (BN / 2) + c * 64;
         const int n = n0 + col0;
         if (n >= p.N) break;
@@ -638,6 +694,28 @@ int launch_gemm_f32(const GemmOperands& ops, const GemmParams& g, cudaStream_t s
   p.a2_kc = 0; p.w_planes = g.w_planes; p.num_taps = 1; p.tap_off[0] = 0;
   return bn == 256 ? launch_pw_t<256, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream)
                    : launch_pw_t<128, ACT_RAW_F32, false, false>(ma, ma, mw, mo, p, stream);
+}
+
+// Cohort-score GEMM with the top-K pre-filter fused into the epilogue (score.cu): scores[M, N] = A * W^T are compared
+// with thr[row] as they leave TMEM; survivors of columns < n_valid go to cand[row * cap + ...], cnt[row] counts them
+// (it may exceed cap: the caller treats that row as unproven).  No score is stored anywhere else.
+int launch_gemm_filter(const GemmOperands& ops, const GemmParams& g, const float* thr, unsigned* cnt, float* cand, int cap,
+                       int n_valid, cudaStream_t stream) {
+  SVB_CHECK(g.num_taps == 1 && g.tap_off[0] == 0 && g.N % 64 == 0, "launch_gemm_filter: pointwise, N % 64 == 0");
+  SVB_CHECK(thr != nullptr && cnt != nullptr && cand != nullptr && cap > 0, "launch_gemm_filter: null filter buffers");
+  SVB_CHECK(ops.a_f16 == ops.w_f16, "activations and weights share one 16-bit format");
+  const int bn = g.N >= 256 ? 256 : 128;
+  CUtensorMap ma, mw;
+  if (make_map(&ma, ops.a, g.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
+  if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;
+  PwParams p{};
+  p.M = g.M; p.N = g.N; p.kc = g.kc_per_tap; p.num_pass = g.num_pass; p.a_plane_cols = g.a_plane_cols;
+  p.a2_kc = 0; p.w_planes = g.w_planes; p.num_taps = 1; p.tap_off[0] = 0;
+  p.w_f16 = ops.w_f16; p.a_f16 = ops.a_f16;
+  p.filt_thr = thr; p.filt_cnt = cnt; p.filt_cand = cand; p.filt_cap = cap; p.filt_ncols = n_valid;
+  // 16 epilogue warps: each thread owns 64 columns of its row (two strips), half the per-warp epilogue time of EW = 8
+  return bn == 256 ? launch_pw_t<256, ACT_FILTER, false, false, 16>(ma, ma, mw, ma, p, stream)
+                   : launch_pw_t<128, ACT_FILTER, false, false, 16>(ma, ma, mw, ma, p, stream);
 }
 
 }  // namespace svb

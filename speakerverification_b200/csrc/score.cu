@@ -209,6 +209,7 @@ __device__ __forceinline__ int lin_bin(float v, float lo, float scale) {
 template <int NT>
 __device__ __forceinline__ void find_bin(const uint32_t* hist, int nb, uint32_t remaining, uint32_t prefix, int shift,
                                          uint32_t* sel, uint32_t* wtot) {
+  static_assert(NT >= 512, "find_bin covers at most 4 bins per thread: 2048 bins need >= 512 threads");
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   constexpr int NW = NT / 32;
   // nb is NT or 2 * NT or 4 * NT (1024 / 2048 bins); unused slots count zero
@@ -668,6 +669,324 @@ topk_stats_sampled_kernel(const float* __restrict__ S, int ld, int N, int K, flo
   }
 }
 
+// ---------------------------------------------------------------- fused pre-filter path (threshold -> filter GEMM -> select)
+// The cohort-score matrix never reaches memory on this path.  Per chunk of utterance rows:
+//   1. a SAMPLE GEMM scores the rows against the first Ns cohort vectors (cohort rows are exchangeable, so any fixed
+//      subset is a sample) -> S1 [rows, Ns] (L2 resident);
+//   2. thr_warp_kernel turns each row's sample into a threshold that about K + 4.5 sqrt(K * N / Ns) of the N
+//      scores will pass (histogram quantile of the sample), and zeroes the row's candidate counter;
+//   3. the FILTER GEMM (gemm_pw.cu, ACT_FILTER) recomputes all N scores and appends those >= thr to the row's
+//      candidate list straight from TMEM;
+//   4. cand_select_warp_kernel does the exact top-K statistics among the candidates (they contain the K largest whenever
+//      there are at least K of them).  Rows it cannot prove -- fewer than K or more than FILT_CAP candidates, heavy ties
+//      -- are appended to a list and redone exactly by fixup_rows_kernel (direct fp32 scores + 3-pass radix select).
+// Extra work: Ns / N of the GEMM FLOPs (1/8); saved: the 4-byte store and the re-read of every score.
+#define FILT_CAP 1024
+
+// cohort [N, D] fp32 -> packed split-bf16 rows [N, 2, Dp] in a PERMUTED order: packed row j holds cohort row
+// (j * stride) mod N, stride coprime to N (about 0.618 N).  The order of the cohort is irrelevant to the top-K
+// statistics, and with this order any prefix of the packed rows is spread evenly over the cohort, so the sample GEMM's
+// first Ns rows stay representative when the caller's cohort is sorted (by speaker, by language, by score ...).
+__global__ void pack_cohort_permuted_kernel(const float* __restrict__ c, int N, int D, int Dp, long long stride,
+                                            bf16* __restrict__ out) {
+  const long long total = static_cast<long long>(N) * Dp;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int d = static_cast<int>(i % Dp);
+    const long long j = i / Dp;
+    const long long src = (j * stride) % N;
+    const float v = d < D ? c[src * D + d] : 0.f;
+    const bf16 h = __float2bfloat16_rn(v);
+    out[j * 2 * Dp + d] = h;
+    out[j * 2 * Dp + Dp + d] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+static long long coprime_stride(int N) {
+  long long s = static_cast<long long>(0.6180339887 * N);
+  if (s < 1) s = 1;
+  auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
+  while (gcd(s, N) != 1) ++s;
+  return s;
+}
+
+// Both per-row kernels run ONE WARP per row (no block barriers: a row is 2560 sample scores / ~550 candidates, far too
+// little work to amortise the ~10 barrier-separated phases of a CTA-per-row kernel -- a CTA-per-row first version spent
+// 65 + 57 us per 8192 rows here, 25 % of the fused path).
+//
+// Threshold from the row's sample: 256-bin linear histogram over the sample's range in this warp's shared-memory slice,
+// scan from the top, thr = lower edge of the bin that holds the want-th largest sample score.  The bin adds at most a
+// handful of sample scores (~5 at cfg5's geometry), i.e. a few dozen extra candidates.
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+thr_warp_kernel(const float* __restrict__ S1, int ld, int Ns, int want, float* __restrict__ thr,
+                unsigned* __restrict__ cnt, int rows) {
+  __shared__ uint32_t hist[WARPS][256];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int r = blockIdx.x * WARPS + wid;
+  if (r >= rows) return;
+  const float* row = S1 + static_cast<long long>(r) * ld;
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  const int n4 = Ns >> 2;                               // ld and Ns are multiples of 4 (Ns a multiple of 256 or = N)
+  float lo = INFINITY, hi = -INFINITY;
+  for (int i = lane; i < n4; i += 32) {
+    const float4 v = row4[i];
+    lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
+    hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+  }
+  for (int i = (n4 << 2) + lane; i < Ns; i += 32) { lo = fminf(lo, row[i]); hi = fmaxf(hi, row[i]); }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  const float range = hi - lo;
+  const float scale = (range > 0.f && range < INFINITY) ? 255.f / range : 0.f;
+  if (scale == 0.f || want > Ns) {          // constant / non-finite sample: everything passes, the row goes to the fix-up
+    if (lane == 0) { thr[r] = -INFINITY; cnt[r] = 0u; }
+    return;
+  }
+  uint32_t* h = hist[wid];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) h[lane * 8 + j] = 0;
+  __syncwarp();
+  auto bin = [&](float v) { return min(255, __float2int_rz((v - lo) * scale)); };
+  for (int i = lane; i < n4; i += 32) {
+    const float4 v = row4[i];
+    atomicAdd(&h[bin(v.x)], 1u); atomicAdd(&h[bin(v.y)], 1u); atomicAdd(&h[bin(v.z)], 1u); atomicAdd(&h[bin(v.w)], 1u);
+  }
+  for (int i = (n4 << 2) + lane; i < Ns; i += 32) atomicAdd(&h[bin(row[i])], 1u);
+  __syncwarp();
+  // lane l owns bins 255 - 8 l ... 255 - 8 l - 7 (descending); inclusive prefix over lanes = count from the top
+  uint32_t c[8], mine = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { c[j] = h[255 - 8 * lane - j]; mine += c[j]; }
+  uint32_t incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const uint32_t excl = incl - mine;
+  if (excl < static_cast<uint32_t>(want) && incl >= static_cast<uint32_t>(want)) {     // exactly one lane
+    uint32_t run = excl;
+    int j = 0;
+#pragma unroll
+    for (int q = 0; q < 7; ++q) if (j == q && run + c[q] < static_cast<uint32_t>(want)) { run += c[q]; j = q + 1; }
+    thr[r] = lo + static_cast<float>(255 - 8 * lane - j) / scale;
+    cnt[r] = 0u;
+  }
+}
+
+// Exact top-K statistics among the candidates of one row, one warp per row: 256-bin linear histogram over the
+// candidates' range, the bin holding the K-th largest, fp64 sums of everything above it, rank-by-counting inside it.
+// Unproven rows (fewer than K or more than FILT_CAP candidates, more than 32 values in the K-th value's bin: heavy
+// ties) go to the fix-up list.
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+cand_select_warp_kernel(const float* __restrict__ cand, const unsigned* __restrict__ cnt, int K, float* __restrict__ mu,
+                        float* __restrict__ sigma, int row0, int rows, unsigned* __restrict__ nflag,
+                        int* __restrict__ flag_list) {
+  __shared__ uint32_t hist[WARPS][256];
+  __shared__ float tie[WARPS][32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int r = blockIdx.x * WARPS + wid;
+  if (r >= rows) return;
+  const unsigned n = cnt[r];
+  if (n < static_cast<unsigned>(K) || n > FILT_CAP) {
+    if (lane == 0) flag_list[atomicAdd(nflag, 1u)] = row0 + r;
+    return;
+  }
+  const float* c = cand + static_cast<long long>(r) * FILT_CAP;
+  const int nj = (static_cast<int>(n) + 31) >> 5;        // warp-uniform trip count (<= FILT_CAP / 32)
+  float v[FILT_CAP / 32];
+  float lo = INFINITY, hi = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < FILT_CAP / 32; ++j) {
+    v[j] = -INFINITY;
+    if (j < nj) {
+      const int i = lane + 32 * j;
+      if (i < static_cast<int>(n)) { v[j] = c[i]; hi = fmaxf(hi, v[j]); lo = fminf(lo, v[j]); }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  const float range = hi - lo;
+  const float scale = (range > 0.f && range < INFINITY) ? 255.f / range : 0.f;      // 0: all equal -> one bin
+  uint32_t* h = hist[wid];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) h[lane + 32 * j] = 0;
+  __syncwarp();
+  auto bin = [&](float x) { return min(255, __float2int_rz((x - lo) * scale)); };
+#pragma unroll
+  for (int j = 0; j < FILT_CAP / 32; ++j)
+    if (j < nj && v[j] != -INFINITY) atomicAdd(&h[bin(v[j])], 1u);
+  __syncwarp();
+  // lane l owns bins 255 - 8 l ... 255 - 8 l - 7 (descending); inclusive prefix over lanes = count from the top
+  uint32_t cb[8], mine = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { cb[j] = h[255 - 8 * lane - j]; mine += cb[j]; }
+  uint32_t incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  const uint32_t excl = incl - mine;
+  const bool owner = excl < static_cast<uint32_t>(K) && incl >= static_cast<uint32_t>(K);
+  int bin_sel = 0;
+  uint32_t need = 0;
+  if (owner) {
+    uint32_t run = excl;
+    int j = 0;
+#pragma unroll
+    for (int q = 0; q < 7; ++q) if (j == q && run + cb[q] < static_cast<uint32_t>(K)) { run += cb[q]; j = q + 1; }
+    bin_sel = 255 - 8 * lane - j;
+    need = static_cast<uint32_t>(K) - run;          // how many of the threshold bin's values belong to the top-K set
+  }
+  const unsigned om = __ballot_sync(0xffffffffu, owner);
+  const int src = __ffs(om) - 1;
+  bin_sel = __shfl_sync(0xffffffffu, bin_sel, src);
+  need = __shfl_sync(0xffffffffu, need, src);
+  double s = 0.0, q = 0.0;
+  uint32_t ntie = 0;
+#pragma unroll
+  for (int j = 0; j < FILT_CAP / 32; ++j) {
+    if (j >= nj) break;                                  // uniform
+    const bool live = v[j] != -INFINITY;
+    const int b = live ? bin(v[j]) : -1;
+    if (b > bin_sel) { s += v[j]; q += static_cast<double>(v[j]) * v[j]; }
+    const unsigned tm = __ballot_sync(0xffffffffu, b == bin_sel);
+    if (b == bin_sel) {
+      const uint32_t pos = ntie + __popc(tm & ((1u << lane) - 1u));
+      if (pos < 32) tie[wid][pos] = v[j];
+    }
+    ntie += __popc(tm);
+  }
+  __syncwarp();
+  if (ntie > 32) {                                   // heavy ties in the threshold bin: exact fix-up
+    if (lane == 0) flag_list[atomicAdd(nflag, 1u)] = row0 + r;
+    return;
+  }
+  if (lane < static_cast<int>(ntie)) {
+    const float me = tie[wid][lane];
+    uint32_t rank = 0;
+    for (int i = 0; i < static_cast<int>(ntie); ++i) {
+      const float t = tie[wid][i];
+      rank += (t > me || (t == me && i < lane)) ? 1u : 0u;
+    }
+    if (rank < need) { s += me; q += static_cast<double>(me) * me; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    const double m = s / K;
+    const double var = fmax(q / K - m * m, 0.0);
+    mu[row0 + r] = static_cast<float>(m);
+    sigma[row0 + r] = static_cast<float>(sqrt(var));
+  }
+}
+
+// Exact fall-back for the rows the fused path could not prove (flag_list[0 .. *nflag)): each CTA takes rows off the
+// list, computes the row's N cohort scores directly in fp32 (one warp per cohort vector, coalesced 128-byte reads,
+// the cohort stays in L2) into its private scratch row and selects with the 3-pass key radix.  Slow (~50 us per row)
+// and exact for any input; a well-conditioned sweep sends ~0.01 % of its rows here.
+__global__ void __launch_bounds__(256)
+fixup_rows_kernel(const float* __restrict__ emean, const float* __restrict__ cohort, int N, int D, int K,
+                  const unsigned* __restrict__ nflag, const int* __restrict__ flag_list, float* __restrict__ scratch,
+                  int scratch_ld, float* __restrict__ mu, float* __restrict__ sigma) {
+  extern __shared__ float e_s[];          // [D]
+  __shared__ uint32_t hist[2048];
+  __shared__ uint32_t sel_prefix, sel_remaining;
+  __shared__ double red_s[8], red_q[8];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  float* srow = scratch + static_cast<long long>(blockIdx.x) * scratch_ld;
+  const unsigned total = *nflag;
+  for (unsigned it = blockIdx.x; it < total; it += gridDim.x) {
+    const int u = flag_list[it];
+    __syncthreads();
+    for (int c = tid; c < D; c += 256) e_s[c] = emean[static_cast<long long>(u) * D + c];
+    __syncthreads();
+    for (int j = wid; j < N; j += 8) {
+      const float* cr = cohort + static_cast<long long>(j) * D;
+      float a = 0.f;
+      for (int c = lane; c < D; c += 32) a = fmaf(e_s[c], __ldg(cr + c), a);
+      a = warp_sum(a);
+      if (lane == 0) srow[j] = a;
+    }
+    __syncthreads();
+    // 3-pass (11 + 11 + 10 bit) key radix select of the K largest (same algorithm as topk_stats_kernel)
+    uint32_t prefix = 0, prefix_mask = 0, remaining = K;
+    const int shifts[3] = {21, 10, 0};
+    const int bits[3] = {11, 11, 10};
+    for (int pass = 0; pass < 3; ++pass) {
+      const int nb = 1 << bits[pass];
+      for (int i = tid; i < nb; i += 256) hist[i] = 0;
+      __syncthreads();
+      for (int i = tid; i < N; i += 256) {
+        const uint32_t k = f2key(srow[i]);
+        if ((k & prefix_mask) == prefix) atomicAdd(&hist[(k >> shifts[pass]) & (nb - 1)], 1u);
+      }
+      __syncthreads();
+      if (tid < 32) {
+        const int per = nb / 32;
+        uint32_t mine = 0;
+        for (int j = 0; j < per; ++j) mine += hist[nb - 1 - (tid * per + j)];
+        uint32_t incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (tid >= o) incl += v;
+        }
+        const uint32_t excl = incl - mine;
+        if (excl < remaining && incl >= remaining) {
+          uint32_t run = excl;
+          for (int j = 0; j < per; ++j) {
+            const int bin = nb - 1 - (tid * per + j);
+            const uint32_t c = hist[bin];
+            if (run + c >= remaining) {
+              sel_prefix = prefix | (static_cast<uint32_t>(bin) << shifts[pass]);
+              sel_remaining = remaining - run;
+              break;
+            }
+            run += c;
+          }
+        }
+      }
+      __syncthreads();
+      prefix = sel_prefix;
+      remaining = sel_remaining;
+      prefix_mask |= static_cast<uint32_t>(nb - 1) << shifts[pass];
+      __syncthreads();
+    }
+    const uint32_t kth = prefix;
+    double s = 0.0, q = 0.0;
+    for (int i = tid; i < N; i += 256) {
+      const float v = srow[i];
+      if (f2key(v) > kth) { s += v; q += static_cast<double>(v) * v; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) { red_s[wid] = s; red_q[wid] = q; }
+    __syncthreads();
+    if (tid == 0) {
+      double ts = 0.0, tq = 0.0;
+      for (int w = 0; w < 8; ++w) { ts += red_s[w]; tq += red_q[w]; }
+      const double kv = key2f(kth);
+      ts += remaining * kv;
+      tq += remaining * kv * kv;
+      const double m = ts / K;
+      const double var = fmax(tq / K - m * m, 0.0);
+      mu[u] = static_cast<float>(m);
+      sigma[u] = static_cast<float>(sqrt(var));
+    }
+  }
+}
+
 // ---------------------------------------------------------------- AS-norm trial scores
 // emean [U, D]; out = 0.5 * ((s - mu_a)/sigma_a + (s - mu_b)/sigma_b), s = <emean_a, emean_b>.
 __global__ void asnorm_trials_kernel(const float* __restrict__ emean, int D, const int32_t* __restrict__ ia,
@@ -830,7 +1149,22 @@ static size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 static const size_t S_CHUNK_BYTES = 144u << 20;
 static const int TOPK_SMEM_MAX_N = 50000;   // row cached in smem (<= 200 KB)
 
-struct AsnormPlan { int Dp, Np, chunk; size_t o_w, o_zeros, o_ones, o_a, o_s, total; };
+// Fused path (see "fused pre-filter path" above): rows per chunk and sample size, buffers overlaid on the S chunk
+static const int FUSED_CHUNK_ROWS = 8192;
+static const int FIXUP_CTAS = 296;
+struct AsnormPlan {
+  int Dp, Np, chunk;
+  size_t o_w, o_zeros, o_ones, o_a, o_s, total;
+  int Ns, fch;                                           // fused path: sample columns, rows per chunk
+  size_t o_s1, o_thr, o_cnt, o_cand, o_nflag, o_flag, o_fix;
+};
+
+static bool fused_enabled() {
+  static const bool on = [] { const char* e = getenv("SVB_TOPK_FUSED"); return e == nullptr || e[0] != '0'; }();
+  return on;
+}
+// the pre-filter pays when K << N and the sample (N / 8 cohort vectors) is large enough for a stable quantile
+static bool fused_applies(int N, int K) { return fused_enabled() && N >= 8192 && K >= 16 && 8 * K <= N && K <= FILT_CAP / 2; }
 
 static AsnormPlan asnorm_plan(int U, int N, int D) {
   AsnormPlan p{};
@@ -857,8 +1191,19 @@ static AsnormPlan asnorm_plan(int U, int N, int D) {
   p.o_zeros = o; o += align256(static_cast<size_t>(p.Np) * 4);
   p.o_ones = o; o += align256(static_cast<size_t>(p.Np) * 4);
   p.o_a = o; o += align256(Upad * 2 * p.Dp * 2);
-  p.o_s = o; o += align256(static_cast<size_t>(p.chunk) * p.Np * 4);
-  p.total = o;
+  p.o_s = o;
+  const size_t old_end = o + align256(static_cast<size_t>(p.chunk) * p.Np * 4);
+  // fused-path buffers share the S-chunk region (only one of the two paths runs in a call)
+  p.Ns = std::min(p.Np, (N / 8 + 255) / 256 * 256);
+  p.fch = static_cast<int>(std::min<long long>(FUSED_CHUNK_ROWS, all * 128));
+  p.o_s1 = o; o += align256(static_cast<size_t>(p.fch) * p.Ns * 4);
+  p.o_thr = o; o += align256(static_cast<size_t>(p.fch) * 4);
+  p.o_cnt = o; o += align256(static_cast<size_t>(p.fch) * 4);
+  p.o_cand = o; o += align256(static_cast<size_t>(p.fch) * FILT_CAP * 4);
+  p.o_nflag = o; o += 256;
+  p.o_flag = o; o += align256(static_cast<size_t>(U) * 4 + 4);
+  p.o_fix = o; o += align256(static_cast<size_t>(FIXUP_CTAS) * p.Np * 4);
+  p.total = std::max(old_end, o);
   return p;
 }
 
@@ -866,6 +1211,18 @@ size_t asnorm_workspace_bytes(int U, int N, int D, int* chunk_out) {
   const AsnormPlan p = asnorm_plan(U, N, D);
   if (chunk_out) *chunk_out = p.chunk;
   return p.total;
+}
+
+// Diagnostic (synchronous): how many rows of the LAST asnorm_stats call on this workspace went through the exact
+// fix-up kernel (fused pre-filter path only; -1 if the call used the store-and-select path).
+int asnorm_fixup_rows(const void* ws, int U, int N, int D, int topk) {
+  int K = topk < 0 ? N + topk : topk;
+  if (K > N) K = N;
+  if (!fused_applies(N, K)) return -1;
+  const AsnormPlan pl = asnorm_plan(U, N, D);
+  unsigned n = 0;
+  if (cudaMemcpy(&n, static_cast<const uint8_t*>(ws) + pl.o_nflag, sizeof(n), cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+  return static_cast<int>(n);
 }
 
 // mu/sigma of the top-K cohort scores of every row of emean [U, D].
@@ -886,13 +1243,60 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
   bf16* a16 = reinterpret_cast<bf16*>(base + pl.o_a);
   float* S = reinterpret_cast<float*>(base + pl.o_s);
   // cohort [N, D] is a k=1 "conv weight" [cout=N, cin=D, 1]; embeddings are split into hi|lo planes once
-  if (pack_conv_weight(cohort, N, D, 1, Dp, 2, wpk, stream)) return -1;
+  const bool fused = fused_applies(N, K);
+  if (fused) {
+    const long long total = static_cast<long long>(N) * Dp;
+    pack_cohort_permuted_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, stream>>>(
+        cohort, N, D, Dp, coprime_stride(N), wpk);
+    count_launch();
+    SVB_CUDA_OK(cudaGetLastError());
+  } else if (pack_conv_weight(cohort, N, D, 1, Dp, 2, wpk, stream)) {
+    return -1;
+  }
   fill_kernel<<<(Np + 255) / 256, 256, 0, stream>>>(zeros, Np, 0.f);
   fill_kernel<<<(Np + 255) / 256, 256, 0, stream>>>(ones, Np, 1.f);
   count_launch(2);
   const size_t Upad = (static_cast<size_t>(U) + 127) / 128 * 128;
   SVB_CUDA_OK(cudaMemsetAsync(a16, 0, Upad * 2 * Dp * 2, stream));
   if (split_bf16(emean, U, D, D, a16, 2 * Dp, 2, Dp, stream)) return -1;
+  if (fused) {
+    // ---- fused pre-filter path: no score is ever stored except the 1/8 sample and the ~2.5 % that pass the threshold
+    float* S1 = reinterpret_cast<float*>(base + pl.o_s1);
+    float* thr = reinterpret_cast<float*>(base + pl.o_thr);
+    unsigned* cnt = reinterpret_cast<unsigned*>(base + pl.o_cnt);
+    float* cand = reinterpret_cast<float*>(base + pl.o_cand);
+    unsigned* nflag = reinterpret_cast<unsigned*>(base + pl.o_nflag);
+    int* flag_list = reinterpret_cast<int*>(base + pl.o_flag);
+    float* fix = reinterpret_cast<float*>(base + pl.o_fix);
+    const int Ns = pl.Ns;
+    const double kf = static_cast<double>(K) * Ns / N;                       // expected sample hits of the K-th score
+    const int want = static_cast<int>(kf + 4.5 * sqrt(kf) + 4.0);
+    SVB_CUDA_OK(cudaMemsetAsync(nflag, 0, sizeof(unsigned), stream));
+    for (int u0 = 0; u0 < U; u0 += pl.fch) {
+      const int rows = std::min(pl.fch, U - u0);
+      GemmOperands ops{};
+      ops.a = a16 + static_cast<size_t>(u0) * 2 * Dp; ops.lda = 2 * Dp; ops.a_cols = 2 * Dp;
+      ops.w = wpk; ops.w_rows = std::min(N, Ns); ops.w_cols = 2 * Dp;
+      GemmParams g{};
+      g.M = rows; g.N = Ns; g.kc_per_tap = Dp / 64; g.num_taps = 1; g.tap_off[0] = 0; g.num_pass = 3;
+      g.a_plane_cols = Dp; g.w_planes = 2; g.act = ACT_NONE; g.store_mode = STORE_ALL; g.out = S1; g.out_ld = Ns;
+      g.out_kind = OUT_F32;
+      if (launch_gemm_f32(ops, g, stream)) return -1;
+      thr_warp_kernel<16><<<(rows + 15) / 16, 512, 0, stream>>>(S1, Ns, std::min(N, Ns), want, thr, cnt, rows);
+      count_launch();
+      ops.w_rows = N;
+      g.N = Np; g.out = nullptr;
+      if (launch_gemm_filter(ops, g, thr, cnt, cand, FILT_CAP, N, stream)) return -1;
+      cand_select_warp_kernel<16><<<(rows + 15) / 16, 512, 0, stream>>>(cand, cnt, K, mu, sigma, u0, rows, nflag, flag_list);
+      count_launch();
+      SVB_CUDA_OK(cudaGetLastError());
+    }
+    fixup_rows_kernel<<<FIXUP_CTAS, 256, static_cast<size_t>(D) * 4, stream>>>(emean, cohort, N, D, K, nflag, flag_list, fix, Np,
+                                                                          mu, sigma);
+    count_launch();
+    SVB_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
   const bool smem_rows = Np <= TOPK_SMEM_MAX_N;   // the launch asks for Np * 4 bytes (N rounded up to 64)
   if (smem_rows) {
     static bool attr_set = false;

@@ -116,6 +116,10 @@ int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long col
 // Plain fp32-output GEMM out[M, N] = A * W^T through the TMA-store epilogue of gemm_pw.cu (N % 64 == 0).
 int launch_gemm_f32(const GemmOperands& ops, const GemmParams& p, cudaStream_t stream);
 
+// Cohort-score GEMM whose epilogue keeps only the scores >= thr[row] (fused top-K pre-filter, gemm_pw.cu / score.cu).
+int launch_gemm_filter(const GemmOperands& ops, const GemmParams& p, const float* thr, unsigned* cnt, float* cand, int cap,
+                       int n_valid, cudaStream_t stream);
+
 // Launches the persistent tcgen05 GEMM.  block_n in {64, 128, 256}.
 int launch_gemm(const GemmOperands& ops, const GemmParams& p, int block_n, cudaStream_t stream);
 

@@ -61,7 +61,7 @@ def mean_embeddings(emb, normalize):
 
 
 @_on_arg_device
-def asnorm_stats(emean, cohorts, top):
+def asnorm_stats(emean, cohorts, top, return_fixups=False):
     """Per-utterance (mu, sigma) of the `top` largest cohort scores; emean [U, D], cohorts [N, D]."""
     U, D = emean.shape
     N = cohorts.shape[0]
@@ -71,6 +71,8 @@ def asnorm_stats(emean, cohorts, top):
     sg = torch.empty(U, dtype=torch.float32, device=emean.device)
     nv.check(nv.lib().svb_asnorm_stats(nv.ptr(emean), U, nv.ptr(cohorts), N, D, int(top), nv.ptr(mu), nv.ptr(sg),
                                        nv.ptr(ws), need, nv.stream_ptr()))
+    if return_fixups:      # diagnostic (synchronises): rows the fused pre-filter sent to the exact fix-up kernel
+        return mu, sg, int(nv.lib().svb_asnorm_fixup_rows(nv.ptr(ws), U, N, D, int(top)))
     return mu, sg
 
 

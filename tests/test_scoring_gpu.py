@@ -150,3 +150,23 @@ def test_pnorm_trials_match_reference(golden_c512):
     assert abs(s - float(g["scores_p2"][0])) <= 1e-5
     assert abs(U.pnorm_similarity(en[int(g["ti"][1])].cpu(), en[int(g["tj"][1])].cpu()) - float(g["scores_p2"][1])) <= 1e-5
     assert U.similarity_measure("no_such_method", en[0], en[1]) is None        # src/utils.py:126-132 falls through
+
+
+@pytest.mark.parametrize("order", ["random", "sorted_by_first_score"])
+def test_fused_prefilter_path_cfg5_like(order):
+    """BASELINE configs[4] geometry at reduced U (4096 utterances vs a 20 000-vector cohort, top-300): the fused path
+    (sample GEMM -> threshold -> filter GEMM epilogue -> candidate select; the score matrix is never stored) against
+    numpy's full sort, and the share of rows that needed the exact fix-up stays tiny -- also when the caller's cohort
+    is SORTED (the packed cohort is stride-permuted, so the sample stays representative)."""
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    e, _ = synth.scoring_embeddings(4096, 200, seed=3)
+    c, _ = synth.scoring_embeddings(20000, 2000, seed=103)
+    if order != "random":
+        c = c[np.argsort(c @ e[0])]                       # ascending in the first utterance's score: worst case for a prefix sample
+    mu, sg, nfix = U.asnorm_stats(torch.from_numpy(e).cuda(), torch.from_numpy(c).cuda(), 300, return_fixups=True)
+    S = -np.sort(-(e.astype(np.float64) @ c.astype(np.float64).T), axis=1)[:, :300]
+    assert np.abs(mu.cpu().numpy() - S.mean(1)).max() <= 2e-6
+    assert np.abs(sg.cpu().numpy() - S.std(1)).max() <= 2e-6
+    print("fused AS-norm path, cohort order", order, ": fix-up rows", nfix, "of 4096")
+    assert 0 <= nfix <= 40
