@@ -196,7 +196,7 @@ int svb_ecapa_forward_mel(const SvbEcapa* e, const SvbFbank* f, const SvbBatch* 
  * SpeakerEncoder.forward with features == 'raw' (src/model.py:104-129): LayerNorm over samples, SincConv_fast +
  * |.| + max_pool1d(3) + first_bn + LeakyReLU(0.3), eight RawNetBasicBlocks with AFMS
  * (src/models/RawNet_baseline.py:13-24, 48-68, 181-361), bn_before_gru, GRU(512 -> gru_node) last state,
- * fc_after_gru.  Weights: fp32 DEVICE pointers in the reference checkpoint layout keyed by state-dict name
+ * fc_after_gru; or, aggregate = 'sap' / 'asp', bn_before_agg + the attentive statistics heads of :200-224 + fc.  Weights: fp32 DEVICE pointers in the reference checkpoint layout keyed by state-dict name
  * without the "__S__." prefix ("ln.gamma", "first_conv.low_hz_", "layer3.0.shortcut.0.weight", ...).
  * Every utterance has exactly n_samples samples (ln.gamma / ln.beta have that length in the reference). */
 typedef struct SvbRawnet2 SvbRawnet2;
@@ -205,7 +205,9 @@ typedef struct SvbRawnet2Cfg {
   int32_t n_out;           /* code_dim / nOut */
   int32_t gru_node;        /* 1024 */
   int32_t sample_rate;
-  int32_t fp32_mode;       /* 0: bf16 tensor-core operands; 1: split-bf16 (fp32-grade parity mode) */
+  int32_t fp32_mode;       /* 0: 16-bit mode (IEEE-half operands); 1: split-bf16 (fp32-grade parity mode) */
+  int32_t aggregate;       /* 0 = 'gru' (default head), 1 = 'sap', 2 = 'asp' (src/models/RawNet2_custom.py:84-112,188-224) */
+  int32_t att_dim;         /* 'asp': channels of the attention bottleneck (128) */
 } SvbRawnet2Cfg;
 int svb_rawnet2_create(const SvbRawnet2Cfg* cfg, const char* const* names, const void* const* ptrs, int n,
                        SvbRawnet2** out);
@@ -243,6 +245,10 @@ int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int norma
 size_t svb_asnorm_workspace_bytes(int U, int N, int D);
 int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu,
                      float* sigma, void* ws, size_t ws_bytes, void* stream);
+/* Diagnostic (profiling): mainloop of a pointwise fp16 layer [M, K] x [N, K]^T with a store-free epilogue; thr_inf[M]
+ * must hold +inf, cnt[M] / cand[M] are scratch. */
+int svb_debug_gemm_noepi(const void* a, const void* w, int M, int N, int K, const float* thr_inf, unsigned* cnt,
+                         float* cand, void* stream);
 /* Diagnostic, synchronous: rows of the last svb_asnorm_stats call on `ws` that the fused pre-filter could not prove and
  * the exact fix-up kernel redid (-1: the call used the store-and-select path). */
 int svb_asnorm_fixup_rows(const void* ws, int U, int N, int D, int topk);

@@ -190,6 +190,33 @@ def make_rawnet(tag="cfg4_rawnet2", n_spk=4, per_spk=4, n_out=512, L4=64000):
     print("wrote", path, os.path.getsize(path) // 1024, "KiB")
 
 
+def make_rawnet_heads(tag="cfg4_rawnet2_heads", n_out=512, L4=64000):
+    """RawNet2_custom with the attentive heads aggregate='sap' and aggregate='asp' (src/models/RawNet2_custom.py:97-112,
+    200-224): embeddings of 16 synthetic 4 s utterances through the reference's SpeakerEncoder(features='raw')."""
+    ref_loader.load()
+    out = {}
+    waves, spk = synth.utterance_set(4, 4, L4)
+    _, ref_utils = ref_loader.load()
+    lab, ti, tj = synth.trial_list(spk, 120)
+    for agg in ("sap", "asp"):
+        net, handle, args = ref_loader.build([512] * 4 + [1536], n_out, sentence_len=4.0, features="raw",
+                                             model_name="RawNet2_custom", aggregate=agg)
+        sd = synth.rawnet2_state_dict(n_out, L4, aggregate=agg)
+        _load_weights(net, sd)
+        bn = _calibrate_bn(net, waves, batch=8)
+        for k, v in bn.items():
+            out["%s/bn/%s" % (agg, k)] = v
+        with torch.no_grad():
+            emb = net(torch.from_numpy(waves))
+        out["%s/emb_batch" % agg] = emb.numpy()
+        out["%s/scores_cos" % agg] = np.asarray([float(ref_utils.cosine_similarity(emb[i:i + 1], emb[j:j + 1]))
+                                                 for i, j in zip(ti, tj)])
+        print(agg, "emb", emb.shape, "scores", out["%s/scores_cos" % agg][:4])
+    path = os.path.join(GOLD, "%s.npz" % tag)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count())
@@ -202,3 +229,5 @@ if __name__ == "__main__":
         make_rawnet()
     if "cfg1i" in which:
         make_inorm()
+    if "cfg4h" in which:
+        make_rawnet_heads()

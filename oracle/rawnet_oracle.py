@@ -101,12 +101,36 @@ def rawnet2_forward(wave, sd, prefix="__S__.", stages=None, sample_rate=16000):
             x = basic_block(x, sd, P + "layer%d.%d." % (li + 1, bi), downsample=(bi == nb - 1))
         if stages is not None:
             stages["layer%d" % (li + 1)] = x
+    if P + "bn_before_agg.weight" in sd:
+        return attentive_head(x, sd, P).squeeze()                                         # :200-224
     x = F.leaky_relu(_bn(x, sd, P + "bn_before_gru."), 0.3)                               # :192-193
     h = gru_last(x.permute(0, 2, 1), sd, P + "gru.")                                      # :194-197
     if stages is not None:
         stages["gru"] = h
     out = F.linear(h, sd[P + "fc_after_gru.weight"], sd[P + "fc_after_gru.bias"])         # :198
     return out.squeeze()
+
+
+def attentive_head(x, sd, P):
+    """aggregate = 'sap' (src/models/RawNet2_custom.py:200-207 with Classic_Attention, RawNet_baseline.py:423-436, and
+    stat_attn_pool / weighted_sd :146-157) or 'asp' (:210-224), selected by the checkpoint's keys; x [B, 512, T]."""
+    x = F.leaky_relu(_bn(x, sd, P + "bn_before_agg."), 0.3)
+    if P + "attention_sap.v" in sd:
+        xt = x.permute(0, 2, 1)                                                            # [B, T, C]
+        lin = F.linear(xt, sd[P + "attention_sap.lin_proj.weight"], sd[P + "attention_sap.lin_proj.bias"])
+        w = F.softmax(torch.tanh(lin @ sd[P + "attention_sap.v"]), dim=1)                  # [B, T]
+        el = xt * w.unsqueeze(2)
+        mean = el.mean(dim=1)                                                              # torch.mean over time (:153)
+        var = (xt * el).sum(dim=1) - mean * mean                                           # weighted_sd (:146-150)
+        pooled = torch.cat([mean, var], dim=1)
+    else:
+        h = F.conv1d(x, sd[P + "attention.0.weight"], sd[P + "attention.0.bias"])
+        h = _bn(F.leaky_relu(h, 0.01), sd, P + "attention.2.")
+        w = F.softmax(F.conv1d(h, sd[P + "attention.3.weight"], sd[P + "attention.3.bias"]), dim=-1)
+        m = (x * w).sum(dim=-1)
+        s = torch.sqrt((((x ** 2) * w).sum(dim=-1) - m ** 2).clamp(min=1e-5))
+        pooled = torch.cat([m, s], dim=1)
+    return F.linear(pooled, sd[P + "fc.weight"], sd[P + "fc.bias"])
 
 
 # ------------------------------------------------------------------ 16-bit-operand emulation

@@ -79,7 +79,8 @@ class SvbEcapaCfg(_c.Structure):
 
 
 class SvbRawnet2Cfg(_c.Structure):
-    _fields_ = [("n_samples", _i32), ("n_out", _i32), ("gru_node", _i32), ("sample_rate", _i32), ("fp32_mode", _i32)]
+    _fields_ = [("n_samples", _i32), ("n_out", _i32), ("gru_node", _i32), ("sample_rate", _i32), ("fp32_mode", _i32),
+                ("aggregate", _i32), ("att_dim", _i32)]
 
 
 _pp = _c.POINTER(_vp)
@@ -110,6 +111,7 @@ _EXTRA_SIGS = {
     "svb_enrol_nearest": ([_vp, _vp, _i32, _i32, _i32, _i32, _c.c_float, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_workspace_bytes": ([_i32, _i32, _i32], _c.c_size_t),
     "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
+    "svb_debug_gemm_noepi": ([_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_fixup_rows": ([_vp, _i32, _i32, _i32, _i32], _i32),
     "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),
     "svb_rawnet2_create": ([_c.POINTER(SvbRawnet2Cfg), _c.POINTER(_c.c_char_p), _c.POINTER(_vp), _i32, _pp], _i32),

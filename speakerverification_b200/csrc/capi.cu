@@ -47,7 +47,7 @@ int asnorm_stats(const float*, int, const float*, int, int, int, float*, float*,
 int asnorm_trials(const float*, int, const int32_t*, const int32_t*, long long, const float*, const float*, float*,
                   cudaStream_t);
 struct Rawnet2;
-int rawnet2_create(int, int, int, int, int, const char* const*, const void* const*, int, Rawnet2**);
+int rawnet2_create(int, int, int, int, int, int, int, const char* const*, const void* const*, int, Rawnet2**);
 void rawnet2_destroy(Rawnet2*);
 size_t rawnet2_workspace_bytes(const Rawnet2*, int);
 long long rawnet2_ws_offset(const Rawnet2*, int, const char*);
@@ -316,6 +316,19 @@ int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int 
   SVB_CHECK(emean && cohort && mu && sigma && U >= 1 && N >= 1 && D >= 1, "bad argument");
   return asnorm_stats(emean, U, cohort, N, D, topk, mu, sigma, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
+// Diagnostic: the GEMM mainloop of a pointwise layer with the epilogue reduced to TMEM reads and compares (nothing
+// stored: thr = +inf everywhere) -- separates operand-feed time from epilogue time (tools/pw_alone.py).
+int svb_debug_gemm_noepi(const void* a, const void* w, int M, int N, int K, const float* thr_inf, unsigned* cnt, float* cand,
+                         void* stream) {
+  if (check_device()) return -1;
+  GemmOperands ops{};
+  ops.a = static_cast<const bf16*>(a); ops.lda = K; ops.a_cols = K;
+  ops.w = static_cast<const bf16*>(w); ops.w_rows = N; ops.w_cols = K; ops.a_f16 = ops.w_f16 = 1;
+  GemmParams g{};
+  g.M = M; g.N = N; g.kc_per_tap = K / 64; g.num_taps = 1; g.tap_off[0] = 0; g.num_pass = 1; g.w_planes = 1;
+  return launch_gemm_filter(ops, g, thr_inf, cnt, cand, 1, N, static_cast<cudaStream_t>(stream));
+}
+
 int svb_asnorm_fixup_rows(const void* ws, int U, int N, int D, int topk) { return asnorm_fixup_rows(ws, U, N, D, topk); }
 
 int svb_asnorm_trials(const float* emean, int D, const int32_t* idx_a, const int32_t* idx_b, int64_t n_trials,
@@ -330,7 +343,8 @@ int svb_rawnet2_create(const SvbRawnet2Cfg* cfg, const char* const* names, const
                        SvbRawnet2** out) {
   if (check_device()) return -1;
   SVB_CHECK(cfg && names && ptrs && out && n > 0, "bad argument");
-  return rawnet2_create(cfg->n_samples, cfg->n_out, cfg->gru_node, cfg->sample_rate, cfg->fp32_mode, names, ptrs, n,
+  return rawnet2_create(cfg->n_samples, cfg->n_out, cfg->gru_node, cfg->sample_rate, cfg->fp32_mode, cfg->aggregate,
+                        cfg->att_dim, names, ptrs, n,
                         reinterpret_cast<Rawnet2**>(out));
 }
 void svb_rawnet2_destroy(SvbRawnet2* e) { rawnet2_destroy(reinterpret_cast<Rawnet2*>(e)); }

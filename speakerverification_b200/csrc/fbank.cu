@@ -120,12 +120,63 @@ fbank_logmel_kernel(const float* __restrict__ wav, const UttDesc* __restrict__ u
 
   for (int i = threadIdx.x; i < MAX_MELS; i += blockDim.x) { mstart[i] = tab->mel_start[i]; mcount[i] = tab->mel_count[i]; moff[i] = tab->mel_off[i]; }
   for (int i = threadIdx.x; i < nnz; i += blockDim.x) melw[i] = tab->mel_w[i];
-  // pre-emphasised, reflect-padded samples of this tile: padded index i <-> sample j = i - 256.
-  // Eight independent samples per thread and iteration: all 16 loads are in flight before the first store
-  // (the one-sample-per-iteration version spent 44 % of the kernel's stall samples waiting here).
+  // pre-emphasised, reflect-padded samples of this tile: padded index i <-> sample j = i0 + i, samp[i] = x[j] - c x[j-1].
   const int nsmp = hop * (nf - 1) + NFFT;
   const int i0 = hop * t0 - NFFT / 2;
-  for (int ib = 0; ib < nsmp; ib += 8 * FB_WARPS * 32) {
+  // Interior tiles (no reflection at either end of the utterance: all but the first and last two tiles of a 3 s crop)
+  // stage their contiguous sample span [i0 - 1, i0 + nsmp) with ONE bulk copy of the TMA engine (cp.async.bulk, 22 KB)
+  // into `samp` itself, then apply the pre-emphasis in place: every thread pulls its strided elements and their left
+  // neighbours into registers, barrier, writes back.  The copy starts at the 16-byte aligned address below the span
+  // (crop offsets are arbitrary), `sh` floats early, and is rounded up to 16 bytes: hence the + 8 floats of slack in the
+  // shared-memory plan and the + 3 in the interior test (never reads past the utterance's last sample).
+  const bool interior = i0 >= 1 && i0 + nsmp + 3 <= L - 1;
+  __shared__ __align__(8) uint64_t stage_bar;
+  if (interior) {
+    const float* src = x + (i0 - 1);
+    const int sh = static_cast<int>((reinterpret_cast<uintptr_t>(src) & 15) >> 2);
+    const uint32_t bytes = static_cast<uint32_t>((sh + nsmp + 1) * 4 + 15) & ~15u;
+    if (threadIdx.x == 0) {
+      mbar_init(smem_u32(&stage_bar), 1);
+      fence_barrier_init();
+      mbar_arrive_expect_tx(smem_u32(&stage_bar), bytes);
+      bulk_load_1d(smem_u32(samp), src - sh, bytes, smem_u32(&stage_bar));
+    }
+    __syncthreads();                                    // the barrier is initialised before anyone polls it
+    mbar_wait(smem_u32(&stage_bar), 0);
+    constexpr int PER = (160 * (FRAMES_PER_TILE - 1) + NFFT + FB_WARPS * 32 - 1) / (FB_WARPS * 32);   // hop <= 160
+    if (hop <= 160) {
+      float cur[PER], prv[PER];
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        const int i = k * FB_WARPS * 32 + threadIdx.x;
+        const int ii = i < nsmp ? i : nsmp - 1;
+        cur[k] = samp[sh + 1 + ii];
+        prv[k] = samp[sh + ii];
+      }
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        const int i = k * FB_WARPS * 32 + threadIdx.x;
+        if (i < nsmp) samp[i] = cur[k] - preemph * prv[k];
+      }
+    } else {                                            // long hops: element-serial in-place pass by one warp
+      __syncthreads();
+      if (warp == 0) {
+        for (int base = 0; base < nsmp; base += 32) {
+          const int i = base + lane;
+          float c = 0.f, pv = 0.f;
+          if (i < nsmp) { c = samp[sh + 1 + i]; pv = samp[sh + i]; }
+          __syncwarp();
+          if (i < nsmp) samp[i] = c - preemph * pv;     // writes index i <= the lowest index still to be read (i + sh)
+          __syncwarp();
+        }
+      }
+    }
+  }
+  // edge tiles: reflect padding of the centred STFT (and of the pre-emphasis) sample by sample.
+  // Eight independent samples per thread and iteration: all 16 loads are in flight before the first store
+  // (the one-sample-per-iteration version spent 44 % of the kernel's stall samples waiting here).
+  for (int ib = 0; ib < nsmp && !interior; ib += 8 * FB_WARPS * 32) {
     float cur[8], prv[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -361,7 +412,7 @@ int fbank_hop(const Fbank* f) { return f->hop; }
 size_t fbank_smem_bytes(const Fbank* f) {
   return FB_WARPS * 2 * EX_FRAME * sizeof(float2) + FB_WARPS * 2 * MAX_MELS * sizeof(float) + 3 * MAX_MELS * sizeof(int) +
          static_cast<size_t>((f->nnz + 3) & ~3) * sizeof(float) +
-         (static_cast<size_t>(f->hop) * (FRAMES_PER_TILE - 1) + NFFT) * sizeof(float);
+         (static_cast<size_t>(f->hop) * (FRAMES_PER_TILE - 1) + NFFT + 8) * sizeof(float);   // + 8: bulk-copy alignment slack
 }
 
 struct InputNorm { const float* weight; const float* bias; float eps; float* scale_ws; };   // weight == nullptr: off

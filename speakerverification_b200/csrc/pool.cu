@@ -176,12 +176,31 @@ se_apply_kernel(const bf16* __restrict__ x, int x_ld, int x_pc, const bf16* __re
     const int c = static_cast<int>(i - row * per_row) * 8;
     const int utt = meta[row].utt;
     if (utt < 0) continue;
-    float v[8], r[8];
-    load8(x + row * x_ld + c, planes, x_pc, v);
-    load8(resid + row * r_ld + c, planes, r_pc, r);
-    const float4 g0 = *reinterpret_cast<const float4*>(gate + static_cast<long long>(utt) * gate_ld + c);
-    const float4 g1 = *reinterpret_cast<const float4*>(gate + static_cast<long long>(utt) * gate_ld + c + 4);
+    // all global loads of the iteration are issued before the first decode (the kernel is a pure HBM stream: with the
+    // loads of V and of the residual serialised behind each other's decode it ran at 56 % instead of 90 % of the copy peak)
+    const uint4 xv = __ldg(reinterpret_cast<const uint4*>(x + row * x_ld + c));
+    const uint4 rv = __ldg(reinterpret_cast<const uint4*>(resid + row * r_ld + c));
+    uint4 xl = make_uint4(0, 0, 0, 0), rl = make_uint4(0, 0, 0, 0);
+    if (planes == 2) {
+      xl = __ldg(reinterpret_cast<const uint4*>(x + row * x_ld + x_pc + c));
+      rl = __ldg(reinterpret_cast<const uint4*>(resid + row * r_ld + r_pc + c));
+    }
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gate + static_cast<long long>(utt) * gate_ld + c));
+    const float4 g1 = __ldg(reinterpret_cast<const float4*>(gate + static_cast<long long>(utt) * gate_ld + c + 4));
     const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w}, rw[4] = {rv.x, rv.y, rv.z, rv.w};
+    const uint32_t xlw[4] = {xl.x, xl.y, xl.z, xl.w}, rlw[4] = {rl.x, rl.y, rl.z, rl.w};
+    float v[8], r[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (planes == 1) {
+        v[2 * q] = f16_lo_f(xw[q]); v[2 * q + 1] = f16_hi_f(xw[q]);
+        r[2 * q] = f16_lo_f(rw[q]); r[2 * q + 1] = f16_hi_f(rw[q]);
+      } else {
+        v[2 * q] = bf16_lo_f(xw[q]) + bf16_lo_f(xlw[q]); v[2 * q + 1] = bf16_hi_f(xw[q]) + bf16_hi_f(xlw[q]);
+        r[2 * q] = bf16_lo_f(rw[q]) + bf16_lo_f(rlw[q]); r[2 * q + 1] = bf16_hi_f(rw[q]) + bf16_hi_f(rlw[q]);
+      }
+    }
     uint32_t hi[4], lo[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {

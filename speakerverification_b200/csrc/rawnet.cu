@@ -283,6 +283,156 @@ struct RnBlock {
   float *alpha = nullptr, *fc_w = nullptr, *fc_b = nullptr;
 };
 
+// ------------------------------------------------------------------ attentive aggregation heads (aggregate = 'asp' / 'sap')
+// RawNet2_custom.py:200-224 on the 29 frames that leave the last residual block; x = lrelu(bn_before_agg(.)) arrives
+// pre-activated from the last rn_apply_kernel.  The heads are 0.06 % of the network's FLOPs: one CTA per utterance,
+// fp32 SIMT, x staged once in shared memory, weights read coalesced from their TRANSPOSED copies (made at create).
+//   asp: w = softmax_T(conv2(BN(LeakyReLU_0.01(conv1(x)))));  m = sum_t x w;  s = sqrt(clamp(sum_t x^2 w - m^2, 1e-5))
+//   sap: a_t = tanh(v . (W x_t + b));  w = softmax_T(a);  mean = (sum_t w_t x_t) / T;  var = sum_t w_t x_t^2 - mean^2
+//   out = fc(cat(m, s))   (fc: Linear(2 * 512, code_dim), shared by both heads)
+enum { AGG_GRU = 0, AGG_SAP = 1, AGG_ASP = 2 };
+static constexpr int AGG_C = 512;
+static constexpr int AGG_TMAX = 32;
+
+__global__ void transpose_kernel(const float* __restrict__ in, int R, int C, float* __restrict__ out) {
+  const long long total = static_cast<long long>(R) * C;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / C), c = static_cast<int>(i - static_cast<long long>(r) * C);
+    out[static_cast<long long>(c) * R + r] = in[i];
+  }
+}
+
+// grid B, block 256.  dynamic smem: x_s [T][512] + h_s [T][att] (asp) / a_s [T] (sap) + pooled [1024]
+__global__ void __launch_bounds__(256)
+rn_agg_kernel(const bf16* __restrict__ a, int a_ld, int planes, int T, int Tp, int mode, int att,
+              const float* __restrict__ w1t, const float* __restrict__ b1, const float* __restrict__ bn_s,
+              const float* __restrict__ bn_h, const float* __restrict__ w2t, const float* __restrict__ b2,
+              const float* __restrict__ sap_v, const float* __restrict__ fc_w, const float* __restrict__ fc_b, int n_out,
+              float* __restrict__ emb, int emb_ld) {
+  extern __shared__ float sm[];
+  float* x_s = sm;                                   // [T][512]
+  float* h_s = x_s + T * AGG_C;                      // asp: [T][att]; sap: [T] attention logits (first T floats)
+  float* pooled = h_s + T * (mode == AGG_ASP ? att : 1) + 32;
+  const int u = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  // stage x: rows u * Tp + 1 + t (valid rows), 8 channels per thread and step
+  for (int i = tid; i < T * (AGG_C / 8); i += 256) {
+    const int t = i / (AGG_C / 8), c = (i - t * (AGG_C / 8)) * 8;
+    float v[8];
+    load8(a + (static_cast<long long>(u) * Tp + 1 + t) * a_ld + c, planes, AGG_C, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x_s[t * AGG_C + c + k] = v[k];
+  }
+  __syncthreads();
+  if (mode == AGG_ASP) {
+    // conv1 (512 -> att) + LeakyReLU(0.01) + BN: thread = (att channel, half of the frames)
+    const int half_t = (T + 1) / 2;
+    for (int o = tid; o < 2 * att; o += 256) {
+      const int ac = o % att, t0 = (o / att) * half_t, t1 = min(T, t0 + half_t);
+      float acc[AGG_TMAX / 2];
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX / 2; ++t) acc[t] = 0.f;
+      for (int c = 0; c < AGG_C; ++c) {
+        const float w = __ldg(w1t + static_cast<long long>(c) * att + ac);
+#pragma unroll
+        for (int t = 0; t < AGG_TMAX / 2; ++t)
+          if (t0 + t < t1) acc[t] = fmaf(w, x_s[(t0 + t) * AGG_C + c], acc[t]);
+      }
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX / 2; ++t)
+        if (t0 + t < t1) {
+          float v = acc[t] + b1[ac];
+          v = v > 0.f ? v : 0.01f * v;
+          h_s[(t0 + t) * att + ac] = fmaf(v, bn_s[ac], bn_h[ac]);
+        }
+    }
+    __syncthreads();
+    // conv2 (att -> 512), softmax over time, weighted statistics: thread = channel
+    for (int c = tid; c < AGG_C; c += 256) {
+      float lg[AGG_TMAX];
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX; ++t) lg[t] = 0.f;
+      for (int k = 0; k < att; ++k) {
+        const float w = __ldg(w2t + static_cast<long long>(k) * AGG_C + c);
+#pragma unroll
+        for (int t = 0; t < AGG_TMAX; ++t)
+          if (t < T) lg[t] = fmaf(w, h_s[t * att + k], lg[t]);
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX; ++t) if (t < T) { lg[t] += b2[c]; mx = fmaxf(mx, lg[t]); }
+      float den = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX; ++t)
+        if (t < T) {
+          const float e = expf(lg[t] - mx), xv = x_s[t * AGG_C + c];
+          den += e; s1 = fmaf(e, xv, s1); s2 = fmaf(e * xv, xv, s2);
+        }
+      const float m = s1 / den;
+      pooled[c] = m;
+      pooled[AGG_C + c] = sqrtf(fmaxf(s2 / den - m * m, 1e-5f));
+    }
+  } else {
+    // sap: a_t = tanh(v . (W x_t + b)) = tanh(sum_o v_o (b_o + sum_c W[o, c] x_t[c])); thread = (o, frame half)
+    const int half_t = (T + 1) / 2;
+    float part[AGG_TMAX / 2];
+#pragma unroll
+    for (int t = 0; t < AGG_TMAX / 2; ++t) part[t] = 0.f;
+    const int grp = tid >> 7;                         // frame half of this thread
+    const int t0 = grp * half_t, t1 = min(T, t0 + half_t);
+    for (int o = tid & 127; o < AGG_C; o += 128) {
+      float acc[AGG_TMAX / 2];
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX / 2; ++t) acc[t] = 0.f;
+      for (int c = 0; c < AGG_C; ++c) {
+        const float w = __ldg(w1t + static_cast<long long>(c) * AGG_C + o);
+#pragma unroll
+        for (int t = 0; t < AGG_TMAX / 2; ++t)
+          if (t0 + t < t1) acc[t] = fmaf(w, x_s[(t0 + t) * AGG_C + c], acc[t]);
+      }
+      const float vo = sap_v[o], bo = b1[o];
+#pragma unroll
+      for (int t = 0; t < AGG_TMAX / 2; ++t) part[t] = fmaf(vo, acc[t] + bo, part[t]);
+    }
+    // reduce the per-thread partial dot products over the 128 threads of each frame half (fixed order: deterministic)
+    float* red = pooled;                              // [256][T/2] scratch, reused before `pooled` is written
+#pragma unroll
+    for (int t = 0; t < AGG_TMAX / 2; ++t) if (t < half_t) red[tid * half_t + t] = part[t];
+    __syncthreads();
+    if (tid < T) {
+      const int g2 = tid / half_t, tt = tid - g2 * half_t;
+      float s = 0.f;
+      for (int k = 0; k < 128; ++k) s += red[(g2 * 128 + k) * half_t + tt];
+      h_s[tid] = tanhf(s);
+    }
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int t = 0; t < T; ++t) mx = fmaxf(mx, h_s[t]);
+    float den = 0.f;
+    for (int t = 0; t < T; ++t) den += expf(h_s[t] - mx);
+    __syncthreads();                                  // everyone has read `red` before pooled overwrites it
+    for (int c = tid; c < AGG_C; c += 256) {
+      float s1 = 0.f, s2 = 0.f;
+      for (int t = 0; t < T; ++t) {
+        const float w = expf(h_s[t] - mx) / den, xv = x_s[t * AGG_C + c];
+        s1 = fmaf(w, xv, s1); s2 = fmaf(w * xv, xv, s2);
+      }
+      const float mean = s1 / static_cast<float>(T);  // torch.mean over time of the weighted frames (:153)
+      pooled[c] = mean;
+      pooled[AGG_C + c] = s2 - mean * mean;           // weighted_sd (:146-150): a variance, no square root
+    }
+  }
+  __syncthreads();
+  // fc: Linear(1024 -> n_out), one warp per output (coalesced weight rows)
+  for (int o = wid; o < n_out; o += 8) {
+    const float* wr = fc_w + static_cast<long long>(o) * 2 * AGG_C;
+    float acc = 0.f;
+    for (int k = lane; k < 2 * AGG_C; k += 32) acc = fmaf(__ldg(wr + k), pooled[k], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) emb[static_cast<long long>(u) * emb_ld + o] = acc + fc_b[o];
+  }
+}
+
 struct Rawnet2 {
   int L = 0, Lp = 0, Mu = 0, T1 = 0, n_out = 0, H = 1024, sr = 16000;
   // bf16 planes of the tensor-core operands (1: bf16 mode, 2: hi|lo fp32 grade) and of the residual carriers.
@@ -298,6 +448,10 @@ struct Rawnet2 {
   bf16 *w_ih = nullptr, *w_hh = nullptr;                 // packed [3H, planes, 512] / [3H, 2, H]
   float *b_ih = nullptr, *b_hh = nullptr, *ones = nullptr, *zeros = nullptr;
   float *fcg_w = nullptr, *fcg_b = nullptr;
+  // aggregate = 'sap' / 'asp' heads (RawNet2_custom.py:97-112,200-224); gbn_s / gbn_h then hold bn_before_agg
+  int aggregate = AGG_GRU, att = 128;
+  float *ag_w1t = nullptr, *ag_b1 = nullptr, *ag_bn_s = nullptr, *ag_bn_h = nullptr, *ag_w2t = nullptr, *ag_b2 = nullptr;
+  float *ag_v = nullptr, *ag_fc_w = nullptr, *ag_fc_b = nullptr;
   std::vector<void*> owned;
 };
 
@@ -397,13 +551,23 @@ static int build_sinc(Rawnet2* e, const float* low_d, const float* band_d, int F
   return 0;
 }
 
-int rawnet2_create(int n_samples, int n_out, int gru_node, int sample_rate, int fp32_mode, const char* const* names,
-                   const void* const* ptrs, int n, Rawnet2** out) {
+static float* dtranspose(Rawnet2* e, const float* src, int R, int C) {
+  float* d = dalloc<float>(e, static_cast<size_t>(R) * C);
+  if (d == nullptr) return nullptr;
+  transpose_kernel<<<std::min((R * C + 255) / 256, 148 * 8), 256>>>(src, R, C, d);
+  return d;
+}
+
+int rawnet2_create(int n_samples, int n_out, int gru_node, int sample_rate, int fp32_mode, int aggregate, int att_dim,
+                   const char* const* names, const void* const* ptrs, int n, Rawnet2** out) {
   SVB_CHECK(n_samples > 1000 && n_out >= 1 && gru_node == 1024, "unsupported RawNet2 configuration (gru_node must be 1024)");
+  SVB_CHECK(aggregate == AGG_GRU || aggregate == AGG_SAP || aggregate == AGG_ASP, "aggregate must be 0 (gru), 1 (sap) or 2 (asp)");
+  SVB_CHECK(aggregate != AGG_ASP || (att_dim >= 1 && att_dim <= 512), "att_dim must be 1..512");
   TensorMap tm;
   for (int i = 0; i < n; ++i) tm[names[i]] = static_cast<const float*>(ptrs[i]);
   Rawnet2* e = new Rawnet2();
   e->L = n_samples; e->n_out = n_out; e->H = gru_node; e->sr = sample_rate; e->planes = fp32_mode ? 2 : 1; e->xplanes = e->planes;
+  e->aggregate = aggregate; e->att = att_dim;
   const int T0 = n_samples - (SINC_TAPS - 1);
   e->T1 = T0 / 3;
   e->Mu = (n_samples + SINC_K + SINC_STRIDE - 1) / SINC_STRIDE;
@@ -436,6 +600,30 @@ int rawnet2_create(int n_samples, int n_out, int gru_node, int sample_rate, int 
       }
     }
     if (!ok) break;
+    if (aggregate != AGG_GRU) {
+      if (make_bn(e, tm, "bn_before_agg.", 512, &e->gbn_s, &e->gbn_h)) break;
+      const float *fw = find(tm, "fc.weight"), *fb = find(tm, "fc.bias");
+      if (!fw || !fb) break;
+      e->ag_fc_w = dcopy(e, fw, static_cast<size_t>(n_out) * 1024); e->ag_fc_b = dcopy(e, fb, n_out);
+      if (aggregate == AGG_SAP) {
+        const float *lw = find(tm, "attention_sap.lin_proj.weight"), *lb = find(tm, "attention_sap.lin_proj.bias");
+        const float* v = find(tm, "attention_sap.v");
+        if (!lw || !lb || !v) break;
+        e->ag_w1t = dtranspose(e, lw, 512, 512); e->ag_b1 = dcopy(e, lb, 512); e->ag_v = dcopy(e, v, 512);
+      } else {
+        const float *w1 = find(tm, "attention.0.weight"), *b1 = find(tm, "attention.0.bias");
+        const float *w2 = find(tm, "attention.3.weight"), *b2 = find(tm, "attention.3.bias");
+        if (!w1 || !b1 || !w2 || !b2) break;
+        if (make_bn(e, tm, "attention.2.", att_dim, &e->ag_bn_s, &e->ag_bn_h)) break;
+        e->ag_w1t = dtranspose(e, w1, att_dim, 512); e->ag_b1 = dcopy(e, b1, att_dim);      // Conv1d weight [att, 512, 1]
+        e->ag_w2t = dtranspose(e, w2, 512, att_dim); e->ag_b2 = dcopy(e, b2, 512);          // Conv1d weight [512, att, 1]
+      }
+      if (!e->ag_fc_w || !e->ag_fc_b || !e->ag_w1t || !e->ag_b1) { set_error("out of device memory"); break; }
+      if (e->T[NB] > AGG_TMAX) { set_error("the attentive heads handle up to %d frames (got %d)", AGG_TMAX, e->T[NB]); break; }
+      if (cudaDeviceSynchronize() != cudaSuccess) { set_error("RawNet2 weight preparation failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+      rc = 0;
+      break;
+    }
     if (make_bn(e, tm, "bn_before_gru.", 512, &e->gbn_s, &e->gbn_h)) break;
     const float *wih = find(tm, "gru.weight_ih_l0"), *whh = find(tm, "gru.weight_hh_l0");
     const float *bih = find(tm, "gru.bias_ih_l0"), *bhh = find(tm, "gru.bias_hh_l0");
@@ -636,8 +824,28 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     cur = nxt;
     if (stop_after == i) return 0;
   }
-  // ---- GRU (RawNet2_custom.py:192-198): input projection for all steps, then T sequential steps
   const int Tg = e->T[NB];
+  if (e->aggregate != AGG_GRU) {
+    // ---- attentive heads (RawNet2_custom.py:200-224): one CTA per utterance on the 29 pre-activated frames
+    const int att = e->aggregate == AGG_ASP ? e->att : 1;
+    const size_t smem = (static_cast<size_t>(Tg) * AGG_C + static_cast<size_t>(Tg) * att + 32 + 4096) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+      SVB_CUDA_OK(cudaFuncSetAttribute(rn_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_set = true;
+    }
+    SVB_CHECK(smem <= 200 * 1024, "attentive head: %zu bytes of shared memory", smem);
+    float* dst = l2norm ? hs : emb;                       // hs ([B, H] fp32, H >= n_out rows' worth) as the un-normalised buffer
+    const int dst_ld = l2norm ? e->n_out : emb_ld;
+    SVB_CHECK(!l2norm || e->n_out <= H, "nOut above gru_node with l2norm");
+    rn_agg_kernel<<<B, 256, smem, st>>>(ab[cur], P * 512, P, Tg, Tg + 2, e->aggregate, e->att, e->ag_w1t, e->ag_b1, e->ag_bn_s,
+                                        e->ag_bn_h, e->ag_w2t, e->ag_b2, e->ag_v, e->ag_fc_w, e->ag_fc_b, e->n_out, dst, dst_ld);
+    count_launch();
+    SVB_CUDA_OK(cudaGetLastError());
+    if (l2norm) return l2norm_rows(dst, dst_ld, emb, emb_ld, B, e->n_out, 1e-12f, st);
+    return 0;
+  }
+  // ---- GRU (RawNet2_custom.py:192-198): input projection for all steps, then T sequential steps
   {
     GemmOperands ops{};
     ops.a = ab[cur]; ops.lda = P * 512; ops.a_cols = P * 512;

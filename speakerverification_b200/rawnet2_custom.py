@@ -63,15 +63,26 @@ class RawNetBasicBlock(nn.Module):   # RawNet_baseline.py:181-232
             self.shortcut = nn.Sequential(nn.Conv1d(inplanes, planes, kernel_size=1, stride=1, bias=False))
 
 
+class Classic_Attention(nn.Module):   # RawNet_baseline.py:423-436 (parameter holder of the 'sap' head)
+    def __init__(self, input_dim, embed_dim):
+        super().__init__()
+        self.lin_proj = nn.Linear(input_dim, embed_dim)
+        self.v = nn.Parameter(torch.randn(embed_dim))
+
+
 class RawNet2Engine:
     """Packed RawNet2 weights + forward (svb_rawnet2_*).  `state` maps reference state-dict names (without
     the '__S__.' prefix) to fp32 CUDA tensors."""
 
-    def __init__(self, state, n_samples, n_out, gru_node=1024, sample_rate=16000, precision="f16"):
+    AGGREGATES = {"gru": 0, "sap": 1, "asp": 2}
+
+    def __init__(self, state, n_samples, n_out, gru_node=1024, sample_rate=16000, precision="f16", aggregate="gru",
+                 att_dim=128):
         from .engine import normalize_precision
         precision = normalize_precision(precision)
         self.n_samples, self.n_out, self.precision = int(n_samples), int(n_out), precision
-        cfg = nv.SvbRawnet2Cfg(self.n_samples, self.n_out, int(gru_node), int(sample_rate), 1 if precision == "fp32" else 0)
+        cfg = nv.SvbRawnet2Cfg(self.n_samples, self.n_out, int(gru_node), int(sample_rate), 1 if precision == "fp32" else 0,
+                               self.AGGREGATES[aggregate], int(att_dim))
         keep, names, ptrs = [], [], []
         for k, v in state.items():
             if not torch.is_tensor(v) or not v.is_floating_point():
@@ -148,8 +159,8 @@ class RawNet2(nn.Module):
                  code_dim=512, in_channels=1, log_input=True, nb_gru_layers=1, gru_node=1024, first_conv_size=251,
                  precision=None, **kwargs):
         super().__init__()
-        if front_proc != "sinc" or aggregate != "gru" or nb_gru_layers != 1 or in_channels != 1:
-            raise NotImplementedError("the libsvb RawNet2 path covers the default front_proc='sinc', aggregate='gru'")
+        if front_proc != "sinc" or aggregate not in ("gru", "sap", "asp") or nb_gru_layers != 1 or in_channels != 1:
+            raise NotImplementedError("the libsvb RawNet2 path covers front_proc='sinc' with aggregate 'gru' / 'sap' / 'asp'")
         if str(kwargs.get("features", "raw")).strip().lower() != "raw":
             raise NotImplementedError("RawNet2 consumes raw waveforms: set features: raw")
         if list(layers) != LAYERS or list(nb_filters) != FILTERS or first_conv_size != 251:
@@ -165,10 +176,20 @@ class RawNet2(nn.Module):
         self.first_bn = nn.BatchNorm1d(nb_filters[0])
         for i in range(6):
             setattr(self, "layer%d" % (i + 1), self._make_layer(block, nb_filters[i], layers[i]))
-        self.bn_before_gru = nn.BatchNorm1d(nb_filters[5])
-        self.gru = nn.GRU(input_size=nb_filters[5], hidden_size=gru_node, num_layers=1, batch_first=True)
-        self.fc_after_gru = nn.Linear(gru_node, code_dim)
-        self.fc = nn.Linear(nb_filters[5] * 2, code_dim)      # unused by the gru head; kept for the checkpoint layout
+        self.aggregate, self.att_dim = aggregate, att_dim
+        if aggregate == "gru":                                # src/models/RawNet2_custom.py:84-112
+            self.bn_before_gru = nn.BatchNorm1d(nb_filters[5])
+            self.gru = nn.GRU(input_size=nb_filters[5], hidden_size=gru_node, num_layers=1, batch_first=True)
+            self.fc_after_gru = nn.Linear(gru_node, code_dim)
+        elif aggregate == "sap":
+            self.bn_before_agg = nn.BatchNorm1d(nb_filters[5])
+            self.attention_sap = Classic_Attention(nb_filters[5], nb_filters[5])
+        else:
+            self.bn_before_agg = nn.BatchNorm1d(nb_filters[5])
+            self.attention = nn.Sequential(nn.Conv1d(nb_filters[5], att_dim, kernel_size=1), nn.LeakyReLU(),
+                                           nn.BatchNorm1d(att_dim), nn.Conv1d(att_dim, nb_filters[5], kernel_size=1),
+                                           nn.Softmax(dim=-1))
+        self.fc = nn.Linear(nb_filters[5] * 2, code_dim)      # the sap / asp embedding layer; unused by the gru head
         if precision is None:
             # the reference's `mixedprec` only autocasts the TRAINING step (src/model.py:256); evaluateFromList /
             # testFromList always run fp32, so fp32-grade is the default and bf16 is opt-in through svb_precision
@@ -194,7 +215,8 @@ class RawNet2(nn.Module):
         fp = self._state_fingerprint()
         if self._engine is None or fp != self._fingerprint:
             self._engine = RawNet2Engine(dict(self.state_dict()), self.n_samples, self.n_out, self.gru_node,
-                                         self.sample_rate, precision=self.precision)
+                                         self.sample_rate, precision=self.precision, aggregate=self.aggregate,
+                                         att_dim=self.att_dim)
             self._fingerprint = fp
         return self._engine
 

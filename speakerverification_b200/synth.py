@@ -165,7 +165,7 @@ RAWNET_LAYERS = [1, 1, 1, 2, 1, 2]
 RAWNET_FILTERS = [128, 128, 256, 256, 512, 512]
 
 
-def rawnet2_param_shapes(n_out=512, n_samples=64000, gru_node=1024, prefix="__S__."):
+def rawnet2_param_shapes(n_out=512, n_samples=64000, gru_node=1024, prefix="__S__.", aggregate="gru", att_dim=128):
     """Ordered (key, shape, kind) list matching RawNet2_custom.MainModel's state-dict (144 entries)."""
     out = []
 
@@ -196,19 +196,34 @@ def rawnet2_param_shapes(n_out=512, n_samples=64000, gru_node=1024, prefix="__S_
             if inpl != planes:
                 out.append((p + "shortcut.0.weight", (planes, inpl, 1), "w"))
             inpl = planes
-    bn(P + "bn_before_gru.", RAWNET_FILTERS[5])
-    out.append((P + "gru.weight_ih_l0", (3 * gru_node, RAWNET_FILTERS[5]), "gru"))
-    out.append((P + "gru.weight_hh_l0", (3 * gru_node, gru_node), "gru"))
-    out.append((P + "gru.bias_ih_l0", (3 * gru_node,), "gru"))
-    out.append((P + "gru.bias_hh_l0", (3 * gru_node,), "gru"))
-    out.append((P + "fc_after_gru.weight", (n_out, gru_node), "lin"))
-    out.append((P + "fc_after_gru.bias", (n_out,), "b"))
+    C5 = RAWNET_FILTERS[5]
+    if aggregate == "gru":
+        bn(P + "bn_before_gru.", C5)
+        out.append((P + "gru.weight_ih_l0", (3 * gru_node, C5), "gru"))
+        out.append((P + "gru.weight_hh_l0", (3 * gru_node, gru_node), "gru"))
+        out.append((P + "gru.bias_ih_l0", (3 * gru_node,), "gru"))
+        out.append((P + "gru.bias_hh_l0", (3 * gru_node,), "gru"))
+        out.append((P + "fc_after_gru.weight", (n_out, gru_node), "lin"))
+        out.append((P + "fc_after_gru.bias", (n_out,), "b"))
+    elif aggregate == "sap":                                  # RawNet2_custom.py:97-100, RawNet_baseline.py:423-429
+        bn(P + "bn_before_agg.", C5)
+        out.append((P + "attention_sap.v", (C5,), "vec"))
+        out.append((P + "attention_sap.lin_proj.weight", (C5, C5), "lin"))
+        out.append((P + "attention_sap.lin_proj.bias", (C5,), "b"))
+    else:                                                     # 'asp', RawNet2_custom.py:102-111
+        bn(P + "bn_before_agg.", C5)
+        out.append((P + "attention.0.weight", (att_dim, C5, 1), "w"))
+        out.append((P + "attention.0.bias", (att_dim,), "b"))
+        bn(P + "attention.2.", att_dim)
+        out.append((P + "attention.3.weight", (C5, att_dim, 1), "w"))
+        out.append((P + "attention.3.bias", (C5,), "b"))
     out.append((P + "fc.weight", (n_out, 2 * RAWNET_FILTERS[5]), "lin"))
     out.append((P + "fc.bias", (n_out,), "b"))
     return out
 
 
-def rawnet2_state_dict(n_out=512, n_samples=64000, gru_node=1024, seed=4321, bn_stats=None, sample_rate=16000):
+def rawnet2_state_dict(n_out=512, n_samples=64000, gru_node=1024, seed=4321, bn_stats=None, sample_rate=16000,
+                       aggregate="gru", att_dim=128):
     """Random RawNet2 weights (numpy float32) under the reference's key names; sinc bands start from the
     reference's mel-spaced initialisation (RawNet_baseline.py:296-309) with a seeded perturbation."""
     rng = np.random.default_rng(seed)
@@ -216,7 +231,7 @@ def rawnet2_state_dict(n_out=512, n_samples=64000, gru_node=1024, seed=4321, bn_
     to_mel = lambda hz: 2595 * np.log10(1 + hz / 700)
     to_hz = lambda mel: 700 * (10 ** (mel / 2595) - 1)
     hz = to_hz(np.linspace(to_mel(10), to_mel(sample_rate / 2 - 100), RAWNET_FILTERS[0] + 1))
-    for key, shape, kind in rawnet2_param_shapes(n_out, n_samples, gru_node):
+    for key, shape, kind in rawnet2_param_shapes(n_out, n_samples, gru_node, aggregate=aggregate, att_dim=att_dim):
         if kind == "w":
             fan_in = shape[1] * shape[2]
             v = rng.uniform(-1.0, 1.0, size=shape) * np.sqrt(4.5 / fan_in)
@@ -224,6 +239,8 @@ def rawnet2_state_dict(n_out=512, n_samples=64000, gru_node=1024, seed=4321, bn_
             v = rng.uniform(-1.0, 1.0, size=shape) * np.sqrt(3.0 / shape[1])
         elif kind == "gru":
             v = rng.uniform(-1.0, 1.0, size=shape) / np.sqrt(gru_node)
+        elif kind == "vec":
+            v = rng.standard_normal(shape) / np.sqrt(shape[0]) * 4.0
         elif kind == "b":
             v = rng.uniform(-0.1, 0.1, size=shape)
         elif kind == "g":

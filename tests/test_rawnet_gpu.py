@@ -167,3 +167,47 @@ def test_rawnet2_batch_invariance_and_api(setup):
         tgt[k].copy_(torch.as_tensor(v))
     out = net(torch.from_numpy(waves[:5]))
     assert torch.allclose(out, full, atol=1e-6)
+
+
+@pytest.mark.parametrize("agg", ["sap", "asp"])
+@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("f16", 0.999, 2e-3)])
+def test_attentive_heads_match_reference(agg, precision, cos_min, tol):
+    """aggregate='sap' / 'asp' (src/models/RawNet2_custom.py:97-112,200-224: bn_before_agg, Classic_Attention /
+    conv-LeakyReLU-BN-conv-softmax attention, weighted statistics, fc) against the reference's own embeddings and cosine
+    trial scores (tests/golden/cfg4_rawnet2_heads.npz), through the engine and through the plugin registry."""
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    from speakerverification_b200.rawnet2_custom import RawNet2Engine
+    g = dict(np.load(os.path.join(ROOT, "tests", "golden", "cfg4_rawnet2_heads.npz")))
+    bn = {k[len(agg) + 4:]: v for k, v in g.items() if k.startswith(agg + "/bn/")}
+    sd = synth.rawnet2_state_dict(aggregate=agg, bn_stats=bn)
+    state = {k[len("__S__."):]: torch.as_tensor(v).cuda() for k, v in sd.items()}
+    waves, spk = synth.utterance_set(4, 4, L4)
+    eng = RawNet2Engine(state, L4, 512, precision=precision, aggregate=agg)
+    got_t = eng.forward(torch.from_numpy(waves).cuda())
+    got, ref = got_t.cpu().numpy(), g[agg + "/emb_batch"]
+    assert np.isfinite(got).all()
+    cos = (got * ref).sum(1) / np.linalg.norm(got, axis=1) / np.linalg.norm(ref, axis=1)
+    lab, ti, tj = synth.trial_list(spk, 120)
+    s = U.cosine_trials(got_t.unsqueeze(1).contiguous(), torch.from_numpy(ti.astype(np.int32)).cuda(),
+                        torch.from_numpy(tj.astype(np.int32)).cuda()).cpu().numpy()
+    dev = np.abs(s - g[agg + "/scores_cos"]).max()
+    print("RawNet2", agg, precision, "min cos", cos.min(), "max trial-score dev", dev)
+    assert cos.min() >= cos_min, cos
+    assert dev <= tol, dev
+    # l2norm path of the head and the plugin registry (SpeakerEncoder(features='raw', aggregate=...))
+    nrm = eng.forward(torch.from_numpy(waves[:3]).cuda(), l2norm=True)
+    assert torch.allclose(nrm, torch.nn.functional.normalize(got_t[:3], dim=1), atol=1e-6)
+    if precision == "fp32":
+        from speakerverification_b200.model import SpeakerEncoder, WrappedModel
+        args = dict(device="cuda", gpu=0, model={"name": "RawNet2_custom", "nOut": 512}, criterion={"name": "AAmSoftmaxAP"},
+                    features="raw", n_mels=80, aggregate=agg,
+                    audio_spec={"sample_rate": 16000, "sentence_len": 4.0, "win_len": 0.025, "hop_len": 0.01},
+                    dataloader_options={"nPerSpeaker": 2}, svb_precision="fp32")
+        net = WrappedModel(SpeakerEncoder(**args))
+        tgt = net.module.state_dict()
+        assert set(k for k in tgt if k.startswith("__S__.")) == set(sd)
+        for k, v in sd.items():
+            tgt[k].copy_(torch.as_tensor(v))
+        out = net(torch.from_numpy(waves[:3]))
+        assert torch.allclose(out, got_t[:3], atol=1e-6)
