@@ -816,9 +816,10 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     const bool need_x = !last && e->blk[i + 1].wsc == nullptr;
     const bf16* src = k.down ? zpb : zb;
     const int rows_per_cta = 128;
+    const int PA = P;
     rn_apply_kernel<<<dim3((Tout + 2 + rows_per_cta - 1) / rows_per_cta, B), 256, 0, st>>>(
         src, PX * k.cout, PX, k.cout, Tout, k.cout, k.alpha, gate, ns, nh, need_x ? xb[nxt] : nullptr, PX * k.cout, k.cout,
-        ab[nxt], P * k.cout, P, k.cout, rows_per_cta);
+        ab[nxt], PA * k.cout, PA, k.cout, rows_per_cta);
     count_launch();
     SVB_CUDA_OK(cudaGetLastError());
     cur = nxt;
