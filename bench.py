@@ -3,11 +3,16 @@
 
   python bench.py [--gpus N --steps K --warmup W] [--impl reference]
 
-Workload (BASELINE.json configs[1]): ECAPA-TDNN C=1024, 80-mel fbank, 10 000 synthetic 3 s 16 kHz
-utterances per GPU, bf16 tensor-core operands.  One step = one pass of the hot path (waveform ->
-embedding) over all utterances.  `value` is device-timed with the waveforms resident in HBM; `e2e`
-goes through the public API (ModelHandling.embed_batches) from pinned HOST buffers with the H2D
-copies and the D2H read of the embeddings inside the timed region.
+Headline workload (BASELINE.json configs[1]): ECAPA-TDNN C=1024, 80-mel fbank, 10 000 synthetic 3 s 16 kHz
+utterances per GPU, 16-bit tensor-core operands (IEEE half, fp32 accumulation: BASELINE's "bf16" config at the same
+tcgen05 rate, see profiles/r02_precision.md).  One step = one pass of the hot path (waveform -> embedding) over all
+utterances.  `value` is device-timed with the waveforms resident in HBM; `e2e` goes through the public API
+(ModelHandling.embed_batches) from pinned HOST buffers with the H2D copies and the D2H read of the embeddings inside
+the timed region.  The default run (--workload all) adds the other BASELINE configs as sub-objects of the same line:
+`eval` (configs[2], ragged 2-20 s + AS-norm), `rawnet2` (configs[3]), `scoring` (configs[4]), at every N; at N = 1 also
+`gpu_library_baseline` (the reference's forward as PyTorch eager runs it on this GPU: cuFFT / cuBLAS / cuDNN, fp32 and
+autocast-bf16) and `cpu_baseline` (the oracle port on the host cores); at N > 1 per-rank step times, one strong-scaling
+line and the distributed API check (evaluateFromList(distributed=True) against the single-GPU call).
 """
 import argparse
 import json
@@ -356,8 +361,8 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
            "dtype": "bf16x3 (split, fp32 grade) GEMM, fp64 top-K statistics", "data": "synthetic",
            "config": {"workload": "scoring sweep (configs[4]): %d trials over %d unique embeddings vs %d-cohort, "
                                   "top-%d AS-norm, D=%d, per GPU" % (NT, U, N, K, D),
-                      "l2": "score matrix produced in L2-resident row chunks; embeddings+cohort %.0f MB per step"
-                            % ((U + N) * D * 4 / 1e6)},
+                      "l2": "the score matrix is never stored (top-K pre-filter in the GEMM epilogue); embeddings + "
+                            "cohort %.0f MB per step, every step re-packs them from fp32" % ((U + N) * D * 4 / 1e6)},
            "e2e": {"value": world * NT * steps / dt, "unit": "trials/s",
                    "h2d_bytes_per_step": (U + N) * D * 4 + 2 * NT * 4, "d2h_bytes_per_step": NT * 4,
                    "api": "utils.score_trials(emb, idx_a, idx_b, 'norm', cohorts, top) from pinned host buffers"},
@@ -365,12 +370,18 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
     if rank == 0:
         hbm, tf_burst, tf_sust, src = peaks()
         flops = 2.0 * U * N * D
-        res["roofline"] = {"kernel": "cohort-score GEMM + top-K select (svb_asnorm_stats), whole phase",
+        res["roofline"] = {"kernel": "svb_asnorm_stats, whole phase: sample GEMM + threshold + FILTER GEMM "
+                                     "(gemm_pw_kernel<256, ACT_FILTER>, 63 % of the phase) + candidate select",
                            "bound": "tensor", "achieved": flops * steps / (ms * 1e-3) / 1e12, "peak": tf_sust / 3.0,
                            "unit": "TFLOP/s", "frac": flops * steps / (ms * 1e-3) / 1e12 / (tf_sust / 3.0),
-                           "traffic": None,
+                           # dram__bytes_read.sum + dram__bytes_write.sum of ONE filter-GEMM launch (8192 utterance rows x
+                           # 20 032 cohort columns, ncu --set full, profiles/r02_ncu.md): 21.76 MB + 0.03 MB against
+                           # (8192 + 20000) * 192 * 4 B = 21.65 MB algorithmic -- the 656 MB score tile never leaves the SM
+                           "traffic": 2.178e7 if (N == 20000 and U >= 8192) else None,
+                           "traffic_unit": "bytes per filter-GEMM launch (8192 rows); algorithmic 2.165e7",
                            "note": "algorithmic 2*U*N*D FLOP per step over the step time; fp32-grade scores cost 3 "
-                                   "bf16 passes, so the bound is the sustained bf16 peak / 3 (" + src + ")"}
+                                   "bf16 passes, so the bound is the sustained bf16 peak / 3 (" + src + "); the fused "
+                                   "path executes 1.128x the algorithmic FLOPs (the 1/8 sample GEMM)"}
         if world == 1 and full_line:
             rate, n, dtc = cpu_scoring_rate(e, c, ia, ib, K, 10.0)
             res["cpu_baseline"] = {"value": rate, "unit": "trials/s", "cores": os.cpu_count(), "kind": "port",
