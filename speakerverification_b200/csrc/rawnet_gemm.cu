@@ -23,6 +23,8 @@
 // hi|lo planes in fp32-grade mode (operand and residual-carrier plane counts are separate parameters).  T is the same for
 // every utterance (the model's LayerNorm weights fix the input length, RawNet_baseline.py:13-24), so
 // utterance / frame of a row are computed arithmetically.
+#include <stdlib.h>
+
 #include "svb_internal.h"
 #include "svb_ptx.cuh"
 
@@ -79,11 +81,27 @@ __device__ __forceinline__ void store_planes(bf16* dst, int planes, int plane_co
   }
 }
 
-template <int BN, int EPI>
+// WRES ("weights resident, taps shared"): the k = 3 convolutions of the 128-channel layers (layer1 / layer2: 21 250 and
+// 7 083 frames per utterance, 37 % of the RawNet2 step).  With N = K = 128 these GEMMs have the arithmetic intensity of
+// a copy: the generic mainloop re-loads the 16 KB W tile with every A tile and loads every A row three times (one
+// row-shifted box per tap), 96 KB from L2 per 128 rows x 64 channels, and ran at 55 % of the HBM peak.  Here all six W
+// tiles (3 taps x 2 K chunks = 96 KB) are loaded ONCE per CTA, and one 136-row A box per K chunk serves the three taps
+// through shared-memory descriptors whose start address is shifted by 0 / 1 / 2 rows (tcgen05 applies the 128B swizzle
+// to absolute address bits, so any 128-byte aligned start row is legal: profiles/r01_desc_shift_probe.txt) -- 17 KB from
+// L2 per 128 rows x 64 channels.
+static constexpr int WRES_A_ROWS = 136;
+static constexpr int WRES_A_BYTES = WRES_A_ROWS * 128;      // 17 408 = 17 x 1024
+static constexpr int WRES_W_BYTES = 6 * 128 * 128;          // 3 taps x 2 K chunks of [128 rows x 64 ch]
+static constexpr int WRES_STAGES = 6;
+static constexpr int WRES_SMEM_BYTES = WRES_W_BYTES + WRES_STAGES * WRES_A_BYTES + 1024;
+
+template <int BN, int EPI, bool WRES = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const RnGemmParams p) {
   using Cfg = RnCfg<BN>;
-  constexpr int STAGES = Cfg::STAGES;
+  constexpr int STAGES = WRES ? WRES_STAGES : Cfg::STAGES;
+  static_assert(!WRES || BN == 128, "the W-resident variant serves the 128-channel layers");
+  __shared__ __align__(8) uint64_t wfull_bar;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES];
   __shared__ __align__(8) uint64_t empty_bar[STAGES];
@@ -115,6 +133,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(smem_u32(&tfull_bar[a]), 1);
       mbar_init(smem_u32(&tempty_bar[a]), 8);
     }
+    mbar_init(smem_u32(&wfull_bar), 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -131,7 +150,22 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (WRES) {
+        const uint32_t wb = smem_u32(&wfull_bar);
+        mbar_arrive_expect_tx(wb, WRES_W_BYTES);
+        for (int j = 0; j < 6; ++j) tma_load_2d(smem_base + j * 16384, &tmW, wb, j * BLOCK_K, 0);    // j = tap * 2 + kcx
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+          const int m0 = tile * BLOCK_M;
+          for (int kcx = 0; kcx < 2; ++kcx) {
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+            mbar_arrive_expect_tx(fb, WRES_A_BYTES);
+            tma_load_2d(smem_base + WRES_W_BYTES + stage * WRES_A_BYTES, &tmA, fb, kcx * BLOCK_K, m0 - 1);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+      for (int tile = blockIdx.x; tile < num_tiles && !WRES; tile += gridDim.x) {
         // n fastest: consecutive CTAs share the A tile (L2), W is small and stays cache resident
         const int m0 = (tile / num_n_tiles) * BLOCK_M;
         const int n0 = (tile % num_n_tiles) * BN;
@@ -165,7 +199,34 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      if (WRES) {
+        mbar_wait(smem_u32(&wfull_bar), 0);
+        tc_fence_after();
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+          const int acc = it & 1;
+          const uint32_t acc_phase = (it >> 1) & 1u;
+          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          uint32_t accf = 0;
+          for (int kcx = 0; kcx < 2; ++kcx) {
+            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            tc_fence_after();
+            const uint32_t sa = smem_base + WRES_W_BYTES + stage * WRES_A_BYTES;
+#pragma unroll
+            for (int tap = 0; tap < 3; ++tap) {
+              const uint64_t adesc = umma_desc_sw128(sa + tap * 128);                      // rows m0 - 1 + tap ...
+              const uint64_t bdesc = umma_desc_sw128(smem_base + (tap * 2 + kcx) * 16384);
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k) { umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accf); accf = 1; }
+            }
+            umma_commit(smem_u32(&empty_bar[stage]));
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit(smem_u32(&tfull_bar[acc]));
+        }
+      }
+      for (int tile = blockIdx.x; tile < num_tiles && !WRES; tile += gridDim.x, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
@@ -309,18 +370,18 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------ host side
-template <int BN, int EPI>
+template <int BN, int EPI, bool WRES = false>
 static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const RnGemmParams& p, cudaStream_t stream) {
   using Cfg = RnCfg<BN>;
+  constexpr int SMEM = WRES ? WRES_SMEM_BYTES : Cfg::SMEM_BYTES;
   static bool attr_set = false;
   if (!attr_set) {
-    SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     Cfg::SMEM_BYTES));
+    SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set = true;
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  rn_gemm_kernel<BN, EPI><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, w, p);
+  rn_gemm_kernel<BN, EPI, WRES><<<grid, NUM_THREADS, SMEM, stream>>>(a, w, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -340,6 +401,15 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   SVB_CHECK(p.N % 128 == 0, "RawNet conv GEMM: N must be a multiple of 128");
   const int bn = (p.N % 256 == 0) ? 256 : 128;
   if (make_map(&mw, w, w_rows, w_cols, w_cols, bn)) return -1;
+  // 128-channel k = 3 layers in the 16-bit mode: W-resident, tap-shared mainloop (SVB_RN_WRES=0: generic mainloop)
+  static const bool wres_on = [] { const char* e = getenv("SVB_RN_WRES"); return e == nullptr || e[0] != '0'; }();
+  if (wres_on && p.N == 128 && p.num_taps == 3 && p.kc_per_tap == 2 && p.num_pass == 1 && p.w_planes == 1 &&
+      p.tap_off[0] == -1 && p.tap_off[1] == 0 && p.tap_off[2] == 1 && (epi == EPI_AFF_LRELU || epi == EPI_ADD)) {
+    CUtensorMap ma136;
+    if (make_map(&ma136, a, a_rows, a_cols, a_ld, WRES_A_ROWS)) return -1;
+    return epi == EPI_AFF_LRELU ? launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, p, stream)
+                                : launch_rn_t<128, EPI_ADD, true>(ma136, mw, p, stream);
+  }
   if (bn == 256) {
     if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, p, stream);
     if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, p, stream);
