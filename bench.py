@@ -328,12 +328,8 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
         out = step()
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
     launches = int(nv.lib().svb_launch_count())
-    if world > 1:
-        t = torch.tensor([ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms, per_rank = rank_stats(e0.elapsed_time(e1), {"device": device, "world": world, "dist": dist})
     value = world * NT * steps / (ms * 1e-3)
     # end to end: host embeddings / cohort / trial indices in, host scores out, through utils.score_trials
     he = torch.from_numpy(e).unsqueeze(1).pin_memory()
@@ -341,8 +337,8 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
     hc = torch.from_numpy(c).pin_memory()
 
     def e2e_step():
-        d = he.to(device, non_blocking=True)
-        return SU.score_trials(d, hia.to(device, non_blocking=True), hib.to(device, non_blocking=True), "norm",
+        # host tensors straight into the public call: it uploads the embeddings in pieces under the cohort GEMM
+        return SU.score_trials(he, hia.to(device, non_blocking=True), hib.to(device, non_blocking=True), "norm",
                                hc.to(device, non_blocking=True), top=K, normalize=False).cpu()
     e2e_step()
     torch.cuda.synchronize()
@@ -367,6 +363,9 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
                    "h2d_bytes_per_step": (U + N) * D * 4 + 2 * NT * 4, "d2h_bytes_per_step": NT * 4,
                    "api": "utils.score_trials(emb, idx_a, idx_b, 'norm', cohorts, top) from pinned host buffers"},
            "gpu_launches": launches}
+    if per_rank is not None:
+        res["per_rank_ms_per_step"] = {k: (v / steps if not isinstance(v, list) else [x / steps for x in v])
+                                       for k, v in per_rank.items()}
     if rank == 0:
         hbm, tf_burst, tf_sust, src = peaks()
         flops = 2.0 * U * N * D

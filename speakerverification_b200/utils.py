@@ -114,11 +114,48 @@ def score_trials(emb, idx_a, idx_b, scoring_mode="cosine", cohorts=None, top=200
     if scoring_mode == "norm":
         if cohorts is None:
             raise ValueError("scoring_mode='norm' needs a cohort bank")
+        if torch.is_tensor(emb) and not emb.is_cuda:
+            return _score_norm_from_host(emb, idx_a, idx_b, cohorts, top, normalize)
         em = mean_embeddings(emb, normalize)
         mu, sg = asnorm_stats(em, _dev(cohorts, emb.device), top)
         return asnorm_trials(em, idx_a, idx_b, mu, sg)
     raise ValueError("scoring_mode %r: the reference knows 'cosine', 'norm' and 'pnorm' (src/model.py:433-444)"
                      % (scoring_mode,))
+
+
+def _score_norm_from_host(emb, idx_a, idx_b, cohorts, top, normalize, rows_per_piece=32768, device=None):
+    """AS-norm with the crop embeddings still on the HOST (pinned for full overlap): the cohort statistics of an
+    utterance depend on that utterance alone, so the [U, n, D] tensor is uploaded in pieces on a side stream while the
+    cohort GEMM of the previous piece runs; the trial kernel starts when the last piece's statistics are in."""
+    if device is None:
+        device = idx_a.device if torch.is_tensor(idx_a) and idx_a.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    with torch.cuda.device(device):
+        U, n, D = emb.shape
+        coh = _dev(cohorts, device)
+        ia = idx_a.to(device, non_blocking=True) if torch.is_tensor(idx_a) else torch.as_tensor(idx_a, device=device)
+        ib = idx_b.to(device, non_blocking=True) if torch.is_tensor(idx_b) else torch.as_tensor(idx_b, device=device)
+        main = torch.cuda.current_stream(device)
+        copy = torch.cuda.Stream(device=device)
+        d_emb = torch.empty((U, n, D), dtype=torch.float32, device=device)
+        em = torch.empty((U, D), dtype=torch.float32, device=device)
+        mu = torch.empty(U, dtype=torch.float32, device=device)
+        sg = torch.empty(U, dtype=torch.float32, device=device)
+        copy.wait_stream(main)
+        events = []
+        for r0 in range(0, U, rows_per_piece):
+            r1 = min(U, r0 + rows_per_piece)
+            with torch.cuda.stream(copy):
+                d_emb[r0:r1].copy_(emb[r0:r1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy)
+            events.append((r0, r1, ev))
+        for r0, r1, ev in events:
+            main.wait_event(ev)
+            em[r0:r1] = mean_embeddings(d_emb[r0:r1], normalize)
+            m, s_ = asnorm_stats(em[r0:r1], coh, top)
+            mu[r0:r1], sg[r0:r1] = m, s_
+        d_emb.record_stream(main)
+        return asnorm_trials(em, ia.to(torch.int32), ib.to(torch.int32), mu, sg)
 
 
 # ------------------------------------------------------------------ per-trial reference signatures

@@ -47,7 +47,7 @@ NEXT_BN = ["layer2.0.bn1.", "layer3.0.bn1.", "layer4.0.bn1.", "layer4.1.bn1.", "
 COUT = [128, 128, 256, 256, 256, 512, 512, 512]
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("f16", 4e-3)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("f16", 2e-3)])      # measured 1.4e-5 / 8.9e-4 of the activation scale
 def test_front_end(setup, precision, tol):
     """LayerNorm + sinc conv + |.| + maxpool3 + first_bn + lrelu (RawNet2_custom.py:171-176) and layer1's bn1+lrelu."""
     sd, state, waves, st, _ = setup

@@ -170,3 +170,20 @@ def test_fused_prefilter_path_cfg5_like(order):
     assert np.abs(sg.cpu().numpy() - S.std(1)).max() <= 2e-6
     print("fused AS-norm path, cohort order", order, ": fix-up rows", nfix, "of 4096")
     assert 0 <= nfix <= 40
+
+
+def test_score_trials_from_host_tensors():
+    """utils.score_trials with the embeddings still on the host (pinned): pieces are uploaded under the cohort GEMM of
+    the previous piece; the scores equal the device-resident call bit for bit (per-utterance statistics do not depend
+    on the piece boundaries)."""
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    e, _ = synth.scoring_embeddings(70000, 300, seed=5)
+    c, _ = synth.scoring_embeddings(20000, 2000, seed=105)
+    rng = np.random.default_rng(1)
+    ia = torch.from_numpy(rng.integers(0, 70000, 50000).astype(np.int32)).cuda()
+    ib = torch.from_numpy(rng.integers(0, 70000, 50000).astype(np.int32)).cuda()
+    host = torch.from_numpy(e).unsqueeze(1).pin_memory()
+    want = U.score_trials(host.cuda(), ia, ib, "norm", c, top=300, normalize=False)
+    got = U.score_trials(host, ia, ib, "norm", c, top=300, normalize=False)
+    assert got.is_cuda and torch.equal(got, want)
