@@ -752,8 +752,8 @@ def bench_encoder(args, ctx, rawnet):
                             "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
                             "traffic": None, "peak_source": src + " (burst, kernel timed alone)", "kernel_ms": front_ms,
                             "note": "algorithmic 4.10 GFLOP per utterance (SURVEY 8a a23)"}
-        if world == 1 and args.workload == "rawnet2":
-            rate, n, dt = cpu_rawnet_rate(12.0)
+        if world == 1:
+            rate, n, dt = cpu_rawnet_rate(12.0 if args.workload == "rawnet2" else 6.0)
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port (%.1f s)" % (n, dt)}
     else:
