@@ -158,6 +158,8 @@ class ModelHandling(object):
             # `freed` event of a buffer's last use in the PREVIOUS call is waited on like one of this call
             bb = self._batch_bufs
             if bb is None or bb["shape"][0] < bs or bb["shape"][1] != L:
+                if bb is not None:
+                    torch.cuda.synchronize(self.device)      # copies / kernels of the previous call may still use the old buffers
                 self._batch_bufs = bb = None
                 bb = self._batch_bufs = {"shape": (bs, L),
                                          "bufs": [torch.empty((bs, L), dtype=torch.float32, device=self.device)
