@@ -173,6 +173,8 @@ typedef struct SvbEcapaCfg {
   int32_t input_norm;      /* input_norm=True of src/models/ECAPA_TDNN.py:406-408,477-478 (the ECAPA branch of the
                             * Raw3_ECAPA hybrid, src/models/Raw3_ECAPA.py:21-24): InstanceNorm1d(n_mels, affine) after the
                             * log / mean normalisation; needs the tensors "instance_norm.weight" / ".bias" */
+  int32_t no_global_context; /* global_context=False (src/models/ECAPA_TDNN.py:204-207,238-248): asp.tdnn has 3C inputs,
+                            * the attention does not see the utterance's global mean / std */
 } SvbEcapaCfg;
 int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const void* const* ptrs, int n,
                      SvbEcapa** out);

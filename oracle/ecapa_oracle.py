@@ -150,9 +150,12 @@ def attentive_stats_pool(x, sd, p, eps=1e-12):
         std = torch.sqrt((m * (x - mean.unsqueeze(2)).pow(2)).sum(2).clamp(eps))
         return mean, std
 
-    m0 = torch.full((x.shape[0], 1, L), 1.0 / L, device=x.device, dtype=x.dtype)
-    mean, std = stats(x, m0)
-    attn = torch.cat([x, mean.unsqueeze(2).expand(-1, -1, L), std.unsqueeze(2).expand(-1, -1, L)], 1)
+    if sd[p + "tdnn.conv.conv.weight"].shape[1] == x.shape[1]:
+        attn = x                                       # global_context=False (:204-207, :247-248)
+    else:
+        m0 = torch.full((x.shape[0], 1, L), 1.0 / L, device=x.device, dtype=x.dtype)
+        mean, std = stats(x, m0)
+        attn = torch.cat([x, mean.unsqueeze(2).expand(-1, -1, L), std.unsqueeze(2).expand(-1, -1, L)], 1)
     attn = tdnn_block(attn, sd, p + "tdnn.", 1, "relu")
     attn = F.conv1d(torch.tanh(attn), sd[p + "conv.conv.weight"], sd[p + "conv.conv.bias"])
     attn = F.softmax(attn, dim=2)

@@ -121,6 +121,29 @@ def make(channels, n_out, tag, n_spk=16, per_spk=4, n_trials=1000, n_cohort=300,
     print("wrote", path, os.path.getsize(path) // 1024, "KiB")
 
 
+def make_nogc(tag="cfg1_c512_nogc", channels=(512, 512, 512, 512, 1536), n_out=192):
+    """ECAPA-TDNN with global_context=False (src/models/ECAPA_TDNN.py:204-207,238-248: the attention of the pooling
+    layer sees x only; asp.tdnn has 3C instead of 9C inputs)."""
+    ref_loader.load()
+    net, handle, args = ref_loader.build(list(channels), n_out, global_context=False)
+    sd = synth.ecapa_state_dict(list(channels), n_out, seed=1234)
+    C3 = channels[-1]
+    sd["__S__.asp.tdnn.conv.conv.weight"] = np.ascontiguousarray(sd["__S__.asp.tdnn.conv.conv.weight"][:, :C3]) * np.float32(1.7)
+    _load_weights(net, sd)
+    waves, spk = synth.utterance_set(16, 4, L + 1)
+    bn = _calibrate_bn(net, waves[:, :L])
+    out = {"bn/" + k: v for k, v in bn.items()}
+    with torch.no_grad():
+        emb = net(torch.from_numpy(waves[:, :L]))
+    out["emb_batch"] = emb.numpy()
+    _, ref_utils = ref_loader.load()
+    lab, ti, tj = synth.trial_list(spk, 1000)
+    out["scores_cos"] = np.asarray([float(ref_utils.cosine_similarity(emb[i:i + 1], emb[j:j + 1])) for i, j in zip(ti, tj)])
+    path = os.path.join(GOLD, "%s.npz" % tag)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB")
+
+
 def make_inorm(tag="cfg1_c512_inorm", channels=(512, 512, 512, 512, 1536), n_out=192):
     """ECAPA-TDNN with input_norm=True (nn.InstanceNorm1d(n_mels, affine=True) after the log / mean normalisation,
     src/models/ECAPA_TDNN.py:406-408,477-478) -- the configuration the Raw3_ECAPA hybrid builds its ECAPA branch
@@ -229,5 +252,7 @@ if __name__ == "__main__":
         make_rawnet()
     if "cfg1i" in which:
         make_inorm()
+    if "cfg1g" in which:
+        make_nogc()
     if "cfg4h" in which:
         make_rawnet_heads()

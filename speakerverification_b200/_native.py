@@ -75,7 +75,7 @@ def _declare(L):
 class SvbEcapaCfg(_c.Structure):
     _fields_ = [("channels", _i32), ("n_mels", _i32), ("n_out", _i32), ("attention_channels", _i32),
                 ("se_channels", _i32), ("res2net_scale", _i32), ("kernel_sizes", _i32 * 5),
-                ("dilations", _i32 * 5), ("fp32_mode", _i32), ("input_norm", _i32)]
+                ("dilations", _i32 * 5), ("fp32_mode", _i32), ("input_norm", _i32), ("no_global_context", _i32)]
 
 
 class SvbRawnet2Cfg(_c.Structure):

@@ -29,8 +29,8 @@ int batch_B(const Batch*);
 int batch_halo(const Batch*);
 const void* batch_utt_tab(const Batch*);
 const int32_t* batch_tile_tab(const Batch*);
-int ecapa_create(int, int, int, int, int, int, const int*, const int*, int, int, const char* const*, const void* const*, int,
-                 Ecapa**);
+int ecapa_create(int, int, int, int, int, int, const int*, const int*, int, int, int, const char* const*, const void* const*,
+                 int, Ecapa**);
 void ecapa_destroy(Ecapa*);
 int ecapa_halo(const Ecapa*);
 size_t ecapa_workspace_bytes(const Ecapa*, const Batch*);
@@ -253,7 +253,7 @@ int svb_ecapa_create(const SvbEcapaCfg* cfg, const char* const* names, const voi
   if (check_device()) return -1;
   SVB_CHECK(cfg && names && ptrs && out, "null argument");
   return ecapa_create(cfg->channels, cfg->n_mels, cfg->n_out, cfg->attention_channels, cfg->se_channels,
-                      cfg->res2net_scale, cfg->kernel_sizes, cfg->dilations, cfg->fp32_mode, cfg->input_norm, names, ptrs, n,
+                      cfg->res2net_scale, cfg->kernel_sizes, cfg->dilations, cfg->fp32_mode, cfg->input_norm, !cfg->no_global_context, names, ptrs, n,
                       reinterpret_cast<Ecapa**>(out));
 }
 void svb_ecapa_destroy(SvbEcapa* e) { ecapa_destroy(reinterpret_cast<Ecapa*>(e)); }

@@ -203,6 +203,7 @@ struct Layer {
 struct Ecapa {
   int C = 0, C3 = 0, Cs = 0, n_mels = 0, n_out = 0, att = 128, se_ch = 128, scale = 8, halo = 0;
   int fp32_mode = 0;  // 0: 16-bit operands (block 0 split-bf16), 1: split-bf16 everywhere (fp32 grade)
+  int global_context = 1;  // 0: AttentiveStatisticsPooling(global_context=False): asp.tdnn sees x only (ECAPA_TDNN.py:204-207,238-248)
   // 16-bit mode stores activations AND weights of the single-plane layers as IEEE half: kind::f16 UMMAs run fp16 at the
   // bf16 rate, and 11 instead of 8 significant bits take the all-pairs score deviation from 2.1e-3 (bf16 operands,
   // round 1) to 2.4e-4 (CPU model, profiles/r02_precision.md).  Stores saturate at +-65504 (BN outputs are O(1-10)).
@@ -294,8 +295,8 @@ static int make_layer(Ecapa* e, const TensorMap& tm, const std::string& p, int c
 }
 
 int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scale, const int* kernel_sizes,
-                 const int* dilations, int fp32_mode, int input_norm, const char* const* names, const void* const* ptrs, int n,
-                 Ecapa** out) {
+                 const int* dilations, int fp32_mode, int input_norm, int global_context, const char* const* names,
+                 const void* const* ptrs, int n, Ecapa** out) {
   SVB_CHECK(C % 512 == 0, "channels must be a multiple of 512 (Res2Net chunks are tiled in 64-column K blocks); got %d", C);
   SVB_CHECK(res2_scale == 8 && att == 128 && se_ch % 4 == 0 && n_mels <= MEL_PLANE,
             "unsupported ECAPA configuration (attention_channels must be 128, res2net_scale 8)");
@@ -311,7 +312,7 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
   SVB_CHECK((n_mels + 63) / 64 * 64 == MEL_PLANE, "block 0 expects the %d-column mel plane", MEL_PLANE);
   Ecapa* e = new Ecapa();      // every check that can fail without touching the device sits above this line
   e->C = C; e->C3 = 3 * C; e->Cs = C / res2_scale; e->n_mels = n_mels; e->n_out = n_out; e->att = att; e->se_ch = se_ch;
-  e->fp32_mode = fp32_mode;
+  e->fp32_mode = fp32_mode; e->global_context = global_context ? 1 : 0;
   for (int i = 0; i < 5; ++i) { e->ks[i] = kernel_sizes[i]; e->dil[i] = dilations[i]; }
   e->halo = halo;
   const int P = fp32_mode ? 2 : 1;
@@ -348,7 +349,9 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
   }
   if (!rc) rc |= make_layer(e, tm, "mfa.", e->C3, e->C3, 1, 1, P, ACT_GELU, true, "conv.conv.", &e->mfa);
   // asp.tdnn: only the first 3C input channels vary over time; the rest become a per-utterance bias
-  if (!rc) rc |= make_layer(e, tm, "asp.tdnn.", att, 3 * e->C3, 1, 1, P, ACT_RELU, true, "conv.conv.", &e->asp_tdnn, e->C3);
+  // (global_context=False: the layer has 3C inputs only and no per-utterance bias)
+  if (!rc) rc |= make_layer(e, tm, "asp.tdnn.", att, (global_context ? 3 : 1) * e->C3, 1, 1, P, ACT_RELU, true, "conv.conv.",
+                            &e->asp_tdnn, e->C3);
   if (!rc) rc |= make_layer(e, tm, "asp.conv.", e->C3, att, 1, 1, P, ACT_NONE, false, "conv.", &e->asp_conv);
   if (!rc) {
     const float* aw = find(tm, "asp.tdnn.conv.conv.weight");
@@ -357,7 +360,7 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
     const float *fw = find(tm, "fc.conv.weight"), *fb = find(tm, "fc.conv.bias");
     if (!aw || !g || !b || !m || !v || !fw || !fb) rc = -1;
     else {
-      e->asp_w = dcopy(e, aw, static_cast<size_t>(att) * 3 * e->C3);
+      e->asp_w = dcopy(e, aw, static_cast<size_t>(att) * (global_context ? 3 : 1) * e->C3);
       e->aspbn_scale = dalloc<float>(e, 2 * e->C3); e->aspbn_shift = dalloc<float>(e, 2 * e->C3);
       rc |= fold_bn(g, b, m, v, 2 * e->C3, 1e-5f, e->aspbn_scale, e->aspbn_shift, 0);
       e->fc_w = dcopy(e, fw, static_cast<size_t>(n_out) * 2 * e->C3); e->fc_b = dcopy(e, fb, n_out);
@@ -628,8 +631,12 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
   } else if (col_stats(Y, P * C3, P, C3, b->d_uttrows, B, C3, 1, 1e-12f, st, st + C3, 2 * C3, stream)) {
     return -1;
   }
-  if (small_linear(e->asp_w + C3, 3 * C3, nullptr, st, 2 * C3, nullptr, nullptr, B, e->att, 2 * C3, LIN_NONE,
-                   F("asp_rowbias"), e->att, F("lin_part"), stream)) return -1;
+  if (e->global_context) {
+    if (small_linear(e->asp_w + C3, 3 * C3, nullptr, st, 2 * C3, nullptr, nullptr, B, e->att, 2 * C3, LIN_NONE,
+                     F("asp_rowbias"), e->att, F("lin_part"), stream)) return -1;
+  } else {
+    SVB_CUDA_OK(cudaMemsetAsync(F("asp_rowbias"), 0, static_cast<size_t>(B) * e->att * 4, stream));   // no global context
+  }
   View yv{Y, P * C3, C3, P * C3};
   if (run_layer(e, b, e->asp_tdnn, yv, nullptr, 0, H("att"), P * e->att, e->att, STORE_ALL, F("asp_rowbias"), e->att, 1, -1,
                 nullptr, nullptr, 0, 0, passes, stream)) return -1;

@@ -55,9 +55,9 @@ class _SERes2Net(nn.Module):
 
 
 class _ASP(nn.Module):
-    def __init__(self, c, att):
+    def __init__(self, c, att, global_context=True):
         super().__init__()
-        self.tdnn = _TDNN(3 * c, att, 1)
+        self.tdnn = _TDNN((3 if global_context else 1) * c, att, 1)      # ECAPA_TDNN.py:204-207
         self.conv = _Conv(att, c, 1)
 
 
@@ -68,8 +68,6 @@ class ECAPA_TDNN(nn.Module):
         super().__init__()
         assert len(channels) == len(kernel_sizes) == len(dilations)
         assert input_size == kwargs["n_mels"], "inappropriate input size, should equal feature_dim"
-        if not global_context:
-            raise NotImplementedError("global_context=False is outside the ECAPA_TDNN hot path")
         if str(kwargs.get("features", "melspectrogram")).strip() != "melspectrogram":
             raise NotImplementedError("the libsvb encoder consumes mel-spectrogram features only")
         self.channels = list(channels)
@@ -77,7 +75,7 @@ class ECAPA_TDNN(nn.Module):
         self.n_mels, self.n_out = input_size, lin_neurons
         self.att, self.se, self.scale = attention_channels, se_channels, res2net_scale
         self.kwargs = kwargs
-        self.input_norm = bool(input_norm)
+        self.input_norm, self.global_context = bool(input_norm), bool(global_context)
         if self.input_norm:      # src/models/ECAPA_TDNN.py:406-408: keys instance_norm.{weight,bias}
             self.instance_norm = nn.InstanceNorm1d(input_size, affine=True, eps=1e-05, momentum=0.1,
                                                    track_running_stats=False)
@@ -92,7 +90,7 @@ class ECAPA_TDNN(nn.Module):
             assert C[i] == C[i - 1], "ECAPA_TDNN uses equal channel counts in the SE-Res2Net blocks"
             self.blocks.append(_SERes2Net(C[i], res2net_scale, se_channels, kernel_sizes[i]))
         self.mfa = _TDNN(C[-1], C[-1], kernel_sizes[-1])
-        self.asp = _ASP(C[-1], attention_channels)
+        self.asp = _ASP(C[-1], attention_channels, global_context)
         self.asp_bn = _Norm(2 * C[-1])
         self.fc = _Conv(2 * C[-1], lin_neurons, 1)
         self._engine, self._fingerprint, self._frontend = None, None, None
@@ -123,7 +121,8 @@ class ECAPA_TDNN(nn.Module):
             self._engine = EcapaEngine(state, self.channels, self.n_mels, self.n_out, self.frontend(),
                                        attention_channels=self.att, se_channels=self.se, res2net_scale=self.scale,
                                        kernel_sizes=self.kernel_sizes, dilations=self.dilations,
-                                       precision=self.precision, input_norm=self.input_norm)
+                                       precision=self.precision, input_norm=self.input_norm,
+                                       global_context=self.global_context)
             self._fingerprint = fp
         return self._engine
 

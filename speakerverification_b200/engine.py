@@ -119,7 +119,7 @@ class EcapaEngine:
 
     def __init__(self, state, channels, n_mels, n_out, frontend, attention_channels=128, se_channels=128,
                  res2net_scale=8, kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), precision="f16",
-                 input_norm=False):
+                 input_norm=False, global_context=True):
         precision = normalize_precision(precision)
         C = int(channels[0])
         if list(channels[:4]) != [C] * 4 or int(channels[4]) != 3 * C:
@@ -132,6 +132,7 @@ class EcapaEngine:
         cfg.dilations = (ctypes.c_int32 * 5)(*dilations)
         cfg.fp32_mode = 1 if precision == "fp32" else 0
         cfg.input_norm = 1 if input_norm else 0
+        cfg.no_global_context = 0 if global_context else 1
         keep, names, ptrs = [], [], []
         for k, v in state.items():
             if not torch.is_tensor(v) or not v.is_floating_point():

@@ -224,3 +224,28 @@ def test_raw3_ecapa_hybrid_plumbing(tmp_path):
     assert torch.allclose(out[:, 192:], want2, atol=1e-6)
     with pytest.raises(NotImplementedError, match="asteroid_filterbanks"):
         SpeakerEncoder(**dict(args, svb_second_encoder=None))
+
+
+@pytest.mark.parametrize("precision,cos_min,tol", [("fp32", 0.9999, 1e-4), ("f16", 0.99995, 6e-4)])
+def test_no_global_context_matches_reference(precision, cos_min, tol):
+    """AttentiveStatisticsPooling(global_context=False) (src/models/ECAPA_TDNN.py:204-207,238-248): asp.tdnn sees x only
+    (3C inputs, no per-utterance bias), against the reference's embeddings and 1000 cosine trial scores."""
+    import os
+    from oracle import synth
+    from speakerverification_b200 import utils as U
+    from speakerverification_b200.engine import EcapaEngine
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "cfg1_c512_nogc.npz")))
+    sd, state = _state(CH512, g)
+    w = torch.as_tensor(sd["__S__.asp.tdnn.conv.conv.weight"][:, :1536].copy() * np.float32(1.7)).cuda()
+    state["asp.tdnn.conv.conv.weight"] = w
+    waves, spk = synth.utterance_set(16, 4, L + 1)
+    eng = EcapaEngine(state, CH512, 80, 192, _frontend(), precision=precision, global_context=False)
+    emb = eng.forward(torch.from_numpy(waves[:, :L]).cuda())
+    e, ref = emb.cpu().numpy(), g["emb_batch"]
+    cos = (e * ref).sum(1) / np.linalg.norm(e, axis=1) / np.linalg.norm(ref, axis=1)
+    lab, ti, tj = synth.trial_list(spk, 1000)
+    sc = U.cosine_trials(emb.unsqueeze(1).contiguous(), torch.from_numpy(ti.astype(np.int32)).cuda(),
+                         torch.from_numpy(tj.astype(np.int32)).cuda()).cpu().numpy()
+    dev = np.abs(sc - g["scores_cos"]).max()
+    print("global_context=False", precision, "min cos", cos.min(), "max score dev", dev)
+    assert cos.min() >= cos_min and dev <= tol, (cos.min(), dev)
