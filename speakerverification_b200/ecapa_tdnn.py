@@ -64,8 +64,13 @@ class _ASP(nn.Module):
 class ECAPA_TDNN(nn.Module):
     def __init__(self, input_size=80, lin_neurons=192, channels=(1024, 1024, 1024, 1024, 3072),
                  kernel_sizes=(5, 3, 3, 3, 1), dilations=(1, 2, 3, 4, 1), attention_channels=128, res2net_scale=8,
-                 se_channels=128, input_norm=False, global_context=True, precision=None, **kwargs):
+                 se_channels=128, input_norm=False, global_context=True, precision=None, activation=None, **kwargs):
         super().__init__()
+        # the reference's `activation` (default torch.nn.GELU, src/models/ECAPA_TDNN.py:377) is fused into the GEMM
+        # epilogues as exact-erf GELU: any other choice has no kernel and must not run silently as GELU
+        if activation is not None and activation is not nn.GELU and not isinstance(activation, nn.GELU):
+            raise NotImplementedError("ECAPA_TDNN activation %r: the libsvb encoder implements the default torch.nn.GELU"
+                                      % (activation,))
         assert len(channels) == len(kernel_sizes) == len(dilations)
         assert input_size == kwargs["n_mels"], "inappropriate input size, should equal feature_dim"
         if str(kwargs.get("features", "melspectrogram")).strip() != "melspectrogram":

@@ -48,6 +48,9 @@ def test_module_trees_carry_the_reference_names():
     assert {"instance_norm.weight", "instance_norm.bias", "blocks.1.tdnn1.conv.conv.weight",
             "blocks.3.res2net_block.blocks.6.norm.norm.running_var", "asp.conv.conv.bias", "fc.conv.weight"} <= keys
     assert len(keys) == 233                                   # 231 + the two InstanceNorm parameters
+    ecapa_tdnn.MainModel(nOut=192, n_mels=80, channels=[512, 512, 512, 512, 1536], activation=torch.nn.GELU)   # Raw3_ECAPA passes it
+    with pytest.raises(NotImplementedError, match="GELU"):
+        ecapa_tdnn.MainModel(nOut=192, n_mels=80, channels=[512, 512, 512, 512, 1536], activation=torch.nn.ReLU)
     spec = {"sample_rate": 16000, "sentence_len": 4.0}
     for agg in ("gru", "sap", "asp"):
         r = rawnet2_custom.MainModel(nOut=512, audio_spec=spec, features="raw", aggregate=agg)
