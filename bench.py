@@ -373,11 +373,12 @@ def run_scoring(args, device, rank, world, dist, steps, full_line=True):
                                      "(gemm_pw_kernel<256, ACT_FILTER>, 63 % of the phase) + candidate select",
                            "bound": "tensor", "achieved": flops * steps / (ms * 1e-3) / 1e12, "peak": tf_sust / 3.0,
                            "unit": "TFLOP/s", "frac": flops * steps / (ms * 1e-3) / 1e12 / (tf_sust / 3.0),
-                           # dram__bytes_read.sum + dram__bytes_write.sum of ONE filter-GEMM launch (8192 utterance rows x
-                           # 20 032 cohort columns, ncu --set full, profiles/r02_ncu.md): 21.76 MB + 0.03 MB against
-                           # (8192 + 20000) * 192 * 4 B = 21.65 MB algorithmic -- the 656 MB score tile never leaves the SM
-                           "traffic": 2.178e7 if (N == 20000 and U >= 8192) else None,
-                           "traffic_unit": "bytes per filter-GEMM launch (8192 rows); algorithmic 2.165e7",
+                           # dram__bytes_read.sum + dram__bytes_write.sum of ONE filter-GEMM launch (32 768 utterance rows x
+                           # 20 032 cohort columns, ncu --set full, profiles/r02_ncu.md): 41.4 MB + 27.5 MB (the write side is
+                           # the candidate lists) against (32768 + 20000) * 192 * 4 B = 40.5 MB of operands -- the 2.6 GB
+                           # fp32 score tile of the chunk never leaves the SM
+                           "traffic": 6.882e7 if (N == 20000 and U >= 32768) else None,
+                           "traffic_unit": "bytes per filter-GEMM launch (32768 rows); operands 4.05e7",
                            "note": "algorithmic 2*U*N*D FLOP per step over the step time; fp32-grade scores cost 3 "
                                    "bf16 passes, so the bound is the sustained bf16 peak / 3 (" + src + "); the fused "
                                    "path executes 1.128x the algorithmic FLOPs (the 1/8 sample GEMM)"}

@@ -1150,7 +1150,13 @@ static const size_t S_CHUNK_BYTES = 144u << 20;
 static const int TOPK_SMEM_MAX_N = 50000;   // row cached in smem (<= 200 KB)
 
 // Fused path (see "fused pre-filter path" above): rows per chunk and sample size, buffers overlaid on the S chunk
-static const int FUSED_CHUNK_ROWS = 8192;
+// Rows per chunk of the fused path.  Measured on one B200 (200 k rows x 20 k cohort): 8192 rows (sample matrix L2
+// resident) 147 M trials/s, 16 384: 148 M, 32 768: 154 M with a third of the launches -- and the launch rate is what two of
+// eight ranks could not sustain in an 8-GPU run (6.7 ms per step on six ranks, 9.4 ms on two).  SVB_TOPK_CHUNK overrides.
+static int fused_chunk_rows() {
+  static const int v = [] { const char* e = getenv("SVB_TOPK_CHUNK"); const int x = e ? atoi(e) : 0; return x >= 128 ? (x + 127) / 128 * 128 : 32768; }();
+  return v;
+}
 static const int FIXUP_CTAS = 296;
 struct AsnormPlan {
   int Dp, Np, chunk;
@@ -1195,7 +1201,7 @@ static AsnormPlan asnorm_plan(int U, int N, int D) {
   const size_t old_end = o + align256(static_cast<size_t>(p.chunk) * p.Np * 4);
   // fused-path buffers share the S-chunk region (only one of the two paths runs in a call)
   p.Ns = std::min(p.Np, (N / 8 + 255) / 256 * 256);
-  p.fch = static_cast<int>(std::min<long long>(FUSED_CHUNK_ROWS, all * 128));
+  p.fch = static_cast<int>(std::min<long long>(fused_chunk_rows(), all * 128));
   p.o_s1 = o; o += align256(static_cast<size_t>(p.fch) * p.Ns * 4);
   p.o_thr = o; o += align256(static_cast<size_t>(p.fch) * 4);
   p.o_cnt = o; o += align256(static_cast<size_t>(p.fch) * 4);
