@@ -544,7 +544,10 @@ gemm_pw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      if (lane == 0) {
+        if (TWO) mbar_arrive_cluster(smem_u32(&tempty_bar[acc]) & 0xFEFFFFFFu);   // the leader issues the pair's MMAs
+        else mbar_arrive(smem_u32(&tempty_bar[acc]));
+      }
     }
     if (lane == 0) bulk_wait<0>();
   }
@@ -713,7 +716,15 @@ int launch_gemm_filter(const GemmOperands& ops, const GemmParams& g, const float
   p.a2_kc = 0; p.w_planes = g.w_planes; p.num_taps = 1; p.tap_off[0] = 0;
   p.w_f16 = ops.w_f16; p.a_f16 = ops.a_f16;
   p.filt_thr = thr; p.filt_cnt = cnt; p.filt_cand = cand; p.filt_cap = cap; p.filt_ncols = n_valid;
-  // 16 epilogue warps: each thread owns 64 columns of its row (two strips), half the per-warp epilogue time of EW = 8
+  // 16 epilogue warps: each thread owns 64 columns of its row (two strips), half the per-warp epilogue time of EW = 8.
+  // Default: the cta_group::2 instance (M = 256 over a CTA pair, each CTA stages half of the W tile): 158-160 against
+  // 153-156 M trials/s for the 1-SM instance in one call (SVB_FILTER_2SM=0 selects the latter).
+  static const bool two = [] { const char* e = getenv("SVB_FILTER_2SM"); return e == nullptr || e[0] != '0'; }();
+  if (bn == 256 && two) {
+    CUtensorMap mw2;
+    if (make_map(&mw2, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn / 2)) return -1;
+    return launch_pw_t<256, ACT_FILTER, false, false, 16, 0, true, true>(ma, ma, mw2, ma, p, stream);
+  }
   return bn == 256 ? launch_pw_t<256, ACT_FILTER, false, false, 16>(ma, ma, mw, ma, p, stream)
                    : launch_pw_t<128, ACT_FILTER, false, false, 16>(ma, ma, mw, ma, p, stream);
 }
