@@ -425,6 +425,7 @@ def cpu_eval_rate(signals, cohort, top, min_seconds):
         so.asnorm_score(embs[nt % len(embs)], embs[(nt + 1) % len(embs)], cohort, top)
         nt += 1
     t_trial = (time.perf_counter() - t1) / nt
+    cpu_eval_rate.last_embeddings = np.concatenate(embs, axis=0)      # [n, D]: reused as a parity probe by run_eval
     return t_emb, t_trial, len(embs), nt, secs
 
 
@@ -560,6 +561,15 @@ def run_eval(args, device, rank, world, dist, steps):
     if world == 1:
         t_emb, t_trial, ne, nt, secs = cpu_eval_rate(signals, cohort, K, 12.0 if args.workload == "eval" else 6.0)
         per_utt = t_emb * (audio_s / U) / (secs / ne) + t_trial * NT / U
+        # the oracle embeddings the CPU leg just produced double as a parity probe of the timed GPU pass (same signals,
+        # same random-init weights): whole-utterance embeddings of the first `ne` utterances longer than 3 s
+        ref = torch.nn.functional.normalize(torch.from_numpy(cpu_eval_rate.last_embeddings), dim=1)
+        keep = [i for i in range(ne) if len(signals[i]) > L]
+        if keep:
+            cs = (ref[keep] * emb[:ne].cpu()[keep]).sum(1)
+            line["parity_check"] = {"against": "oracle.ecapa_oracle.embed (CPU fp32) on the same int16 signals",
+                                    "utterances": len(keep), "min_cos": float(cs.min()),
+                                    "max_pair_score_dev": float((ref[keep] @ ref[keep].T - emb[:ne].cpu()[keep] @ emb[:ne].cpu()[keep].T).abs().max())}
         line["cpu_baseline"] = {"value": 1.0 / per_utt, "unit": "utterances/s", "cores": os.cpu_count(), "kind": "port",
                                 "sample": "%d whole utterances (%.0f s of audio) + %d AS-norm trials, torch/numpy oracle "
                                           "port; composed per utterance at the workload's mean length and trials per "
@@ -758,6 +768,15 @@ def bench_encoder(args, ctx, rawnet):
             line["cpu_baseline"] = {"value": rate, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "%d x 4 s utterances, batch 8, torch fp32 oracle port (%.1f s)" % (n, dt)}
     else:
+        if world == 1:
+            # baseline leg: the CPU oracle as a CHECKER of the timed pass (16 of its utterances, same random-init weights)
+            from oracle import ecapa_oracle as eo
+            osd = {k: torch.as_tensor(v) for k, v in weights.items()}
+            ref = torch.nn.functional.normalize(eo.embed(waves[:16].cpu(), osd), dim=1)
+            got = torch.nn.functional.normalize(emb[:16].cpu(), dim=1)
+            line["parity_check"] = {"against": "oracle.ecapa_oracle.embed (CPU fp32) on 16 utterances of the timed pass",
+                                    "min_cos": float((ref * got).sum(1).min()),
+                                    "max_pair_score_dev": float((ref @ ref.T - got @ got.T).abs().max())}
         ach, gemm_ms = gemm_roofline(device, args.batch_rows)
         line["config"] = {"workload": "ECAPA-TDNN C=1024 nOut=192, 80-mel fbank (16 kHz, n_fft 512, win 400, hop 160), "
                                       "%d synthetic 3 s utterances per GPU (configs[1])" % U,
