@@ -728,8 +728,26 @@ thr_warp_kernel(const float* __restrict__ S1, int ld, int Ns, int want, float* _
   const float* row = S1 + static_cast<long long>(r) * ld;
   const float4* row4 = reinterpret_cast<const float4*>(row);
   const int n4 = Ns >> 2;                               // ld and Ns are multiples of 4 (Ns a multiple of 256 or = N)
+  // the sample row is read ONCE: up to 20 float4 per lane (Ns <= 2560, i.e. N <= 20 480) stay in registers between the
+  // range pass and the histogram pass (the chunk's sample matrix is 335 MB at 32 768 rows: not L2 resident); longer
+  // samples re-read the tail from memory
+  constexpr int REG4 = 20;
+  float4 keep[REG4];
   float lo = INFINITY, hi = -INFINITY;
-  for (int i = lane; i < n4; i += 32) {
+#pragma unroll
+  for (int j = 0; j < REG4; ++j) {
+    const int i = lane + 32 * j;
+    keep[j] = i < n4 ? row4[i] : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+  }
+#pragma unroll
+  for (int j = 0; j < REG4; ++j) {
+    if (lane + 32 * j < n4) {
+      const float4 v = keep[j];
+      lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
+      hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+    }
+  }
+  for (int i = lane + 32 * REG4; i < n4; i += 32) {
     const float4 v = row4[i];
     lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
     hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
@@ -750,7 +768,14 @@ thr_warp_kernel(const float* __restrict__ S1, int ld, int Ns, int want, float* _
   for (int j = 0; j < 8; ++j) h[lane * 8 + j] = 0;
   __syncwarp();
   auto bin = [&](float v) { return min(255, __float2int_rz((v - lo) * scale)); };
-  for (int i = lane; i < n4; i += 32) {
+#pragma unroll
+  for (int j = 0; j < REG4; ++j) {
+    if (lane + 32 * j < n4) {
+      const float4 v = keep[j];
+      atomicAdd(&h[bin(v.x)], 1u); atomicAdd(&h[bin(v.y)], 1u); atomicAdd(&h[bin(v.z)], 1u); atomicAdd(&h[bin(v.w)], 1u);
+    }
+  }
+  for (int i = lane + 32 * REG4; i < n4; i += 32) {
     const float4 v = row4[i];
     atomicAdd(&h[bin(v.x)], 1u); atomicAdd(&h[bin(v.y)], 1u); atomicAdd(&h[bin(v.z)], 1u); atomicAdd(&h[bin(v.w)], 1u);
   }
@@ -1284,10 +1309,13 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
       ops.a = a16 + static_cast<size_t>(u0) * 2 * Dp; ops.lda = 2 * Dp; ops.a_cols = 2 * Dp;
       ops.w = wpk; ops.w_rows = std::min(N, Ns); ops.w_cols = 2 * Dp;
       GemmParams g{};
-      g.M = rows; g.N = Ns; g.kc_per_tap = Dp / 64; g.num_taps = 1; g.tap_off[0] = 0; g.num_pass = 3;
+      // the SAMPLE scores only place a histogram bin edge (bin width ~2e-3): the hi x hi pass alone (error ~3e-4) is
+      // enough for them; the filter GEMM below recomputes every score with all three split passes
+      g.M = rows; g.N = Ns; g.kc_per_tap = Dp / 64; g.num_taps = 1; g.tap_off[0] = 0; g.num_pass = 1;
       g.a_plane_cols = Dp; g.w_planes = 2; g.act = ACT_NONE; g.store_mode = STORE_ALL; g.out = S1; g.out_ld = Ns;
       g.out_kind = OUT_F32;
       if (launch_gemm_f32(ops, g, stream)) return -1;
+      g.num_pass = 3;
       thr_warp_kernel<16><<<(rows + 15) / 16, 512, 0, stream>>>(S1, Ns, std::min(N, Ns), want, thr, cnt, rows);
       count_launch();
       ops.w_rows = N;
