@@ -187,3 +187,30 @@ def test_score_trials_from_host_tensors():
     want = U.score_trials(host.cuda(), ia, ib, "norm", c, top=300, normalize=False)
     got = U.score_trials(host, ia, ib, "norm", c, top=300, normalize=False)
     assert got.is_cuda and torch.equal(got, want)
+
+
+def test_fused_path_stays_inside_its_buffers():
+    """Canary check of the fused AS-norm path through the raw C ABI (compute-sanitizer is not available on the pool):
+    workspace, mu and sigma are carved out of larger buffers whose guard bytes must survive; odd sizes (U not a multiple
+    of 128, N not a multiple of 64)."""
+    import ctypes
+    from oracle import synth
+    from speakerverification_b200 import _native as nv
+    U_, N, D, K = 4133, 20011, 192, 300
+    e, _ = synth.scoring_embeddings(U_, 100, seed=7)
+    c, _ = synth.scoring_embeddings(N, 500, seed=107)
+    emb, coh = torch.from_numpy(e).cuda(), torch.from_numpy(c).cuda()
+    need = int(nv.lib().svb_asnorm_workspace_bytes(U_, N, D))
+    G = 1 << 16
+    big = torch.full((need + 2 * G,), 0xA5, dtype=torch.uint8, device="cuda")
+    out = torch.full((2, U_ + 512), 7.25, dtype=torch.float32, device="cuda")
+    ws = big[G:G + need]
+    assert ws.data_ptr() % 256 == 0
+    nv.check(nv.lib().svb_asnorm_stats(nv.ptr(emb), U_, nv.ptr(coh), N, D, K, ctypes.c_void_p(out[0, 256:].data_ptr()),
+                                       ctypes.c_void_p(out[1, 256:].data_ptr()), nv.ptr(ws), need, nv.stream_ptr()))
+    torch.cuda.synchronize()
+    assert bool((big[:G] == 0xA5).all()) and bool((big[G + need:] == 0xA5).all())
+    assert bool((out[:, :256] == 7.25).all()) and bool((out[:, 256 + U_:] == 7.25).all())
+    S = -np.sort(-(e.astype(np.float64) @ c.astype(np.float64).T), axis=1)[:, :K]
+    assert np.abs(out[0, 256:256 + U_].cpu().numpy() - S.mean(1)).max() <= 2e-6
+    assert np.abs(out[1, 256:256 + U_].cpu().numpy() - S.std(1)).max() <= 2e-6
