@@ -1,13 +1,13 @@
 #!/bin/bash
-# round 2, call H: full GPU suite + the default bench line (N = 1) as the driver runs it
+# round 2: the full GPU suite + the default bench line (N = 1) exactly as the driver runs it + the reference arm
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -4
 SECONDS=0
-timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/r2h_bench_n1.json 2> gpurun_out/r2h_bench_n1.err
+timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/r2_bench_n1.json 2> gpurun_out/r2_bench_n1.err
 echo "bench rc=$? wall ${SECONDS}s"
 python - <<'PY'
 import json
-d=json.loads(open('gpurun_out/r2h_bench_n1.json').read())
+d=json.loads(open('gpurun_out/r2_bench_n1.json').read())
 print('embed', d['value'], 'e2e', d['e2e']['value'], 'step frac', d['step_tensor']['frac'], 'mfa', d['roofline']['achieved'], d['clocks'])
 for k in ('eval','rawnet2','scoring'):
     print(k, d[k]['value'], d[k]['unit'], 'e2e', (d[k].get('e2e') or {}).get('value'), 'roof', d[k]['roofline']['frac'], 'cpu', (d[k].get('cpu_baseline') or {}).get('value'))
