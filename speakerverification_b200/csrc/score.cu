@@ -679,7 +679,8 @@ topk_stats_sampled_kernel(const float* __restrict__ S, int ld, int N, int K, flo
 //      candidate list straight from TMEM;
 //   4. cand_select_warp_kernel does the exact top-K statistics among the candidates (they contain the K largest whenever
 //      there are at least K of them).  Rows it cannot prove -- fewer than K or more than FILT_CAP candidates, heavy ties
-//      -- are appended to a list and redone exactly by fixup_rows_kernel (direct fp32 scores + 3-pass radix select).
+//      -- are appended to a list and redone exactly by fixup_scores_kernel + fixup_rows_kernel (direct fp32 scores
+//      + 3-pass radix select).
 // Extra work: Ns / N of the GEMM FLOPs (1/8); saved: the 4-byte store and the re-read of every score.
 #define FILT_CAP 1024
 
@@ -915,10 +916,65 @@ cand_select_warp_kernel(const float* __restrict__ cand, const unsigned* __restri
   }
 }
 
-// Exact fall-back for the rows the fused path could not prove (flag_list[0 .. *nflag)): each CTA takes rows off the
-// list, computes the row's N cohort scores directly in fp32 (one warp per cohort vector, coalesced 128-byte reads,
-// the cohort stays in L2) into its private scratch row and selects with the 3-pass key radix.  Slow (~50 us per row)
-// and exact for any input; a well-conditioned sweep sends ~0.01 % of its rows here.
+// Exact fall-back for the rows the fused path could not prove (flag_list[0 .. *nflag)): the row's N cohort scores are
+// recomputed directly in fp32 (one warp per cohort vector, coalesced reads, the cohort stays in L2) and selected with
+// the 3-pass key radix.  A sweep of random embeddings flags ~3e-6 of its rows (the 4.5-sigma margin of the sampled
+// threshold), i.e. one row in every third 100 000-row call, so the common case is ONE flagged row: its score row is
+// spread over the whole GPU (fixup_scores_kernel, 128 cohort vectors per work item, ~10 us) instead of being walked by
+// one CTA (2.6 ms measured: 2 500 dependent L2 round trips per warp -- two of eight ranks paid it in the round-2
+// 8-GPU run).  Flagged rows beyond the first FIXUP_CTAS are computed by the CTA that selects them (slow, exact).
+static constexpr int FIXUP_SLICE = 128;
+
+// scores of cohort vectors [j0, j1) against e_s into srow; warps of the CTA interleave groups of four vectors so that
+// 4 * D / 32 independent loads are in flight per lane.  Same summation order per score as a one-vector loop.
+__device__ __forceinline__ void fixup_scores_span(const float* __restrict__ e_s, const float* __restrict__ cohort, int D,
+                                                  int j0, int j1, float* __restrict__ srow, int wid, int lane, int nw) {
+  for (int j = j0 + wid * 4; j < j1; j += nw * 4) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    const float* c0 = cohort + static_cast<long long>(j) * D;
+    const float* c1 = cohort + static_cast<long long>(min(j + 1, j1 - 1)) * D;
+    const float* c2 = cohort + static_cast<long long>(min(j + 2, j1 - 1)) * D;
+    const float* c3 = cohort + static_cast<long long>(min(j + 3, j1 - 1)) * D;
+    for (int c = lane; c < D; c += 32) {
+      const float e = e_s[c];
+      a0 = fmaf(e, __ldg(c0 + c), a0);
+      a1 = fmaf(e, __ldg(c1 + c), a1);
+      a2 = fmaf(e, __ldg(c2 + c), a2);
+      a3 = fmaf(e, __ldg(c3 + c), a3);
+    }
+    a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2); a3 = warp_sum(a3);
+    const float v = lane == 0 ? a0 : lane == 1 ? a1 : lane == 2 ? a2 : a3;
+    if (lane < 4 && j + lane < j1) srow[j + lane] = v;
+  }
+}
+
+// Work item = (flagged row f < min(*nflag, max_rows), slice of FIXUP_SLICE cohort vectors); scores go to scratch row f.
+__global__ void __launch_bounds__(256)
+fixup_scores_kernel(const float* __restrict__ emean, const float* __restrict__ cohort, int N, int D,
+                    const unsigned* __restrict__ nflag, const int* __restrict__ flag_list, float* __restrict__ scratch,
+                    int scratch_ld, int max_rows) {
+  extern __shared__ float e_s[];          // [D]
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const unsigned rows = min(*nflag, static_cast<unsigned>(max_rows));
+  const unsigned nslices = static_cast<unsigned>((N + FIXUP_SLICE - 1) / FIXUP_SLICE);
+  const unsigned long long total = static_cast<unsigned long long>(rows) * nslices;
+  int cur = -1;
+  for (unsigned long long it = blockIdx.x; it < total; it += gridDim.x) {
+    const int f = static_cast<int>(it / nslices), sl = static_cast<int>(it % nslices);
+    if (f != cur) {
+      __syncthreads();
+      const int u = flag_list[f];
+      for (int c = tid; c < D; c += 256) e_s[c] = emean[static_cast<long long>(u) * D + c];
+      __syncthreads();
+      cur = f;
+    }
+    fixup_scores_span(e_s, cohort, D, sl * FIXUP_SLICE, min(N, (sl + 1) * FIXUP_SLICE),
+                      scratch + static_cast<long long>(f) * scratch_ld, wid, lane, 8);
+  }
+}
+
+// Selection: CTA b takes flagged rows b, b + gridDim.x, ...; the first one's scores are already in scratch row b
+// (fixup_scores_kernel, gridDim.x == its max_rows), later ones are computed here into the same row.
 __global__ void __launch_bounds__(256)
 fixup_rows_kernel(const float* __restrict__ emean, const float* __restrict__ cohort, int N, int D, int K,
                   const unsigned* __restrict__ nflag, const int* __restrict__ flag_list, float* __restrict__ scratch,
@@ -933,16 +989,12 @@ fixup_rows_kernel(const float* __restrict__ emean, const float* __restrict__ coh
   for (unsigned it = blockIdx.x; it < total; it += gridDim.x) {
     const int u = flag_list[it];
     __syncthreads();
-    for (int c = tid; c < D; c += 256) e_s[c] = emean[static_cast<long long>(u) * D + c];
-    __syncthreads();
-    for (int j = wid; j < N; j += 8) {
-      const float* cr = cohort + static_cast<long long>(j) * D;
-      float a = 0.f;
-      for (int c = lane; c < D; c += 32) a = fmaf(e_s[c], __ldg(cr + c), a);
-      a = warp_sum(a);
-      if (lane == 0) srow[j] = a;
+    if (it != blockIdx.x) {
+      for (int c = tid; c < D; c += 256) e_s[c] = emean[static_cast<long long>(u) * D + c];
+      __syncthreads();
+      fixup_scores_span(e_s, cohort, D, 0, N, srow, wid, lane, 8);
+      __syncthreads();
     }
-    __syncthreads();
     // 3-pass (11 + 11 + 10 bit) key radix select of the K largest (same algorithm as topk_stats_kernel)
     uint32_t prefix = 0, prefix_mask = 0, remaining = K;
     const int shifts[3] = {21, 10, 0};
@@ -1176,8 +1228,8 @@ static const int TOPK_SMEM_MAX_N = 50000;   // row cached in smem (<= 200 KB)
 
 // Fused path (see "fused pre-filter path" above): rows per chunk and sample size, buffers overlaid on the S chunk
 // Rows per chunk of the fused path.  Measured on one B200 (200 k rows x 20 k cohort): 8192 rows (sample matrix L2
-// resident) 147 M trials/s, 16 384: 148 M, 32 768: 154 M with a third of the launches -- and the launch rate is what two of
-// eight ranks could not sustain in an 8-GPU run (6.7 ms per step on six ranks, 9.4 ms on two).  SVB_TOPK_CHUNK overrides.
+// resident) 147 M trials/s, 16 384: 148 M, 32 768: 154 M with a third of the launches.  (The two slow ranks of the round-2
+// 8-GPU runs were NOT a launch-rate effect: they had one flagged row each, see fixup_scores_kernel.)  SVB_TOPK_CHUNK overrides.
 static int fused_chunk_rows() {
   static const int v = [] { const char* e = getenv("SVB_TOPK_CHUNK"); const int x = e ? atoi(e) : 0; return x >= 128 ? (x + 127) / 128 * 128 : 32768; }();
   return v;
@@ -1325,8 +1377,11 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
       count_launch();
       SVB_CUDA_OK(cudaGetLastError());
     }
+    fixup_scores_kernel<<<FIXUP_CTAS * 2, 256, static_cast<size_t>(D) * 4, stream>>>(emean, cohort, N, D, nflag, flag_list, fix,
+                                                                                Np, FIXUP_CTAS);
     fixup_rows_kernel<<<FIXUP_CTAS, 256, static_cast<size_t>(D) * 4, stream>>>(emean, cohort, N, D, K, nflag, flag_list, fix, Np,
                                                                           mu, sigma);
+    count_launch();
     count_launch();
     SVB_CUDA_OK(cudaGetLastError());
     return 0;

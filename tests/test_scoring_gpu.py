@@ -214,3 +214,24 @@ def test_fused_path_stays_inside_its_buffers():
     S = -np.sort(-(e.astype(np.float64) @ c.astype(np.float64).T), axis=1)[:, :K]
     assert np.abs(out[0, 256:256 + U_].cpu().numpy() - S.mean(1)).max() <= 2e-6
     assert np.abs(out[1, 256:256 + U_].cpu().numpy() - S.std(1)).max() <= 2e-6
+
+
+def test_fixup_rows_beyond_the_spread_capacity():
+    """700 of 1000 rows are forced to the exact fix-up (5000 tied maxima: more candidates than the filter keeps), more
+    than the 296 score rows fixup_scores_kernel spreads over the GPU, so both the spread rows and the rows a CTA
+    recomputes itself are covered; the other 300 rows are ordinary.  All against numpy's full sort."""
+    from speakerverification_b200 import utils as U
+    rng = np.random.default_rng(11)
+    N, D, K, R = 20000, 64, 300, 1000
+    c = (0.05 * rng.standard_normal((N, D))).astype(np.float32)
+    c[:, 0] = 0.01 * rng.standard_normal(N)
+    c[rng.permutation(N)[:5000], 0] = 0.75
+    e = (0.2 * rng.standard_normal((R, D))).astype(np.float32)
+    tied = rng.permutation(R)[:700]
+    e[tied] = 0.0
+    e[tied, 0] = (0.5 + rng.random(700)).astype(np.float32)
+    mu, sg, nfix = U.asnorm_stats(torch.from_numpy(e).cuda(), torch.from_numpy(c).cuda(), K, return_fixups=True)
+    assert nfix >= 700
+    S = -np.sort(-(e.astype(np.float64) @ c.astype(np.float64).T), axis=1)[:, :K]
+    assert np.abs(mu.cpu().numpy() - S.mean(1)).max() <= 2e-6
+    assert np.abs(sg.cpu().numpy() - S.std(1)).max() <= 2e-6
