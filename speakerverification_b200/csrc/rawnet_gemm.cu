@@ -46,7 +46,7 @@ struct RnCfg {
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;   // power of two
 };
 
-__device__ __forceinline__ float lrelu03(float x) { return x > 0.f ? x : 0.3f * x; }
+__device__ __forceinline__ float lrelu03(float x) { return fmaxf(x, 0.3f * x); }   // slope < 1: max picks the right branch
 
 // 32 lanes x 16 consecutive fp32 columns
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -89,17 +89,32 @@ __device__ __forceinline__ void store_planes(bf16* dst, int planes, int plane_co
 // through shared-memory descriptors whose start address is shifted by 0 / 1 / 2 rows (tcgen05 applies the 128B swizzle
 // to absolute address bits, so any 128-byte aligned start row is legal: profiles/r01_desc_shift_probe.txt) -- 17 KB from
 // L2 per 128 rows x 64 channels.
+//
+// conv2 (EPI_ADD) of these layers also takes its RESIDUAL through the tensor core: the shortcut tile [128 rows x 128 ch]
+// is two more TMA boxes per tile, multiplied by an identity matrix that sits in shared memory next to W (fp16 x 1.0 in
+// an fp32 accumulator is exact).  The epilogue then has no global load at all.  Before: 8 epilogue warps each waited for
+// two dependent DRAM round trips per tile (ncu: issue active 11 %, DRAM 38 %, 3.08 ms for layer1's conv2).
 static constexpr int WRES_A_ROWS = 136;
 static constexpr int WRES_A_BYTES = WRES_A_ROWS * 128;      // 17 408 = 17 x 1024
 static constexpr int WRES_W_BYTES = 6 * 128 * 128;          // 3 taps x 2 K chunks of [128 rows x 64 ch]
-static constexpr int WRES_STAGES = 6;
-static constexpr int WRES_SMEM_BYTES = WRES_W_BYTES + WRES_STAGES * WRES_A_BYTES + 1024;
+static constexpr int WRES_I_BYTES = 2 * 128 * 128;          // identity [128 x 128], 2 K chunks (EPI_ADD only)
+static constexpr int WRES_R_BYTES = 128 * 128;              // one residual box [128 rows x 64 ch]
+template <int EPI> struct WresCfg {
+  static constexpr bool RES = EPI == 2;                     // EPI_ADD
+  static constexpr int STAGES = RES ? 5 : 6;
+  static constexpr int FIXED_BYTES = WRES_W_BYTES + (RES ? WRES_I_BYTES : 0);
+  static constexpr int SMEM_BYTES = FIXED_BYTES + STAGES * WRES_A_BYTES + 1024;
+};
 
 template <int BN, int EPI, bool WRES = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const RnGemmParams p) {
+rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+               const __grid_constant__ CUtensorMap tmR, const RnGemmParams p) {
   using Cfg = RnCfg<BN>;
-  constexpr int STAGES = WRES ? WRES_STAGES : Cfg::STAGES;
+  using WC = WresCfg<EPI>;
+  constexpr int STAGES = WRES ? WC::STAGES : Cfg::STAGES;
+  constexpr bool RESMMA = WRES && WC::RES;                  // residual added by an identity MMA
+  constexpr int AFF_MAX = 512;                              // affine parameters cached in shared memory up to this N
   static_assert(!WRES || BN == 128, "the W-resident variant serves the 128-channel layers");
   __shared__ __align__(8) uint64_t wfull_bar;
   extern __shared__ uint8_t smem_raw[];
@@ -108,10 +123,34 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __shared__ __align__(8) uint64_t tfull_bar[2];
   __shared__ __align__(8) uint64_t tempty_bar[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float4 s_aff[EPI == 0 ? 128 : (EPI == 1 ? AFF_MAX / 2 : 1)];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+
+  // affine parameters of the epilogue, once per CTA: sinc {s1, h1, s2, h2} per filter; conv1 {s[2i], h[2i], s[2i+1], h[2i+1]}
+  if (EPI == 0) {
+    for (int i = threadIdx.x; i < 128; i += NUM_THREADS) s_aff[i] = make_float4(p.s1[i], p.h1[i], p.s2[i], p.h2[i]);
+  } else if (EPI == 1) {
+    if (p.N <= AFF_MAX)
+      for (int i = threadIdx.x; i < p.N / 2; i += NUM_THREADS)
+        s_aff[i] = make_float4(p.s1[2 * i], p.h1[2 * i], p.s1[2 * i + 1], p.h1[2 * i + 1]);
+  }
+  if (RESMMA) {
+    // identity in the K-major 128B-swizzled operand layout: element (n, n) lives in K chunk n / 64 at
+    // byte n * 128 + (((n % 64) / 8) ^ (n & 7)) * 16 + (n % 8) * 2
+    const uint32_t i_smem = smem_base + WRES_W_BYTES;
+    for (int i = threadIdx.x; i < WRES_I_BYTES / 16; i += NUM_THREADS)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(i_smem + i * 16), "r"(0) : "memory");
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      const int n = threadIdx.x;
+      const uint32_t addr = i_smem + (n >> 6) * 16384 + n * 128 + ((((n & 63) >> 3) ^ (n & 7)) << 4) + (n & 7) * 2;
+      asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<unsigned short>(0x3c00)) : "memory");   // 1.0 (IEEE half)
+    }
+    fence_proxy_async();
+  }
 
   const int num_m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
   const int num_n_tiles = (p.N + BN - 1) / BN;
@@ -160,7 +199,14 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t fb = smem_u32(&full_bar[stage]);
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
             mbar_arrive_expect_tx(fb, WRES_A_BYTES);
-            tma_load_2d(smem_base + WRES_W_BYTES + stage * WRES_A_BYTES, &tmA, fb, kcx * BLOCK_K, m0 - 1);
+            tma_load_2d(smem_base + WC::FIXED_BYTES + stage * WRES_A_BYTES, &tmA, fb, kcx * BLOCK_K, m0 - 1);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          for (int kcx = 0; kcx < 2 && RESMMA; ++kcx) {
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+            mbar_arrive_expect_tx(fb, WRES_R_BYTES);
+            tma_load_2d(smem_base + WC::FIXED_BYTES + stage * WRES_A_BYTES, &tmR, fb, kcx * BLOCK_K, m0);
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
         }
@@ -212,7 +258,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int kcx = 0; kcx < 2; ++kcx) {
             mbar_wait(smem_u32(&full_bar[stage]), phase);
             tc_fence_after();
-            const uint32_t sa = smem_base + WRES_W_BYTES + stage * WRES_A_BYTES;
+            const uint32_t sa = smem_base + WC::FIXED_BYTES + stage * WRES_A_BYTES;
 #pragma unroll
             for (int tap = 0; tap < 3; ++tap) {
               const uint64_t adesc = umma_desc_sw128(sa + tap * 128);                      // rows m0 - 1 + tap ...
@@ -220,6 +266,16 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
               for (int k = 0; k < BLOCK_K / 16; ++k) { umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accf); accf = 1; }
             }
+            umma_commit(smem_u32(&empty_bar[stage]));
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          for (int kcx = 0; kcx < 2 && RESMMA; ++kcx) {
+            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(smem_base + WC::FIXED_BYTES + stage * WRES_A_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(smem_base + WRES_W_BYTES + kcx * 16384);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
             umma_commit(smem_u32(&empty_bar[stage]));
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
@@ -294,9 +350,10 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 c[q] = fabsf(__uint_as_float(j < 32 ? ra[j < 32 ? j : 0] : rb[j >= 32 ? j - 32 : 0]));
               }
               const float mx = fmaxf(c[0], fmaxf(c[1], c[2]));
-              const float x = lrelu03(fmaf(mx, __ldg(p.s1 + f + i), __ldg(p.h1 + f + i)));
+              const float4 af = s_aff[f + i];
+              const float x = lrelu03(fmaf(mx, af.x, af.y));
               x0[i] = x;
-              a0[i] = lrelu03(fmaf(x, __ldg(p.s2 + f + i), __ldg(p.h2 + f + i)));
+              a0[i] = lrelu03(fmaf(x, af.z, af.w));
             }
             store_planes<16>(p.out + orow * p.out_ld + f, p.out_planes, p.out_plane_cols, x0);
             store_planes<16>(p.out2 + orow * p.out2_ld + f, p.out2_planes, p.out2_plane_cols, a0);
@@ -320,9 +377,23 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           float v[32];
           if (EPI == EPI_AFF_LRELU) {
             // zero rows stay zero: they are the next conv's padding
+            if (p.N <= AFF_MAX) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              v[i] = valid ? lrelu03(fmaf(__uint_as_float(r[i]), __ldg(p.s1 + n + i), __ldg(p.h1 + n + i))) : 0.f;
+              for (int i = 0; i < 16; ++i) {
+                const float4 af = s_aff[(n >> 1) + i];
+                v[2 * i] = valid ? lrelu03(fmaf(__uint_as_float(r[2 * i]), af.x, af.y)) : 0.f;
+                v[2 * i + 1] = valid ? lrelu03(fmaf(__uint_as_float(r[2 * i + 1]), af.z, af.w)) : 0.f;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                v[i] = valid ? lrelu03(fmaf(__uint_as_float(r[i]), __ldg(p.s1 + n + i), __ldg(p.h1 + n + i))) : 0.f;
+            }
+            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          } else if (EPI == EPI_ADD && RESMMA) {
+            if (!valid) continue;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
             store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
           } else if (EPI == EPI_ADD) {
             if (!valid) continue;
@@ -371,9 +442,10 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
 // ------------------------------------------------------------------ host side
 template <int BN, int EPI, bool WRES = false>
-static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const RnGemmParams& p, cudaStream_t stream) {
+static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& r, const RnGemmParams& p,
+                       cudaStream_t stream) {
   using Cfg = RnCfg<BN>;
-  constexpr int SMEM = WRES ? WRES_SMEM_BYTES : Cfg::SMEM_BYTES;
+  constexpr int SMEM = WRES ? WresCfg<EPI>::SMEM_BYTES : Cfg::SMEM_BYTES;
   static bool attr_set = false;
   if (!attr_set) {
     SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
@@ -381,7 +453,7 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const RnGemmP
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  rn_gemm_kernel<BN, EPI, WRES><<<grid, NUM_THREADS, SMEM, stream>>>(a, w, p);
+  rn_gemm_kernel<BN, EPI, WRES><<<grid, NUM_THREADS, SMEM, stream>>>(a, w, r, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -396,7 +468,7 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   if (epi == EPI_SINC) {
     SVB_CHECK(p.N % 192 == 0, "sinc GEMM: N must be a multiple of 192");
     if (make_map(&mw, w, w_rows, w_cols, w_cols, 192)) return -1;
-    return launch_rn_t<192, EPI_SINC>(ma, mw, p, stream);
+    return launch_rn_t<192, EPI_SINC>(ma, mw, ma, p, stream);
   }
   SVB_CHECK(p.N % 128 == 0, "RawNet conv GEMM: N must be a multiple of 128");
   const int bn = (p.N % 256 == 0) ? 256 : 128;
@@ -404,20 +476,22 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   // 128-channel k = 3 layers in the 16-bit mode: W-resident, tap-shared mainloop (SVB_RN_WRES=0: generic mainloop)
   static const bool wres_on = [] { const char* e = getenv("SVB_RN_WRES"); return e == nullptr || e[0] != '0'; }();
   if (wres_on && p.N == 128 && p.num_taps == 3 && p.kc_per_tap == 2 && p.num_pass == 1 && p.w_planes == 1 &&
-      p.tap_off[0] == -1 && p.tap_off[1] == 0 && p.tap_off[2] == 1 && (epi == EPI_AFF_LRELU || epi == EPI_ADD)) {
-    CUtensorMap ma136;
+      p.tap_off[0] == -1 && p.tap_off[1] == 0 && p.tap_off[2] == 1 &&
+      (epi == EPI_AFF_LRELU || (epi == EPI_ADD && p.add_planes == 1 && p.add_ld == 128))) {
+    CUtensorMap ma136, mr;
     if (make_map(&ma136, a, a_rows, a_cols, a_ld, WRES_A_ROWS)) return -1;
-    return epi == EPI_AFF_LRELU ? launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, p, stream)
-                                : launch_rn_t<128, EPI_ADD, true>(ma136, mw, p, stream);
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, ma136, p, stream);
+    if (make_map(&mr, p.add, a_rows, 128, p.add_ld, BLOCK_M)) return -1;      // the shortcut has the rows of the output
+    return launch_rn_t<128, EPI_ADD, true>(ma136, mw, mr, p, stream);
   }
   if (bn == 256) {
-    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, p, stream);
-    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, p, stream);
-    return launch_rn_t<256, EPI_PLAIN>(ma, mw, p, stream);
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, p, stream);
+    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, p, stream);
+    return launch_rn_t<256, EPI_PLAIN>(ma, mw, ma, p, stream);
   }
-  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, p, stream);
-  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, p, stream);
-  return launch_rn_t<128, EPI_PLAIN>(ma, mw, p, stream);
+  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, ma, p, stream);
+  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, ma, p, stream);
+  return launch_rn_t<128, EPI_PLAIN>(ma, mw, ma, p, stream);
 }
 
 }  // namespace svb
