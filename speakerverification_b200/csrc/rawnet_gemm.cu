@@ -33,9 +33,13 @@ namespace svb {
 static constexpr int BLOCK_M = 128;
 static constexpr int BLOCK_K = 64;
 static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
-static constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
-
 enum { EPI_SINC = 0, EPI_AFF_LRELU = 1, EPI_ADD = 2, EPI_PLAIN = 3 };
+
+// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, then 8 epilogue warps -- 16 for the sinc layer, whose epilogue (96
+// accumulators -> abs, max-pool, two affine + LeakyReLU, two stores per thread and tile) was latency bound with 8:
+// ncu r02, tensor pipe 34 %, issue 30 %, DRAM 18 % busy at 3.2 us per tile against 1.0 us of MMAs.
+static constexpr int SINC_EPI_WARPS = 16;
+template <int EPI> struct RnThreads { static constexpr int N = EPI == EPI_SINC ? 128 + 32 * SINC_EPI_WARPS : 384; };
 
 template <int BN>
 struct RnCfg {
@@ -99,6 +103,13 @@ static constexpr int WRES_A_BYTES = WRES_A_ROWS * 128;      // 17 408 = 17 x 102
 static constexpr int WRES_W_BYTES = 6 * 128 * 128;          // 3 taps x 2 K chunks of [128 rows x 64 ch]
 static constexpr int WRES_I_BYTES = 2 * 128 * 128;          // identity [128 x 128], 2 K chunks (EPI_ADD only)
 static constexpr int WRES_R_BYTES = 128 * 128;              // one residual box [128 rows x 64 ch]
+// W-resident sinc variant (16-bit mode: one pass, K = 320 = 5 k-blocks): the five W boxes of the CTA's current n-tile stay
+// in shared memory, the stage ring carries A boxes only.  The generic mainloop moved 40 KB per k-block from L2 (ncu
+// r02: 40.6 GB L2->SM per launch = 9.4 TB/s, the limiter at 34 % tensor-pipe and 18 % DRAM utilisation); this one 16 KB.
+static constexpr int WSINC_KB = 5;
+static constexpr int WSINC_W_BYTES = WSINC_KB * 192 * 128;  // 122 880
+static constexpr int WSINC_STAGES = 6;
+static constexpr int WSINC_SMEM_BYTES = WSINC_W_BYTES + WSINC_STAGES * A_STAGE_BYTES + 1024;
 template <int EPI> struct WresCfg {
   static constexpr bool RES = EPI == 2;                     // EPI_ADD
   static constexpr int STAGES = RES ? 5 : 6;
@@ -107,16 +118,22 @@ template <int EPI> struct WresCfg {
 };
 
 template <int BN, int EPI, bool WRES = false>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(RnThreads<EPI>::N, 1)
 rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmR, const RnGemmParams p) {
   using Cfg = RnCfg<BN>;
   using WC = WresCfg<EPI>;
-  constexpr int STAGES = WRES ? WC::STAGES : Cfg::STAGES;
+  constexpr int STAGES = WRES ? (EPI == EPI_SINC ? WSINC_STAGES : WC::STAGES) : Cfg::STAGES;
   constexpr bool RESMMA = WRES && WC::RES;                  // residual added by an identity MMA
   constexpr int AFF_MAX = 512;                              // affine parameters cached in shared memory up to this N
-  static_assert(!WRES || BN == 128, "the W-resident variant serves the 128-channel layers");
+  constexpr int NUM_THREADS = RnThreads<EPI>::N;
+  constexpr int EPI_WARPS = NUM_THREADS / 32 - 4;
+  constexpr bool WCONV = WRES && EPI != EPI_SINC;           // 128-channel k = 3 layers, all of W resident
+  constexpr bool WSINC = WRES && EPI == EPI_SINC;           // sinc layer, the W tile of ONE n-tile resident
+  static_assert(!WCONV || BN == 128, "the W-resident conv variant serves the 128-channel layers");
+  static_assert(!WSINC || BN == 192, "the W-resident sinc variant uses 192-column tiles");
   __shared__ __align__(8) uint64_t wfull_bar;
+  __shared__ __align__(8) uint64_t wfree_bar;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES];
   __shared__ __align__(8) uint64_t empty_bar[STAGES];
@@ -158,6 +175,14 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int kc = p.kc_per_tap;
   const int kb_per_tap = p.num_pass * kc;
   const int num_kb = p.num_taps * kb_per_tap;
+  // tile schedule: interleaved over the CTAs with n fastest (consecutive CTAs share the A tile in L2) -- except WSINC,
+  // where every CTA takes ONE contiguous run of the n-major tile order so that its W tile changes at most twice
+  const int t_per = WSINC ? (num_tiles + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x) : 0;
+  const int t_begin = WSINC ? static_cast<int>(blockIdx.x) * t_per : static_cast<int>(blockIdx.x);
+  const int t_end = WSINC ? min(num_tiles, t_begin + t_per) : num_tiles;
+  const int t_step = WSINC ? 1 : static_cast<int>(gridDim.x);
+  auto tile_m = [&](int tile) { return WSINC ? tile % num_m_tiles : tile / num_n_tiles; };
+  auto tile_n = [&](int tile) { return WSINC ? tile / num_m_tiles : tile % num_n_tiles; };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -170,9 +195,10 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&tfull_bar[a]), 1);
-      mbar_init(smem_u32(&tempty_bar[a]), 8);
+      mbar_init(smem_u32(&tempty_bar[a]), EPI_WARPS);
     }
     mbar_init(smem_u32(&wfull_bar), 1);
+    mbar_init(smem_u32(&wfree_bar), 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -189,7 +215,28 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      if (WRES) {
+      if (WSINC) {
+        const uint32_t wb = smem_u32(&wfull_bar);
+        int cur_nt = -1;
+        uint32_t wfree_phase = 0;
+        for (int tile = t_begin; tile < t_end; ++tile) {
+          const int m0 = tile_m(tile) * BLOCK_M, nt = tile_n(tile);
+          if (nt != cur_nt) {
+            if (cur_nt >= 0) { mbar_wait(smem_u32(&wfree_bar), wfree_phase); wfree_phase ^= 1u; }   // old W no longer read
+            mbar_arrive_expect_tx(wb, WSINC_W_BYTES);
+            for (int kb = 0; kb < WSINC_KB; ++kb) tma_load_2d(smem_base + kb * Cfg::B_STAGE_BYTES, &tmW, wb, kb * BLOCK_K, nt * BN);
+            cur_nt = nt;
+          }
+          for (int kb = 0; kb < WSINC_KB; ++kb) {
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+            mbar_arrive_expect_tx(fb, A_STAGE_BYTES);
+            tma_load_2d(smem_base + WSINC_W_BYTES + stage * A_STAGE_BYTES, &tmA, fb, kb * BLOCK_K, m0 + p.tap_off[0]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+      if (WCONV) {
         const uint32_t wb = smem_u32(&wfull_bar);
         mbar_arrive_expect_tx(wb, WRES_W_BYTES);
         for (int j = 0; j < 6; ++j) tma_load_2d(smem_base + j * 16384, &tmW, wb, j * BLOCK_K, 0);    // j = tap * 2 + kcx
@@ -213,8 +260,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       for (int tile = blockIdx.x; tile < num_tiles && !WRES; tile += gridDim.x) {
         // n fastest: consecutive CTAs share the A tile (L2), W is small and stays cache resident
-        const int m0 = (tile / num_n_tiles) * BLOCK_M;
-        const int n0 = (tile % num_n_tiles) * BN;
+        const int m0 = tile_m(tile) * BLOCK_M;
+        const int n0 = tile_n(tile) * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / kb_per_tap;
           const int rem = kb - tap * kb_per_tap;
@@ -245,7 +292,33 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      if (WRES) {
+      if (WSINC) {
+        int cur_nt = -1;
+        uint32_t wfull_phase = 0;
+        for (int tile = t_begin; tile < t_end; ++tile, ++it) {
+          const int nt = tile_n(tile);
+          if (nt != cur_nt) { mbar_wait(smem_u32(&wfull_bar), wfull_phase); wfull_phase ^= 1u; cur_nt = nt; }
+          const int acc = it & 1;
+          const uint32_t acc_phase = (it >> 1) & 1u;
+          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          for (int kb = 0; kb < WSINC_KB; ++kb) {
+            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(smem_base + WSINC_W_BYTES + stage * A_STAGE_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(smem_base + kb * Cfg::B_STAGE_BYTES);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            umma_commit(smem_u32(&empty_bar[stage]));
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit(smem_u32(&tfull_bar[acc]));
+          if (tile + 1 < t_end && tile_n(tile + 1) != cur_nt) umma_commit(smem_u32(&wfree_bar));
+        }
+      }
+      if (WCONV) {
         mbar_wait(smem_u32(&wfull_bar), 0);
         tc_fence_after();
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
@@ -307,11 +380,11 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================================================== epilogue
     const int ew = warp - 4;
     const int quad = ew & 3;   // TMEM lane quadrant of this warp
-    const int half = ew >> 2;  // column half of the tile
+    const int half = ew >> 2;  // column half of the tile (sinc: column group of the warp)
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m0 = (tile / num_n_tiles) * BLOCK_M;
-      const int nt = tile % num_n_tiles;
+    for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
+      const int m0 = tile_m(tile) * BLOCK_M;
+      const int nt = tile_n(tile);
       const int n0 = nt * BN;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
@@ -323,24 +396,30 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int utt = static_cast<int>(row / p.Mu);
         const int ml = static_cast<int>(row - static_cast<long long>(utt) * p.Mu);
         const int jg = nt >> 1;
-        const int f0 = (nt & 1) * 64 + half * 32;
         const int t_out = 16 * ml + jg;
         const bool valid = row < p.M && utt < p.B && t_out < p.T;
         const long long orow = static_cast<long long>(utt) * p.Tp + 1 + t_out;
         mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
         tc_fence_after();
+        // the tile's 192 columns are 4 pieces of 48 = 16 filters x 3 pooling phases; a warp owns 4 / (EPI_WARPS / 4) of them
+        constexpr int PPW = 16 / EPI_WARPS;
 #pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
-          // 48 accumulator columns = 16 filters x 3 pooling phases
+        for (int h2 = 0; h2 < PPW; ++h2) {
+          const int piece = half * PPW + h2;
           uint32_t ra[32];
           uint32_t rb[16];
-          const uint32_t col = half * 96 + h2 * 48;
+          const uint32_t col = piece * 48;
           tmem_ld32(tbase + col, ra);
           tmem_ld16(tbase + col + 32, rb);
           tmem_ld_wait();
+          if (h2 == PPW - 1) {          // the accumulator is in registers: hand the TMEM buffer back before the arithmetic
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          }
           if (valid) {
             float x0[16], a0[16];
-            const int f = f0 + h2 * 16;
+            const int f = (nt & 1) * 64 + piece * 16;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               float c[3];
@@ -364,16 +443,64 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int t = static_cast<int>(row - static_cast<long long>(utt) * p.Tp) - 1;
         const bool in_m = row < p.M;
         const bool valid = in_m && t >= 0 && t < p.T;
+        if (EPI == EPI_ADD && !RESMMA) {
+          // the residual's hi plane (the only one in the 16-bit mode) is requested BEFORE the accumulator is waited for:
+          // its DRAM latency hides under the tile's MMAs instead of adding one round trip per 32-column chunk
+          uint4 res[BN / 64][4];
+          const bf16* ap0 = p.add + row * p.add_ld + n0 + half * (BN / 2);
+#pragma unroll
+          for (int c = 0; c < BN / 64; ++c)
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              res[c][i] = (valid && n0 + half * (BN / 2) + c * 32 < p.N) ? __ldg(reinterpret_cast<const uint4*>(ap0 + c * 32) + i)
+                                                                         : make_uint4(0u, 0u, 0u, 0u);
+          mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < BN / 64; ++c) {
+            const int col0 = half * (BN / 2) + c * 32;
+            uint32_t r[32];
+            tmem_ld32(tbase + col0, r);
+            tmem_ld_wait();
+            const int n = n0 + col0;
+            if (n >= p.N || !valid) continue;
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t w[4] = {res[c][i].x, res[c][i].y, res[c][i].z, res[c][i].w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                v[8 * i + 2 * q] = __uint_as_float(r[8 * i + 2 * q]) + (p.add_planes == 1 ? f16_lo_f(w[q]) : bf16_lo_f(w[q]));
+                v[8 * i + 2 * q + 1] = __uint_as_float(r[8 * i + 2 * q + 1]) + (p.add_planes == 1 ? f16_hi_f(w[q]) : bf16_hi_f(w[q]));
+              }
+            }
+            if (p.add_planes == 2) {
+              const bf16* ap = p.add + row * p.add_ld + n;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + p.add_plane_cols) + i);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  v[8 * i + 2 * q] += bf16_lo_f(w[q]);
+                  v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
+                }
+              }
+            }
+            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          continue;
+        }
         mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
         tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < BN / 64; ++c) {
-          const int col0 = half * (BN / 2) + c * 32;
-          uint32_t r[32];
-          tmem_ld32(tbase + col0, r);
-          tmem_ld_wait();
+        // one 32-column chunk of this thread's row: affine + LeakyReLU (conv1) or plain (shortcut conv, and conv2 whose
+        // residual the identity MMA already added), packed and stored
+        auto emit = [&](int col0, const uint32_t (&r)[32]) {
           const int n = n0 + col0;
-          if (n >= p.N || !in_m) continue;
+          if (n >= p.N || !in_m) return;
           float v[32];
           if (EPI == EPI_AFF_LRELU) {
             // zero rows stay zero: they are the next conv's padding
@@ -389,46 +516,36 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               for (int i = 0; i < 32; ++i)
                 v[i] = valid ? lrelu03(fmaf(__uint_as_float(r[i]), __ldg(p.s1 + n + i), __ldg(p.h1 + n + i))) : 0.f;
             }
-            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
-          } else if (EPI == EPI_ADD && RESMMA) {
-            if (!valid) continue;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
-          } else if (EPI == EPI_ADD) {
-            if (!valid) continue;
-            const bf16* ap = p.add + row * p.add_ld + n;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap) + i);
-              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                v[8 * i + 2 * q] = __uint_as_float(r[8 * i + 2 * q]) + (p.add_planes == 1 ? f16_lo_f(w[q]) : bf16_lo_f(w[q]));
-                v[8 * i + 2 * q + 1] = __uint_as_float(r[8 * i + 2 * q + 1]) + (p.add_planes == 1 ? f16_hi_f(w[q]) : bf16_hi_f(w[q]));
-              }
-            }
-            if (p.add_planes == 2) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + p.add_plane_cols) + i);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  v[8 * i + 2 * q] += bf16_lo_f(w[q]);
-                  v[8 * i + 2 * q + 1] += bf16_hi_f(w[q]);
-                }
-              }
-            }
-            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
           } else {
-            if (!valid) continue;
+            if (!valid) return;
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
           }
+          store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+        };
+        if (BN == 128) {
+          // both chunks into registers, TMEM buffer handed back, then the arithmetic and the stores
+          uint32_t r0[32], r1[32];
+          tmem_ld32(tbase + half * 64, r0);
+          tmem_ld32(tbase + half * 64 + 32, r1);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          emit(half * 64, r0);
+          emit(half * 64 + 32, r1);
+          continue;
+        }
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int col0 = half * (BN / 2) + c * 32;
+          uint32_t r[32];
+          tmem_ld32(tbase + col0, r);
+          tmem_ld_wait();
+          emit(col0, r);
         }
       }
+      if (EPI == EPI_SINC) continue;            // released inside
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
@@ -445,7 +562,7 @@ template <int BN, int EPI, bool WRES = false>
 static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& r, const RnGemmParams& p,
                        cudaStream_t stream) {
   using Cfg = RnCfg<BN>;
-  constexpr int SMEM = WRES ? WresCfg<EPI>::SMEM_BYTES : Cfg::SMEM_BYTES;
+  constexpr int SMEM = WRES ? (EPI == EPI_SINC ? WSINC_SMEM_BYTES : WresCfg<EPI>::SMEM_BYTES) : Cfg::SMEM_BYTES;
   static bool attr_set = false;
   if (!attr_set) {
     SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
@@ -453,7 +570,7 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  rn_gemm_kernel<BN, EPI, WRES><<<grid, NUM_THREADS, SMEM, stream>>>(a, w, r, p);
+  rn_gemm_kernel<BN, EPI, WRES><<<grid, RnThreads<EPI>::N, SMEM, stream>>>(a, w, r, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -468,6 +585,9 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   if (epi == EPI_SINC) {
     SVB_CHECK(p.N % 192 == 0, "sinc GEMM: N must be a multiple of 192");
     if (make_map(&mw, w, w_rows, w_cols, w_cols, 192)) return -1;
+    static const bool wsinc_on = [] { const char* e = getenv("SVB_RN_WSINC"); return e == nullptr || e[0] != '0'; }();
+    if (wsinc_on && p.num_pass == 1 && p.num_taps == 1 && p.kc_per_tap == WSINC_KB)
+      return launch_rn_t<192, EPI_SINC, true>(ma, mw, ma, p, stream);
     return launch_rn_t<192, EPI_SINC>(ma, mw, ma, p, stream);
   }
   SVB_CHECK(p.N % 128 == 0, "RawNet conv GEMM: N must be a multiple of 128");
