@@ -687,7 +687,10 @@ int launch_gemm_pw(const GemmOperands& ops, const GemmParams& g, cudaStream_t st
 int launch_gemm_f32(const GemmOperands& ops, const GemmParams& g, cudaStream_t stream) {
   SVB_CHECK(g.num_taps == 1 && g.tap_off[0] == 0 && g.N % 64 == 0, "launch_gemm_f32: pointwise, N % 64 == 0");
   SVB_CHECK((reinterpret_cast<uintptr_t>(g.out) & 15) == 0 && (g.out_ld * 4) % 16 == 0, "fp32 output must be 16-byte aligned");
-  const int bn = g.N >= 256 ? 256 : 128;
+  // 256-column tiles unless they would leave SMs idle (the GRU's recurrent GEMM: 592 x 3072 is 60 tiles of 256
+  // columns on 148 SMs, 120 of 128 columns: 23.9 -> 20.0 us per launch)
+  const long long tiles256 = static_cast<long long>((g.M + BLOCK_M - 1) / BLOCK_M) * ((g.N + 255) / 256);
+  const int bn = (g.N >= 256 && tiles256 >= num_sms()) ? 256 : 128;
   CUtensorMap ma, mw, mo;
   if (make_map(&ma, ops.a, g.M, ops.a_cols, ops.lda, BLOCK_M)) return -1;
   if (make_map(&mw, ops.w, ops.w_rows, ops.w_cols, ops.w_cols, bn)) return -1;

@@ -308,9 +308,11 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc_fence_after();
             const uint64_t adesc = umma_desc_sw128(smem_base + WSINC_W_BYTES + stage * A_STAGE_BYTES);
             const uint64_t bdesc = umma_desc_sw128(smem_base + kb * Cfg::B_STAGE_BYTES);
+            // the shifted filters end at column 250 + 47 = 297: the last 16 of the 320 K columns are zero in every W row
+            const int ksteps = kb == WSINC_KB - 1 ? BLOCK_K / 16 - 1 : BLOCK_K / 16;
 #pragma unroll
             for (int k = 0; k < BLOCK_K / 16; ++k)
-              umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+              if (k < ksteps) umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
             umma_commit(smem_u32(&empty_bar[stage]));
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
