@@ -247,6 +247,18 @@ int svb_mean_embeddings(const float* emb, int U, int n_per_utt, int D, int norma
 size_t svb_asnorm_workspace_bytes(int U, int N, int D);
 int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu,
                      float* sigma, void* ws, size_t ws_bytes, void* stream);
+/* svb_asnorm_stats without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same inputs, outputs and results as svb_asnorm_stats; the workspace is a file-scope device array
+ * of svb_asnorm_static_bytes() = 16 MiB inside the library (every GPU that loads libsvb holds it until the process
+ * exits).  Geometries with svb_asnorm_workspace_bytes(U, N, D) above that limit are rejected with an error message
+ * (e.g. 1024 utterances x 2048 cohort vectors x 192 fits).  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  All calls on a device SHARE the array: calls that overlap on the GPU (different
+ * streams or host threads) race -- serialise them; the array keeps the previous call's contents and the call itself
+ * clears what must start at zero. */
+size_t svb_asnorm_static_bytes(void);
+int svb_asnorm_stats_static(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu,
+                            float* sigma, void* stream);
 /* Diagnostic (profiling): mainloop of a pointwise fp16 layer [M, K] x [N, K]^T with a store-free epilogue; thr_inf[M]
  * must hold +inf, cnt[M] / cand[M] are scratch. */
 int svb_debug_gemm_noepi(const void* a, const void* w, int M, int N, int K, const float* thr_inf, unsigned* cnt,

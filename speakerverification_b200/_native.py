@@ -113,6 +113,8 @@ _EXTRA_SIGS = {
     "svb_asnorm_stats": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _c.c_size_t, _vp], _i32),
     "svb_debug_gemm_noepi": ([_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp], _i32),
     "svb_asnorm_fixup_rows": ([_vp, _i32, _i32, _i32, _i32], _i32),
+    "svb_asnorm_static_bytes": ([], _c.c_size_t),
+    "svb_asnorm_stats_static": ([_vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp], _i32),
     "svb_asnorm_trials": ([_vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp], _i32),
     "svb_rawnet2_create": ([_c.POINTER(SvbRawnet2Cfg), _c.POINTER(_c.c_char_p), _c.POINTER(_vp), _i32, _pp], _i32),
     "svb_rawnet2_destroy": ([_vp], None),

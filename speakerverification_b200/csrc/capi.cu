@@ -44,6 +44,8 @@ int mean_rows(const float*, int, int, int, int, float*, cudaStream_t);
 int enrol_nearest(const float*, const float*, int, int, int, int, float, int, float*, float*, int32_t*, cudaStream_t);
 size_t asnorm_workspace_bytes(int, int, int, int*);
 int asnorm_stats(const float*, int, const float*, int, int, int, float*, float*, void*, size_t, cudaStream_t);
+int asnorm_stats_static(const float*, int, const float*, int, int, int, float*, float*, cudaStream_t);
+size_t asnorm_static_bytes();
 int asnorm_trials(const float*, int, const int32_t*, const int32_t*, long long, const float*, const float*, float*,
                   cudaStream_t);
 struct Rawnet2;
@@ -315,6 +317,14 @@ int svb_asnorm_stats(const float* emean, int U, const float* cohort, int N, int 
   if (check_device()) return -1;
   SVB_CHECK(emean && cohort && mu && sigma && U >= 1 && N >= 1 && D >= 1, "bad argument");
   return asnorm_stats(emean, U, cohort, N, D, topk, mu, sigma, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+}
+// No-allocation variant (no reference counterpart): workspace in a 16 MiB file-scope device array
+size_t svb_asnorm_static_bytes(void) { return asnorm_static_bytes(); }
+int svb_asnorm_stats_static(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu, float* sigma,
+                            void* stream) {
+  if (check_device()) return -1;
+  SVB_CHECK(emean && cohort && mu && sigma && U >= 1 && N >= 1 && D >= 1, "bad argument");
+  return asnorm_stats_static(emean, U, cohort, N, D, topk, mu, sigma, static_cast<cudaStream_t>(stream));
 }
 // Diagnostic: the GEMM mainloop of a pointwise layer with the epilogue reduced to TMEM reads and compares (nothing
 // stored: thr = +inf everywhere) -- separates operand-feed time from epilogue time (tools/pw_alone.py).

@@ -1445,4 +1445,38 @@ int asnorm_trials(const float* emean, int D, const int32_t* ia, const int32_t* i
   return 0;
 }
 
+// ---------------------------------------------------------------- AS-norm statistics without any allocation
+// Added (no counterpart in the reference): callers that cannot allocate -- code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc -- get the top-K cohort statistics with
+// the workspace of asnorm_stats in a file-scope device array instead of a caller buffer.  Every GPU that loads the
+// library holds ASNORM_STATIC_BYTES of device memory until the process exits.  ALL calls on a device share the array:
+// calls that overlap on the GPU (two streams, two host threads) race; the array keeps the previous call's contents, and
+// asnorm_stats itself clears what must start at zero (operand padding, counters) at the start of every call.
+static constexpr size_t ASNORM_STATIC_BYTES = 16u << 20;          // 16 MiB, e.g. 1024 utterances x 2048 cohort vectors x 192
+static __device__ __align__(256) unsigned char g_asnorm_scratch[ASNORM_STATIC_BYTES];
+
+size_t asnorm_static_bytes() { return ASNORM_STATIC_BYTES; }
+
+int asnorm_stats_static(const float* emean, int U, const float* cohort, int N, int D, int topk, float* mu, float* sigma,
+                        cudaStream_t stream) {
+  const size_t need = asnorm_workspace_bytes(U, N, D, nullptr);
+  SVB_CHECK(need <= ASNORM_STATIC_BYTES,
+            "svb_asnorm_stats_static: U=%d, N=%d, D=%d needs %zu bytes of scratch, the built-in array holds %zu; use "
+            "svb_asnorm_stats with a caller workspace", U, N, D, need, static_cast<size_t>(ASNORM_STATIC_BYTES));
+  // g_asnorm_scratch is a host-side stand-in in this function: the device address comes from the runtime, once per
+  // device, with that device current
+  static constexpr int MAX_DEV = 64;
+  static void* dev_ptr[MAX_DEV] = {};
+  int dev = 0;
+  SVB_CUDA_OK(cudaGetDevice(&dev));
+  SVB_CHECK(dev >= 0 && dev < MAX_DEV, "device ordinal %d out of range", dev);
+  void* ws = __atomic_load_n(&dev_ptr[dev], __ATOMIC_ACQUIRE);
+  if (ws == nullptr) {
+    SVB_CUDA_OK(cudaGetSymbolAddress(&ws, g_asnorm_scratch));
+    SVB_CHECK(ws != nullptr && (reinterpret_cast<uintptr_t>(ws) & 255) == 0, "static scratch array is not 256-byte aligned");
+    __atomic_store_n(&dev_ptr[dev], ws, __ATOMIC_RELEASE);
+  }
+  return asnorm_stats(emean, U, cohort, N, D, topk, mu, sigma, ws, ASNORM_STATIC_BYTES, stream);
+}
+
 }  // namespace svb
