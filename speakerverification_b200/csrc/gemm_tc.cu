@@ -335,6 +335,27 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
+// Store view of the sinc layer's output (rawnet_gemm.cu): activations [utt][1 + t][ld] with t = 16 * ml + jg seen as a
+// 4-D tensor (channel, jg, ml, utt) so that one box = 32 consecutive ml of one (jg, utt) x 32 channels (64 B rows, 64B
+// swizzle).  `base` = row 1 of utterance 0; ml_extent = T / 16 (every jg is a valid frame below it).
+int make_map_sinc_out(CUtensorMap* m, const void* base, int channels, long long ld, int ml_extent, long long rows_per_utt,
+                      int utts) {
+  EncodeTiledFn fn = get_encode_fn();
+  SVB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  SVB_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0 && ml_extent >= 1,
+            "TMA store view must be 16-byte aligned (base %p, ld %lld)", base, ld);
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(channels), 16, static_cast<cuuint64_t>(ml_extent), static_cast<cuuint64_t>(utts)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 32,
+                           static_cast<cuuint64_t>(rows_per_utt) * ld * 2};
+  cuuint32_t box[4] = {32, 1, 32, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SVB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (sinc store view) failed with code %d", static_cast<int>(r));
+  return 0;
+}
+
 // Same matrix with box = [32 cols (64 B), box_rows] and 64B swizzle: the 2 KB store boxes of gemm_pw's 16-warp epilogue.
 int make_map_sw64(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();

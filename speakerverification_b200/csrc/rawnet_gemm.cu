@@ -39,7 +39,10 @@ enum { EPI_SINC = 0, EPI_AFF_LRELU = 1, EPI_ADD = 2, EPI_PLAIN = 3 };
 // accumulators -> abs, max-pool, two affine + LeakyReLU, two stores per thread and tile) was latency bound with 8:
 // ncu r02, tensor pipe 34 %, issue 30 %, DRAM 18 % busy at 3.2 us per tile against 1.0 us of MMAs.
 static constexpr int SINC_EPI_WARPS = 16;
-template <int EPI> struct RnThreads { static constexpr int N = EPI == EPI_SINC ? 128 + 32 * SINC_EPI_WARPS : 384; };
+// (the W-resident sinc variant stores through TMA boxes of 32 rows x 32 filters per warp and runs 8 epilogue warps)
+template <int EPI, bool WRES = false> struct RnThreads {
+  static constexpr int N = (EPI == EPI_SINC && !WRES) ? 128 + 32 * SINC_EPI_WARPS : 384;
+};
 
 template <int BN>
 struct RnCfg {
@@ -101,32 +104,37 @@ __device__ __forceinline__ void store_planes(bf16* dst, int planes, int plane_co
 static constexpr int WRES_A_ROWS = 136;
 static constexpr int WRES_A_BYTES = WRES_A_ROWS * 128;      // 17 408 = 17 x 1024
 static constexpr int WRES_W_BYTES = 6 * 128 * 128;          // 3 taps x 2 K chunks of [128 rows x 64 ch]
-static constexpr int WRES_I_BYTES = 2 * 128 * 128;          // identity [128 x 128], 2 K chunks (EPI_ADD only)
+static constexpr int WRES_I_BYTES = 64 * 128;               // identity [64 x 64] (EPI_ADD only): one N = 64 MMA per column half
+// Outputs of the W-resident variants leave through shared memory and TMA stores (one 32-row box per epilogue warp): a
+// thread-per-row STG.128 touches 32 lines per instruction, and the LSU data pipe was the busiest unit of these kernels
+// (ncu r02: l1tex__data_pipe_lsu_wavefronts 71 % for the sinc layer).
+static constexpr int WRES_OUT_BYTES = 8 * 4096;
 static constexpr int WRES_R_BYTES = 128 * 128;              // one residual box [128 rows x 64 ch]
 // W-resident sinc variant (16-bit mode: one pass, K = 320 = 5 k-blocks): the five W boxes of the CTA's current n-tile stay
 // in shared memory, the stage ring carries A boxes only.  The generic mainloop moved 40 KB per k-block from L2 (ncu
 // r02: 40.6 GB L2->SM per launch = 9.4 TB/s, the limiter at 34 % tensor-pipe and 18 % DRAM utilisation); this one 16 KB.
 static constexpr int WSINC_KB = 5;
 static constexpr int WSINC_W_BYTES = WSINC_KB * 192 * 128;  // 122 880
-static constexpr int WSINC_STAGES = 6;
-static constexpr int WSINC_SMEM_BYTES = WSINC_W_BYTES + WSINC_STAGES * A_STAGE_BYTES + 1024;
+static constexpr int WSINC_STAGES = 4;
+static constexpr int WSINC_SMEM_BYTES = WSINC_W_BYTES + WSINC_STAGES * A_STAGE_BYTES + WRES_OUT_BYTES + 1024;
 template <int EPI> struct WresCfg {
   static constexpr bool RES = EPI == 2;                     // EPI_ADD
-  static constexpr int STAGES = RES ? 5 : 6;
+  static constexpr int STAGES = 5;
   static constexpr int FIXED_BYTES = WRES_W_BYTES + (RES ? WRES_I_BYTES : 0);
-  static constexpr int SMEM_BYTES = FIXED_BYTES + STAGES * WRES_A_BYTES + 1024;
+  static constexpr int SMEM_BYTES = FIXED_BYTES + STAGES * WRES_A_BYTES + WRES_OUT_BYTES + 1024;
 };
 
 template <int BN, int EPI, bool WRES = false>
-__global__ void __launch_bounds__(RnThreads<EPI>::N, 1)
+__global__ void __launch_bounds__(RnThreads<EPI, WRES>::N, 1)
 rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-               const __grid_constant__ CUtensorMap tmR, const RnGemmParams p) {
+               const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
+               const __grid_constant__ CUtensorMap tmO2, const RnGemmParams p) {
   using Cfg = RnCfg<BN>;
   using WC = WresCfg<EPI>;
   constexpr int STAGES = WRES ? (EPI == EPI_SINC ? WSINC_STAGES : WC::STAGES) : Cfg::STAGES;
   constexpr bool RESMMA = WRES && WC::RES;                  // residual added by an identity MMA
   constexpr int AFF_MAX = 512;                              // affine parameters cached in shared memory up to this N
-  constexpr int NUM_THREADS = RnThreads<EPI>::N;
+  constexpr int NUM_THREADS = RnThreads<EPI, WRES>::N;
   constexpr int EPI_WARPS = NUM_THREADS / 32 - 4;
   constexpr bool WCONV = WRES && EPI != EPI_SINC;           // 128-channel k = 3 layers, all of W resident
   constexpr bool WSINC = WRES && EPI == EPI_SINC;           // sinc layer, the W tile of ONE n-tile resident
@@ -155,15 +163,15 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         s_aff[i] = make_float4(p.s1[2 * i], p.h1[2 * i], p.s1[2 * i + 1], p.h1[2 * i + 1]);
   }
   if (RESMMA) {
-    // identity in the K-major 128B-swizzled operand layout: element (n, n) lives in K chunk n / 64 at
-    // byte n * 128 + (((n % 64) / 8) ^ (n & 7)) * 16 + (n % 8) * 2
+    // 64 x 64 identity in the K-major 128B-swizzled operand layout: element (n, n) at byte
+    // n * 128 + ((n / 8) ^ (n & 7)) * 16 + (n % 8) * 2
     const uint32_t i_smem = smem_base + WRES_W_BYTES;
     for (int i = threadIdx.x; i < WRES_I_BYTES / 16; i += NUM_THREADS)
       asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(i_smem + i * 16), "r"(0) : "memory");
     __syncthreads();
-    if (threadIdx.x < 128) {
+    if (threadIdx.x < 64) {
       const int n = threadIdx.x;
-      const uint32_t addr = i_smem + (n >> 6) * 16384 + n * 128 + ((((n & 63) >> 3) ^ (n & 7)) << 4) + (n & 7) * 2;
+      const uint32_t addr = i_smem + n * 128 + (((n >> 3) ^ (n & 7)) << 4) + (n & 7) * 2;
       asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(static_cast<unsigned short>(0x3c00)) : "memory");   // 1.0 (IEEE half)
     }
     fence_proxy_async();
@@ -348,9 +356,11 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(smem_u32(&full_bar[stage]), phase);
             tc_fence_after();
             const uint64_t adesc = umma_desc_sw128(smem_base + WC::FIXED_BYTES + stage * WRES_A_BYTES);
-            const uint64_t bdesc = umma_desc_sw128(smem_base + WRES_W_BYTES + kcx * 16384);
+            // channels 64 kcx .. 64 kcx + 63 of the residual land in the same accumulator columns: N = 64, D shifted
+            const uint64_t bdesc = umma_desc_sw128(smem_base + WRES_W_BYTES);
+            const uint32_t idesc64 = umma_idesc_f16(BLOCK_M, 64, 1, 1);
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+            for (int k = 0; k < BLOCK_K / 16; ++k) umma_bf16(d_tmem + kcx * 64, adesc + 2 * k, bdesc + 2 * k, idesc64, 1u);
             umma_commit(smem_u32(&empty_bar[stage]));
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
@@ -383,6 +393,9 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int ew = warp - 4;
     const int quad = ew & 3;   // TMEM lane quadrant of this warp
     const int half = ew >> 2;  // column half of the tile (sinc: column group of the warp)
+    // W-resident variants: this warp's 4 KB staging box behind the stage ring
+    const uint32_t out_box = smem_base + (WSINC ? WSINC_W_BYTES + STAGES * A_STAGE_BYTES : WC::FIXED_BYTES + STAGES * WRES_A_BYTES) +
+                             ew * 4096;
     int it = 0;
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
       const int m0 = tile_m(tile) * BLOCK_M;
@@ -405,6 +418,80 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         // the tile's 192 columns are 4 pieces of 48 = 16 filters x 3 pooling phases; a warp owns 4 / (EPI_WARPS / 4) of them
         constexpr int PPW = 16 / EPI_WARPS;
+        if (WSINC) {
+          // 8 warps: 32 rows x 32 filters per warp and output, staged as 64-byte rows (64B swizzle) and stored by TMA
+          // through the (channel, jg, ml, utt) view; frames of the last, partial ml of an utterance go out directly
+          uint32_t xk[16], ak[16];
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            uint32_t ra[32];
+            uint32_t rb[16];
+            const uint32_t col = (half * 2 + h2) * 48;
+            tmem_ld32(tbase + col, ra);
+            tmem_ld16(tbase + col + 32, rb);
+            tmem_ld_wait();
+            if (h2 == 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+            }
+            const int f = (nt & 1) * 64 + (half * 2 + h2) * 16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float xv[2], av[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int j = 3 * (2 * i + e);
+                const float c0 = fabsf(__uint_as_float(j < 32 ? ra[j < 32 ? j : 0] : rb[j >= 32 ? j - 32 : 0]));
+                const float c1 = fabsf(__uint_as_float(j + 1 < 32 ? ra[j + 1 < 32 ? j + 1 : 0] : rb[j + 1 >= 32 ? j + 1 - 32 : 0]));
+                const float c2 = fabsf(__uint_as_float(j + 2 < 32 ? ra[j + 2 < 32 ? j + 2 : 0] : rb[j + 2 >= 32 ? j + 2 - 32 : 0]));
+                const float4 af = s_aff[f + 2 * i + e];
+                xv[e] = lrelu03(fmaf(fmaxf(c0, fmaxf(c1, c2)), af.x, af.y));
+                av[e] = lrelu03(fmaf(xv[e], af.z, af.w));
+              }
+              xk[h2 * 8 + i] = pack_f16x2(xv[0], xv[1]);
+              ak[h2 * 8 + i] = pack_f16x2(av[0], av[1]);
+            }
+          }
+          // the TMA box covers the rows of the warp's FIRST utterance with ml < T / 16 (the rest is clipped by the view's
+          // extents: a negative start coordinate for the next utterance's rows faults on store, measured); the last,
+          // partial ml of an utterance and a warp's rows in the next utterance are stored directly
+          const int ml_full = p.T >> 4;
+          const int utt_w = __shfl_sync(0xffffffffu, utt, 0);
+          if (valid && (ml >= ml_full || utt != utt_w)) {
+            const int f = (nt & 1) * 64 + half * 32;
+            uint4* dx = reinterpret_cast<uint4*>(p.out + orow * p.out_ld + f);
+            uint4* da = reinterpret_cast<uint4*>(p.out2 + orow * p.out2_ld + f);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              dx[i] = make_uint4(xk[4 * i], xk[4 * i + 1], xk[4 * i + 2], xk[4 * i + 3]);
+              da[i] = make_uint4(ak[4 * i], ak[4 * i + 1], ak[4 * i + 2], ak[4 * i + 3]);
+            }
+          }
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+          const uint32_t xrow = out_box + lane * 64, arow = xrow + 2048;
+          const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(xrow + ((j ^ sw) << 4)), "r"(xk[4 * j]),
+                         "r"(xk[4 * j + 1]), "r"(xk[4 * j + 2]), "r"(xk[4 * j + 3]) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(arow + ((j ^ sw) << 4)), "r"(ak[4 * j]),
+                         "r"(ak[4 * j + 1]), "r"(ak[4 * j + 2]), "r"(ak[4 * j + 3]) : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            const long long rw0 = static_cast<long long>(m0) + quad * 32;
+            const int utt0 = static_cast<int>(rw0 / p.Mu);
+            const int ml0 = static_cast<int>(rw0 - static_cast<long long>(utt0) * p.Mu);
+            const int c0 = (nt & 1) * 64 + half * 32;
+            tma_store_4d(&tmO, out_box, c0, jg, ml0, utt0);
+            tma_store_4d(&tmO2, out_box + 2048, c0, jg, ml0, utt0);
+            bulk_commit();
+          }
+          continue;
+        }
 #pragma unroll
         for (int h2 = 0; h2 < PPW; ++h2) {
           const int piece = half * PPW + h2;
@@ -525,6 +612,45 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
         };
+        if (WCONV) {
+          // 64 columns of this thread's row into registers, TMEM handed back, affine + LeakyReLU (conv1) or nothing
+          // (conv2: the identity MMA already added the residual), packed into the warp's 32 x 64 box (128-byte rows,
+          // 128B swizzle) and stored by TMA.  Padding rows are written as zeros, rows beyond M are clipped by the map.
+          uint32_t r0[32], r1[32];
+          tmem_ld32(tbase + half * 64, r0);
+          tmem_ld32(tbase + half * 64 + 32, r1);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          uint32_t pk[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float v0 = __uint_as_float(i < 16 ? r0[2 * (i & 15)] : r1[2 * (i & 15)]);
+            float v1 = __uint_as_float(i < 16 ? r0[2 * (i & 15) + 1] : r1[2 * (i & 15) + 1]);
+            if (EPI == EPI_AFF_LRELU) {
+              const float4 af = s_aff[half * 32 + i];
+              v0 = lrelu03(fmaf(v0, af.x, af.y));
+              v1 = lrelu03(fmaf(v1, af.z, af.w));
+            }
+            pk[i] = valid ? pack_f16x2(v0, v1) : 0u;
+          }
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+          const uint32_t my_row = out_box + lane * 128;
+          const uint32_t sw = lane & 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(pk[4 * j]),
+                         "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3]) : "memory");
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmO, out_box, half * 64, m0 + quad * 32);
+            bulk_commit();
+          }
+          continue;
+        }
         if (BN == 128) {
           // both chunks into registers, TMEM buffer handed back, then the arithmetic and the stores
           uint32_t r0[32], r1[32];
@@ -552,6 +678,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
     }
+    if (WRES && lane == 0) bulk_wait<0>();       // the last TMA stores read shared memory of this CTA
   }
 
   tc_fence_before();
@@ -561,8 +688,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
 // ------------------------------------------------------------------ host side
 template <int BN, int EPI, bool WRES = false>
-static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& r, const RnGemmParams& p,
-                       cudaStream_t stream) {
+static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& r, const CUtensorMap& o,
+                       const CUtensorMap& o2, const RnGemmParams& p, cudaStream_t stream) {
   using Cfg = RnCfg<BN>;
   constexpr int SMEM = WRES ? (EPI == EPI_SINC ? WSINC_SMEM_BYTES : WresCfg<EPI>::SMEM_BYTES) : Cfg::SMEM_BYTES;
   static bool attr_set = false;
@@ -572,7 +699,7 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  rn_gemm_kernel<BN, EPI, WRES><<<grid, RnThreads<EPI>::N, SMEM, stream>>>(a, w, r, p);
+  rn_gemm_kernel<BN, EPI, WRES><<<grid, RnThreads<EPI, WRES>::N, SMEM, stream>>>(a, w, r, o, o2, p);
   count_launch();
   SVB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -588,9 +715,15 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
     SVB_CHECK(p.N % 192 == 0, "sinc GEMM: N must be a multiple of 192");
     if (make_map(&mw, w, w_rows, w_cols, w_cols, 192)) return -1;
     static const bool wsinc_on = [] { const char* e = getenv("SVB_RN_WSINC"); return e == nullptr || e[0] != '0'; }();
-    if (wsinc_on && p.num_pass == 1 && p.num_taps == 1 && p.kc_per_tap == WSINC_KB)
-      return launch_rn_t<192, EPI_SINC, true>(ma, mw, ma, p, stream);
-    return launch_rn_t<192, EPI_SINC>(ma, mw, ma, p, stream);
+    if (wsinc_on && p.num_pass == 1 && p.num_taps == 1 && p.kc_per_tap == WSINC_KB && p.out_planes == 1 &&
+        p.out2_planes == 1 && p.T >= 16) {
+      // store views (channel, jg, ml, utt) of the two outputs, from row 1 (frame 0) of utterance 0
+      CUtensorMap mo, mo2;
+      if (make_map_sinc_out(&mo, p.out + p.out_ld, 128, p.out_ld, p.T / 16, p.Tp, p.B)) return -1;
+      if (make_map_sinc_out(&mo2, p.out2 + p.out2_ld, 128, p.out2_ld, p.T / 16, p.Tp, p.B)) return -1;
+      return launch_rn_t<192, EPI_SINC, true>(ma, mw, ma, mo, mo2, p, stream);
+    }
+    return launch_rn_t<192, EPI_SINC>(ma, mw, ma, ma, ma, p, stream);
   }
   SVB_CHECK(p.N % 128 == 0, "RawNet conv GEMM: N must be a multiple of 128");
   const int bn = (p.N % 256 == 0) ? 256 : 128;
@@ -599,21 +732,22 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   static const bool wres_on = [] { const char* e = getenv("SVB_RN_WRES"); return e == nullptr || e[0] != '0'; }();
   if (wres_on && p.N == 128 && p.num_taps == 3 && p.kc_per_tap == 2 && p.num_pass == 1 && p.w_planes == 1 &&
       p.tap_off[0] == -1 && p.tap_off[1] == 0 && p.tap_off[2] == 1 &&
-      (epi == EPI_AFF_LRELU || (epi == EPI_ADD && p.add_planes == 1 && p.add_ld == 128))) {
-    CUtensorMap ma136, mr;
+      p.out_planes == 1 && (epi == EPI_AFF_LRELU || (epi == EPI_ADD && p.add_planes == 1 && p.add_ld == 128))) {
+    CUtensorMap ma136, mr, mo;
     if (make_map(&ma136, a, a_rows, a_cols, a_ld, WRES_A_ROWS)) return -1;
-    if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, ma136, p, stream);
+    if (make_map(&mo, p.out, p.M, 128, p.out_ld, 32)) return -1;              // store boxes: 32 rows x 64 channels
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, ma136, mo, mo, p, stream);
     if (make_map(&mr, p.add, a_rows, 128, p.add_ld, BLOCK_M)) return -1;      // the shortcut has the rows of the output
-    return launch_rn_t<128, EPI_ADD, true>(ma136, mw, mr, p, stream);
+    return launch_rn_t<128, EPI_ADD, true>(ma136, mw, mr, mo, mo, p, stream);
   }
   if (bn == 256) {
-    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, p, stream);
-    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, p, stream);
-    return launch_rn_t<256, EPI_PLAIN>(ma, mw, ma, p, stream);
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, ma, ma, p, stream);
+    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, ma, ma, p, stream);
+    return launch_rn_t<256, EPI_PLAIN>(ma, mw, ma, ma, ma, p, stream);
   }
-  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, ma, p, stream);
-  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, ma, p, stream);
-  return launch_rn_t<128, EPI_PLAIN>(ma, mw, ma, p, stream);
+  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, ma, ma, ma, p, stream);
+  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, ma, ma, ma, p, stream);
+  return launch_rn_t<128, EPI_PLAIN>(ma, mw, ma, ma, ma, p, stream);
 }
 
 }  // namespace svb

@@ -112,6 +112,8 @@ int absmax_host(const float* x, long long n, float* result_host);   // synchrono
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 
 int make_map_sw64(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
+int make_map_sinc_out(CUtensorMap* m, const void* base, int channels, long long ld, int ml_extent, long long rows_per_utt,
+                      int utts);
 int make_map_f32(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_rows);
 // Plain fp32-output GEMM out[M, N] = A * W^T through the TMA-store epilogue of gemm_pw.cu (N % 64 == 0).
 int launch_gemm_f32(const GemmOperands& ops, const GemmParams& p, cudaStream_t stream);
