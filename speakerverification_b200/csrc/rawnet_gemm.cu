@@ -49,7 +49,8 @@ struct RnCfg {
   static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = (BN >= 192) ? 4 : 6;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
+  static constexpr int OUT_BYTES = 8 * 2048;                      // one 32-row x 32-column store box per epilogue warp
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024;
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;   // power of two
 };
 
@@ -393,9 +394,30 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int ew = warp - 4;
     const int quad = ew & 3;   // TMEM lane quadrant of this warp
     const int half = ew >> 2;  // column half of the tile (sinc: column group of the warp)
-    // W-resident variants: this warp's 4 KB staging box behind the stage ring
-    const uint32_t out_box = smem_base + (WSINC ? WSINC_W_BYTES + STAGES * A_STAGE_BYTES : WC::FIXED_BYTES + STAGES * WRES_A_BYTES) +
-                             ew * 4096;
+    // this warp's staging box behind the stage ring: 4 KB in the W-resident variants, 2 KB (32 rows x 32 columns, 64B
+    // swizzle) in the generic ones
+    const uint32_t out_box = WRES ? smem_base + (WSINC ? WSINC_W_BYTES + STAGES * A_STAGE_BYTES : WC::FIXED_BYTES + STAGES * WRES_A_BYTES) + ew * 4096
+                                  : smem_base + STAGES * Cfg::STAGE_BYTES + (ew & 7) * 2048;
+    // generic instances, 16-bit mode: 32 columns of this thread's row -> the warp's box -> one TMA store (all lanes call)
+    auto tma_chunk = [&](int gcol, int grow, const float (&v)[32]) {
+      uint32_t pk[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) pk[i] = pack_f16x2(v[2 * i], v[2 * i + 1]);
+      if (lane == 0) bulk_wait_read<0>();
+      __syncwarp();
+      const uint32_t my_row = out_box + lane * 64;
+      const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(pk[4 * j]),
+                     "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3]) : "memory");
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(&tmO, out_box, gcol, grow);
+        bulk_commit();
+      }
+    };
     int it = 0;
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
       const int m0 = tile_m(tile) * BLOCK_M;
@@ -552,7 +574,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tmem_ld32(tbase + col0, r);
             tmem_ld_wait();
             const int n = n0 + col0;
-            if (n >= p.N || !valid) continue;
+            if (n >= p.N || (!valid && !p.tma_out)) continue;
             float v[32];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -576,7 +598,15 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
               }
             }
-            store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+            if (p.tma_out) {                    // single plane; padding rows are written as zeros
+              if (!valid) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+              }
+              tma_chunk(n, m0 + quad * 32, v);
+            } else {
+              store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+            }
           }
           tc_fence_before();
           __syncwarp();
@@ -589,7 +619,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // residual the identity MMA already added), packed and stored
         auto emit = [&](int col0, const uint32_t (&r)[32]) {
           const int n = n0 + col0;
-          if (n >= p.N || !in_m) return;
+          if (n >= p.N || (!in_m && !p.tma_out)) return;
           float v[32];
           if (EPI == EPI_AFF_LRELU) {
             // zero rows stay zero: they are the next conv's padding
@@ -606,11 +636,12 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 v[i] = valid ? lrelu03(fmaf(__uint_as_float(r[i]), __ldg(p.s1 + n + i), __ldg(p.h1 + n + i))) : 0.f;
             }
           } else {
-            if (!valid) return;
+            if (!valid && !p.tma_out) return;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+            for (int i = 0; i < 32; ++i) v[i] = valid ? __uint_as_float(r[i]) : 0.f;
           }
-          store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
+          if (p.tma_out) tma_chunk(n, m0 + quad * 32, v);
+          else store_planes<32>(p.out + row * p.out_ld + n, p.out_planes, p.out_plane_cols, v);
         };
         if (WCONV) {
           // 64 columns of this thread's row into registers, TMEM handed back, affine + LeakyReLU (conv1) or nothing
@@ -678,7 +709,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
     }
-    if (WRES && lane == 0) bulk_wait<0>();       // the last TMA stores read shared memory of this CTA
+    if (lane == 0) bulk_wait<0>();               // the last TMA stores read shared memory of this CTA
   }
 
   tc_fence_before();
@@ -740,14 +771,20 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
     if (make_map(&mr, p.add, a_rows, 128, p.add_ld, BLOCK_M)) return -1;      // the shortcut has the rows of the output
     return launch_rn_t<128, EPI_ADD, true>(ma136, mw, mr, mo, mo, p, stream);
   }
+  // generic mainloop; in the 16-bit mode (one output plane) the tile leaves through 32 x 32 TMA store boxes
+  static const bool tma_on = [] { const char* e = getenv("SVB_RN_TMA_OUT"); return e == nullptr || e[0] != '0'; }();
+  RnGemmParams q = p;
+  CUtensorMap mo = ma;
+  q.tma_out = (tma_on && p.out_planes == 1) ? 1 : 0;
+  if (q.tma_out && make_map_sw64(&mo, p.out, p.M, p.N, p.out_ld, 32)) return -1;
   if (bn == 256) {
-    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, ma, ma, p, stream);
-    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, ma, ma, p, stream);
-    return launch_rn_t<256, EPI_PLAIN>(ma, mw, ma, ma, ma, p, stream);
+    if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, mo, mo, q, stream);
+    if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, mo, mo, q, stream);
+    return launch_rn_t<256, EPI_PLAIN>(ma, mw, ma, mo, mo, q, stream);
   }
-  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, ma, ma, ma, p, stream);
-  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, ma, ma, ma, p, stream);
-  return launch_rn_t<128, EPI_PLAIN>(ma, mw, ma, ma, ma, p, stream);
+  if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU>(ma, mw, ma, mo, mo, q, stream);
+  if (epi == EPI_ADD) return launch_rn_t<128, EPI_ADD>(ma, mw, ma, mo, mo, q, stream);
+  return launch_rn_t<128, EPI_PLAIN>(ma, mw, ma, mo, mo, q, stream);
 }
 
 }  // namespace svb
