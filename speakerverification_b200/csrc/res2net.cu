@@ -318,7 +318,14 @@ res2net_chain_kernel(const __grid_constant__ ChainMaps tm, const ChainParams p) 
 // while the previous step's epilogue runs.
 static constexpr int RS_ROWS = 400;                 // strip rows in smem: 4 guard + 384 window + 4 guard + 8 pad
 static constexpr int RS_PLANE = RS_ROWS * 128;      // bytes per 64-channel K chunk plane
-static constexpr int RS_PITCH = 80;                 // staging tile row pitch (64 data bytes + 16: conflict-free row writes)
+// staging tile: 64-byte rows, 16-byte chunk c of row r at ((c ^ ((r >> 1) & 3)) << 4): conflict-free both for the
+// thread-per-row accesses and for the coalesced ones (4 lanes per row, 2 rows per quarter warp).  (An 80-byte pitch
+// without swizzle made every coalesced access a 2-way conflict: ncu r02, 18 % of the kernel's shared wavefronts, in a
+// kernel whose busiest unit is the LSU data pipe at 72 %.)
+static constexpr int RS_PITCH = 64;
+__device__ __forceinline__ uint32_t rs_addr(uint32_t stg, int row, int chunk) {
+  return stg + row * RS_PITCH + ((chunk ^ ((row >> 1) & 3)) << 4);
+}
 static constexpr int RS_BOX = 200;                  // TMA box rows for the step-1 strip load (2 boxes per plane)
 
 struct alignas(64) ChainMapsS {
@@ -529,13 +536,13 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
               // transpose the x tile: coalesced registers -> staging -> own row
 #pragma unroll
               for (int i = 0; i < 4; ++i)
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + (8 * i + crow) * RS_PITCH + cchk * 16),
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rs_addr(stg, 8 * i + crow, cchk)),
                              "r"(xc[i].x), "r"(xc[i].y), "r"(xc[i].z), "r"(xc[i].w) : "memory");
               __syncwarp();
 #pragma unroll
               for (int i = 0; i < 4; ++i)
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(xrow[i].x), "=r"(xrow[i].y), "=r"(xrow[i].z),
-                             "=r"(xrow[i].w) : "r"(stg + lane * RS_PITCH + i * 16) : "memory");
+                             "=r"(xrow[i].w) : "r"(rs_addr(stg, lane, i)) : "memory");
               __syncwarp();
               const int gn = (g + 1 < NG) ? g + 1 : 0, mn = (g + 1 < NG) ? mt : mt + 1;
               if (mn < RC_MT) load_x(mn, gn, j, xc);
@@ -560,7 +567,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
             // y_j -> R: own row into staging, then coalesced stores of the segment's output rows
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + lane * RS_PITCH + i * 16), "r"(pk[4 * i]),
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rs_addr(stg, lane, i)), "r"(pk[4 * i]),
                            "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
             __syncwarp();
             bf16* rbase = rbase0 + (mt * 128 * p.r_ld + j * CS + g * 32);
@@ -570,7 +577,7 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
               if ((m_out[mt] >> rr) & 1u) {
                 uint4 o;
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
-                             : "r"(stg + rr * RS_PITCH + cchk * 16) : "memory");
+                             : "r"(rs_addr(stg, rr, cchk)) : "memory");
                 *reinterpret_cast<uint4*>(rbase + 8 * i * p.r_ld) = o;
               }
             }
