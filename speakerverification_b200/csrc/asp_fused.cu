@@ -321,10 +321,9 @@ template <bool SPLIT, bool FIXMAX>
 static int launch_asp(const CUtensorMap& ma, const CUtensorMap& my, const CUtensorMap& mw, const AspParams& p,
                       cudaStream_t stream) {
   using Cfg = AspCfg<SPLIT>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(asp_fused_kernel<SPLIT, FIXMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
   }
   const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
   asp_fused_kernel<SPLIT, FIXMAX><<<grid, ASP_THREADS, Cfg::SMEM_BYTES, stream>>>(ma, my, mw, p);

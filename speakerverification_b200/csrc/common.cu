@@ -29,6 +29,16 @@ int num_sms() {
   return n;
 }
 
+// Kernel attributes (cudaFuncSetAttribute) and device allocations belong to ONE device: code that does something "once"
+// asks per device ordinal, so that a process that drives several GPUs (one engine per device) works on all of them.
+bool first_on_device(unsigned long long* seen) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (__atomic_fetch_or(seen, bit, __ATOMIC_ACQ_REL) & bit) return false;
+  return true;
+}
+
 int count_launch(int n) {
   g_launches += n;
   return 0;

@@ -465,12 +465,11 @@ int fbank_forward(const Fbank* f, const float* wav, const void* utt_tab, const i
                   const float* in_w, const float* in_b, float in_eps, float* in_scale_ws) {
   SVB_CHECK(mode == 1 || plane_cols >= f->n_mels, "plane_cols must be >= n_mels");
   const size_t smem = fbank_smem_bytes(f);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(fbank_logmel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      static_cast<int>(smem)));
     SVB_CUDA_OK(cudaFuncSetAttribute(fbank_logmel_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    attr_set = true;
   }
   fbank_logmel_kernel<<<ntiles, FB_WARPS * 32, smem, stream>>>(
       wav, static_cast<const UttDesc*>(utt_tab), reinterpret_cast<const int2*>(tile_tab), f->d_tab, f->hop,

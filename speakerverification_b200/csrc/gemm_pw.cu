@@ -566,11 +566,10 @@ template <int BN, int ACT, bool RBT, bool HILO, int EW = 8, int STATS = 0, bool 
 static int launch_pw_t(const CUtensorMap& a, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& o,
                        const PwParams& p, cudaStream_t stream) {
   using Cfg = PwCfg<BN, EW, TWO>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(gemm_pw_kernel<BN, ACT, RBT, HILO, EW, STATS, MC, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::SMEM_BYTES));
-    attr_set = true;
   }
   const int m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M, n_tiles = (p.N + BN - 1) / BN;
   if (MC) {

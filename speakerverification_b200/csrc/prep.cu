@@ -176,15 +176,19 @@ __global__ void row_meta_kernel(const long long* __restrict__ row0, int B, int h
 
 namespace {
 struct MetaSlot { long long* host = nullptr; long long* dev = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; bool used = false; };
-MetaSlot g_meta_ring[4];
-int g_meta_pos = 0;
+constexpr int META_DEVS = 16;
+MetaSlot g_meta_ring[META_DEVS][4];        // per device: the staging buffers and the event live on one GPU
+int g_meta_pos[META_DEVS] = {};
 }  // namespace
 
 int build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row_meta, long long total_rows,
                    cudaStream_t stream) {
   SVB_CHECK(B > 0 && halo >= 0, "bad row_meta arguments");
-  MetaSlot& sl = g_meta_ring[g_meta_pos];
-  g_meta_pos = (g_meta_pos + 1) & 3;
+  int dev = 0;
+  SVB_CUDA_OK(cudaGetDevice(&dev));
+  SVB_CHECK(dev >= 0 && dev < META_DEVS, "device ordinal %d out of range", dev);
+  MetaSlot& sl = g_meta_ring[dev][g_meta_pos[dev]];
+  g_meta_pos[dev] = (g_meta_pos[dev] + 1) & 3;
   if (sl.used) SVB_CUDA_OK(cudaEventSynchronize(sl.done));     // its upload of 4 calls ago has executed
   const size_t need = static_cast<size_t>(B) + 1;
   if (sl.cap < need) {

@@ -876,10 +876,9 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     // ---- attentive heads (RawNet2_custom.py:200-224): one CTA per utterance on the 29 pre-activated frames
     const int att = e->aggregate == AGG_ASP ? e->att : 1;
     const size_t smem = (static_cast<size_t>(Tg) * AGG_C + static_cast<size_t>(Tg) * att + 32 + 4096) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+    if (first_on_device(&attr_devs)) {
       SVB_CUDA_OK(cudaFuncSetAttribute(rn_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_set = true;
     }
     SVB_CHECK(smem <= 200 * 1024, "attentive head: %zu bytes of shared memory", smem);
     float* dst = l2norm ? hs : emb;                       // hs ([B, H] fp32, H >= n_out rows' worth) as the un-normalised buffer

@@ -723,10 +723,9 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
                        const CUtensorMap& o2, const RnGemmParams& p, cudaStream_t stream) {
   using Cfg = RnCfg<BN>;
   constexpr int SMEM = WRES ? (EPI == EPI_SINC ? WSINC_SMEM_BYTES : WresCfg<EPI>::SMEM_BYTES) : Cfg::SMEM_BYTES;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_set = true;
   }
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();

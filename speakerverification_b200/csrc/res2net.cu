@@ -649,10 +649,9 @@ res2net_chain_smem_kernel(const __grid_constant__ ChainMapsS tm, const ChainPara
 template <int CS>
 static int launch_chain_smem(const ChainMapsS& tm, const ChainParams& p, cudaStream_t stream) {
   constexpr int SMEM = (CS / 64) * RS_PLANE + 3 * (CS / 64) * CS * 128 + 8 * 32 * RS_PITCH + 2 * 3 * CS * 4 + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(res2net_chain_smem_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_set = true;
   }
   const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
   res2net_chain_smem_kernel<CS><<<grid, RC_THREADS, SMEM, stream>>>(tm, p);
@@ -670,10 +669,9 @@ int res2net_seg_frames() { return RC_SEG; }
 template <int CS, bool SPLIT>
 static int launch_chain(const ChainMaps& tm, const ChainParams& p, cudaStream_t stream) {
   constexpr int SMEM = RC_STAGES * (3 * RC_A_BYTES + 16384) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(res2net_chain_kernel<CS, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_set = true;
   }
   const int grid = p.n_items < num_sms() ? p.n_items : num_sms();
   res2net_chain_kernel<CS, SPLIT><<<grid, RC_THREADS, SMEM, stream>>>(tm, p);

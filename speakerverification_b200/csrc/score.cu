@@ -1388,11 +1388,10 @@ int asnorm_stats(const float* emean, int U, const float* cohort, int N, int D, i
   }
   const bool smem_rows = Np <= TOPK_SMEM_MAX_N;   // the launch asks for Np * 4 bytes (N rounded up to 64)
   if (smem_rows) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+    if (first_on_device(&attr_devs)) {
       SVB_CUDA_OK(cudaFuncSetAttribute(topk_stats_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        TOPK_SMEM_MAX_N * 4));
-      attr_set = true;
     }
   }
   for (int u0 = 0; u0 < U; u0 += chunk) {

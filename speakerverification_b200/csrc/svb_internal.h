@@ -31,6 +31,7 @@ void set_error(const char* fmt, ...);
   } while (0)
 
 int num_sms();
+bool first_on_device(unsigned long long* seen);   // true once per device ordinal (per-device kernel attributes)
 int count_launch(int n = 1);  // running count of kernel launches (reported by bench.py)
 
 // ------------------------------------------------------------------ rows

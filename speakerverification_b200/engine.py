@@ -43,18 +43,31 @@ class Frontend:
         self.fb = fb if fb is not None else slaney_mel_filterbank(
             n_fft // 2 + 1, float(fmin), float(fmax) if fmax else sr / 2.0, n_mels, sr)
         self.preemph = float(coef) if pre_emphasis else 0.0
-        w = np.ascontiguousarray(self.window.numpy(), dtype=np.float32)
-        f = np.ascontiguousarray(self.fb.cpu().numpy(), dtype=np.float32)
-        h = _vp()
-        nv.check(nv.lib().svb_fbank_create(w.ctypes.data_as(_vp), win_length, hop_length, n_fft,
-                                           f.ctypes.data_as(_vp), n_fft // 2 + 1, n_mels, self.preemph, 1e-6,
-                                           ctypes.byref(h)))
-        self.handle = h
+        self._win_np = np.ascontiguousarray(self.window.numpy(), dtype=np.float32)
+        self._fb_np = np.ascontiguousarray(self.fb.cpu().numpy(), dtype=np.float32)
+        self._handles = {}                   # device ordinal -> SvbFbank* (its tables live on that GPU)
+        _ = self.handle                      # fail early (bad geometry) on the device that is current now
+
+    @property
+    def handle(self):
+        """The SvbFbank handle of the CURRENT device: engines read it inside their own device context, so one
+        Frontend serves engines on several GPUs of one process."""
+        dev = torch.cuda.current_device()
+        h = self._handles.get(dev)
+        if h is None:
+            h = _vp()
+            nv.check(nv.lib().svb_fbank_create(self._win_np.ctypes.data_as(_vp), self.win_length, self.hop, self.n_fft,
+                                               self._fb_np.ctypes.data_as(_vp), self.n_fft // 2 + 1, self.n_mels,
+                                               self.preemph, 1e-6, ctypes.byref(h)))
+            self._handles[dev] = h
+        return h
 
     def __del__(self):
-        if getattr(self, "handle", None) and nv is not None and getattr(nv, "_lib", None) is not None:   # nv is None at interpreter shutdown
-            nv._lib.svb_fbank_destroy(self.handle)
-            self.handle = None
+        if nv is None or getattr(nv, "_lib", None) is None:          # interpreter shutdown
+            return
+        for h in getattr(self, "_handles", {}).values():
+            nv._lib.svb_fbank_destroy(h)
+        self._handles = {}
 
 
 class BatchPlan:
