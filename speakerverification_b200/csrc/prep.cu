@@ -1,5 +1,6 @@
 // Operand preparation kernels: fp32 -> bf16 hi/lo planes, Conv1d weight packing, BN folding,
 // and the row bookkeeping table of the time-major-with-halos layout.
+#include <mutex>
 #include <cuda_fp16.h>
 #include <string.h>
 
@@ -179,11 +180,13 @@ struct MetaSlot { long long* host = nullptr; long long* dev = nullptr; size_t ca
 constexpr int META_DEVS = 16;
 MetaSlot g_meta_ring[META_DEVS][4];        // per device: the staging buffers and the event live on one GPU
 int g_meta_pos[META_DEVS] = {};
+std::mutex g_meta_mutex;                 // the ring is shared by every host thread of the process
 }  // namespace
 
 int build_row_meta(const int32_t* frames_host, int B, int halo, int32_t* row_meta, long long total_rows,
                    cudaStream_t stream) {
   SVB_CHECK(B > 0 && halo >= 0, "bad row_meta arguments");
+  std::lock_guard<std::mutex> lock(g_meta_mutex);
   int dev = 0;
   SVB_CUDA_OK(cudaGetDevice(&dev));
   SVB_CHECK(dev >= 0 && dev < META_DEVS, "device ordinal %d out of range", dev);
