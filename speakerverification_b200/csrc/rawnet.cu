@@ -31,6 +31,7 @@ int split_bf16(const float*, long long, int, int, bf16*, int, int, int, cudaStre
 int l2norm_rows(const float*, int, float*, int, int, int, float, cudaStream_t);
 int launch_rn_gemm(int, const bf16*, long long, long long, long long, const bf16*, int, int, const RnGemmParams&,
                    cudaStream_t);
+bool rn_conv2_pool_supported(int channels, int planes, int xplanes, int T);
 enum { EPI_SINC = 0, EPI_AFF_LRELU = 1, EPI_ADD = 2, EPI_PLAIN = 3 };
 
 static constexpr int SINC_STRIDE = 48;     // samples per GEMM row (= 16 pooled outputs)
@@ -148,36 +149,45 @@ rn_pool_kernel(const bf16* __restrict__ z, int z_ld, int planes, int plane_cols,
   const int g = tid % cg, tl = tid / cg, tstep = 256 / cg;
   const int t0 = chunk * frames_per_chunk, t1 = min(Tout, t0 + frames_per_chunk);
   float sum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (int tb = t0 + tl; tb < t1; tb += 2 * tstep) {
-    // two output frames per iteration: all (up to six) loads are issued before the first decode
+  // six row loads are issued before the first decode: two output frames x three pooled rows, or (pool == 1: sums only)
+  // six frames
+  const int per = pool == 3 ? 2 : 6;
+  for (int tb = t0 + tl; tb < t1; tb += per * tstep) {
     Raw8 raw[2][3];
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-      const int t = min(tb + k * tstep, t1 - 1);
-      const long long r = static_cast<long long>(utt) * (Tin + 2) + 1 + static_cast<long long>(t) * pool;
-      raw[k][0] = ldraw8(z + r * z_ld + g * 8, planes, plane_cols);
-      if (pool == 3) {
-        raw[k][1] = ldraw8(z + (r + 1) * z_ld + g * 8, planes, plane_cols);
-        raw[k][2] = ldraw8(z + (r + 2) * z_ld + g * 8, planes, plane_cols);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int t = min(tb + (pool == 3 ? k : 3 * k + j) * tstep, t1 - 1);
+        const long long r = static_cast<long long>(utt) * (Tin + 2) + 1 + (pool == 3 ? static_cast<long long>(t) * 3 + j : t);
+        raw[k][j] = ldraw8(z + r * z_ld + g * 8, planes, plane_cols);
       }
     }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-      const int t = tb + k * tstep;
-      if (t >= t1) break;
-      float v[8];
-      decode8(raw[k][0], planes, v);
       if (pool == 3) {
-        float a[8], b[8];
+        const int t = tb + k * tstep;
+        if (t >= t1) break;
+        float v[8], a[8], b[8];
+        decode8(raw[k][0], planes, v);
         decode8(raw[k][1], planes, a);
         decode8(raw[k][2], planes, b);
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], fmaxf(a[i], b[i]));
         const long long ro = static_cast<long long>(utt) * (Tout + 2) + 1 + t;
         store8(zp + ro * zp_ld + g * 8, planes, zp_plane_cols, v);
-      }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) sum[i] += v[i];
+        for (int i = 0; i < 8; ++i) sum[i] += v[i];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          if (tb + (3 * k + j) * tstep >= t1) break;
+          float v[8];
+          decode8(raw[k][j], planes, v);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) sum[i] += v[i];
+        }
+      }
     }
   }
 #pragma unroll
@@ -769,13 +779,15 @@ int rawnet2_frames(const Rawnet2* e, int level) { return (level >= 0 && level <=
 
 // ------------------------------------------------------------------ forward
 static int conv_gemm(const Rawnet2* e, int epi, const bf16* a, int B, int T, int cin, const bf16* w, int cout, int k,
-                     const float* s, const float* h, const bf16* add, bf16* out, int out_planes, cudaStream_t st) {
+                     const float* s, const float* h, const bf16* add, bf16* out, int out_planes, cudaStream_t st,
+                     int pool_tout = 0) {
   RnGemmParams g{};
   const int P = e->planes;   // operand planes (a / h and the packed weights)
   g.M = B * (T + 2); g.N = cout; g.kc_per_tap = cin / 64; g.num_taps = k;
   g.tap_off[0] = k == 3 ? -1 : 0; g.tap_off[1] = 0; g.tap_off[2] = 1;
   g.num_pass = P == 2 ? 3 : 1; g.a_plane_cols = cin; g.w_planes = P;
-  g.T = T; g.Tp = T + 2; g.s1 = s; g.h1 = h;
+  g.T = T; g.Tp = T + 2; g.s1 = s; g.h1 = h; g.B = B;
+  if (pool_tout > 0) { g.pool3 = 1; g.Tout = pool_tout; }   // `out` is the pooled tensor [B][pool_tout + 2][cout]
   g.add = add; g.add_ld = e->xplanes * cout; g.add_planes = e->xplanes; g.add_plane_cols = cout;
   g.out = out; g.out_ld = out_planes * cout; g.out_planes = out_planes; g.out_plane_cols = cout;
   return launch_rn_gemm(epi, a, g.M, static_cast<long long>(P) * cin, static_cast<long long>(P) * cin, w, cout,
@@ -843,11 +855,18 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
       if (conv_gemm(e, EPI_PLAIN, a_in, B, Tin, k.cin, k.wsc, k.cout, 1, nullptr, nullptr, nullptr, scb, PX, st)) return -1;
       shortcut = scb;
     }
-    if (conv_gemm(e, EPI_ADD, hb, B, Tin, k.cout, k.w2, k.cout, 3, nullptr, nullptr, shortcut, zb, PX, st)) return -1;
     const int pool = k.down ? 3 : 1;
     const int nchunk = pool_chunks(Tout);
-    {
-      const int cg = k.cout / 8, tstep = 256 / cg;
+    const int cg = k.cout / 8, tstep = 256 / cg;
+    if (k.down && k.wsc == nullptr && rn_conv2_pool_supported(k.cout, P, PX, Tin)) {
+      // layer 1 in the 16-bit mode: conv2 pools its own output (z, 5.4 MB per utterance, is never written) and a
+      // sums-only pass over the pooled tensor (a third of z) feeds the AFMS gate
+      if (conv_gemm(e, EPI_ADD, hb, B, Tin, k.cout, k.w2, k.cout, 3, nullptr, nullptr, shortcut, zpb, PX, st, Tout)) return -1;
+      rn_pool_kernel<<<dim3(nchunk, B), 256, static_cast<size_t>(tstep) * k.cout * 4, st>>>(
+          zpb, PX * k.cout, PX, k.cout, Tout, 1, nullptr, PX * k.cout, k.cout, Tout, k.cout, 256, psum);
+      count_launch();
+    } else {
+      if (conv_gemm(e, EPI_ADD, hb, B, Tin, k.cout, k.w2, k.cout, 3, nullptr, nullptr, shortcut, zb, PX, st)) return -1;
       rn_pool_kernel<<<dim3(nchunk, B), 256, static_cast<size_t>(tstep) * k.cout * 4, st>>>(
           zb, PX * k.cout, PX, k.cout, Tin, pool, zpb, PX * k.cout, k.cout, Tout, k.cout, 256, psum);
       count_launch();

@@ -54,6 +54,12 @@ struct RnCfg {
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;   // power of two
 };
 
+// max of two packed IEEE halves (same result as decoding, fmaxf and re-encoding)
+__device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
 __device__ __forceinline__ float lrelu03(float x) { return fmaxf(x, 0.3f * x); }   // slope < 1: max picks the right branch
 
 // 32 lanes x 16 consecutive fp32 columns
@@ -178,7 +184,12 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_proxy_async();
   }
 
-  const int num_m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  // pool3 (W-resident conv2 with the max-pool fused in): rows per utterance are a multiple of 3 and row 0 is padding, so
+  // every pooling window is rows 1 + 3 W .. 3 + 3 W of the whole buffer; tiles start at row 1 + 126 i and hold 42 whole
+  // windows (their last two rows are recomputed by the next tile: 1.6 % more MMA work)
+  const bool pool3 = WRES && EPI == EPI_ADD && p.pool3 != 0;
+  const int mpitch = pool3 ? 126 : BLOCK_M, moff = pool3 ? 1 : 0;
+  const int num_m_tiles = (p.M - moff + mpitch - 1) / mpitch;
   const int num_n_tiles = (p.N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
   const int kc = p.kc_per_tap;
@@ -250,7 +261,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_arrive_expect_tx(wb, WRES_W_BYTES);
         for (int j = 0; j < 6; ++j) tma_load_2d(smem_base + j * 16384, &tmW, wb, j * BLOCK_K, 0);    // j = tap * 2 + kcx
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-          const int m0 = tile * BLOCK_M;
+          const int m0 = tile * mpitch + moff;
           for (int kcx = 0; kcx < 2; ++kcx) {
             const uint32_t fb = smem_u32(&full_bar[stage]);
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
@@ -420,7 +431,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     };
     int it = 0;
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-      const int m0 = tile_m(tile) * BLOCK_M;
+      const int m0 = tile_m(tile) * mpitch + moff;
       const int nt = tile_n(tile);
       const int n0 = nt * BN;
       const int acc = it & 1;
@@ -664,12 +675,52 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               v0 = lrelu03(fmaf(v0, af.x, af.y));
               v1 = lrelu03(fmaf(v1, af.z, af.w));
             }
-            pk[i] = valid ? pack_f16x2(v0, v1) : 0u;
+            pk[i] = (valid || pool3) ? pack_f16x2(v0, v1) : 0u;
+          }
+          const uint32_t my_row = out_box + lane * 128;
+          const uint32_t sw = lane & 7;
+          if (pool3) {
+            // the four warps of this column half share one 128-row x 64-column staging tile (their boxes are adjacent):
+            // rows in, barrier, then (window, 16-byte chunk) items: three rows -> max -> one 16-byte store of the pooled
+            // row (8 lanes cover a 128-byte line).  Windows of the padding triple at the end of an utterance are skipped.
+            named_bar_sync(1 + half, 128);                     // everybody is done reading the previous tile's rows
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(pk[4 * j]),
+                           "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3]) : "memory");
+            named_bar_sync(1 + half, 128);
+            const uint32_t tile_s = out_box - quad * 4096;     // first row of this half's staging tile
+            const int wpu = p.Tp / 3;                          // windows per utterance (the last one is padding)
+            const long long w_first = static_cast<long long>(m0 - 1) / 3;
+#pragma unroll
+            for (int k2 = 0; k2 < 3; ++k2) {
+              const int idx = quad * 32 + lane + 128 * k2;
+              const int wl = idx >> 3, c = idx & 7;
+              if (wl >= 42) break;
+              uint4 q[3];
+#pragma unroll
+              for (int r3 = 0; r3 < 3; ++r3) {
+                const int rr = 3 * wl + r3;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q[r3].x), "=r"(q[r3].y), "=r"(q[r3].z), "=r"(q[r3].w)
+                             : "r"(tile_s + rr * 128 + ((c ^ (rr & 7)) << 4)) : "memory");
+              }
+              const long long wg = w_first + wl;
+              const int utt_w = static_cast<int>(wg / wpu);
+              const int jw = static_cast<int>(wg - static_cast<long long>(utt_w) * wpu);
+              if (utt_w < p.B && jw < p.Tout) {
+                uint4 o;
+                o.x = hmax2_u32(q[0].x, hmax2_u32(q[1].x, q[2].x));
+                o.y = hmax2_u32(q[0].y, hmax2_u32(q[1].y, q[2].y));
+                o.z = hmax2_u32(q[0].z, hmax2_u32(q[1].z, q[2].z));
+                o.w = hmax2_u32(q[0].w, hmax2_u32(q[1].w, q[2].w));
+                bf16* dst = p.out + (static_cast<long long>(utt_w) * (p.Tout + 2) + 1 + jw) * p.out_ld + half * 64 + c * 8;
+                *reinterpret_cast<uint4*>(dst) = o;
+              }
+            }
+            continue;
           }
           if (lane == 0) bulk_wait_read<0>();
           __syncwarp();
-          const uint32_t my_row = out_box + lane * 128;
-          const uint32_t sw = lane & 7;
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ sw) << 4)), "r"(pk[4 * j]),
@@ -735,6 +786,16 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
   return 0;
 }
 
+// conv2 + max_pool1d(3) in one kernel: 128 channels, 16-bit mode, rows per utterance (T + 2) a multiple of 3
+bool rn_conv2_pool_supported(int channels, int planes, int xplanes, int T) {
+  static const bool on = [] {
+    const char* w = getenv("SVB_RN_WRES");
+    const char* f = getenv("SVB_RN_POOLFUSE");
+    return (w == nullptr || w[0] != '0') && (f == nullptr || f[0] != '0');
+  }();
+  return on && channels == 128 && planes == 1 && xplanes == 1 && (T + 2) % 3 == 0 && T >= 3;
+}
+
 // a: activation matrix (or the sliding-window waveform view when epi == EPI_SINC: a_ld = 48, a_cols = extent)
 int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, long long a_ld, const bf16* w,
                    int w_rows, int w_cols, const RnGemmParams& p, cudaStream_t stream) {
@@ -765,7 +826,10 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
       p.out_planes == 1 && (epi == EPI_AFF_LRELU || (epi == EPI_ADD && p.add_planes == 1 && p.add_ld == 128))) {
     CUtensorMap ma136, mr, mo;
     if (make_map(&ma136, a, a_rows, a_cols, a_ld, WRES_A_ROWS)) return -1;
-    if (make_map(&mo, p.out, p.M, 128, p.out_ld, 32)) return -1;              // store boxes: 32 rows x 64 channels
+    if (p.pool3) {
+      SVB_CHECK(epi == EPI_ADD && p.Tp % 3 == 0 && p.Tout == p.T / 3 && p.B >= 1, "fused max-pool: conv2 of a block whose rows per utterance are a multiple of 3");
+      mo = ma136;                                                             // pooled rows are stored directly
+    } else if (make_map(&mo, p.out, p.M, 128, p.out_ld, 32)) return -1;       // store boxes: 32 rows x 64 channels
     if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, ma136, mo, mo, p, stream);
     if (make_map(&mr, p.add, a_rows, 128, p.add_ld, BLOCK_M)) return -1;      // the shortcut has the rows of the output
     return launch_rn_t<128, EPI_ADD, true>(ma136, mw, mr, mo, mo, p, stream);
@@ -776,6 +840,7 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
   CUtensorMap mo = ma;
   q.tma_out = (tma_on && p.out_planes == 1) ? 1 : 0;
   if (q.tma_out && make_map_sw64(&mo, p.out, p.M, p.N, p.out_ld, 32)) return -1;
+  SVB_CHECK(!p.pool3, "fused max-pool needs the W-resident conv2 (rn_conv2_pool_supported)");
   if (bn == 256) {
     if (epi == EPI_AFF_LRELU) return launch_rn_t<256, EPI_AFF_LRELU>(ma, mw, ma, mo, mo, q, stream);
     if (epi == EPI_ADD) return launch_rn_t<256, EPI_ADD>(ma, mw, ma, mo, mo, q, stream);

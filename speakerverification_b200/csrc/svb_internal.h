@@ -95,6 +95,7 @@ struct RnGemmParams {
   int kc_per_tap, num_taps, tap_off[3], num_pass, a_plane_cols, w_planes;
   int T, Tp;               // valid rows per utterance / rows per utterance of the OUTPUT layout
   int Mu, B;               // sinc: GEMM rows (48-sample windows) per utterance, utterances
+  int pool3, Tout;         // W-resident conv2 only: max_pool1d(3) fused into the epilogue, `out` is the POOLED tensor [B][Tout + 2][N]
   int tma_out;             // set by launch_rn_gemm: single-plane output leaves through shared memory + TMA stores
   const float *s1, *h1;    // affine applied to the accumulator (first_bn / bn2)
   const float *s2, *h2;    // sinc: second affine (layer1 bn1) for the pre-activated copy
