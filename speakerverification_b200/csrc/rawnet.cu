@@ -859,7 +859,7 @@ int rawnet2_forward(const Rawnet2* e, const float* wav, long long wav_ld, int B,
     const int nchunk = pool_chunks(Tout);
     const int cg = k.cout / 8, tstep = 256 / cg;
     if (k.down && k.wsc == nullptr && rn_conv2_pool_supported(k.cout, P, PX, Tin)) {
-      // layer 1 in the 16-bit mode: conv2 pools its own output (z, 5.4 MB per utterance, is never written) and a
+      // layers 1 and 2 in the 16-bit mode: conv2 pools its own output (z, 5.4 / 1.8 MB per utterance, is never written) and a
       // sums-only pass over the pooled tensor (a third of z) feeds the AFMS gate
       if (conv_gemm(e, EPI_ADD, hb, B, Tin, k.cout, k.w2, k.cout, 3, nullptr, nullptr, shortcut, zpb, PX, st, Tout)) return -1;
       rn_pool_kernel<<<dim3(nchunk, B), 256, static_cast<size_t>(tstep) * k.cout * 4, st>>>(

@@ -184,12 +184,13 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_proxy_async();
   }
 
-  // pool3 (W-resident conv2 with the max-pool fused in): rows per utterance are a multiple of 3 and row 0 is padding, so
-  // every pooling window is rows 1 + 3 W .. 3 + 3 W of the whole buffer; tiles start at row 1 + 126 i and hold 42 whole
-  // windows (their last two rows are recomputed by the next tile: 1.6 % more MMA work)
+  // pool3 (W-resident conv2 with the max-pool fused in): tiles never span utterances; tile i of an utterance starts at
+  // its frame 126 i (row utt * Tp + 1 + 126 i) and holds 42 whole pooling windows -- the last two rows of a tile are
+  // recomputed by the next one and the last tile of an utterance runs into rows it discards (1.6 % + < 1.5 % more MMAs)
   const bool pool3 = WRES && EPI == EPI_ADD && p.pool3 != 0;
-  const int mpitch = pool3 ? 126 : BLOCK_M, moff = pool3 ? 1 : 0;
-  const int num_m_tiles = (p.M - moff + mpitch - 1) / mpitch;
+  const int tpu = pool3 ? (p.Tout + 41) / 42 : 1;                 // tiles per utterance
+  const int num_m_tiles = pool3 ? p.B * tpu : (p.M + BLOCK_M - 1) / BLOCK_M;
+  auto tile_row0 = [&](int mt) { return pool3 ? (mt / tpu) * p.Tp + 1 + (mt % tpu) * 126 : mt * BLOCK_M; };
   const int num_n_tiles = (p.N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
   const int kc = p.kc_per_tap;
@@ -261,7 +262,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_arrive_expect_tx(wb, WRES_W_BYTES);
         for (int j = 0; j < 6; ++j) tma_load_2d(smem_base + j * 16384, &tmW, wb, j * BLOCK_K, 0);    // j = tap * 2 + kcx
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-          const int m0 = tile * mpitch + moff;
+          const int m0 = tile_row0(tile);
           for (int kcx = 0; kcx < 2; ++kcx) {
             const uint32_t fb = smem_u32(&full_bar[stage]);
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
@@ -431,7 +432,7 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     };
     int it = 0;
     for (int tile = t_begin; tile < t_end; tile += t_step, ++it) {
-      const int m0 = tile_m(tile) * mpitch + moff;
+      const int m0 = tile_row0(tile_m(tile));
       const int nt = tile_n(tile);
       const int n0 = nt * BN;
       const int acc = it & 1;
@@ -690,8 +691,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                            "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3]) : "memory");
             named_bar_sync(1 + half, 128);
             const uint32_t tile_s = out_box - quad * 4096;     // first row of this half's staging tile
-            const int wpu = p.Tp / 3;                          // windows per utterance (the last one is padding)
-            const long long w_first = static_cast<long long>(m0 - 1) / 3;
+            const int mt = tile_m(tile);
+            const int utt_w = mt / tpu, j_first = (mt - utt_w * tpu) * 42;
 #pragma unroll
             for (int k2 = 0; k2 < 3; ++k2) {
               const int idx = quad * 32 + lane + 128 * k2;
@@ -704,10 +705,8 @@ rn_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q[r3].x), "=r"(q[r3].y), "=r"(q[r3].z), "=r"(q[r3].w)
                              : "r"(tile_s + rr * 128 + ((c ^ (rr & 7)) << 4)) : "memory");
               }
-              const long long wg = w_first + wl;
-              const int utt_w = static_cast<int>(wg / wpu);
-              const int jw = static_cast<int>(wg - static_cast<long long>(utt_w) * wpu);
-              if (utt_w < p.B && jw < p.Tout) {
+              const int jw = j_first + wl;
+              if (jw < p.Tout) {
                 uint4 o;
                 o.x = hmax2_u32(q[0].x, hmax2_u32(q[1].x, q[2].x));
                 o.y = hmax2_u32(q[0].y, hmax2_u32(q[1].y, q[2].y));
@@ -778,7 +777,7 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
   if (first_on_device(&attr_devs)) {
     SVB_CUDA_OK(cudaFuncSetAttribute(rn_gemm_kernel<BN, EPI, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   }
-  const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
+  const int tiles = p.pool3 ? p.B * ((p.Tout + 41) / 42) : ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
   rn_gemm_kernel<BN, EPI, WRES><<<grid, RnThreads<EPI, WRES>::N, SMEM, stream>>>(a, w, r, o, o2, p);
   count_launch();
@@ -786,14 +785,14 @@ static int launch_rn_t(const CUtensorMap& a, const CUtensorMap& w, const CUtenso
   return 0;
 }
 
-// conv2 + max_pool1d(3) in one kernel: 128 channels, 16-bit mode, rows per utterance (T + 2) a multiple of 3
+// conv2 + max_pool1d(3) in one kernel: 128 channels, 16-bit mode
 bool rn_conv2_pool_supported(int channels, int planes, int xplanes, int T) {
   static const bool on = [] {
     const char* w = getenv("SVB_RN_WRES");
     const char* f = getenv("SVB_RN_POOLFUSE");
     return (w == nullptr || w[0] != '0') && (f == nullptr || f[0] != '0');
   }();
-  return on && channels == 128 && planes == 1 && xplanes == 1 && (T + 2) % 3 == 0 && T >= 3;
+  return on && channels == 128 && planes == 1 && xplanes == 1 && T >= 3;
 }
 
 // a: activation matrix (or the sliding-window waveform view when epi == EPI_SINC: a_ld = 48, a_cols = extent)
@@ -827,7 +826,7 @@ int launch_rn_gemm(int epi, const bf16* a, long long a_rows, long long a_cols, l
     CUtensorMap ma136, mr, mo;
     if (make_map(&ma136, a, a_rows, a_cols, a_ld, WRES_A_ROWS)) return -1;
     if (p.pool3) {
-      SVB_CHECK(epi == EPI_ADD && p.Tp % 3 == 0 && p.Tout == p.T / 3 && p.B >= 1, "fused max-pool: conv2 of a block whose rows per utterance are a multiple of 3");
+      SVB_CHECK(epi == EPI_ADD && p.Tout == p.T / 3 && p.Tout >= 1 && p.B >= 1, "fused max-pool: conv2 with Tout = T / 3 pooled frames");
       mo = ma136;                                                             // pooled rows are stored directly
     } else if (make_map(&mo, p.out, p.M, 128, p.out_ld, 32)) return -1;       // store boxes: 32 rows x 64 channels
     if (epi == EPI_AFF_LRELU) return launch_rn_t<128, EPI_AFF_LRELU, true>(ma136, mw, ma136, mo, mo, p, stream);
