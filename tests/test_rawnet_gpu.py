@@ -239,3 +239,53 @@ def test_attentive_heads_match_reference(agg, tol16, precision, cos_min, tol):
             tgt[k].copy_(torch.as_tensor(v))
         out = net(torch.from_numpy(waves[:3]))
         assert torch.allclose(out, got_t[:3], atol=1e-6)
+
+
+@pytest.mark.parametrize("n_samples", [48000, 35000])
+def test_rawnet2_other_lengths_match_oracle(n_samples, golden_rawnet):
+    """Other crop lengths than BASELINE's 4 s: the frame counts of every level change (48 000 samples: 15 916 / 5 305 /
+    1 768 / 589 ... frames; 35 000: 11 583 / 3 861 / 1 287 ...), and with them the partial last window row of the sinc
+    store view, the number of pooling windows in the last tile of an utterance and the utterance boundaries inside
+    tiles.  The geometry-sensitive stages (front end, blocks 0-2) are compared with the CPU oracle stage by stage in
+    both modes; the embedding is a sanity bound only (this random-init network amplifies rounding in a few
+    ill-conditioned channels of the late blocks at these lengths -- it follows the utterance, not its batch position)."""
+    from oracle import rawnet_oracle as ro, synth
+    from speakerverification_b200.rawnet2_custom import RawNet2Engine
+    bn = {k[3:]: v for k, v in golden_rawnet.items() if k.startswith("bn/")}     # calibrated running statistics (per channel)
+    sd = synth.rawnet2_state_dict(n_samples=n_samples, bn_stats=bn)
+    tsd = {k: torch.as_tensor(v) for k, v in sd.items()}
+    waves, _ = synth.utterance_set(3, 2, n_samples)
+    waves = waves[:3]
+    torch.set_num_threads(os.cpu_count())
+    st = {}
+    with torch.no_grad():
+        want = ro.rawnet2_forward(waves, sd, stages=st).numpy()
+        refs = [_pre(st["front"], sd, "__S__.layer1.0.bn1.")]
+        x = st["front"]
+        for i, (name, nxt) in enumerate([("layer1.0", "layer2.0.bn1."), ("layer2.0", "layer3.0.bn1."), ("layer3.0", "layer4.0.bn1.")]):
+            x = ro.basic_block(x, tsd, "__S__." + name + ".", True)
+            refs.append(_pre(x, sd, "__S__." + nxt))
+    state = {k[len("__S__."):]: torch.as_tensor(v).cuda() for k, v in sd.items()}
+    w = torch.from_numpy(waves).cuda()
+    for precision, tols in (("fp32", [2e-4, 3e-4, 3e-4, 3e-4]), ("f16", [2e-3, 2e-3, 2e-3, 2.6e-3])):
+        eng = RawNet2Engine(state, n_samples, 512, precision=precision)
+        for stop, (ref, tol) in enumerate(zip(refs, tols)):
+            os.environ["SVB_RAWNET_STOP"] = str(stop - 1)
+            try:
+                eng.forward(w)
+                torch.cuda.synchronize()
+            finally:
+                del os.environ["SVB_RAWNET_STOP"]
+            got = eng.stage(3, "a0" if stop % 2 == 0 else "a1", stop, ref.shape[2]).cpu().numpy()
+            assert got.shape == ref.shape, (got.shape, ref.shape)
+            err = np.abs(got - ref).max() / np.abs(ref).max()
+            print("RawNet2", n_samples, precision, "stage", stop, ref.shape, "max err / scale %.2e" % err)
+            assert err <= tol, (precision, stop, err)
+        emb = eng.forward(w).cpu().numpy()
+        cosf = lambda a, b: (a * b).sum(1) / np.linalg.norm(a, axis=1) / np.linalg.norm(b, axis=1)
+        assert np.isfinite(emb).all()
+        if precision == "fp32":
+            assert cosf(emb, want).min() >= 0.999, cosf(emb, want)
+        # (16-bit embedding at these lengths: finite only.  On this random-init network a few late channels amplify rounding
+        # so much that even the CPU emulation with the kernels' rounding sites agrees with the engine to cos 0.98-0.997
+        # only; the parity claim of the 16-bit mode is made on BASELINE's 4 s configuration, test_rawnet2_f16_mode.)
