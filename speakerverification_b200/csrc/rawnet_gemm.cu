@@ -19,10 +19,18 @@
 //  EPI_PLAIN       1x1 shortcut conv                                    (RawNet_baseline.py:213-217,222)
 //
 // Activations are time-major rows [utt][1 zero row | T rows | 1 zero row][C] bf16: the zero rows ARE the conv's
-// zero padding, so the k=3 taps are row-shifted TMA loads.  Every tensor is one bf16 plane in bf16 mode and
-// hi|lo planes in fp32-grade mode (operand and residual-carrier plane counts are separate parameters).  T is the same for
-// every utterance (the model's LayerNorm weights fix the input length, RawNet_baseline.py:13-24), so
+// zero padding, so the k=3 taps are row-shifted TMA loads.  Every tensor is one plane of IEEE half in the 16-bit mode
+// and bf16 hi|lo planes in fp32-grade mode (operand and residual-carrier plane counts are separate parameters).  T is
+// the same for every utterance (the model's LayerNorm weights fix the input length, RawNet_baseline.py:13-24), so
 // utterance / frame of a row are computed arithmetically.
+//
+// 16-bit mode variants (template WRES / runtime flags, each with an environment switch for A/B runs):
+//   * sinc: the W boxes of the CTA's n-tile resident, A-only stage ring, outputs through staging boxes and 4-D TMA stores;
+//   * 128-channel conv1 / conv2: all of W resident, one 136-row A box per K chunk for the three taps, the residual
+//     through an identity MMA, outputs through staging boxes and TMA stores, and (conv2 of the down-sampling blocks)
+//     max_pool1d(3) fused into the epilogue on per-utterance tiles of 42 pooling windows;
+//   * 256 / 512-channel layers: generic mainloop, outputs through 32 x 32 staging boxes and TMA stores, residual
+//     requested before the accumulator wait.
 #include <stdlib.h>
 
 #include "svb_internal.h"
