@@ -69,6 +69,7 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
   __shared__ __align__(8) uint64_t wfull_bar, wempty_bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float4 merge_buf[2][128];
+  __shared__ __align__(8) uint64_t mfull_bar[2], mempty_bar[2];   // hand-over of warpgroup 1's partial statistics
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -98,6 +99,10 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
     }
     mbar_init(smem_u32(&wfull_bar), 1);
     mbar_init(smem_u32(&wempty_bar), 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&mfull_bar[a]), 4);
+      mbar_init(smem_u32(&mempty_bar[a]), 4);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -290,10 +295,23 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
         if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[wg]));
         ++nproc;
       }
-      // merge the two warpgroups' partial statistics; warpgroup 0 writes the pooled mean / std
-      float4* mb = merge_buf[item & 1];
-      if (wg == 1) mb[ch_local] = make_float4(m, l, s1, s2);
-      named_bar_sync(1, 256);
+      // merge the two warpgroups' partial statistics; warpgroup 0 writes the pooled mean / std.  The hand-over is a
+      // two-slot mailbox (mbarriers), not a barrier over both warpgroups: the chunk counter alternates which of them
+      // gets the item's extra chunk (3 chunks per 3 s crop), so over two items they do the same work -- but only if the
+      // one that finishes an item first may start the next (a 256-thread barrier here made it wait: 10 % of the
+      // kernel's stall samples, ncu r02).
+      const int li = item - item_begin;
+      const int mslot = li & 1;
+      const uint32_t mphase = static_cast<uint32_t>(li >> 1) & 1u;
+      float4* mb = merge_buf[mslot];
+      if (wg == 1) {
+        mbar_wait(smem_u32(&mempty_bar[mslot]), mphase ^ 1u);       // the slot's previous content has been read
+        mb[ch_local] = make_float4(m, l, s1, s2);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&mfull_bar[mslot]));
+      } else {
+        mbar_wait(smem_u32(&mfull_bar[mslot]), mphase);
+      }
       if (wg == 0) {
         const float4 o = mb[ch_local];
         const float M = fmaxf(m, o.x);
@@ -307,6 +325,8 @@ asp_fused_kernel(const __grid_constant__ CUtensorMap tmAtt, const __grid_constan
         float* po = p.pooled + static_cast<long long>(b) * p.pooled_ld;
         po[c] = gm + d;
         po[p.C3 + c] = sqrtf(fmaxf(var, p.eps));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&mempty_bar[mslot]));
       }
     }
   }
