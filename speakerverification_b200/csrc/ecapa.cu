@@ -29,6 +29,10 @@ int colsum_finalize(const long long*, const long long*, int, const void*, int, i
 int small_linear(const float*, int, const float*, const float*, int, const float*, const float*, int, int, int, int,
                  float*, int, float*, cudaStream_t);
 size_t small_linear_ws_floats(int, int, int);
+bool se_gate_supported(int, int);
+int se_gate(const long long*, int, const float*, int, const void*, int, int, const float*, const float*, const float*,
+            const float*, float*, int, cudaStream_t);
+int transpose_f32(const float*, int, int, float*, cudaStream_t);
 int se_apply(const bf16*, int, int, const bf16*, int, int, const float*, int, const RowMeta*, long long, int, int, bf16*,
              int, int, cudaStream_t);
 int asp_fused(const bf16*, const bf16*, int, int, const bf16*, int, long long, const void*, int, int, const float*, int, float,
@@ -215,6 +219,7 @@ struct Ecapa {
   bf16* block0_wk = nullptr;
   int block0_kpad = 0;
   float *se_w1[3] = {}, *se_b1[3] = {}, *se_w2[3] = {}, *se_b2[3] = {};
+  float *se_w1t[3] = {}, *se_w2t[3] = {};      // transposed copies for the one-launch SE gate (se_gate, pool.cu)
   float *asp_bound = nullptr;  // per-channel bound of the asp.conv logits in log2 units, or nullptr (asp_fused.cu, FIXMAX)
   float *asp_w = nullptr;  // asp.tdnn conv weight fp32 [att, 9C] (the [mean;std] columns feed the per-utterance bias)
   float *aspbn_scale = nullptr, *aspbn_shift = nullptr, *fc_w = nullptr, *fc_b = nullptr;
@@ -341,6 +346,14 @@ int ecapa_create(int C, int n_mels, int n_out, int att, int se_ch, int res2_scal
     if (!w1 || !b1 || !w2 || !b2) { rc = -1; break; }
     e->se_w1[i] = dcopy(e, w1, static_cast<size_t>(se_ch) * C); e->se_b1[i] = dcopy(e, b1, se_ch);
     e->se_w2[i] = dcopy(e, w2, static_cast<size_t>(C) * se_ch); e->se_b2[i] = dcopy(e, b2, C);
+    if (se_gate_supported(C, se_ch) && e->se_w1[i] != nullptr && e->se_w2[i] != nullptr) {
+      e->se_w1t[i] = dalloc<float>(e, static_cast<size_t>(se_ch) * C);
+      e->se_w2t[i] = dalloc<float>(e, static_cast<size_t>(C) * se_ch);
+      if (e->se_w1t[i] != nullptr && e->se_w2t[i] != nullptr) {
+        transpose_f32(e->se_w1[i], se_ch, C, e->se_w1t[i], nullptr);      // [se_ch][C] -> [C][se_ch]
+        transpose_f32(e->se_w2[i], C, se_ch, e->se_w2t[i], nullptr);      // [C][se_ch] -> [se_ch][C]
+      }
+    }
   }
   if (!rc && input_norm) {
     const float *iw = find(tm, "instance_norm.weight"), *ib = find(tm, "instance_norm.bias");
@@ -601,15 +614,28 @@ int ecapa_forward(const Ecapa* e, const Fbank* fb, const Batch* b, const float* 
     if (run_layer(e, b, e->tdnn2[i], rv, &uv, Cs / 64, V, P * C, C, STORE_ALL, nullptr, 0, 0, -1, nullptr, nullptr, 0, 0,
                   passes, stream, fuse_stats ? se_sum : nullptr, nullptr, C)) return -1;
     // SE: time mean -> C->se->C gate -> gate * V + residual, written into the MFA concat buffer
-    if (fuse_stats) {
-      if (colsum_finalize(se_sum, nullptr, C, b->d_uttrows, B, C, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
-    } else if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) {
-      return -1;
+    static const bool se_fused_on = [] { const char* v = getenv("SVB_SE_FUSED"); return v == nullptr || v[0] != '0'; }();
+    const bool se_one = se_fused_on && e->se_w1t[i] != nullptr && e->se_w2t[i] != nullptr;
+    if (se_one && fuse_stats) {
+      // mean conversion + both SE linears in one launch, straight from the epilogue's column sums
+      if (se_gate(se_sum, C, nullptr, 0, b->d_uttrows, B, C, e->se_w1t[i], e->se_b1[i], e->se_w2t[i], e->se_b2[i],
+                  F("se_gate"), C, stream)) return -1;
+    } else {
+      if (fuse_stats) {
+        if (colsum_finalize(se_sum, nullptr, C, b->d_uttrows, B, C, 0.f, F("se_mean"), nullptr, C, stream)) return -1;
+      } else if (col_stats(V, P * C, P, C, b->d_uttrows, B, C, 0, 0.f, F("se_mean"), nullptr, C, stream)) {
+        return -1;
+      }
+      if (se_one) {
+        if (se_gate(nullptr, 0, F("se_mean"), C, b->d_uttrows, B, C, e->se_w1t[i], e->se_b1[i], e->se_w2t[i], e->se_b2[i],
+                    F("se_gate"), C, stream)) return -1;
+      } else {
+        if (small_linear(e->se_w1[i], C, e->se_b1[i], F("se_mean"), C, nullptr, nullptr, B, e->se_ch, C, LIN_RELU,
+                         F("se_hidden"), e->se_ch, F("lin_part"), stream)) return -1;
+        if (small_linear(e->se_w2[i], e->se_ch, e->se_b2[i], F("se_hidden"), e->se_ch, nullptr, nullptr, B, C, e->se_ch,
+                         LIN_SIGMOID, F("se_gate"), C, F("lin_part"), stream)) return -1;
+      }
     }
-    if (small_linear(e->se_w1[i], C, e->se_b1[i], F("se_mean"), C, nullptr, nullptr, B, e->se_ch, C, LIN_RELU,
-                     F("se_hidden"), e->se_ch, F("lin_part"), stream)) return -1;
-    if (small_linear(e->se_w2[i], e->se_ch, e->se_b2[i], F("se_hidden"), e->se_ch, nullptr, nullptr, B, C, e->se_ch,
-                     LIN_SIGMOID, F("se_gate"), C, F("lin_part"), stream)) return -1;
     bf16* o = XC + i * C;
     if (se_apply(V, P * C, C, cur.p, cur.ld, cur.plane_cols, F("se_gate"), C, b->d_meta, M, C, P, o, P * C3, C3, stream))
       return -1;

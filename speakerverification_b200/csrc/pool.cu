@@ -312,6 +312,150 @@ int colsum_finalize(const long long* sum, const long long* sq, int stats_ld, con
   return 0;
 }
 
+// ---------------------------------------------------------------- SE gate in one launch
+// gate[u, :] = sigmoid(W2 . relu(W1 . mean[u, :] + b1) + b2)  (SEBlock, src/models/ECAPA_TDNN.py:181-203), mean = the
+// per-utterance time mean of the block output, taken either from the fixed-point column sums of the GEMM epilogue
+// (colsum_finalize's conversion) or from a float buffer.  Replaces colsum_finalize + two split-K linears + a reduce
+// (4 launches, ~70 us per block at 592 utterances: each of them latency bound) by one kernel of SE_UPC utterances per
+// CTA.  Weights come TRANSPOSED (w1t [C][128], w2t [128][C]) so that a warp reads whole rows.  Hidden width 128.
+// Phase 1: warp w owns C / 8 input channels, lane 4 hidden units; fixed-order reduction over the 8 warps (run-to-run
+// bit reproducible).  Phase 2: a thread owns 4 adjacent output channels per 1024.
+static constexpr int SE_UPC = 4, SE_H = 128;
+
+__global__ void __launch_bounds__(512)
+se_gate_kernel(const long long* __restrict__ sum, int sum_ld, const float* __restrict__ mean_in, int mean_ld,
+               const UttRows* __restrict__ utts, int B, int C, const float* __restrict__ w1t,
+               const float* __restrict__ b1, const float* __restrict__ w2t, const float* __restrict__ b2,
+               float* __restrict__ gate, int gate_ld) {
+  extern __shared__ __align__(16) float se_smem[];
+  float* mean = se_smem;                                  // [SE_UPC][C]
+  float* part = mean + SE_UPC * C;                        // [16][SE_UPC][SE_H]; phase 2: [256][SE_UPC * 4]
+  float* hid = part + 16 * SE_UPC * SE_H;                 // [SE_UPC][SE_H]
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int u0 = blockIdx.x * SE_UPC;
+  for (int i = tid; i < SE_UPC * C; i += 512) {
+    const int u = i / C, c = i - u * C;
+    float m = 0.f;
+    if (u0 + u < B) {
+      if (sum != nullptr) {
+        const double inv = 1.0 / (4294967296.0 * static_cast<double>(utts[u0 + u].T));
+        m = static_cast<float>(static_cast<double>(sum[static_cast<long long>(u0 + u) * sum_ld + c]) * inv);
+      } else {
+        m = mean_in[static_cast<long long>(u0 + u) * mean_ld + c];
+      }
+    }
+    mean[i] = m;
+  }
+  __syncthreads();
+  {
+    // phase 1: warp w owns input channels [w C / 16, (w + 1) C / 16), lane owns hidden units 4 lane .. 4 lane + 3
+    float acc[SE_UPC][4];
+#pragma unroll
+    for (int u = 0; u < SE_UPC; ++u)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[u][j] = 0.f;
+    const int kper = C / 16, k0 = wid * kper;
+    const float4* wp = reinterpret_cast<const float4*>(w1t + static_cast<long long>(k0) * SE_H) + lane;
+#pragma unroll 16
+    for (int k = 0; k < kper; ++k) {
+      const float4 w = __ldg(wp + static_cast<long long>(k) * (SE_H / 4));
+#pragma unroll
+      for (int u = 0; u < SE_UPC; ++u) {
+        const float m = mean[u * C + k0 + k];
+        acc[u][0] = fmaf(m, w.x, acc[u][0]); acc[u][1] = fmaf(m, w.y, acc[u][1]);
+        acc[u][2] = fmaf(m, w.z, acc[u][2]); acc[u][3] = fmaf(m, w.w, acc[u][3]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < SE_UPC; ++u)
+      *reinterpret_cast<float4*>(part + (wid * SE_UPC + u) * SE_H + lane * 4) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+  }
+  __syncthreads();
+  for (int i = tid; i < SE_UPC * SE_H; i += 512) {
+    const int u = i / SE_H, o = i - u * SE_H;
+    float s = __ldg(b1 + o);
+#pragma unroll
+    for (int w = 0; w < 16; ++w) s += part[(w * SE_UPC + u) * SE_H + o];      // fixed order: bit reproducible
+    hid[i] = fmaxf(s, 0.f);
+  }
+  __syncthreads();
+  // phase 2: thread (t & 255) owns output channels 4 t .. 4 t + 3 (+ 1024 i); the two thread halves split the hidden
+  // units and the upper half hands its partial sums over through shared memory
+  const int th = tid & 255, jh = tid >> 8;
+  for (int o4 = th * 4; o4 < C; o4 += 1024) {
+    float acc[SE_UPC][4];
+#pragma unroll
+    for (int u = 0; u < SE_UPC; ++u)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[u][j] = 0.f;
+    const float4* wp = reinterpret_cast<const float4*>(w2t + static_cast<long long>(jh) * (SE_H / 2) * C + o4);
+#pragma unroll 16
+    for (int j = 0; j < SE_H / 2; ++j) {
+      const float4 w = __ldg(wp + static_cast<long long>(j) * (C / 4));
+#pragma unroll
+      for (int u = 0; u < SE_UPC; ++u) {
+        const float h = hid[u * SE_H + jh * (SE_H / 2) + j];
+        acc[u][0] = fmaf(h, w.x, acc[u][0]); acc[u][1] = fmaf(h, w.y, acc[u][1]);
+        acc[u][2] = fmaf(h, w.z, acc[u][2]); acc[u][3] = fmaf(h, w.w, acc[u][3]);
+      }
+    }
+    __syncthreads();                                     // (uniform: C is the same for every thread) part is free again
+    if (jh == 1) {
+#pragma unroll
+      for (int u = 0; u < SE_UPC; ++u)
+        *reinterpret_cast<float4*>(part + (th * SE_UPC + u) * 4) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+    }
+    __syncthreads();
+    if (jh == 0) {
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(b2 + o4));
+#pragma unroll
+      for (int u = 0; u < SE_UPC; ++u) {
+        if (u0 + u >= B) break;
+        const float4 q = *reinterpret_cast<const float4*>(part + (th * SE_UPC + u) * 4);
+        float4 g;
+        g.x = 1.f / (1.f + expf(-(acc[u][0] + q.x + bb.x))); g.y = 1.f / (1.f + expf(-(acc[u][1] + q.y + bb.y)));
+        g.z = 1.f / (1.f + expf(-(acc[u][2] + q.z + bb.z))); g.w = 1.f / (1.f + expf(-(acc[u][3] + q.w + bb.w)));
+        *reinterpret_cast<float4*>(gate + static_cast<long long>(u0 + u) * gate_ld + o4) = g;
+      }
+    }
+  }
+}
+
+bool se_gate_supported(int C, int se_ch) { return se_ch == SE_H && C % 1024 == 0 && C <= 4096; }
+
+int se_gate(const long long* sum, int sum_ld, const float* mean_in, int mean_ld, const void* utts, int B, int C,
+            const float* w1t, const float* b1, const float* w2t, const float* b2, float* gate, int gate_ld,
+            cudaStream_t stream) {
+  SVB_CHECK(se_gate_supported(C, SE_H) && gate_ld % 4 == 0 && (sum != nullptr || mean_in != nullptr), "se_gate: unsupported geometry");
+  const size_t smem = (static_cast<size_t>(SE_UPC) * C + 17 * SE_UPC * SE_H) * sizeof(float);
+  static unsigned long long attr_devs = 0;   // per device: kernel attributes do not carry over
+  if (first_on_device(&attr_devs))
+    SVB_CUDA_OK(cudaFuncSetAttribute(se_gate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  SVB_CHECK(smem <= 96 * 1024, "se_gate: %zu bytes of shared memory", smem);
+  se_gate_kernel<<<(B + SE_UPC - 1) / SE_UPC, 512, smem, stream>>>(sum, sum_ld, mean_in, mean_ld,
+                                                                  static_cast<const UttRows*>(utts), B, C, w1t, b1, w2t, b2,
+                                                                  gate, gate_ld);
+  count_launch();
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void transpose_f32_kernel(const float* __restrict__ in, int R, int C, float* __restrict__ out) {
+  const long long total = static_cast<long long>(R) * C;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / C), c = static_cast<int>(i - static_cast<long long>(r) * C);
+    out[static_cast<long long>(c) * R + r] = in[i];
+  }
+}
+
+// out [C][R] = in [R][C]^T (engine creation only)
+int transpose_f32(const float* in, int R, int C, float* out, cudaStream_t stream) {
+  transpose_f32_kernel<<<256, 256, 0, stream>>>(in, R, C, out);
+  SVB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 // Reflect-halo fix-up after a k > 1 layer that stored every row in place (gemm_pw): halo row -h of every utterance
 // becomes a copy of frame h, halo row T-1+h a copy of frame T-1-h (F.pad(..., 'reflect'), src/models/layers/cnn.py:157),
 // exactly what gemm_tc's STORE_MIRROR epilogue writes.  grid (utterances, 2 * halo), 16-byte copies of the whole row.
